@@ -1,0 +1,347 @@
+#!/usr/bin/env python
+"""Throughput of the placement hot path on the configuration BASELINE.json's metric is quoted on.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload C2] [--reads R]
+
+Workload (default C2 = BASELINE.json configs[1]): synthetic nucleotide database, k = 10, 4999 branches,
+~33 M (branch, score) entries; 10 M synthetic 150-bp reads per GPU per step. A step = one pass of the hot
+path (encode -> look-up -> accumulate -> top-k/LWR) over the whole read set.
+
+  value  reads/s with reads, offsets and result arrays resident in HBM (epk_place_device, CUDA events)
+  e2e    reads/s through epk_place with pinned HOST buffers, H2D and D2H inside the timed region
+  roofline.achieved  algorithmic bytes per launch (L + 16*n_k + 8*sum(l) + 24*K per read)
+                     / launch duration; peak = measured copy bandwidth of MEASURED_PEAKS.json
+  cpu_baseline       the reference's place.cpp (oracle/_ref, OpenMP, all host cores) on a bounded sample
+
+Multi-GPU (torchrun, one rank per GPU): reads are sharded across ranks, the database is replicated,
+there is no data-path collective; NCCL only carries the barrier and the max-over-ranks of the time.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "placed queries/sec"
+UNIT = "reads/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="C2", choices=["C2", "C4", "C1p"])
+    ap.add_argument("--reads", type=int, default=0, help="reads per GPU per step (default: the workload's)")
+    ap.add_argument("--variant", type=int, default=0)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+WORKLOAD_READS = {"C2": 10_000_000, "C4": 1_000_000, "C1p": 100_000}
+
+
+def workload_config(name, n_reads, world):
+    from epik_b200 import synth
+    alphabet, k, n_leaves, p_occ, m, read_len = synth.CONFIGS[name]
+    return {
+        "workload": "%s: synthetic %s DB k=%d, %d branches, p_occ=%.2f, m=%.0f; %d x %d-letter reads per GPU per step"
+                    % (name, "amino" if alphabet else "nucl", k, 2 * n_leaves - 1, p_occ, m, n_reads, read_len),
+        "reads_per_gpu": n_reads, "read_len": read_len, "k": k, "branches": 2 * n_leaves - 1,
+        "keep_at_most": 7, "keep_factor": 0.01, "omega": 1.5,
+        "parallelism": "query-sharded x%d, DB replicated" % world,
+        "l2": "inputs larger than L2 (reads %.0f MB + DB per step vs 126 MB L2); no explicit flush" % (n_reads * read_len / 1e6),
+    }
+
+
+def make_reads_chunked(alphabet, n, length, first, out_bytes):
+    from epik_b200 import synth
+    step = 1_000_000
+    for a in range(0, n, step):
+        m = min(step, n - a)
+        data, _ = synth.make_reads(alphabet, m, length, first=first + a)
+        out_bytes[a * length:(a + m) * length] = data
+
+
+class ClockSampler:
+    """SM clock and throttle reasons during the timed region (pynvml, 100 ms period)."""
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thread = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+            getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonHwPowerBrakeSlowdown", 0x80): "hw_power_brake_slowdown",
+        }
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    mask = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(0.1)
+
+    def start(self):
+        if self.nv is not None:
+            self._thread = threading.Thread(target=self._run, daemon=True)
+            self._thread.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._thread is not None:
+            self._thread.join()
+        return {"sm_mhz": float(np.median(self.samples)) if self.samples else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def cpu_reference(db, alphabet, read_len, seconds_target, steps=1, warmup=0):
+    """Times the reference's CPU placer (oracle/_ref if built, else the port) on a bounded sample.
+    Returns (reads/s of the timed steps, kind, cores, sample description)."""
+    from epik_b200 import synth
+    from oracle import oracle as O
+    kind = "reference" if O.available("reference", alphabet) else "port"
+    cores = host_threads()
+    o = O.Oracle(db, 7, 0.01, cores, kind=kind)
+    probe_n = 4000 * max(1, cores // 4)
+    data, off = synth.make_reads(alphabet, probe_n, read_len, first=900_000_000)
+    o.place_packed(data, off, threads=cores)  # warm the caches / thread pool
+    r = o.place_packed(data, off, threads=cores)
+    rate = probe_n / max(r["seconds"], 1e-9)
+    n = int(max(probe_n, min(5_000_000, rate * seconds_target)))
+    n -= n % 2000
+    data, off = synth.make_reads(alphabet, n, read_len, first=0)
+    times = []
+    for i in range(warmup + steps):
+        r = o.place_packed(data, off, threads=cores, batch_size=2000)
+        if i >= warmup:
+            times.append(r["seconds"])
+    value = n * len(times) / sum(times)
+    sample = "%d reads of the workload (the first %d), batches of 2000 (main.cpp:214), timer around placer::place only " \
+             "(main.cpp:343-345), %d OpenMP threads" % (n, n, cores)
+    return value, ("reference" if kind == "reference" else "port"), cores, sample, sum(times) / len(times)
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU implementation of the path on the host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from epik_b200 import synth
+    alphabet, k, n_leaves, p_occ, m, read_len = synth.CONFIGS[args.workload]
+    n_reads = args.reads or WORKLOAD_READS[args.workload]
+    db = synth.make_config_db(args.workload)
+    total = max(args.steps + args.warmup, 1)
+    value, kind, cores, sample, step_s = cpu_reference(db, alphabet, read_len, seconds_target=min(20.0, 150.0 / total),
+                                                       steps=args.steps, warmup=args.warmup)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": step_s * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args.workload, n_reads, args.gpus),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "kmer_lookups_per_sec": value * (read_len - k + 1),
+        "note": "CPU arm: %s; each step is a bounded sample of the workload, not the full read set" % (
+            "reference place.cpp compiled unmodified over the i2l shim (oracle/_ref)" if kind == "reference"
+            else "oracle port (oracle/_ref not built)"),
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from epik_b200 import synth
+    from epik_b200.placer import Database, PinnedArray, Placer
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (epik_b200 has no CPU path)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    alphabet, k, n_leaves, p_occ, m, read_len = synth.CONFIGS[args.workload]
+    n = args.reads or WORKLOAD_READS[args.workload]
+    K = 7
+    flat = synth.make_config_db(args.workload)
+    db = Database(flat, device=local)
+    placer = Placer(db, K, 0.01, variant=args.variant)
+
+    # ---- inputs: pinned host copies (for e2e) and device-resident copies (for value) ----
+    h_seq = PinnedArray((n * read_len,), np.uint8)
+    h_off = PinnedArray((n + 1,), np.uint64)
+    make_reads_chunked(alphabet, n, read_len, rank * n, h_seq.array)
+    h_off.array[:] = np.arange(n + 1, dtype=np.uint64) * np.uint64(read_len)
+    d_seq = torch.from_numpy(h_seq.array).to(dev)
+    d_off = torch.from_numpy(h_off.array.view(np.int64)).to(dev)
+    d_out = {"n_place": torch.zeros(n, dtype=torch.int32, device=dev),
+             "branch": torch.zeros(n * K, dtype=torch.int32, device=dev),
+             "score": torch.zeros(n * K, dtype=torch.float32, device=dev),
+             "lwr": torch.zeros(n * K, dtype=torch.float64, device=dev),
+             "count": torch.zeros(n * K, dtype=torch.int32, device=dev)}
+    stream = torch.cuda.Stream(device=dev)
+
+    # ---- value: everything resident in HBM ----
+    for _ in range(args.warmup):
+        placer.place_device(d_seq, d_off, n, d_out, stream=stream)
+    stream.synchronize()
+    counters = placer.counters()
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    with torch.cuda.stream(stream):
+        ev[0].record(stream)
+        for i in range(args.steps):
+            placer.place_device(d_seq, d_off, n, d_out, stream=stream)
+            ev[i + 1].record(stream)
+    stream.synchronize()
+    barrier()
+    clocks = sampler.stop()
+    step_ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps)]
+    total_s = max_over_ranks(sum(step_ms) / 1e3)
+    value = world * n * args.steps / total_s
+    launches = int(counters["n_launches"]) * args.steps
+
+    # a checksum of the results so that the work cannot be optimised away, and a sanity check
+    n_place_sum = int(d_out["n_place"].sum().item())
+    assert n_place_sum > 0
+
+    # ---- roofline of the placement kernel (the only kernel that moves data) ----
+    bytes_per_launch = n * (read_len + 16 * (read_len - k + 1) + 24 * K) + 8 * int(counters["n_entries"])
+    kernel_s = (sum(step_ms) / len(step_ms)) / 1e3
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, burst copy)"
+    else:
+        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        t = json.load(open(tpath)).get(args.workload)
+        if t and t.get("reads") == n:
+            traffic = t["dram_bytes_per_launch"]
+    achieved = bytes_per_launch / kernel_s / 1e9
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": traffic, "kernel": "epk::place_kernel", "bytes_per_launch": bytes_per_launch,
+                "launch_ms": kernel_s * 1e3, "peak_source": peak_src,
+                "entries_per_read": counters["n_entries"] / n, "hits_per_read": counters["n_hits"] / n}
+
+    # ---- e2e: pinned host buffers through epk_place, copies inside the timed region ----
+    e2e = None
+    if not args.no_e2e:
+        out = placer.alloc_result(n, pinned=True, lengths=False)
+        e2e_warm = min(args.warmup, 1)
+        for _ in range(e2e_warm):
+            placer.place_packed(h_seq.array, h_off.array, out=out)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            placer.place_packed(h_seq.array, h_off.array, out=out)
+        torch.cuda.synchronize()
+        t1 = time.perf_counter()
+        e2e_s = max_over_ranks(t1 - t0)
+        barrier()
+        assert int(out["n_place"].sum()) == n_place_sum, "host and device paths disagree"
+        e2e = {"value": world * n * args.steps / e2e_s, "unit": UNIT,
+               "h2d_bytes_per_step": int(n * read_len + (n + 1) * 8),
+               "d2h_bytes_per_step": int(n * (4 + K * 20)),
+               "ms_per_step": e2e_s / args.steps * 1e3,
+               "api": "epk_place (C ABI), pinned host buffers, %d-read chunks on 3 streams" % (1 << 18)}
+
+    # ---- CPU baseline: rank 0, N = 1 only ----
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        v, kind, cores, sample, _ = cpu_reference(flat, alphabet, read_len, seconds_target=15.0)
+        cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample}
+
+    total_reads = sum_over_ranks(float(n))
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": total_s / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": workload_config(args.workload, n, world),
+            "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+            "kmer_lookups_per_sec": value * (read_len - k + 1), "reads_per_step_all_gpus": int(total_reads),
+            "dtype_note": "scores accumulate in f32 (bit-identical to the reference), likelihood weight ratios in f64",
+            "db": {k2: int(v2) if isinstance(v2, (int, np.integer)) else float(v2) for k2, v2 in db.info.items()},
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

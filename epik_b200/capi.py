@@ -1,0 +1,117 @@
+"""ctypes binding of the C ABI in include/epik_b200.h (libepik_b200.so, built by __graft_entry__.build()).
+
+This is the stub a Python caller of the reference would add; the C++ equivalent is in INTEGRATION.md.
+There is no fallback: if the shared library is missing, importing this module raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libepik_b200.so")
+
+EPK_OK, EPK_E_INVALID, EPK_E_CUDA, EPK_E_NOMEM, EPK_E_SHORT_SEQ, EPK_E_UNSUPPORTED = range(6)
+STATUS_NAMES = ["EPK_OK", "EPK_E_INVALID", "EPK_E_CUDA", "EPK_E_NOMEM", "EPK_E_SHORT_SEQ", "EPK_E_UNSUPPORTED"]
+UINT64_MAX = (1 << 64) - 1
+
+# every symbol include/epik_b200.h declares (tests check that the library exports them all)
+SYMBOLS = [
+    "epk_abi_version", "epk_last_error", "epk_device_count", "epk_db_create", "epk_db_get_info", "epk_db_destroy",
+    "epk_placer_create", "epk_placer_destroy", "epk_place", "epk_place_device", "epk_group_batch", "epk_kmers",
+    "epk_placer_counters", "epk_host_alloc", "epk_host_free",
+]
+
+
+class EpkError(RuntimeError):
+    def __init__(self, status: int, message: str):
+        super().__init__("%s: %s" % (STATUS_NAMES[status] if 0 <= status < len(STATUS_NAMES) else status, message))
+        self.status = status
+
+
+class DbDesc(C.Structure):
+    _fields_ = [
+        ("alphabet", C.c_uint32), ("kmer_size", C.c_uint32), ("omega", C.c_float), ("n_keys", C.c_uint64),
+        ("keys", C.c_void_p), ("offsets", C.c_void_p), ("entries", C.c_void_p), ("filter_value", C.c_void_p),
+        ("n_nodes", C.c_uint32), ("branch_length", C.c_void_p), ("subtree_num_nodes", C.c_void_p),
+        ("subtree_total_length", C.c_void_p),
+    ]
+
+
+class LoadFilter(C.Structure):
+    _fields_ = [("mu", C.c_double), ("omega", C.c_float), ("max_entries", C.c_uint64)]
+
+
+class DbInfo(C.Structure):
+    _fields_ = [
+        ("alphabet", C.c_uint32), ("kmer_size", C.c_uint32), ("n_nodes", C.c_uint32), ("table_kind", C.c_uint32),
+        ("omega", C.c_float), ("threshold", C.c_float), ("log10_threshold", C.c_float),
+        ("n_keys_loaded", C.c_uint64), ("n_entries_loaded", C.c_uint64), ("n_entries_total", C.c_uint64),
+        ("table_slots", C.c_uint64), ("device_bytes", C.c_uint64),
+    ]
+
+
+class PlacerOpts(C.Structure):
+    _fields_ = [("variant", C.c_uint32), ("chunk_reads", C.c_uint32), ("reserved", C.c_uint32 * 6)]
+
+
+class Result(C.Structure):
+    _fields_ = [
+        ("n_place", C.c_void_p), ("branch", C.c_void_p), ("score", C.c_void_p), ("lwr", C.c_void_p),
+        ("count", C.c_void_p), ("distal", C.c_void_p), ("pendant", C.c_void_p),
+    ]
+
+
+class Counters(C.Structure):
+    _fields_ = [("n_reads", C.c_uint64), ("n_windows", C.c_uint64), ("n_hits", C.c_uint64), ("n_entries", C.c_uint64),
+                ("n_launches", C.c_uint64), ("n_short", C.c_uint64)]
+
+
+_lib = None
+
+
+def lib():
+    """The loaded libepik_b200.so; raises if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            "%s is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(epik_b200 has no CPU or pure-Python path)" % LIB_PATH)
+    l = C.CDLL(LIB_PATH)
+    l.epk_abi_version.restype = C.c_uint32
+    l.epk_last_error.restype = C.c_char_p
+    l.epk_device_count.restype = C.c_int
+    l.epk_db_create.restype = C.c_int
+    l.epk_db_create.argtypes = [C.POINTER(DbDesc), C.POINTER(LoadFilter), C.c_int, C.POINTER(C.c_void_p)]
+    l.epk_db_get_info.restype = C.c_int
+    l.epk_db_get_info.argtypes = [C.c_void_p, C.POINTER(DbInfo)]
+    l.epk_db_destroy.argtypes = [C.c_void_p]
+    l.epk_db_destroy.restype = None
+    l.epk_placer_create.restype = C.c_int
+    l.epk_placer_create.argtypes = [C.c_void_p, C.c_uint64, C.c_double, C.POINTER(PlacerOpts), C.POINTER(C.c_void_p)]
+    l.epk_placer_destroy.argtypes = [C.c_void_p]
+    l.epk_placer_destroy.restype = None
+    l.epk_place.restype = C.c_int
+    l.epk_place.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.POINTER(Result)]
+    l.epk_place_device.restype = C.c_int
+    l.epk_place_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.POINTER(Result), C.c_void_p]
+    l.epk_group_batch.restype = C.c_int
+    l.epk_group_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
+    l.epk_kmers.restype = C.c_int
+    l.epk_kmers.argtypes = [C.c_void_p, C.c_char_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p,
+                            C.c_void_p, C.POINTER(C.c_uint64)]
+    l.epk_placer_counters.restype = C.c_int
+    l.epk_placer_counters.argtypes = [C.c_void_p, C.POINTER(Counters)]
+    l.epk_host_alloc.restype = C.c_void_p
+    l.epk_host_alloc.argtypes = [C.c_size_t]
+    l.epk_host_free.argtypes = [C.c_void_p]
+    l.epk_host_free.restype = None
+    _lib = l
+    return l
+
+
+def check(status: int) -> None:
+    if status != EPK_OK:
+        raise EpkError(status, lib().epk_last_error().decode(errors="replace"))

@@ -1,0 +1,407 @@
+// epk_db_*: builds the HBM-resident database from the CSR description (include/epik_b200.h).
+// Stands in for i2l::load + what placer::placer precomputes from the tree
+// (epik/src/epik/main.cpp:277, epik/src/epik/place.cpp:83-126).
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <limits>
+#include <vector>
+#include <cub/cub.cuh>
+
+#include "common.cuh"
+#include "db.h"
+#include "db_build.cuh"
+
+namespace epk
+{
+namespace
+{
+    thread_local std::string g_last_error;
+
+    // DNA: A C G T -> 0..3 (U as T), IUPAC sets; amino acids: the RAPPAS order
+    // R H K D E S T N Q C G P A I L M F W Y V -> 0..19 (U as C, O as L), B Z J X sets.
+    // Everything else (gaps, '*', digits ...) is LETTER_GAP. [i2l absent: SURVEY.md Appendix B]
+    void set_letter(uint32_t* table, char c, std::initializer_list<int> codes)
+    {
+        uint32_t v = 0;
+        if (codes.size() == 1) { v = static_cast<uint32_t>(*codes.begin()); }
+        else
+        {
+            v = LETTER_AMBIGUOUS;
+            for (int code : codes) { v |= 1u << (8 + code); }
+        }
+        table[static_cast<unsigned char>(c)] = v;
+        table[static_cast<unsigned char>(c) | 0x20u] = v; // lower case
+    }
+
+    // Host -> device through two pinned staging buffers, copies overlapped with the host memcpy.
+    void upload(void* dst, const void* src, size_t bytes, cudaStream_t stream)
+    {
+        if (bytes == 0) { return; }
+        cudaPointerAttributes attr{};
+        if (cudaPointerGetAttributes(&attr, src) == cudaSuccess && attr.type == cudaMemoryTypeHost)
+        {
+            EPK_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, stream));
+            EPK_CUDA(cudaStreamSynchronize(stream));
+            return;
+        }
+        cudaGetLastError();
+        const size_t piece = std::min<size_t>(bytes, 32u << 20);
+        pinned_buffer<unsigned char> stage[2];
+        cudaEvent_t done[2];
+        for (int i = 0; i < 2; ++i)
+        {
+            stage[i].resize(piece);
+            EPK_CUDA(cudaEventCreateWithFlags(&done[i], cudaEventDisableTiming));
+        }
+        try
+        {
+            int slot = 0;
+            for (size_t at = 0; at < bytes; at += piece, slot ^= 1)
+            {
+                const size_t n = std::min(piece, bytes - at);
+                EPK_CUDA(cudaEventSynchronize(done[slot]));
+                std::memcpy(stage[slot].get(), static_cast<const unsigned char*>(src) + at, n);
+                EPK_CUDA(cudaMemcpyAsync(static_cast<unsigned char*>(dst) + at, stage[slot].get(), n,
+                                         cudaMemcpyHostToDevice, stream));
+                EPK_CUDA(cudaEventRecord(done[slot], stream));
+            }
+            EPK_CUDA(cudaStreamSynchronize(stream));
+        }
+        catch (...)
+        {
+            cudaStreamSynchronize(stream);
+            for (auto& e : done) { cudaEventDestroy(e); }
+            throw;
+        }
+        for (auto& e : done) { cudaEventDestroy(e); }
+    }
+
+    uint64_t exclusive_scan(const uint64_t* in, uint64_t* out, uint64_t n, cudaStream_t stream)
+    {
+        // returns the total; out[i] = sum of in[0, i)
+        if (n == 0) { return 0; }
+        size_t tmp_bytes = 0;
+        EPK_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, in, out, n, stream));
+        device_buffer<unsigned char> tmp(tmp_bytes);
+        uint64_t last_in = 0, last_out = 0;
+        EPK_CUDA(cudaMemcpyAsync(&last_in, in + n - 1, 8, cudaMemcpyDeviceToHost, stream));
+        EPK_CUDA(cub::DeviceScan::ExclusiveSum(tmp.get(), tmp_bytes, in, out, n, stream));
+        EPK_CUDA(cudaMemcpyAsync(&last_out, out + n - 1, 8, cudaMemcpyDeviceToHost, stream));
+        EPK_CUDA(cudaStreamSynchronize(stream));
+        return last_in + last_out;
+    }
+} // namespace
+
+void set_last_error(const std::string& message) { g_last_error = message; }
+const std::string& last_error() { return g_last_error; }
+
+void make_letter_table(uint32_t alphabet, uint32_t* table)
+{
+    for (int i = 0; i < 256; ++i) { table[i] = LETTER_GAP; }
+    if (alphabet == EPK_DNA)
+    {
+        set_letter(table, 'A', { 0 }); set_letter(table, 'C', { 1 }); set_letter(table, 'G', { 2 });
+        set_letter(table, 'T', { 3 }); set_letter(table, 'U', { 3 });
+        set_letter(table, 'R', { 0, 2 }); set_letter(table, 'Y', { 1, 3 }); set_letter(table, 'S', { 1, 2 });
+        set_letter(table, 'W', { 0, 3 }); set_letter(table, 'K', { 2, 3 }); set_letter(table, 'M', { 0, 1 });
+        set_letter(table, 'B', { 1, 2, 3 }); set_letter(table, 'D', { 0, 2, 3 }); set_letter(table, 'H', { 0, 1, 3 });
+        set_letter(table, 'V', { 0, 1, 2 }); set_letter(table, 'N', { 0, 1, 2, 3 });
+    }
+    else
+    {
+        const char* order = "RHKDESTNQCGPAILMFWYV";
+        for (int i = 0; i < 20; ++i) { set_letter(table, order[i], { i }); }
+        set_letter(table, 'U', { 9 }); set_letter(table, 'O', { 14 });
+        set_letter(table, 'B', { 3, 7 }); set_letter(table, 'Z', { 4, 8 }); set_letter(table, 'J', { 13, 14 });
+        set_letter(table, 'X', { 0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16, 17, 18, 19 });
+    }
+}
+
+float score_threshold(uint32_t alphabet, float omega, uint32_t k)
+{
+    // i2l::score_threshold(omega, k) (call site place.cpp:87): (omega / |alphabet|)^k in float
+    return std::pow(omega / static_cast<float>(alphabet == EPK_AA ? 20 : 4), static_cast<float>(k));
+}
+} // namespace epk
+
+using namespace epk;
+
+static void build_db(const epk_db_desc& d, const epk_load_filter* filter, int device, epk_db& db)
+{
+    if (d.alphabet != EPK_DNA && d.alphabet != EPK_AA) { throw error(EPK_E_INVALID, "unknown alphabet"); }
+    const uint32_t bits = d.alphabet == EPK_AA ? 5 : 2;
+    if (d.kmer_size == 0 || d.kmer_size * bits > 32) { throw error(EPK_E_INVALID, "k-mer size does not fit a 32-bit key"); }
+    if (d.n_nodes == 0) { throw error(EPK_E_INVALID, "empty tree"); }
+    if (d.n_keys > 0xFFFFFFFFull) { throw error(EPK_E_INVALID, "too many keys"); }
+    if ((d.n_keys && (!d.keys || !d.offsets)) || !d.branch_length || !d.subtree_num_nodes || !d.subtree_total_length)
+    {
+        throw error(EPK_E_INVALID, "null array in the database description");
+    }
+    int n_devices = 0;
+    if (cudaGetDeviceCount(&n_devices) != cudaSuccess || n_devices == 0)
+    {
+        cudaGetLastError();
+        throw error(EPK_E_CUDA, "no CUDA device: epik_b200 has no CPU path");
+    }
+    if (device < 0 || device >= n_devices) { throw error(EPK_E_INVALID, "no such CUDA device"); }
+    EPK_CUDA(cudaSetDevice(device));
+    db.device = device;
+
+    const uint64_t n_keys = d.n_keys;
+    const uint64_t n_total = n_keys ? d.offsets[n_keys] : 0;
+    if (n_keys && d.offsets[0] != 0) { throw error(EPK_E_INVALID, "offsets[0] must be 0"); }
+    if (n_total && !d.entries) { throw error(EPK_E_INVALID, "null entries"); }
+
+    float omega = d.omega;
+    bool use_min_score = false;
+    float min_score = 0.0f;
+    uint64_t budget = std::numeric_limits<uint64_t>::max();
+    if (filter)
+    {
+        if (!(filter->mu >= 0.0 && filter->mu <= 1.0)) { throw error(EPK_E_INVALID, "mu must be in [0, 1]"); } // main.cpp:196-202
+        omega = filter->omega;
+        use_min_score = true;
+        min_score = std::log10(score_threshold(d.alphabet, filter->omega, d.kmer_size));
+        if (filter->mu < 1.0) { budget = static_cast<uint64_t>(filter->mu * static_cast<double>(n_total)); }
+        budget = std::min(budget, filter->max_entries);
+    }
+
+    cudaStream_t stream;
+    EPK_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    struct stream_guard { cudaStream_t s; ~stream_guard() { cudaStreamDestroy(s); } } guard{ stream };
+
+    // ---- raw CSR to the device ----
+    device_buffer<uint32_t> keys(n_keys);
+    device_buffer<uint64_t> offsets(n_keys + 1);
+    device_buffer<uint2> entries(n_total);
+    static_assert(sizeof(epk_entry) == sizeof(uint2), "posting layout");
+    if (n_keys)
+    {
+        upload(keys.get(), d.keys, n_keys * 4, stream);
+        upload(offsets.get(), d.offsets, (n_keys + 1) * 8, stream);
+    }
+    else { EPK_CUDA(cudaMemsetAsync(offsets.get(), 0, 8, stream)); }
+    upload(entries.get(), d.entries, n_total * 8, stream);
+
+    const unsigned T = 256;
+    device_buffer<uint64_t> new_len(n_keys), padded_len(n_keys), new_off(n_keys);
+    uint64_t n_padded = 0;
+    if (n_keys)
+    {
+        // ---- informative-k-mer prefix (mu / max_entries) ----
+        device_buffer<uint8_t> keep;
+        if (budget < n_total)
+        {
+            device_buffer<uint64_t> len(n_keys), sorted_len(n_keys), before(n_keys);
+            list_lengths_kernel<<<blocks_for(n_keys, T), T, 0, stream>>>(offsets.get(), n_keys, len.get());
+            device_buffer<uint32_t> order;
+            if (d.filter_value)
+            {
+                device_buffer<float> fv(n_keys), fv_sorted(n_keys);
+                device_buffer<uint32_t> idx(n_keys);
+                order.resize(n_keys);
+                upload(fv.get(), d.filter_value, n_keys * 4, stream);
+                iota_kernel<<<blocks_for(n_keys, T), T, 0, stream>>>(idx.get(), n_keys);
+                size_t tmp_bytes = 0;
+                EPK_CUDA(cub::DeviceRadixSort::SortPairsDescending(nullptr, tmp_bytes, fv.get(), fv_sorted.get(),
+                                                                   idx.get(), order.get(), n_keys, 0, 32, stream));
+                device_buffer<unsigned char> tmp(tmp_bytes);
+                EPK_CUDA(cub::DeviceRadixSort::SortPairsDescending(tmp.get(), tmp_bytes, fv.get(), fv_sorted.get(),
+                                                                   idx.get(), order.get(), n_keys, 0, 32, stream));
+                EPK_CUDA(cudaStreamSynchronize(stream));
+            }
+            gather_lengths_kernel<<<blocks_for(n_keys, T), T, 0, stream>>>(len.get(), order.get(), n_keys, sorted_len.get());
+            exclusive_scan(sorted_len.get(), before.get(), n_keys, stream);
+            keep.resize(n_keys);
+            prefix_cut_kernel<<<blocks_for(n_keys, T), T, 0, stream>>>(before.get(), order.get(), n_keys, budget, keep.get());
+            EPK_CUDA(cudaStreamSynchronize(stream));
+        }
+        // ---- per-entry omega threshold, packed layout ----
+        surviving_lengths_kernel<<<blocks_for(n_keys * 32, T), T, 0, stream>>>(
+            offsets.get(), entries.get(), keep.get(), n_keys, min_score, use_min_score, new_len.get(), padded_len.get());
+        n_padded = exclusive_scan(padded_len.get(), new_off.get(), n_keys, stream);
+    }
+    db.postings.resize(std::max<uint64_t>(n_padded, 2));
+    EPK_CUDA(cudaMemsetAsync(db.postings.get(), 0, 16, stream));
+    device_buffer<unsigned long long> totals(2);
+    device_buffer<uint32_t> status(1);
+    EPK_CUDA(cudaMemsetAsync(totals.get(), 0, 16, stream));
+    EPK_CUDA(cudaMemsetAsync(status.get(), 0, 4, stream));
+    if (n_keys)
+    {
+        pack_lists_kernel<<<blocks_for(n_keys * 32, T), T, 0, stream>>>(
+            offsets.get(), entries.get(), new_len.get(), new_off.get(), n_keys, min_score, use_min_score, db.postings.get());
+        count_loaded_kernel<<<std::min(blocks_for(n_keys, T), 1024u), T, 0, stream>>>(new_len.get(), n_keys, totals.get());
+    }
+    unsigned long long h_totals[2] = { 0, 0 };
+    EPK_CUDA(cudaMemcpyAsync(h_totals, totals.get(), 16, cudaMemcpyDeviceToHost, stream));
+    EPK_CUDA(cudaStreamSynchronize(stream));
+    EPK_CUDA(cudaGetLastError());
+    entries.release();
+
+    // ---- key table ----
+    device_db& dd = db.d;
+    std::memset(&dd, 0, sizeof(dd));
+    const uint32_t key_bits = bits * d.kmer_size;
+    if (key_bits <= 26)
+    {
+        db.table_kind = TABLE_DIRECT;
+        db.table_slots = 1ull << key_bits;
+        db.direct.resize(db.table_slots);
+        EPK_CUDA(cudaMemsetAsync(db.direct.get(), 0, db.direct.bytes(), stream));
+        if (n_keys)
+        {
+            fill_direct_kernel<<<blocks_for(n_keys, T), T, 0, stream>>>(
+                keys.get(), new_len.get(), new_off.get(), n_keys, db.table_slots,
+                reinterpret_cast<unsigned long long*>(db.direct.get()), status.get());
+        }
+    }
+    else
+    {
+        db.table_kind = TABLE_HASH;
+        uint64_t slots = 1024;
+        while (slots < 2 * h_totals[1]) { slots <<= 1; }
+        if (slots > (1ull << 32)) { throw error(EPK_E_UNSUPPORTED, "hash table too large"); }
+        uint32_t log2 = 0;
+        while ((1ull << log2) < slots) { ++log2; }
+        db.table_slots = slots;
+        db.hashed.resize(slots);
+        dd.hash_mask = slots - 1;
+        dd.hash_shift = 32 - log2;
+        clear_hash_kernel<<<blocks_for(slots, T), T, 0, stream>>>(db.hashed.get(), slots);
+        if (n_keys)
+        {
+            fill_hash_kernel<<<blocks_for(n_keys, T), T, 0, stream>>>(
+                keys.get(), new_len.get(), new_off.get(), n_keys, db.hashed.get(), dd.hash_mask, dd.hash_shift, status.get());
+            check_hash_kernel<<<blocks_for(n_keys, T), T, 0, stream>>>(
+                keys.get(), new_len.get(), new_off.get(), n_keys, db.hashed.get(), dd.hash_mask, dd.hash_shift, status.get());
+        }
+    }
+    // ---- validation of the lists ----
+    if (n_keys)
+    {
+        const uint32_t words = (d.n_nodes + 31) / 32;
+        unsigned warps = 8;
+        while (warps > 1 && static_cast<size_t>(warps) * words * 4 > 96 * 1024) { warps >>= 1; }
+        const size_t smem = static_cast<size_t>(warps) * words * 4;
+        if (smem > 200 * 1024) { throw error(EPK_E_UNSUPPORTED, "tree too large"); }
+        EPK_CUDA(cudaFuncSetAttribute(validate_lists_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+        validate_lists_kernel<<<1184, warps * 32, smem, stream>>>(db.postings.get(), new_len.get(), new_off.get(), n_keys,
+                                                                  d.n_nodes, status.get());
+    }
+    uint32_t h_status = 0;
+    EPK_CUDA(cudaMemcpyAsync(&h_status, status.get(), 4, cudaMemcpyDeviceToHost, stream));
+    EPK_CUDA(cudaStreamSynchronize(stream));
+    EPK_CUDA(cudaGetLastError());
+    if (h_status & BUILD_DUPLICATE_KEY) { throw error(EPK_E_INVALID, "duplicate k-mer key in the database"); }
+    if (h_status & BUILD_KEY_RANGE) { throw error(EPK_E_INVALID, "k-mer key out of range for this k"); }
+    if (h_status & BUILD_BAD_BRANCH) { throw error(EPK_E_INVALID, "branch id >= node count in a posting list"); }
+    if (h_status & BUILD_DUPLICATE_BRANCH) { throw error(EPK_E_INVALID, "a posting list names the same branch twice"); }
+    if (h_status & BUILD_LIST_TOO_LONG) { throw error(EPK_E_UNSUPPORTED, "posting list longer than 2^24 - 1 entries"); }
+
+    // ---- letters, thresholds, tree tables ----
+    uint32_t table[256];
+    make_letter_table(d.alphabet, table);
+    db.letters.resize(256);
+    EPK_CUDA(cudaMemcpy(db.letters.get(), table, sizeof(table), cudaMemcpyHostToDevice));
+
+    dd.direct = db.direct.get();
+    dd.hashed = db.hashed.get();
+    dd.postings = db.postings.get();
+    dd.table_kind = db.table_kind;
+    dd.k = d.kmer_size;
+    dd.bits = bits;
+    dd.key_mask = key_bits >= 32 ? 0xFFFFFFFFu : ((1u << key_bits) - 1u);
+    dd.n_nodes = d.n_nodes;
+    dd.alphabet = d.alphabet;
+    dd.threshold = score_threshold(d.alphabet, omega, d.kmer_size);
+    dd.log_threshold = std::log10(dd.threshold); // place.cpp:88, float log10
+
+    // place.cpp:98-125: distal = branch_length / 2, pendant = mean subtree branch length + distal
+    db.distal.resize(d.n_nodes);
+    db.pendant.resize(d.n_nodes);
+    for (uint32_t i = 0; i < d.n_nodes; ++i)
+    {
+        const double distal = d.branch_length[i] / 2;
+        double mean = 0.0;
+        if (d.subtree_num_nodes[i] > 1) { mean = d.subtree_total_length[i] / static_cast<double>(d.subtree_num_nodes[i]); }
+        db.distal[i] = distal;
+        db.pendant[i] = mean + distal;
+    }
+
+    db.omega = omega;
+    db.n_entries_total = n_total;
+    db.n_entries_loaded = h_totals[0];
+    db.n_keys_loaded = h_totals[1];
+}
+
+extern "C" epk_status epk_db_create(const epk_db_desc* desc, const epk_load_filter* filter, int device, epk_db** out)
+{
+    return guarded([&] {
+        if (!desc || !out) { throw error(EPK_E_INVALID, "null argument"); }
+        *out = nullptr;
+        auto db = std::make_unique<epk_db>();
+        build_db(*desc, filter, device, *db);
+        *out = db.release();
+    });
+}
+
+extern "C" epk_status epk_db_get_info(const epk_db* db, epk_db_info* info)
+{
+    return guarded([&] {
+        if (!db || !info) { throw error(EPK_E_INVALID, "null argument"); }
+        info->alphabet = db->d.alphabet;
+        info->kmer_size = db->d.k;
+        info->n_nodes = db->d.n_nodes;
+        info->table_kind = db->table_kind;
+        info->omega = db->omega;
+        info->threshold = db->d.threshold;
+        info->log10_threshold = db->d.log_threshold;
+        info->n_keys_loaded = db->n_keys_loaded;
+        info->n_entries_loaded = db->n_entries_loaded;
+        info->n_entries_total = db->n_entries_total;
+        info->table_slots = db->table_slots;
+        info->device_bytes = db->direct.bytes() + db->hashed.bytes() + db->postings.bytes() + db->letters.bytes();
+    });
+}
+
+extern "C" void epk_db_destroy(epk_db* db)
+{
+    if (db)
+    {
+        cudaSetDevice(db->device);
+        delete db;
+    }
+}
+
+extern "C" const char* epk_last_error(void) { return epk::last_error().c_str(); }
+extern "C" uint32_t epk_abi_version(void) { return EPK_ABI_VERSION; }
+
+extern "C" int epk_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess)
+    {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+extern "C" void* epk_host_alloc(size_t bytes)
+{
+    void* p = nullptr;
+    if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess)
+    {
+        cudaGetLastError();
+        epk::set_last_error("cudaMallocHost failed");
+        return nullptr;
+    }
+    return p;
+}
+
+extern "C" void epk_host_free(void* p)
+{
+    if (p) { cudaFreeHost(p); }
+}

@@ -1,0 +1,240 @@
+// Load-time kernels: the device side of i2l::load(db_file, mu, omega, max_entries)
+// (call site epik/src/epik/main.cpp:277) after the file has been parsed into CSR arrays.
+//
+//   1. informative-k-mer filter: k-mers ordered by decreasing filter value (stable radix sort;
+//      with no filter values the given order is the file order), whole k-mers kept while the
+//      entries taken so far are below min(mu * total, max_entries); of a kept k-mer only the
+//      entries scoring >= log10(score_threshold(user omega, k)) survive.
+//      [UNVERIFIED vs upstream i2l — the submodule is absent; SURVEY.md Appendix B]
+//   2. layout: surviving lists are packed at 16-byte boundaries (even entry counts) by an
+//      exclusive scan + a warp-per-list compaction;
+//   3. key table: direct-address slots or open addressing (see device_db.cuh).
+//   4. validation: branch ids < n_nodes and distinct within a list (the placement kernel
+//      relies on it to add a list without atomics).
+#pragma once
+
+#include <cstdint>
+#include <cuda_runtime.h>
+#include "device_db.cuh"
+
+namespace epk
+{
+// len[i] = offsets[i + 1] - offsets[i]
+__global__ void list_lengths_kernel(const uint64_t* offsets, uint64_t n_keys, uint64_t* len)
+{
+    const uint64_t i = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x;
+    if (i < n_keys) { len[i] = offsets[i + 1] - offsets[i]; }
+}
+
+__global__ void iota_kernel(uint32_t* idx, uint64_t n)
+{
+    const uint64_t i = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x;
+    if (i < n) { idx[i] = static_cast<uint32_t>(i); }
+}
+
+// sorted_len[j] = len[order[j]]
+__global__ void gather_lengths_kernel(const uint64_t* len, const uint32_t* order, uint64_t n_keys, uint64_t* sorted_len)
+{
+    const uint64_t j = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x;
+    if (j < n_keys) { sorted_len[j] = len[order ? order[j] : j]; }
+}
+
+// keep[order[j]] = entries taken before k-mer j < budget
+__global__ void prefix_cut_kernel(const uint64_t* before, const uint32_t* order, uint64_t n_keys, uint64_t budget,
+                                  uint8_t* keep)
+{
+    const uint64_t j = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x;
+    if (j < n_keys) { keep[order ? order[j] : j] = before[j] < budget ? 1 : 0; }
+}
+
+// One warp per list: surviving entry count (and its even-padded size).
+__global__ void surviving_lengths_kernel(const uint64_t* offsets, const uint2* entries, const uint8_t* keep,
+                                         uint64_t n_keys, float min_score, bool use_min_score,
+                                         uint64_t* new_len, uint64_t* padded_len)
+{
+    const uint64_t i = (blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x) >> 5;
+    const uint32_t lane = threadIdx.x & 31u;
+    if (i >= n_keys) { return; }
+    uint64_t n = 0;
+    if (!keep || keep[i])
+    {
+        const uint64_t b = offsets[i], e = offsets[i + 1];
+        if (!use_min_score) { n = e - b; }
+        else
+        {
+            uint32_t mine = 0;
+            for (uint64_t j = b + lane; j < e; j += 32)
+            {
+                mine += __uint_as_float(entries[j].y) >= min_score ? 1u : 0u;
+            }
+            for (int d = 16; d > 0; d >>= 1) { mine += __shfl_xor_sync(0xFFFFFFFFu, mine, d); }
+            n = mine;
+        }
+    }
+    if (lane == 0)
+    {
+        new_len[i] = n;
+        padded_len[i] = (n + 1) & ~1ull;
+    }
+}
+
+// One warp per list: copies the surviving entries, in order, to their packed position.
+__global__ void pack_lists_kernel(const uint64_t* offsets, const uint2* entries, const uint64_t* new_len,
+                                  const uint64_t* new_off, uint64_t n_keys, float min_score, bool use_min_score,
+                                  uint2* postings)
+{
+    const uint64_t i = (blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x) >> 5;
+    const uint32_t lane = threadIdx.x & 31u;
+    if (i >= n_keys) { return; }
+    const uint64_t n = new_len[i];
+    if (n == 0) { return; }
+    const uint64_t b = offsets[i], e = offsets[i + 1];
+    uint2* dst = postings + new_off[i];
+    uint64_t written = 0;
+    for (uint64_t j0 = b; j0 < e; j0 += 32)
+    {
+        const uint64_t j = j0 + lane;
+        uint2 v = make_uint2(0, 0);
+        bool ok = false;
+        if (j < e)
+        {
+            v = entries[j];
+            ok = !use_min_score || __uint_as_float(v.y) >= min_score;
+        }
+        const uint32_t ballot = __ballot_sync(0xFFFFFFFFu, ok);
+        if (ok) { dst[written + __popc(ballot & ((1u << lane) - 1u))] = v; }
+        written += __popc(ballot);
+    }
+    if (lane == 0 && (n & 1)) { dst[n] = make_uint2(0, 0); } // pad entry, never applied
+}
+
+// status bits
+constexpr uint32_t BUILD_DUPLICATE_KEY = 1, BUILD_KEY_RANGE = 2, BUILD_BAD_BRANCH = 4, BUILD_DUPLICATE_BRANCH = 8,
+                   BUILD_LIST_TOO_LONG = 16;
+
+__global__ void fill_direct_kernel(const uint32_t* keys, const uint64_t* new_len, const uint64_t* new_off,
+                                   uint64_t n_keys, uint64_t n_slots, unsigned long long* slots, uint32_t* status)
+{
+    const uint64_t i = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x;
+    if (i >= n_keys) { return; }
+    const uint64_t n = new_len[i];
+    if (keys[i] >= n_slots) { atomicOr(status, BUILD_KEY_RANGE); return; }
+    if (n > LEN_MASK) { atomicOr(status, BUILD_LIST_TOO_LONG); return; }
+    if (n == 0) { return; }
+    const unsigned long long packed = (new_off[i] << LEN_BITS) | n;
+    if (atomicExch(slots + keys[i], packed) != 0ull) { atomicOr(status, BUILD_DUPLICATE_KEY); }
+}
+
+__global__ void clear_hash_kernel(uint4* slots, uint64_t n_slots)
+{
+    const uint64_t i = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x;
+    if (i < n_slots) { slots[i] = make_uint4(0, HASH_EMPTY, 0, 0); }
+}
+
+// Linear probing; a slot is claimed by a compare-and-swap on its length word. Keys are unique, so
+// builders never need to compare keys (a half-written slot is simply "taken").
+__global__ void fill_hash_kernel(const uint32_t* keys, const uint64_t* new_len, const uint64_t* new_off,
+                                 uint64_t n_keys, uint4* slots, uint64_t mask, uint32_t shift, uint32_t* status)
+{
+    const uint64_t i = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x;
+    if (i >= n_keys) { return; }
+    const uint64_t n = new_len[i];
+    if (n == 0) { return; }
+    if (n >= HASH_EMPTY || n > LEN_MASK) { atomicOr(status, BUILD_LIST_TOO_LONG); return; }
+    const uint32_t key = keys[i];
+    uint64_t h = hash_slot(key, shift);
+    while (true)
+    {
+        uint32_t* words = reinterpret_cast<uint32_t*>(slots + h);
+        if (atomicCAS(words + 1, HASH_EMPTY, static_cast<uint32_t>(n)) == HASH_EMPTY)
+        {
+            words[0] = key;
+            words[2] = static_cast<uint32_t>(new_off[i]);
+            words[3] = static_cast<uint32_t>(new_off[i] >> 32);
+            return;
+        }
+        h = (h + 1) & mask;
+    }
+}
+
+// After the hash table is complete: every key must be found exactly where a probe ends
+// (detects duplicate keys: the second copy stops at the first).
+__global__ void check_hash_kernel(const uint32_t* keys, const uint64_t* new_len, const uint64_t* new_off,
+                                  uint64_t n_keys, const uint4* slots, uint64_t mask, uint32_t shift, uint32_t* status)
+{
+    const uint64_t i = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x;
+    if (i >= n_keys || new_len[i] == 0) { return; }
+    const uint32_t key = keys[i];
+    uint64_t h = hash_slot(key, shift);
+    while (true)
+    {
+        const uint4 s = slots[h];
+        if (s.y == HASH_EMPTY) { atomicOr(status, BUILD_DUPLICATE_KEY); return; }
+        if (s.x == key)
+        {
+            const uint64_t off = (static_cast<uint64_t>(s.w) << 32) | s.z;
+            if (off != new_off[i]) { atomicOr(status, BUILD_DUPLICATE_KEY); }
+            return;
+        }
+        h = (h + 1) & mask;
+    }
+}
+
+// One warp per list, a bitmap of n_nodes bits per warp in shared memory.
+__global__ void validate_lists_kernel(const uint2* postings, const uint64_t* new_len, const uint64_t* new_off,
+                                      uint64_t n_keys, uint32_t n_nodes, uint32_t* status)
+{
+    extern __shared__ uint32_t bitmap_all[];
+    const uint32_t words = (n_nodes + 31) / 32;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t warp = threadIdx.x >> 5;
+    const uint32_t warps_per_block = blockDim.x >> 5;
+    uint32_t* bitmap = bitmap_all + static_cast<size_t>(warp) * words;
+    for (uint32_t w = lane; w < words; w += 32) { bitmap[w] = 0; }
+    __syncwarp();
+    for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * warps_per_block + warp; i < n_keys;
+         i += static_cast<uint64_t>(gridDim.x) * warps_per_block)
+    {
+        const uint64_t n = new_len[i];
+        const uint2* list = postings + new_off[i];
+        bool bad = false;
+        for (uint64_t j = lane; j < n; j += 32)
+        {
+            const uint32_t b = list[j].x;
+            if (b >= n_nodes) { atomicOr(status, BUILD_BAD_BRANCH); bad = true; continue; }
+            const uint32_t bit = 1u << (b & 31u);
+            if (atomicOr(bitmap + (b >> 5), bit) & bit) { atomicOr(status, BUILD_DUPLICATE_BRANCH); }
+        }
+        __syncwarp();
+        for (uint64_t j = lane; j < n; j += 32)
+        {
+            const uint32_t b = list[j].x;
+            if (b < n_nodes) { bitmap[b >> 5] = 0; }
+        }
+        (void)bad;
+        __syncwarp();
+    }
+}
+
+// totals[0] = sum of new_len, totals[1] = number of non-empty lists
+__global__ void count_loaded_kernel(const uint64_t* new_len, uint64_t n_keys, unsigned long long* totals)
+{
+    uint64_t entries = 0, lists = 0;
+    for (uint64_t i = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x; i < n_keys;
+         i += static_cast<uint64_t>(gridDim.x) * blockDim.x)
+    {
+        entries += new_len[i];
+        lists += new_len[i] != 0;
+    }
+    for (int d = 16; d > 0; d >>= 1)
+    {
+        entries += __shfl_xor_sync(0xFFFFFFFFu, entries, d);
+        lists += __shfl_xor_sync(0xFFFFFFFFu, lists, d);
+    }
+    if ((threadIdx.x & 31u) == 0)
+    {
+        atomicAdd(totals, static_cast<unsigned long long>(entries));
+        atomicAdd(totals + 1, static_cast<unsigned long long>(lists));
+    }
+}
+} // namespace epk

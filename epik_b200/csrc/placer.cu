@@ -1,0 +1,508 @@
+// epk_placer_* / epk_place*: the host side of epik::placer (reference
+// epik/include/epik/place.h:81-140, epik/src/epik/place.cpp:83-126,201-275) in front of the
+// sm_100a placement kernel (place_kernel.cuh).
+#include <algorithm>
+#include <cstring>
+#include <memory>
+#include <string_view>
+#include <unordered_map>
+#include <vector>
+
+#include "common.cuh"
+#include "db.h"
+#include "place_kernel.cuh"
+
+namespace epk
+{
+namespace
+{
+    constexpr int N_SLOTS = 3; // chunks in flight in epk_place: copy in / compute / copy out
+
+    __global__ void fold_counters_kernel(const unsigned long long* launch, unsigned long long* totals)
+    {
+        for (int i = 1; i < CTR_COUNT; ++i) { atomicAdd(totals + i, launch[i]); }
+    }
+
+    // letter codes straight from the sequence bytes (the placement kernel stages them in shared memory)
+    struct letter_codes
+    {
+        const uint32_t* letters;
+        const char* seq;
+        __device__ uint32_t operator[](uint64_t i) const { return letters[static_cast<uint8_t>(seq[i])] & 0xFFu; }
+    };
+
+    // One thread, one sequence: the (window, key) stream in the order place.cpp:294-313 consumes it,
+    // through the same classify_window / db_search the placement kernel runs.
+    template<uint32_t TABLE>
+    __global__ void kmers_kernel(device_db db, const uint32_t* letters, const char* seq, uint64_t len, uint64_t cap,
+                                 uint32_t* pos, uint32_t* key, uint32_t* group, long long* hit_len,
+                                 unsigned long long* n_out)
+    {
+        if (threadIdx.x != 0) { return; }
+        uint64_t n = 0;
+        for (uint64_t w = 0; w + db.k <= len; ++w)
+        {
+            const window_class c = classify_window(letter_codes{ letters, seq + w }, 0u, db.k, db.bits);
+            if (c.gaps != 0 || c.ambs > 1) { continue; }
+            uint32_t resolutions = 1, shift = 0, n_keys = 1;
+            if (c.ambs == 1)
+            {
+                resolutions = letters[static_cast<uint8_t>(seq[w + c.amb_at])] >> 8;
+                shift = db.bits * (db.k - 1 - c.amb_at);
+                n_keys = __popc(resolutions);
+            }
+            while (resolutions)
+            {
+                const uint32_t code = c.ambs ? __ffs(resolutions) - 1 : 0;
+                resolutions &= resolutions - 1;
+                const uint32_t kk = c.key | (code << shift);
+                if (n < cap)
+                {
+                    const uint64_t found = db_search<TABLE>(db, kk);
+                    pos[n] = static_cast<uint32_t>(w);
+                    key[n] = kk;
+                    group[n] = n_keys;
+                    hit_len[n] = (found & LEN_MASK) ? static_cast<long long>(found & LEN_MASK) : -1;
+                }
+                ++n;
+            }
+        }
+        *n_out = n;
+    }
+
+    struct out_arrays
+    {
+        device_buffer<uint32_t> n_place, branch, count;
+        device_buffer<float> score;
+        device_buffer<double> lwr;
+    };
+
+    struct chunk_slot
+    {
+        cudaStream_t stream = nullptr;
+        device_buffer<char> seq;
+        device_buffer<uint64_t> off;
+        out_arrays out;
+        device_buffer<unsigned long long> counters;
+        pinned_buffer<char> h_seq;        // staging when the caller's memory is pageable
+        pinned_buffer<uint64_t> h_off;
+        pinned_buffer<unsigned char> h_out;
+        size_t reads_cap = 0, bytes_cap = 0;
+        // pending copy-out of the previous chunk that used this slot (pageable destination)
+        bool pending = false;
+        uint32_t pending_first = 0, pending_n = 0;
+    };
+} // namespace
+} // namespace epk
+
+using namespace epk;
+
+struct epk_placer
+{
+    const epk_db* db = nullptr;
+    uint32_t keep_at_most = 0;
+    double keep_factor = 0.0;
+    uint32_t variant = 0;
+    uint32_t chunk_reads = 0;
+    int n_sms = 0;
+    uint32_t warps_per_cta = 0;
+    size_t smem_bytes = 0;
+    device_buffer<uint32_t> fake_order;
+    device_buffer<unsigned long long> totals;          // folded work counters
+    device_buffer<unsigned long long> device_counters; // per-launch counters of epk_place_device
+    chunk_slot slots[N_SLOTS];
+    uint64_t n_launches = 0, n_reads = 0;
+    cudaStream_t last_stream = nullptr;
+    bool totals_dirty = false;
+};
+
+namespace
+{
+    using kernel_fn = void (*)(const place_params);
+
+    kernel_fn pick_kernel(const epk_placer& pl)
+    {
+        const bool direct = pl.db->table_kind == TABLE_DIRECT;
+        if (pl.keep_at_most <= 8)
+        {
+            return direct ? place_kernel<TABLE_DIRECT, 8, 8> : place_kernel<TABLE_HASH, 8, 8>;
+        }
+        return direct ? place_kernel<TABLE_DIRECT, 32, 4> : place_kernel<TABLE_HASH, 32, 4>;
+    }
+
+    // one launch over n sequences already on the device
+    void launch(epk_placer& pl, const char* d_seq, const uint64_t* d_off, uint32_t n, const epk_result& d_out,
+                unsigned long long* counters, cudaStream_t stream)
+    {
+        place_params p{};
+        p.db = pl.db->d;
+        p.seq = d_seq;
+        p.seq_off = d_off;
+        p.n = n;
+        p.keep_at_most = pl.keep_at_most;
+        p.keep_factor = pl.keep_factor;
+        p.n_place = d_out.n_place;
+        p.branch = d_out.branch;
+        p.score = d_out.score;
+        p.lwr = d_out.lwr;
+        p.count = d_out.count;
+        p.letters = pl.db->letters.get();
+        p.fake_order = pl.fake_order.get();
+        p.counters = counters;
+        EPK_CUDA(cudaMemsetAsync(counters, 0, CTR_COUNT * sizeof(unsigned long long), stream));
+        if (n)
+        {
+            const unsigned grid = static_cast<unsigned>(std::min<uint64_t>(pl.n_sms, (n + pl.warps_per_cta - 1) / pl.warps_per_cta));
+            pick_kernel(pl)<<<grid, pl.warps_per_cta * 32, pl.smem_bytes, stream>>>(p);
+            EPK_CUDA(cudaGetLastError());
+            fold_counters_kernel<<<1, 1, 0, stream>>>(counters, pl.totals.get());
+            EPK_CUDA(cudaGetLastError());
+            pl.n_launches += 2;
+        }
+        pl.n_reads += n;
+        pl.totals_dirty = true;
+        pl.last_stream = stream;
+    }
+
+    void reserve_slot(epk_placer& pl, chunk_slot& s, size_t reads, size_t bytes, bool stage_in, bool stage_out)
+    {
+        const size_t K = pl.keep_at_most;
+        if (reads > s.reads_cap)
+        {
+            EPK_CUDA(cudaStreamSynchronize(s.stream));
+            const size_t cap = std::max(reads, static_cast<size_t>(pl.chunk_reads));
+            s.off.resize(cap + 1);
+            s.out.n_place.resize(cap);
+            s.out.branch.resize(cap * K);
+            s.out.count.resize(cap * K);
+            s.out.score.resize(cap * K);
+            s.out.lwr.resize(cap * K);
+            s.h_off.release();
+            s.h_out.release();
+            s.reads_cap = cap;
+        }
+        if (bytes > s.bytes_cap)
+        {
+            EPK_CUDA(cudaStreamSynchronize(s.stream));
+            const size_t cap = bytes + bytes / 4 + 4096;
+            s.seq.resize(cap);
+            s.h_seq.release();
+            s.bytes_cap = cap;
+        }
+        if (stage_in)
+        {
+            if (s.h_seq.size() < s.bytes_cap) { s.h_seq.resize(s.bytes_cap); }
+            if (s.h_off.size() < s.reads_cap + 1) { s.h_off.resize(s.reads_cap + 1); }
+        }
+        if (stage_out && s.h_out.size() < s.reads_cap * (4 + K * 20))
+        {
+            s.h_out.resize(s.reads_cap * (4 + K * 20));
+        }
+    }
+
+    bool is_pinned(const void* p)
+    {
+        cudaPointerAttributes attr{};
+        if (cudaPointerGetAttributes(&attr, p) != cudaSuccess)
+        {
+            cudaGetLastError();
+            return false;
+        }
+        return attr.type == cudaMemoryTypeHost;
+    }
+
+    // layout of the pinned result staging of a slot: n_place | branch | count | score | lwr
+    struct staged_out
+    {
+        uint32_t *n_place, *branch, *count;
+        float* score;
+        double* lwr;
+        staged_out(unsigned char* base, size_t cap, size_t K)
+        {
+            lwr = reinterpret_cast<double*>(base);
+            n_place = reinterpret_cast<uint32_t*>(base + cap * K * 8);
+            branch = n_place + cap;
+            count = branch + cap * K;
+            score = reinterpret_cast<float*>(count + cap * K);
+        }
+    };
+
+    void finish_slot(epk_placer& pl, chunk_slot& s, const epk_result& out)
+    {
+        if (!s.pending) { return; }
+        EPK_CUDA(cudaStreamSynchronize(s.stream));
+        const size_t K = pl.keep_at_most;
+        const staged_out st(s.h_out.get(), s.reads_cap, K);
+        const size_t first = s.pending_first, n = s.pending_n;
+        std::memcpy(out.n_place + first, st.n_place, n * 4);
+        std::memcpy(out.branch + first * K, st.branch, n * K * 4);
+        std::memcpy(out.count + first * K, st.count, n * K * 4);
+        std::memcpy(out.score + first * K, st.score, n * K * 4);
+        std::memcpy(out.lwr + first * K, st.lwr, n * K * 8);
+        s.pending = false;
+    }
+} // namespace
+
+extern "C" epk_status epk_placer_create(const epk_db* db, uint64_t keep_at_most, double keep_factor,
+                                        const epk_placer_opts* opts, epk_placer** out)
+{
+    return guarded([&] {
+        if (!db || !out) { throw error(EPK_E_INVALID, "null argument"); }
+        *out = nullptr;
+        if (keep_at_most == 0 || keep_at_most > 32) { throw error(EPK_E_UNSUPPORTED, "keep_at_most must be in [1, 32]"); }
+        EPK_CUDA(cudaSetDevice(db->device));
+        auto pl = std::make_unique<epk_placer>();
+        pl->db = db;
+        pl->keep_at_most = static_cast<uint32_t>(keep_at_most);
+        pl->keep_factor = keep_factor;
+        pl->variant = opts ? opts->variant : 0;
+        pl->chunk_reads = opts && opts->chunk_reads ? opts->chunk_reads : (1u << 18);
+
+        int max_smem = 0;
+        EPK_CUDA(cudaDeviceGetAttribute(&pl->n_sms, cudaDevAttrMultiProcessorCount, db->device));
+        EPK_CUDA(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, db->device));
+        const size_t per_warp = warp_smem_bytes(db->d.n_nodes);
+        if (CTA_SMEM_FIXED + per_warp > static_cast<size_t>(max_smem))
+        {
+            throw error(EPK_E_UNSUPPORTED, "tree too large for the shared-memory accumulators of this build");
+        }
+        pl->warps_per_cta = static_cast<uint32_t>(
+            std::min<size_t>(MAX_WARPS_PER_CTA, (static_cast<size_t>(max_smem) - CTA_SMEM_FIXED) / per_warp));
+        pl->smem_bytes = CTA_SMEM_FIXED + pl->warps_per_cta * per_warp;
+        EPK_CUDA(cudaFuncSetAttribute(pick_kernel(*pl), cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      static_cast<int>(pl->smem_bytes)));
+
+        // zero-hit queries: keep_at_most placements on branches 0..K-1, all tied, pushed through
+        // std::partial_sort (place.cpp:141-156). The order it leaves them in is the library's; ask it.
+        struct tied { uint32_t branch; float score; };
+        std::vector<tied> fake(pl->keep_at_most);
+        for (uint32_t i = 0; i < pl->keep_at_most; ++i) { fake[i] = { i, 0.0f }; }
+        std::partial_sort(fake.begin(), fake.end(), fake.end(), [](const tied& a, const tied& b) { return a.score > b.score; });
+        std::vector<uint32_t> order(pl->keep_at_most);
+        for (uint32_t i = 0; i < pl->keep_at_most; ++i) { order[i] = fake[i].branch; }
+        pl->fake_order.resize(order.size());
+        EPK_CUDA(cudaMemcpy(pl->fake_order.get(), order.data(), order.size() * 4, cudaMemcpyHostToDevice));
+
+        pl->totals.resize(CTR_COUNT);
+        pl->device_counters.resize(CTR_COUNT);
+        EPK_CUDA(cudaMemset(pl->totals.get(), 0, pl->totals.bytes()));
+        for (auto& s : pl->slots)
+        {
+            EPK_CUDA(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+            s.counters.resize(CTR_COUNT);
+        }
+        *out = pl.release();
+    });
+}
+
+extern "C" void epk_placer_destroy(epk_placer* pl)
+{
+    if (!pl) { return; }
+    cudaSetDevice(pl->db->device);
+    for (auto& s : pl->slots)
+    {
+        if (s.stream)
+        {
+            cudaStreamSynchronize(s.stream);
+            cudaStreamDestroy(s.stream);
+        }
+    }
+    delete pl;
+}
+
+extern "C" epk_status epk_place_device(epk_placer* pl, const char* d_seq, const uint64_t* d_seq_off, uint32_t n,
+                                       const epk_result* d_out, void* stream)
+{
+    return guarded([&] {
+        if (!pl || !d_out || (n && (!d_seq_off || !d_out->n_place || !d_out->branch || !d_out->score || !d_out->lwr || !d_out->count)))
+        {
+            throw error(EPK_E_INVALID, "null argument");
+        }
+        if (d_out->distal || d_out->pendant) { throw error(EPK_E_INVALID, "distal/pendant must be NULL for device results"); }
+        EPK_CUDA(cudaSetDevice(pl->db->device));
+        const cudaStream_t s = static_cast<cudaStream_t>(stream);
+        EPK_CUDA(cudaMemsetAsync(pl->totals.get(), 0, pl->totals.bytes(), s));
+        pl->n_launches = 0;
+        pl->n_reads = 0;
+        launch(*pl, d_seq, d_seq_off, n, *d_out, pl->device_counters.get(), s);
+    });
+}
+
+extern "C" epk_status epk_place(epk_placer* pl, const char* seq, const uint64_t* seq_off, uint32_t n, const epk_result* out)
+{
+    return guarded([&] {
+        if (!pl || !out || (n && (!seq_off || !out->n_place || !out->branch || !out->score || !out->lwr || !out->count)))
+        {
+            throw error(EPK_E_INVALID, "null argument");
+        }
+        EPK_CUDA(cudaSetDevice(pl->db->device));
+        const size_t K = pl->keep_at_most;
+        const uint32_t k = pl->db->d.k;
+        EPK_CUDA(cudaMemset(pl->totals.get(), 0, pl->totals.bytes()));
+        pl->n_launches = 0;
+        pl->n_reads = 0;
+        if (n == 0) { return; }
+
+        const bool in_pinned = is_pinned(seq) && is_pinned(seq_off);
+        const bool out_pinned = is_pinned(out->n_place) && is_pinned(out->branch) && is_pinned(out->score)
+                                && is_pinned(out->lwr) && is_pinned(out->count);
+        const size_t max_chunk_bytes = 256u << 20;
+
+        uint32_t first = 0;
+        int turn = 0;
+        while (first < n)
+        {
+            // chunk = up to chunk_reads sequences and about max_chunk_bytes letters
+            uint32_t last = static_cast<uint32_t>(std::min<uint64_t>(n, static_cast<uint64_t>(first) + pl->chunk_reads));
+            while (last > first + 1 && seq_off[last] - seq_off[first] > max_chunk_bytes)
+            {
+                last = first + (last - first) / 2;
+            }
+            const uint32_t m = last - first;
+            const size_t bytes = seq_off[last] - seq_off[first];
+            chunk_slot& s = pl->slots[turn % N_SLOTS];
+            ++turn;
+            finish_slot(*pl, s, *out);
+            reserve_slot(*pl, s, m, bytes, !in_pinned, !out_pinned);
+
+            const char* h_seq = seq + seq_off[first];
+            const uint64_t* h_off = seq_off + first;
+            if (!in_pinned)
+            {
+                EPK_CUDA(cudaStreamSynchronize(s.stream)); // staging buffers free again
+                std::memcpy(s.h_seq.get(), h_seq, bytes);
+                std::memcpy(s.h_off.get(), h_off, (static_cast<size_t>(m) + 1) * 8);
+                h_seq = s.h_seq.get();
+                h_off = s.h_off.get();
+            }
+            if (bytes) { EPK_CUDA(cudaMemcpyAsync(s.seq.get(), h_seq, bytes, cudaMemcpyHostToDevice, s.stream)); }
+            EPK_CUDA(cudaMemcpyAsync(s.off.get(), h_off, (static_cast<size_t>(m) + 1) * 8, cudaMemcpyHostToDevice, s.stream));
+
+            epk_result d{};
+            d.n_place = s.out.n_place.get();
+            d.branch = s.out.branch.get();
+            d.score = s.out.score.get();
+            d.lwr = s.out.lwr.get();
+            d.count = s.out.count.get();
+            // offsets stay absolute: bias the base pointer instead of rewriting them
+            launch(*pl, s.seq.get() - seq_off[first], s.off.get(), m, d, s.counters.get(), s.stream);
+
+            if (out_pinned)
+            {
+                EPK_CUDA(cudaMemcpyAsync(out->n_place + first, d.n_place, m * 4ull, cudaMemcpyDeviceToHost, s.stream));
+                EPK_CUDA(cudaMemcpyAsync(out->branch + first * K, d.branch, m * K * 4, cudaMemcpyDeviceToHost, s.stream));
+                EPK_CUDA(cudaMemcpyAsync(out->count + first * K, d.count, m * K * 4, cudaMemcpyDeviceToHost, s.stream));
+                EPK_CUDA(cudaMemcpyAsync(out->score + first * K, d.score, m * K * 4, cudaMemcpyDeviceToHost, s.stream));
+                EPK_CUDA(cudaMemcpyAsync(out->lwr + first * K, d.lwr, m * K * 8, cudaMemcpyDeviceToHost, s.stream));
+            }
+            else
+            {
+                const staged_out st(s.h_out.get(), s.reads_cap, K);
+                EPK_CUDA(cudaMemcpyAsync(st.n_place, d.n_place, m * 4ull, cudaMemcpyDeviceToHost, s.stream));
+                EPK_CUDA(cudaMemcpyAsync(st.branch, d.branch, m * K * 4, cudaMemcpyDeviceToHost, s.stream));
+                EPK_CUDA(cudaMemcpyAsync(st.count, d.count, m * K * 4, cudaMemcpyDeviceToHost, s.stream));
+                EPK_CUDA(cudaMemcpyAsync(st.score, d.score, m * K * 4, cudaMemcpyDeviceToHost, s.stream));
+                EPK_CUDA(cudaMemcpyAsync(st.lwr, d.lwr, m * K * 8, cudaMemcpyDeviceToHost, s.stream));
+                s.pending = true;
+                s.pending_first = first;
+                s.pending_n = m;
+            }
+            first = last;
+        }
+        for (auto& s : pl->slots)
+        {
+            finish_slot(*pl, s, *out);
+            EPK_CUDA(cudaStreamSynchronize(s.stream));
+        }
+        unsigned long long totals[CTR_COUNT];
+        EPK_CUDA(cudaMemcpy(totals, pl->totals.get(), sizeof(totals), cudaMemcpyDeviceToHost));
+        if (totals[CTR_SHORT] != 0)
+        {
+            throw error(EPK_E_SHORT_SEQ, std::to_string(totals[CTR_SHORT]) + " sequence(s) shorter than k - 1 = "
+                                             + std::to_string(k - 1) + " letters");
+        }
+        // distal / pendant are look-ups by branch (place.cpp:434-437); zero for the zero-hit placements
+        if (out->distal || out->pendant)
+        {
+            const auto& db = *pl->db;
+            for (size_t i = 0; i < n; ++i)
+            {
+                for (size_t j = 0; j < K; ++j)
+                {
+                    const size_t at = i * K + j;
+                    const bool real = j < out->n_place[i] && out->count[at] != 0;
+                    if (out->distal) { out->distal[at] = real ? db.distal[out->branch[at]] : 0.0; }
+                    if (out->pendant) { out->pendant[at] = real ? db.pendant[out->branch[at]] : 0.0; }
+                }
+            }
+        }
+    });
+}
+
+extern "C" epk_status epk_placer_counters(epk_placer* pl, epk_counters* out)
+{
+    return guarded([&] {
+        if (!pl || !out) { throw error(EPK_E_INVALID, "null argument"); }
+        EPK_CUDA(cudaSetDevice(pl->db->device));
+        if (pl->last_stream || pl->totals_dirty) { EPK_CUDA(cudaStreamSynchronize(pl->last_stream)); }
+        unsigned long long totals[CTR_COUNT];
+        EPK_CUDA(cudaMemcpy(totals, pl->totals.get(), sizeof(totals), cudaMemcpyDeviceToHost));
+        out->n_reads = pl->n_reads;
+        out->n_windows = totals[CTR_WINDOWS];
+        out->n_hits = totals[CTR_HITS];
+        out->n_entries = totals[CTR_ENTRIES];
+        out->n_short = totals[CTR_SHORT];
+        out->n_launches = pl->n_launches;
+    });
+}
+
+extern "C" epk_status epk_group_batch(const char* seq, const uint64_t* seq_off, uint32_t n, uint32_t* group_rep)
+{
+    return guarded([&] {
+        if (n && (!seq_off || !group_rep)) { throw error(EPK_E_INVALID, "null argument"); }
+        // place.cpp:73-81: identical sequences of a batch share one placement
+        std::unordered_map<std::string_view, uint32_t> first_of;
+        first_of.reserve(n);
+        for (uint32_t i = 0; i < n; ++i)
+        {
+            const std::string_view s(seq + seq_off[i], seq_off[i + 1] - seq_off[i]);
+            group_rep[i] = first_of.try_emplace(s, i).first->second;
+        }
+    });
+}
+
+extern "C" epk_status epk_kmers(const epk_db* db, const char* seq, uint64_t len, uint64_t cap, uint32_t* pos,
+                                uint32_t* key, uint32_t* group, int64_t* hit_len, uint64_t* n_out)
+{
+    return guarded([&] {
+        if (!db || !n_out || (len && !seq) || (cap && (!pos || !key || !group || !hit_len))) { throw error(EPK_E_INVALID, "null argument"); }
+        EPK_CUDA(cudaSetDevice(db->device));
+        device_buffer<char> d_seq(len + 1);
+        device_buffer<uint32_t> d_pos(cap + 1), d_key(cap + 1), d_group(cap + 1);
+        device_buffer<long long> d_hit(cap + 1);
+        device_buffer<unsigned long long> d_n(1);
+        if (len) { EPK_CUDA(cudaMemcpy(d_seq.get(), seq, len, cudaMemcpyHostToDevice)); }
+        if (db->table_kind == TABLE_DIRECT)
+        {
+            kmers_kernel<TABLE_DIRECT><<<1, 32>>>(db->d, db->letters.get(), d_seq.get(), len, cap, d_pos.get(), d_key.get(),
+                                                  d_group.get(), d_hit.get(), d_n.get());
+        }
+        else
+        {
+            kmers_kernel<TABLE_HASH><<<1, 32>>>(db->d, db->letters.get(), d_seq.get(), len, cap, d_pos.get(), d_key.get(),
+                                                d_group.get(), d_hit.get(), d_n.get());
+        }
+        EPK_CUDA(cudaGetLastError());
+        unsigned long long n = 0;
+        EPK_CUDA(cudaMemcpy(&n, d_n.get(), 8, cudaMemcpyDeviceToHost));
+        const size_t m = static_cast<size_t>(std::min<uint64_t>(n, cap));
+        if (m)
+        {
+            EPK_CUDA(cudaMemcpy(pos, d_pos.get(), m * 4, cudaMemcpyDeviceToHost));
+            EPK_CUDA(cudaMemcpy(key, d_key.get(), m * 4, cudaMemcpyDeviceToHost));
+            EPK_CUDA(cudaMemcpy(group, d_group.get(), m * 4, cudaMemcpyDeviceToHost));
+            EPK_CUDA(cudaMemcpy(hit_len, d_hit.get(), m * 8, cudaMemcpyDeviceToHost));
+        }
+        *n_out = n;
+    });
+}

@@ -55,8 +55,6 @@ class FlatDB:
         assert len(self.offsets) == len(self.keys) + 1 and self.offsets[0] == 0
         assert len(self.entries) == int(self.offsets[-1])
         assert len(self.subtree_num_nodes) == self.n_nodes == len(self.subtree_total_length)
-        if len(self.entries):
-            assert int(self.entries["branch"].max()) < self.n_nodes
         assert self.kmer_size * self.bits_per_letter <= 32
 
 

@@ -1,0 +1,228 @@
+"""Host-side mirror of the reference's placer interface, on top of the C ABI.
+
+    reference (C++)                                            here
+    i2l::load(file, mu, omega, max_entries)  main.cpp:277      Database(flat_db, mu=..., omega=..., max_entries=...)
+    epik::placer(db, tree, keep_at_most, keep_factor, threads) Placer(db, keep_at_most, keep_factor)
+    placer.place(seq_records, threads) -> placed_collection    Placer.place(records) -> PlacedCollection
+      place.h:94-103, place.cpp:201-275                        Placer.place_packed(bytes, offsets) -> arrays
+
+All computing happens in libepik_b200.so (hand-written sm_100a kernels); this module only marshals
+numpy / torch buffers across the ABI. Nothing here falls back to the CPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+
+import numpy as np
+
+from . import capi
+from .flatdb import ENTRY_DTYPE, FlatDB
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def pack_sequences(seqs):
+    """list of bytes/str -> (uint8 array, uint64 offsets[n+1])."""
+    bs = [s.encode() if isinstance(s, str) else bytes(s) for s in seqs]
+    off = np.zeros(len(bs) + 1, dtype=np.uint64)
+    if bs:
+        off[1:] = np.cumsum([len(b) for b in bs], dtype=np.uint64)
+    data = np.frombuffer(b"".join(bs), dtype=np.uint8).copy() if bs else np.zeros(0, np.uint8)
+    return data, off
+
+
+class PinnedArray:
+    """numpy views over pinned host memory from epk_host_alloc (fast path of epk_place)."""
+
+    def __init__(self, shape, dtype):
+        self.dtype = np.dtype(dtype)
+        self.shape = tuple(np.atleast_1d(shape))
+        n = int(np.prod(self.shape)) * self.dtype.itemsize
+        self._p = capi.lib().epk_host_alloc(max(n, 1))
+        if not self._p:
+            raise MemoryError("epk_host_alloc(%d)" % n)
+        buf = (C.c_char * max(n, 1)).from_address(self._p)
+        self.array = np.frombuffer(buf, dtype=self.dtype, count=int(np.prod(self.shape))).reshape(self.shape)
+
+    def free(self):
+        if getattr(self, "_p", None):
+            self.array = None
+            capi.lib().epk_host_free(self._p)
+            self._p = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class Database:
+    """HBM-resident phylo-k-mer database (epk_db). `mu`, `omega`, `max_entries` are the load-filter
+    arguments of i2l::load (main.cpp:277); leave all three None to load everything."""
+
+    def __init__(self, db: FlatDB, mu: float | None = None, omega: float | None = None,
+                 max_entries: int | None = None, device: int = 0):
+        l = capi.lib()
+        db.validate()
+        self.flat = db
+        keys = np.ascontiguousarray(db.keys, np.uint32)
+        offsets = np.ascontiguousarray(db.offsets, np.uint64)
+        entries = np.ascontiguousarray(db.entries, ENTRY_DTYPE)
+        fv = None if db.filter_value is None else np.ascontiguousarray(db.filter_value, np.float32)
+        bl = np.ascontiguousarray(db.branch_length, np.float64)
+        sn = np.ascontiguousarray(db.subtree_num_nodes, np.uint64)
+        st = np.ascontiguousarray(db.subtree_total_length, np.float64)
+        desc = capi.DbDesc(int(db.alphabet), int(db.kmer_size), float(db.omega), len(keys), _ptr(keys), _ptr(offsets),
+                           _ptr(entries), _ptr(fv), len(bl), _ptr(bl), _ptr(sn), _ptr(st))
+        flt = None
+        if mu is not None or omega is not None or max_entries is not None:
+            flt = capi.LoadFilter(1.0 if mu is None else float(mu), float(db.omega if omega is None else omega),
+                                  capi.UINT64_MAX if max_entries is None else int(max_entries))
+        handle = C.c_void_p()
+        capi.check(l.epk_db_create(C.byref(desc), C.byref(flt) if flt is not None else None, int(device), C.byref(handle)))
+        self.handle = handle
+        self.device = int(device)
+        info = capi.DbInfo()
+        capi.check(l.epk_db_get_info(self.handle, C.byref(info)))
+        self.info = {name: getattr(info, name) for name, _ in capi.DbInfo._fields_}
+
+    def kmers(self, seq):
+        """(pos, key, group, hit_len) of one sequence, computed on the device (epk_kmers)."""
+        b = seq.encode() if isinstance(seq, str) else bytes(seq)
+        cap = max(1, len(b) * 20)
+        pos, key, group = (np.zeros(cap, np.uint32) for _ in range(3))
+        hit = np.zeros(cap, np.int64)
+        n = C.c_uint64(0)
+        capi.check(capi.lib().epk_kmers(self.handle, b, len(b), cap, _ptr(pos), _ptr(key), _ptr(group), _ptr(hit), C.byref(n)))
+        assert n.value <= cap
+        return pos[:n.value], key[:n.value], group[:n.value], hit[:n.value]
+
+    def close(self):
+        if getattr(self, "handle", None):
+            capi.lib().epk_db_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+@dataclass
+class Placement:
+    """epik::placement (place.h:45-56)."""
+    branch_id: int
+    score: float
+    weight_ratio: float
+    count: int
+    distal_length: float
+    pendant_length: float
+
+
+@dataclass
+class PlacedSequence:
+    """epik::placed_sequence (place.h:59-68)."""
+    sequence: bytes
+    placements: list
+
+
+@dataclass
+class PlacedCollection:
+    """epik::placed_collection (place.h:72-75): sequence -> headers of the records that carry it,
+    and one PlacedSequence per unique sequence."""
+    sequence_map: dict = field(default_factory=dict)
+    placed_seqs: list = field(default_factory=list)
+
+
+class Placer:
+    """epik::placer (place.h:81-140)."""
+
+    def __init__(self, db: Database, keep_at_most: int = 7, keep_factor: float = 0.01, variant: int = 0,
+                 chunk_reads: int = 0):
+        self.db = db
+        self.keep_at_most = int(keep_at_most)
+        self.keep_factor = float(keep_factor)
+        opts = capi.PlacerOpts(int(variant), int(chunk_reads))
+        handle = C.c_void_p()
+        capi.check(capi.lib().epk_placer_create(db.handle, self.keep_at_most, self.keep_factor, C.byref(opts), C.byref(handle)))
+        self.handle = handle
+
+    def close(self):
+        if getattr(self, "handle", None):
+            capi.lib().epk_placer_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ------------------------------------------------------------------ array interface -----
+    def alloc_result(self, n: int, pinned: bool = False, lengths: bool = True):
+        K = self.keep_at_most
+        spec = [("n_place", (n,), np.uint32), ("branch", (n, K), np.uint32), ("score", (n, K), np.float32),
+                ("lwr", (n, K), np.float64), ("count", (n, K), np.uint32)]
+        if lengths:
+            spec += [("distal", (n, K), np.float64), ("pendant", (n, K), np.float64)]
+        if pinned:
+            keep = {name: PinnedArray(shape, dt) for name, shape, dt in spec}
+            out = {name: pa.array for name, pa in keep.items()}
+            out["_pinned"] = keep
+            return out
+        return {name: np.zeros(shape, dt) for name, shape, dt in spec}
+
+    def place_packed(self, data, offsets, out=None):
+        """epk_place over packed sequences in HOST memory. Returns the arrays of epk_result."""
+        data = np.ascontiguousarray(data, np.uint8) if not isinstance(data, np.ndarray) or data.dtype != np.uint8 else data
+        offsets = np.ascontiguousarray(offsets, np.uint64) if not isinstance(offsets, np.ndarray) or offsets.dtype != np.uint64 else offsets
+        n = len(offsets) - 1
+        if out is None:
+            out = self.alloc_result(n)
+        res = capi.Result(_ptr(out["n_place"]), _ptr(out["branch"]), _ptr(out["score"]), _ptr(out["lwr"]),
+                          _ptr(out["count"]), _ptr(out.get("distal")), _ptr(out.get("pendant")))
+        dptr = _ptr(data) if data.size else None
+        capi.check(capi.lib().epk_place(self.handle, dptr, _ptr(offsets), n, C.byref(res)))
+        return out
+
+    def place_device(self, d_seq, d_off, n: int, d_out: dict, stream=None):
+        """epk_place_device: everything already in HBM. Arguments are objects with .data_ptr()
+        (torch tensors); asynchronous on `stream` (a torch.cuda.Stream or None)."""
+        res = capi.Result(d_out["n_place"].data_ptr(), d_out["branch"].data_ptr(), d_out["score"].data_ptr(),
+                          d_out["lwr"].data_ptr(), d_out["count"].data_ptr(), None, None)
+        s = None if stream is None else C.c_void_p(stream.cuda_stream)
+        capi.check(capi.lib().epk_place_device(self.handle, d_seq.data_ptr(), d_off.data_ptr(), int(n), C.byref(res), s))
+
+    def counters(self) -> dict:
+        c = capi.Counters()
+        capi.check(capi.lib().epk_placer_counters(self.handle, C.byref(c)))
+        return {name: getattr(c, name) for name, _ in capi.Counters._fields_}
+
+    # ------------------------------------------------------- the reference's interface -----
+    def place(self, records, batch_size: int = 0) -> PlacedCollection:
+        """placer::place (place.cpp:201-275) for a list of (header, sequence) records: identical
+        sequences are placed once and keep the list of their headers (place.cpp:73-81,207)."""
+        headers = [h for h, _ in records]
+        seqs = [s.encode() if isinstance(s, str) else bytes(s) for _, s in records]
+        data, off = pack_sequences(seqs)
+        n = len(seqs)
+        out = self.place_packed(data, off)
+        rep = np.zeros(n, np.uint32)
+        if n:
+            capi.check(capi.lib().epk_group_batch(_ptr(data) if data.size else None, _ptr(off), n, _ptr(rep)))
+        result = PlacedCollection()
+        for i in range(n):
+            result.sequence_map.setdefault(seqs[i], []).append(headers[i])
+            if rep[i] != i:
+                continue
+            m = int(out["n_place"][i])
+            result.placed_seqs.append(PlacedSequence(seqs[i], [
+                Placement(int(out["branch"][i, j]), float(out["score"][i, j]), float(out["lwr"][i, j]),
+                          int(out["count"][i, j]), float(out["distal"][i, j]), float(out["pendant"][i, j]))
+                for j in range(m)]))
+        return result

@@ -1,0 +1,185 @@
+/* epik_b200 — C ABI of the B200 (sm_100a) placement hot path of EPIK.
+ *
+ * EPIK has no plugin/FFI interface of its own: the seam this library sits behind is the C++ class
+ * epik::placer (reference epik/include/epik/place.h:81-140) and the i2l::phylo_kmer_db it reads
+ * (call sites epik/src/epik/place.cpp:87,113-114,294,300,311; epik/src/epik/main.cpp:277-295).
+ * Every entry point below names the reference interface it stands in for. The ABI is plain C:
+ * pointers and sizes only, no C++ types, no exceptions, no torch types. Errors come back as an
+ * epk_status plus a thread-local message (epk_last_error), the way main.cpp:384-388 turns a
+ * std::runtime_error into "Error: ..." and a non-zero exit code.
+ *
+ * There is no CPU fallback: every call that computes needs a CUDA device and fails with
+ * EPK_E_CUDA when there is none.
+ */
+#ifndef EPIK_B200_H
+#define EPIK_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define EPK_ABI_VERSION 1
+
+typedef enum epk_status
+{
+    EPK_OK = 0,
+    EPK_E_INVALID = 1,      /* bad argument / malformed database description            */
+    EPK_E_CUDA = 2,         /* CUDA runtime error or no device                          */
+    EPK_E_NOMEM = 3,        /* host or device allocation failed                         */
+    EPK_E_SHORT_SEQ = 4,    /* a sequence shorter than k-1 letters: the reference dies  */
+                            /* on it (size_t wrap -> vector::reserve, place.cpp:291)    */
+    EPK_E_UNSUPPORTED = 5   /* shape outside what the kernels were built for            */
+} epk_status;
+
+enum { EPK_DNA = 0, EPK_AA = 1 };
+
+/* One posting: i2l::pkdb_value {branch, score} (place.cpp:358 structured binding;
+ * main.cpp:257 uses its sizeof as the --max-ram accounting unit, 8 bytes). */
+typedef struct epk_entry
+{
+    uint32_t branch; /* post-order node id */
+    float score;     /* log10 probability  */
+} epk_entry;
+
+/* What i2l::phylo_kmer_db holds after i2l::load (main.cpp:277), flattened to CSR:
+ * keys[i] owns entries[offsets[i] .. offsets[i+1]). All pointers are HOST memory and are only
+ * read during epk_db_create. */
+typedef struct epk_db_desc
+{
+    uint32_t alphabet;                  /* EPK_DNA (2 bits/letter) or EPK_AA (5 bits/letter)      */
+    uint32_t kmer_size;                 /* db.kmer_size()                                          */
+    float omega;                        /* db.omega()                                              */
+    uint64_t n_keys;
+    const uint32_t* keys;               /* [n_keys] unique k-mer codes (phylo_kmer::key_type)      */
+    const uint64_t* offsets;            /* [n_keys + 1]                                            */
+    const epk_entry* entries;           /* [offsets[n_keys]]; branches distinct within one list    */
+    const float* filter_value;          /* [n_keys] or NULL; larger = more informative. Needed     */
+                                        /* only when a load filter with mu < 1 / max_entries is    */
+                                        /* given (the order i2l stores k-mers in on disk)          */
+    uint32_t n_nodes;                   /* tree.get_node_count() (place.cpp:99,166)                */
+    const double* branch_length;        /* [n_nodes] get_by_postorder_id(i)->get_branch_length()   */
+    const uint64_t* subtree_num_nodes;  /* [n_nodes] db.tree_index()[i] (place.cpp:113)            */
+    const double* subtree_total_length; /* [n_nodes] db.tree_index()[i] (place.cpp:114)            */
+} epk_db_desc;
+
+/* The three filter arguments of i2l::load(file, mu, omega, max_entries) (main.cpp:277; --mu,
+ * --omega, --max-ram of epik.py:40-55 / main.cpp:215-218,252-265). */
+typedef struct epk_load_filter
+{
+    double mu;            /* keep the mu most informative fraction of the entries, in [0, 1]      */
+    float omega;          /* user omega: entries scoring below log10((omega/|alphabet|)^k) go    */
+    uint64_t max_entries; /* --max-ram / sizeof(pkdb_value); UINT64_MAX = unlimited              */
+} epk_load_filter;
+
+typedef struct epk_db_info
+{
+    uint32_t alphabet, kmer_size, n_nodes, table_kind; /* table_kind: 0 direct-address, 1 hash    */
+    float omega;                 /* omega in force after the load filter (db.omega())             */
+    float threshold;             /* i2l::score_threshold(omega, k)        (place.cpp:87)          */
+    float log10_threshold;       /* std::log10(threshold)                 (place.cpp:88)          */
+    uint64_t n_keys_loaded;
+    uint64_t n_entries_loaded;   /* db.get_num_entries_loaded()           (main.cpp:290)          */
+    uint64_t n_entries_total;    /* db.get_num_entries_total()            (main.cpp:291)          */
+    uint64_t table_slots;        /* slots of the HBM key table                                    */
+    uint64_t device_bytes;       /* HBM held by this database                                     */
+} epk_db_info;
+
+typedef struct epk_db epk_db;
+typedef struct epk_placer epk_placer;
+
+/* Options of a placer beyond the reference's constructor arguments. Zero-initialise for defaults. */
+typedef struct epk_placer_opts
+{
+    uint32_t variant;        /* 0 = default; 1 = register-staged gathers; 2 = TMA bulk-copy ring  */
+    uint32_t chunk_reads;    /* reads per pipelined H2D/kernel/D2H chunk of epk_place; 0 = auto   */
+    uint32_t reserved[6];
+} epk_placer_opts;
+
+/* Results of placing n sequences, row-major [n][keep_at_most]; row i is filled up to n_place[i],
+ * best placement first (place.cpp:153-156 order). These are the fields of epik::placement
+ * (place.h:45-56). distal/pendant may be NULL (they are table look-ups by branch,
+ * place.cpp:98-125,434-437). For epk_place all pointers are HOST memory (pinned is faster:
+ * epk_host_alloc); for epk_place_device they are DEVICE memory and distal/pendant must be NULL. */
+typedef struct epk_result
+{
+    uint32_t* n_place; /* [n]                                                                      */
+    uint32_t* branch;  /* [n*K] placement.branch_id                                                */
+    float* score;      /* [n*K] placement.score        (jplace "likelihood")                       */
+    double* lwr;       /* [n*K] placement.weight_ratio (jplace "like_weight_ratio")                */
+    uint32_t* count;   /* [n*K] placement.count                                                    */
+    double* distal;    /* [n*K] or NULL                                                            */
+    double* pendant;   /* [n*K] or NULL                                                            */
+} epk_result;
+
+/* ABI version of the loaded library (EPK_ABI_VERSION it was built with). */
+uint32_t epk_abi_version(void);
+
+/* Message of the last failing call on this thread ("" if none). */
+const char* epk_last_error(void);
+
+/* Number of CUDA devices visible (0 when there is none or the driver is missing). */
+int epk_device_count(void);
+
+/* Stands in for i2l::load(db_file, mu, omega, max_entries) (main.cpp:277) once the file has been
+ * parsed: applies the load filter (NULL = keep everything) ON THE DEVICE, flattens the map into an
+ * HBM-resident key table (direct-address when alphabet_bits*k <= 26, open addressing otherwise)
+ * plus 16-byte aligned (branch, score) posting lists, and precomputes the distal / pendant tables
+ * of placer::placer (place.cpp:98-125). `device` is the CUDA ordinal. */
+epk_status epk_db_create(const epk_db_desc* desc, const epk_load_filter* filter, int device, epk_db** out);
+epk_status epk_db_get_info(const epk_db* db, epk_db_info* info);
+void epk_db_destroy(epk_db* db);
+
+/* epik::placer::placer(db, tree, keep_at_most, keep_factor, num_threads) (place.h:94-95,
+ * place.cpp:83-126). The tree comes with the database description; there are no host threads to
+ * size scratch for. The database must outlive the placer (place.h:91-93). */
+epk_status epk_placer_create(const epk_db* db, uint64_t keep_at_most, double keep_factor,
+                             const epk_placer_opts* opts, epk_placer** out);
+void epk_placer_destroy(epk_placer* placer);
+
+/* epik::placer::place(seq_records, num_threads) (place.h:103, place.cpp:201-275) for n sequences
+ * given as packed bytes: sequence i = seq[seq_off[i] .. seq_off[i+1]). HOST buffers; the call
+ * streams them to the device in chunks (pinned staging, copies overlapped with the kernels) and
+ * returns when `out` is complete. Results are per INPUT record: identical sequences get identical
+ * rows, which is what the reference's per-batch grouping (place.cpp:207) amounts to; use
+ * epk_group_batch for the grouping itself. */
+epk_status epk_place(epk_placer* placer, const char* seq, const uint64_t* seq_off, uint32_t n,
+                     const epk_result* out);
+
+/* Same work with everything already resident in HBM: DEVICE pointers, asynchronous on `stream`
+ * (a cudaStream_t, NULL = the legacy default stream). */
+epk_status epk_place_device(epk_placer* placer, const char* d_seq, const uint64_t* d_seq_off, uint32_t n,
+                            const epk_result* d_out, void* stream);
+
+/* group_by_sequence_content (place.cpp:73-81) for one batch: group_rep[i] = index of the first
+ * record of [0, n) with the same sequence. HOST buffers. */
+epk_status epk_group_batch(const char* seq, const uint64_t* seq_off, uint32_t n, uint32_t* group_rep);
+
+/* The k-mer stream of one sequence in the order query_kmers (place.cpp:278-316) consumes it, one
+ * record per (window, resolved key): pos = window start, key = code, group = number of keys of
+ * the window (1 = unambiguous), hit_len = posting-list length or -1 when the key is absent.
+ * Computed ON THE DEVICE by the same encode + probe code the placement kernel runs. Returns the
+ * number of records through *n_out (only `cap` are written). HOST buffers. */
+epk_status epk_kmers(const epk_db* db, const char* seq, uint64_t len, uint64_t cap,
+                     uint32_t* pos, uint32_t* key, uint32_t* group, int64_t* hit_len, uint64_t* n_out);
+
+/* Work counters of the last epk_place / epk_place_device call on this placer (for roofline
+ * arithmetic): windows looked up, hits, posting entries gathered, kernels launched. */
+typedef struct epk_counters
+{
+    uint64_t n_reads, n_windows, n_hits, n_entries, n_launches;
+    uint64_t n_short; /* sequences shorter than k - 1 letters (left with n_place = 0) */
+} epk_counters;
+epk_status epk_placer_counters(epk_placer* placer, epk_counters* out);
+
+/* Pinned host memory for the buffers of epk_place. */
+void* epk_host_alloc(size_t bytes);
+void epk_host_free(void* p);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif /* EPIK_B200_H */

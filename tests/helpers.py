@@ -1,0 +1,85 @@
+"""Shared pieces of the test-suite: the KAT-1 toy database, golden fixtures,
+and the comparison rules (bit-exact integers, 1e-5 relative scores, tie-aware placement sets)."""
+from __future__ import annotations
+
+import json
+import os
+
+import numpy as np
+
+from epik_b200 import flatdb, synth
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+DNA_CODE = {"A": 0, "C": 1, "G": 2, "T": 3}
+
+
+def encode_dna(kmer: str) -> int:
+    key = 0
+    for ch in kmer:
+        key = (key << 2) | DNA_CODE[ch]
+    return key
+
+
+def kat1_db() -> flatdb.FlatDB:
+    """The toy database of KAT-1: k = 3, omega = 1.5, 10 nodes."""
+    kmers = {
+        "ACG": [(2, -0.5), (3, -1.0)],
+        "CGT": [(2, -0.25), (5, -2.0)],
+        "AAA": [(7, -0.1)],
+        "GAA": [(7, -0.2), (8, -0.3)],
+    }
+    n = 10
+    return flatdb.from_dict(flatdb.DNA, 3, 1.5, kmers, [0.1 * (i + 1) for i in range(n)], [i + 1 for i in range(n)],
+                            [0.5 * i for i in range(n)], encode=encode_dna)
+
+
+KAT1_SEQS = ["ACGT", "TTTTT", "RAA", "ACGT", "AC"]
+
+
+def load_json(name: str):
+    with open(os.path.join(GOLDEN, name)) as f:
+        return json.load(f)
+
+
+def golden_case_db(case: dict) -> flatdb.FlatDB:
+    """Rebuilds the synthetic database a golden case was generated from (pure function of the seed)."""
+    return synth.make_db(case["alphabet"], case["k"], case["n_leaves"], case["p_occ"], case["m"],
+                         omega=case["omega"], seed=case["seed"])
+
+
+def assert_same_placements(got: dict, want: dict, score_rtol: float = 1e-5, lwr_rtol: float = 1e-9,
+                           lengths: bool = True, what: str = ""):
+    """Parity rule of BASELINE.json: n_place and counts identical, branches identical except inside
+    groups of exactly tied scores (documented tie rule: lower branch id first on the GPU, libstdc++
+    partial_sort order in the reference), scores within 1e-5 relative, LWR within lwr_rtol."""
+    n_place = np.asarray(want["n_place"])
+    assert np.array_equal(np.asarray(got["n_place"]), n_place), what + " n_place"
+    K = want["branch"].shape[1]
+    valid = np.arange(K)[None, :] < n_place[:, None]
+    gs, ws = np.asarray(got["score"]), np.asarray(want["score"])
+    np.testing.assert_allclose(gs[valid], ws[valid], rtol=score_rtol, atol=0, err_msg=what + " score")
+    np.testing.assert_allclose(np.asarray(got["lwr"])[valid], np.asarray(want["lwr"])[valid], rtol=lwr_rtol, atol=0,
+                               err_msg=what + " lwr")
+    gb, wb = np.asarray(got["branch"]), np.asarray(want["branch"])
+    same = (gb == wb) | ~valid
+    for i in np.nonzero(~same.all(axis=1))[0]:
+        # rows that differ may only differ by a permutation inside runs of equal scores
+        m = int(n_place[i])
+        assert np.array_equal(ws[i, :m], gs[i, :m]) or np.allclose(ws[i, :m], gs[i, :m], rtol=score_rtol), what
+        j = 0
+        while j < m:
+            e = j
+            while e + 1 < m and ws[i, e + 1] == ws[i, j]:
+                e += 1
+            if e + 1 == m and m == K:
+                # the run touches the cut: members outside the kept set may differ
+                assert len(set(gb[i, j:e + 1])) == e + 1 - j, what
+            else:
+                assert sorted(gb[i, j:e + 1]) == sorted(wb[i, j:e + 1]), "%s row %d: branches differ beyond ties" % (what, i)
+            j = e + 1
+    cnt_ok = (np.asarray(got["count"]).astype(np.uint64) == np.asarray(want["count"]).astype(np.uint64)) | ~valid | ~(gb == wb)
+    assert cnt_ok.all(), what + " count"
+    if lengths and "distal" in got and "distal" in want:
+        ok = (gb == wb) & valid
+        np.testing.assert_allclose(np.asarray(got["distal"])[ok], np.asarray(want["distal"])[ok], rtol=1e-15, err_msg=what)
+        np.testing.assert_allclose(np.asarray(got["pendant"])[ok], np.asarray(want["pendant"])[ok], rtol=1e-15, err_msg=what)

@@ -1,0 +1,234 @@
+"""GPU parity tests: the CUDA path, called through the C ABI, against the CPU oracle and the
+committed outputs of the reference (tests/golden/). Integer work (k-mer codes, hits, counts,
+branch choices) must be bit-exact; scores within 1e-5 relative (they are in fact bit-identical for
+the one-warp-per-query kernel, which is asserted separately); LWR within 1e-9 relative (FP64 sum in
+a different order + CUDA's exp10 vs glibc's pow)."""
+import numpy as np
+import pytest
+
+from epik_b200 import capi, synth
+from epik_b200.placer import Database, Placer, pack_sequences
+from oracle import oracle as O
+from tests import helpers
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _build(built):
+    return built
+
+
+def best_oracle(db, keep_at_most=7, keep_factor=0.01, threads=4):
+    kind = "reference" if O.available("reference", int(db.alphabet)) else "port"
+    return O.Oracle(db, keep_at_most, keep_factor, threads, kind=kind), kind
+
+
+def test_extension_is_loaded_and_sees_the_gpu():
+    assert capi.lib().epk_device_count() >= 1
+
+
+def test_kat1_known_answers():
+    """SURVEY.md Appendix D values, straight from the kernel."""
+    db = Database(helpers.kat1_db())
+    assert db.info["threshold"] == np.float32(0.052734375)
+    p = Placer(db)
+    r = p.place_packed(*pack_sequences(helpers.KAT1_SEQS))
+    for i in (0, 3):
+        assert r["n_place"][i] == 3 and list(r["branch"][i, :3]) == [2, 3, 5]
+        np.testing.assert_allclose(r["score"][i, :3], [-0.25, -0.75930208, -1.09263539], rtol=1e-7)
+        np.testing.assert_allclose(r["lwr"][i, :3], [0.31214008, 0.0966156451, 0.044845012], rtol=1e-7)
+        assert list(r["count"][i, :3]) == [2, 1, 1]
+        np.testing.assert_allclose(r["distal"][i, 0], 0.15)
+        np.testing.assert_allclose(r["pendant"][i, 0], 0.483333, rtol=1e-5)
+    assert r["n_place"][1] == 7 and list(r["branch"][1]) == [3, 4, 1, 0, 5, 2, 6]
+    np.testing.assert_allclose(r["score"][1], -1.27790618, rtol=1e-7)
+    np.testing.assert_allclose(r["lwr"][1], 0.1, rtol=1e-12)
+    assert not r["count"][1].any() and not r["distal"][1].any() and not r["pendant"][1].any()
+    assert r["n_place"][2] == 2 and list(r["branch"][2, :2]) == [7, 8]
+    np.testing.assert_allclose(r["score"][2, :2], [0.0999774411, 0.0674062148], rtol=1e-6)
+    np.testing.assert_allclose(r["lwr"][2, :2], [0.231972609, 0.215211503], rtol=1e-7)
+    assert r["n_place"][4] == 7 and np.all(r["score"][4] == 0) and np.all(np.signbit(r["score"][4]))
+    g = np.load(helpers.GOLDEN + "/reference_outputs.npz")
+    want = {k: g["kat1/" + k] for k in ("n_place", "branch", "score", "lwr", "count", "distal", "pendant")}
+    helpers.assert_same_placements(r, want, what="kat1 golden")
+    assert np.array_equal(r["score"], want["score"])
+
+
+@pytest.mark.parametrize("case", helpers.load_json("cases.json"), ids=lambda c: c["name"])
+def test_golden_cases(case):
+    """Committed outputs of the reference's own place.cpp."""
+    g = np.load(helpers.GOLDEN + "/reference_outputs.npz")
+    flat = helpers.golden_case_db(case)
+    data, off = synth.make_reads(case["alphabet"], case["n_reads"], case["read_len"], seed=case["seed"] + 1000,
+                                 amb_rate=case["amb_rate"])
+    db = Database(flat)
+    assert [db.info["threshold"], db.info["log10_threshold"]] == [np.float32(x) for x in case["thresholds"]]
+    assert db.info["n_entries_loaded"] == case["n_entries"] and db.info["n_keys_loaded"] == case["n_keys"]
+    p = Placer(db, case["keep_at_most"], case["keep_factor"])
+    r = p.place_packed(data, off)
+    name = case["name"]
+    want = {k: g[name + "/" + k] for k in ("n_place", "branch", "score", "lwr", "count", "distal", "pendant")}
+    helpers.assert_same_placements(r, want, what=name)
+    # stronger than the contract: window-ordered accumulation makes the float scores bit-identical
+    K = case["keep_at_most"]
+    valid = np.arange(K)[None, :] < want["n_place"][:, None]
+    assert np.array_equal(r["score"][valid], want["score"][valid]), "scores are not bit-identical"
+    # k-mer codes and hits: bit-exact
+    at = 0
+    for i, n in enumerate(g[name + "/kmers_len"]):
+        seq = bytes(data[int(off[i]):int(off[i + 1])])
+        pos, key, group, hit = db.kmers(seq)
+        want_k = g[name + "/kmers"][:, at:at + n]
+        at += n
+        assert np.array_equal(np.stack([pos, key, group, hit]).astype(np.int64), want_k), i
+
+
+@pytest.mark.parametrize("alphabet,k,n_leaves,p_occ,m,read_len,amb", [
+    (0, 10, 2500, 0.6, 32.0, 150, 0.0),     # C2-shaped (full-size tree, full database)
+    (0, 10, 652, 0.6, 24.0, 1500, 0.001),   # C1': D652-shaped, long reads (several window chunks)
+    (0, 12, 1200, 0.05, 20.0, 150, 0.005),  # k = 12: 24-bit direct table
+    (0, 14, 300, 0.0002, 10.0, 200, 0.01),  # k = 14: hashed table for DNA
+    (1, 6, 1000, 0.002, 16.0, 100, 0.01),   # C4-shaped: amino acids, hashed table
+    (1, 4, 200, 0.3, 10.0, 60, 0.03),       # amino acids, direct table
+])
+def test_oracle_parity_on_synthetic_shapes(alphabet, k, n_leaves, p_occ, m, read_len, amb):
+    flat = synth.make_db(alphabet, k, n_leaves, p_occ, m, seed=1000 + k)
+    n = 3000 if read_len <= 200 else 300
+    data, off = synth.make_reads(alphabet, n, read_len, seed=77, amb_rate=amb)
+    db = Database(flat)
+    p = Placer(db)
+    got = p.place_packed(data, off)
+    oracle, kind = best_oracle(flat)
+    want = oracle.place_packed(data, off, threads=4)
+    helpers.assert_same_placements(got, want, what="%s k=%d" % (kind, k))
+    valid = np.arange(7)[None, :] < want["n_place"][:, None]
+    assert np.array_equal(got["score"][valid], want["score"][valid])
+    c = p.counters()
+    assert c["n_reads"] == n and c["n_windows"] == n * (read_len - k + 1) and c["n_short"] == 0
+    # hits / entries of the exact windows of a few reads, from the oracle's k-mer stream
+    for i in range(5):
+        seq = bytes(data[int(off[i]):int(off[i + 1])])
+        a, b = db.kmers(seq), oracle.kmers(seq)
+        for x, y in zip(a, b):
+            assert np.array_equal(x, y)
+
+
+def test_ragged_empty_and_edge_inputs():
+    flat = synth.make_db(0, 6, 60, 0.5, 6.0, seed=5)
+    db = Database(flat)
+    p = Placer(db)
+    oracle, kind = best_oracle(flat, threads=1)
+    # no sequences at all
+    r = p.place_packed(np.zeros(0, np.uint8), np.zeros(1, np.uint64))
+    assert r["n_place"].shape == (0,)
+    # ragged lengths from k-1 up, all-gap, all-N, lower case, duplicates
+    rng = np.random.default_rng(3)
+    seqs = ["ACGTA", "ACGTAC", "------", "NNNNNNNN", "acgtacgtacgt", "ACGTACGTACGT", "ACGTAC",
+            "A" * 300, "ACGT" * 200, "ACGU" * 10, "ACG-TACGTAC..ACGTACGNACGTACRYACGT", "*" * 20]
+    seqs += ["".join(rng.choice(list("ACGT"), size=int(L))) for L in rng.integers(5, 700, size=200)]
+    got = p.place(list(enumerate(seqs)))
+    want = oracle.place(seqs, threads=1)
+    arr = p.place_packed(*pack_sequences(seqs))
+    helpers.assert_same_placements(arr, want, what="ragged " + kind)
+    # the reference-shaped result: one placed sequence per unique sequence, headers grouped
+    assert len(got.placed_seqs) == len(set(seqs))
+    assert got.sequence_map[b"ACGTAC"] == [1, 6]
+    # a sequence shorter than k - 1 letters: the reference aborts; the ABI reports it
+    with pytest.raises(capi.EpkError) as e:
+        p.place_packed(*pack_sequences(["ACGTACGT", "ACG"]))
+    assert e.value.status == capi.EPK_E_SHORT_SEQ
+    # the placer is still usable afterwards
+    arr = p.place_packed(*pack_sequences(seqs[:5]))
+    helpers.assert_same_placements(arr, oracle.place(seqs[:5]), what="after error")
+
+
+@pytest.mark.parametrize("keep_at_most,keep_factor", [(1, 0.01), (3, 0.5), (7, 0.0), (8, 1.0), (12, 0.01), (32, 0.001)])
+def test_keep_at_most_and_keep_factor(keep_at_most, keep_factor):
+    flat = synth.make_db(0, 7, 100, 0.6, 8.0, seed=21)
+    data, off = synth.make_reads(0, 500, 90, seed=22, amb_rate=0.01)
+    got = Placer(Database(flat), keep_at_most, keep_factor).place_packed(data, off)
+    oracle, kind = best_oracle(flat, keep_at_most, keep_factor, threads=2)
+    helpers.assert_same_placements(got, oracle.place_packed(data, off, threads=2), what=kind)
+
+
+def test_long_reads_underflow_the_likelihood_mass():
+    """10^score underflows FP64 for long queries: score_sum == 0 -> every LWR 0, nothing filtered
+    (place.cpp:243-251)."""
+    flat = synth.make_db(0, 10, 200, 0.3, 10.0, seed=31)
+    data, off = synth.make_reads(0, 20, 6000, seed=32)
+    got = Placer(Database(flat)).place_packed(data, off)
+    oracle, kind = best_oracle(flat, threads=2)
+    want = oracle.place_packed(data, off, threads=2)
+    assert np.all(want["lwr"] == 0) and np.all(want["n_place"] == 7)
+    helpers.assert_same_placements(got, want, what=kind)
+    assert np.all(got["lwr"] == 0)
+
+
+def test_pinned_and_pageable_host_buffers_and_chunking_agree():
+    flat = synth.make_db(0, 8, 150, 0.6, 10.0, seed=41)
+    data, off = synth.make_reads(0, 5000, 100, seed=42)
+    db = Database(flat)
+    base = Placer(db).place_packed(data, off)
+    # small chunks: many launches, three slots in flight
+    p = Placer(db, chunk_reads=257)
+    r = p.place_packed(data, off)
+    assert p.counters()["n_launches"] == 2 * ((5000 + 256) // 257)
+    # pinned in/out
+    from epik_b200.placer import PinnedArray
+    pd, po = PinnedArray(data.shape, np.uint8), PinnedArray(off.shape, np.uint64)
+    pd.array[:] = data
+    po.array[:] = off
+    out = p.alloc_result(5000, pinned=True)
+    r2 = p.place_packed(pd.array, po.array, out=out)
+    for k in ("n_place", "branch", "score", "lwr", "count", "distal", "pendant"):
+        assert np.array_equal(base[k], r[k]), k
+        assert np.array_equal(base[k], r2[k]), k
+
+
+def test_device_resident_call_matches_host_call():
+    import torch
+    flat = synth.make_db(0, 8, 150, 0.6, 10.0, seed=41)
+    data, off = synth.make_reads(0, 4000, 100, seed=43)
+    p = Placer(Database(flat))
+    base = p.place_packed(data, off)
+    dev = torch.device("cuda:0")
+    d_seq = torch.from_numpy(data).to(dev)
+    d_off = torch.from_numpy(off.view(np.int64)).to(dev)
+    K = 7
+    d_out = {"n_place": torch.zeros(4000, dtype=torch.int32, device=dev),
+             "branch": torch.zeros(4000 * K, dtype=torch.int32, device=dev),
+             "score": torch.zeros(4000 * K, dtype=torch.float32, device=dev),
+             "lwr": torch.zeros(4000 * K, dtype=torch.float64, device=dev),
+             "count": torch.zeros(4000 * K, dtype=torch.int32, device=dev)}
+    stream = torch.cuda.Stream()
+    with torch.cuda.stream(stream):
+        p.place_device(d_seq, d_off, 4000, d_out, stream=stream)
+    stream.synchronize()
+    assert np.array_equal(d_out["n_place"].cpu().numpy().view(np.uint32), base["n_place"])
+    assert np.array_equal(d_out["branch"].cpu().numpy().view(np.uint32).reshape(-1, K), base["branch"])
+    assert np.array_equal(d_out["score"].cpu().numpy().reshape(-1, K), base["score"])
+    assert np.array_equal(d_out["lwr"].cpu().numpy().reshape(-1, K), base["lwr"])
+    c = p.counters()
+    assert c["n_reads"] == 4000 and c["n_launches"] == 2
+
+
+def test_database_validation_errors():
+    flat = helpers.kat1_db()
+    bad = helpers.kat1_db()
+    bad.entries["branch"][1] = bad.entries["branch"][0]  # same branch twice in one list
+    with pytest.raises(capi.EpkError) as e:
+        Database(bad)
+    assert e.value.status == capi.EPK_E_INVALID
+    bad = helpers.kat1_db()
+    bad.entries["branch"][0] = 10  # >= n_nodes
+    with pytest.raises(capi.EpkError):
+        Database(bad)
+    bad = helpers.kat1_db()
+    bad.keys[1] = bad.keys[0]
+    with pytest.raises(capi.EpkError):
+        Database(bad)
+    with pytest.raises(capi.EpkError):
+        Placer(Database(flat), keep_at_most=33)
+    with pytest.raises(capi.EpkError):
+        Database(flat, mu=1.5)  # check_mu, main.cpp:196-202
