@@ -197,11 +197,10 @@ __global__ void validate_lists_kernel(const uint2* postings, const uint64_t* new
     {
         const uint64_t n = new_len[i];
         const uint2* list = postings + new_off[i];
-        bool bad = false;
         for (uint64_t j = lane; j < n; j += 32)
         {
             const uint32_t b = list[j].x;
-            if (b >= n_nodes) { atomicOr(status, BUILD_BAD_BRANCH); bad = true; continue; }
+            if (b >= n_nodes) { atomicOr(status, BUILD_BAD_BRANCH); continue; }
             const uint32_t bit = 1u << (b & 31u);
             if (atomicOr(bitmap + (b >> 5), bit) & bit) { atomicOr(status, BUILD_DUPLICATE_BRANCH); }
         }
@@ -211,7 +210,6 @@ __global__ void validate_lists_kernel(const uint2* postings, const uint64_t* new
             const uint32_t b = list[j].x;
             if (b < n_nodes) { bitmap[b >> 5] = 0; }
         }
-        (void)bad;
         __syncwarp();
     }
 }

@@ -100,6 +100,7 @@ using namespace epk;
 struct epk_placer
 {
     const epk_db* db = nullptr;
+    int device = 0; // copy: the destructor must not touch the database (it may already be gone)
     uint32_t keep_at_most = 0;
     double keep_factor = 0.0;
     uint32_t variant = 0;
@@ -150,6 +151,10 @@ namespace
         p.fake_order = pl.fake_order.get();
         p.counters = counters;
         EPK_CUDA(cudaMemsetAsync(counters, 0, CTR_COUNT * sizeof(unsigned long long), stream));
+        {
+            const cudaError_t stale = cudaGetLastError();
+            if (stale != cudaSuccess) { throw error(EPK_E_CUDA, std::string("stale CUDA error before launch: ") + cudaGetErrorString(stale)); }
+        }
         if (n)
         {
             const unsigned grid = static_cast<unsigned>(std::min<uint64_t>(pl.n_sms, (n + pl.warps_per_cta - 1) / pl.warps_per_cta));
@@ -253,6 +258,7 @@ extern "C" epk_status epk_placer_create(const epk_db* db, uint64_t keep_at_most,
         EPK_CUDA(cudaSetDevice(db->device));
         auto pl = std::make_unique<epk_placer>();
         pl->db = db;
+        pl->device = db->device;
         pl->keep_at_most = static_cast<uint32_t>(keep_at_most);
         pl->keep_factor = keep_factor;
         pl->variant = opts ? opts->variant : 0;
@@ -298,7 +304,7 @@ extern "C" epk_status epk_placer_create(const epk_db* db, uint64_t keep_at_most,
 extern "C" void epk_placer_destroy(epk_placer* pl)
 {
     if (!pl) { return; }
-    cudaSetDevice(pl->db->device);
+    cudaSetDevice(pl->device);
     for (auto& s : pl->slots)
     {
         if (s.stream)
