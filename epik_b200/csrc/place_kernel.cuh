@@ -5,22 +5,25 @@
 // select_best_placements (:134-159) + the LWR loop (:241-264) + filter_by_ratio (:188-199).
 //
 // Per query a warp
-//   1. stages the letter codes of a chunk of CHUNK windows in shared memory, builds the k-mer
-//      codes (2 or 5 bits per letter) and probes the key table, lanes striding over windows;
-//   2. compacts the hits in window order and gathers their posting lists with 128-bit loads
-//      (two (branch, score) entries per lane), U lists in flight per lane, and adds them to
-//      the per-branch accumulators {float S, uint32 C} held in shared memory. Lists are applied
-//      in window order and a list never names a branch twice, so every S[b] sees exactly the
-//      additions of place.cpp:358-367 in the same order: the sums are bit-identical to the
-//      reference's and no atomics are needed;
+//   1. stages the letter codes of a chunk of CHUNK windows in shared memory; every lane rolls the
+//      2-bit / 5-bit k-mer code over WPL consecutive windows and probes the key table (WPL
+//      independent loads in flight per lane);
+//   2. expands the hits, in window order, into segment descriptors (<= 64 postings each) and
+//      gathers them with 128-bit loads (two (branch, score) postings per lane), U segments in
+//      flight while the previous U are being applied to the per-branch accumulators
+//      {float S, uint32 C} in shared memory. Segments are applied in window order and a list
+//      never names a branch twice, so every S[b] sees exactly the additions of place.cpp:358-367
+//      in the same order: the sums are bit-identical to the reference's, without atomics;
 //   3. (only for reads that have windows with one ambiguous letter) replays place.cpp:373-415;
-//   4. sweeps the accumulators once: omega-threshold correction (place.cpp:417-422), FP64
-//      10^S summed over all touched branches (sum_scores), a per-lane top-K kept in registers,
-//      accumulators reset to zero on the way;
-//   5. merges the per-lane lists with warp shuffles, computes the likelihood weight ratios in
-//      FP64 and applies keep_factor.
+//   4. sweeps the accumulators twice. Pass A: omega-threshold correction (place.cpp:417-422),
+//      FP64 10^S summed over all touched branches (sum_scores) and the per-lane maximum. The
+//      keep_at_most-th largest lane maximum is a lower bound of the keep_at_most-th best score,
+//      so pass B only has to collect the few branches at or above it (and clears the
+//      accumulators on the way);
+//   5. picks the best keep_at_most candidates with warp reductions, computes the likelihood
+//      weight ratios in FP64 and applies keep_factor.
 // Float expressions that the reference evaluates without fused multiply-add are written with
-// __fmul_rn/__fadd_rn/__fdiv_rn so that nvcc cannot contract them.
+// __fmul_rn/__fadd_rn so that nvcc cannot contract them.
 #pragma once
 
 #include <cstdint>
@@ -29,11 +32,17 @@
 
 namespace epk
 {
-constexpr int CHUNK = 256;             // windows staged per pass
-constexpr int ROUNDS = CHUNK / 32;     // windows per lane per pass
+constexpr int WPL = 8;                 // consecutive windows per lane per chunk
+constexpr int CHUNK = 32 * WPL;        // windows staged per pass
 constexpr int CODE_BYTES = CHUNK + 32; // letter codes of one pass (k - 1 <= 31 extra letters)
-constexpr int MAX_WARPS_PER_CTA = 16;
+constexpr int SEG_CAP = 256;           // segment descriptors buffered per warp
+constexpr int SEG_LEN = 64;            // postings per segment: one 128-bit load per lane
+constexpr int CAND_CAP = 128;          // top-k candidates buffered per warp (aliases the segments)
+constexpr int MAX_WARPS_PER_CTA = 8;
 constexpr uint32_t NO_BRANCH = 0xFFFFFFFFu;
+constexpr uint32_t FULL = 0xFFFFFFFFu;
+
+static_assert(CAND_CAP * 12 <= SEG_CAP * 8, "candidate arrays alias the segment buffer");
 
 enum counter_slot { CTR_CURSOR = 0, CTR_WINDOWS = 1, CTR_HITS = 2, CTR_ENTRIES = 3, CTR_SHORT = 4, CTR_COUNT = 8 };
 
@@ -60,7 +69,7 @@ __host__ __device__ inline size_t warp_smem_bytes(uint32_t n_nodes)
 {
     size_t acc = (static_cast<size_t>(n_nodes) * 8 + 15) & ~static_cast<size_t>(15);
     size_t seen = ((static_cast<size_t>(n_nodes) + 31) / 32 * 4 + 15) & ~static_cast<size_t>(15);
-    return acc + seen + CHUNK * 8 + CODE_BYTES;
+    return acc + seen + SEG_CAP * 8 + CODE_BYTES;
 }
 constexpr size_t CTA_SMEM_FIXED = 1024; // letter table
 
@@ -93,74 +102,228 @@ __device__ __forceinline__ window_class classify_window(CodePtr codes, uint32_t 
     return c;
 }
 
-__device__ __forceinline__ bool better(float s1, uint32_t b1, float s2, uint32_t b2)
+// ---- arithmetic helpers -------------------------------------------------------------------
+
+// 10^s in FP64 for a float exponent (sum_scores and the LWR loop call std::pow(10.0, double(s)),
+// place.cpp:44-47,175,254). 10^s = 2^n * 2^f with n = rint(s*log2(10)), |f| <= 1/2; 2^f by its
+// Taylor polynomial of degree 12 (truncation 1.7e-16 relative), log2(10) carried in two doubles
+// so that the reduction loses nothing. About 1.5 ulp; exponents near the FP64 range ends go to
+// the library routine (gradual underflow is part of the reference's behaviour for long queries).
+__device__ __forceinline__ double exp10_of_float(float s)
 {
-    // higher score first (place.cpp:128-131); exact ties: lower branch id first (documented rule)
-    return s1 > s2 || (s1 == s2 && b1 < b2);
+    if (!(fabsf(s) < 300.0f)) { return exp10(static_cast<double>(s)); }
+    const double x = static_cast<double>(s);
+    const double t = x * 3.321928094887362;
+    const double t_lo = fma(x, 1.661617516973592e-16, fma(x, 3.321928094887362, -t));
+    const double shifted = t + 6755399441055744.0; // 2^52 + 2^51: integer part lands in the low word
+    const int n = __double2loint(shifted);
+    const double f = (t - (shifted - 6755399441055744.0)) + t_lo;
+    double p = 2.5678435993488206e-11;
+    p = fma(p, f, 4.4455382718708116e-10);
+    p = fma(p, f, 7.054911620801123e-09);
+    p = fma(p, f, 1.01780860092397e-07);
+    p = fma(p, f, 1.321548679014431e-06);
+    p = fma(p, f, 1.5252733804059841e-05);
+    p = fma(p, f, 0.0001540353039338161);
+    p = fma(p, f, 0.0013333558146428443);
+    p = fma(p, f, 0.009618129107628477);
+    p = fma(p, f, 0.05550410866482158);
+    p = fma(p, f, 0.24022650695910072);
+    p = fma(p, f, 0.6931471805599453);
+    p = fma(p, f, 1.0);
+    return __hiloint2double(__double2hiint(p) + (n << 20), __double2loint(p));
 }
 
-// place.cpp:358-367 for one entry
-__device__ __forceinline__ void add_entry(float2* acc, uint32_t branch, uint32_t score_bits)
+// x / kf, correctly rounded (place.cpp:421 divides the corrected score by the k-mer size):
+// q = x*r, one FMA residual step with r = RN(1/kf). Checked exhaustively against x / kf for
+// every float with 1e-30 < |x| < 1e30 and kf = 1..32; the rest takes the IEEE routine.
+__device__ __forceinline__ float div_by_k(float x, float kf, float rcp)
 {
-    float2 a = acc[branch];
-    a.x += __uint_as_float(score_bits);
-    a.y = __uint_as_float(__float_as_uint(a.y) + 1u);
-    acc[branch] = a;
+    const float ax = fabsf(x);
+    if (!(ax > 1e-30f && ax < 1e30f)) { return __fdiv_rn(x, kf); }
+    const float q = __fmul_rn(x, rcp);
+    return __fmaf_rn(__fmaf_rn(-q, kf, x), rcp, q);
 }
 
-// Gathers the posting lists of hits[0, nh) (packed offset|length, window order) and applies them
-// in order. U segments of up to 64 entries are in flight per pass.
-template<int U>
-__device__ __forceinline__ uint64_t gather_hits(const device_db& db, float2* acc, const uint64_t* hits,
-                                                uint32_t nh, uint32_t lane)
+// order-preserving map float -> uint32 (and back); -0 and +0 are made one value first
+__device__ __forceinline__ uint32_t score_key(float s)
 {
-    uint64_t n_entries = 0;
-    uint32_t h = 0, pos = 0;
-    uint64_t cur = nh ? hits[0] : 0;
-    while (h < nh)
+    const uint32_t u = __float_as_uint(__fadd_rn(s, 0.0f));
+    return (u >> 31) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float key_score(uint32_t key)
+{
+    return __uint_as_float((key >> 31) ? (key & 0x7FFFFFFFu) : ~key);
+}
+
+__device__ __forceinline__ uint32_t warp_inclusive_sum(uint32_t v, uint32_t lane)
+{
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1)
     {
-        uint4 v[U];
-        uint32_t cnt[U];
+        const uint32_t o = __shfl_up_sync(FULL, v, d);
+        if (lane >= static_cast<uint32_t>(d)) { v += o; }
+    }
+    return v;
+}
+
+// ---- gathering posting lists ---------------------------------------------------------------
+
+// segment descriptor: (index of the first posting) << 7 | number of postings (1..64)
+template<int U>
+__device__ __forceinline__ void load_segments(const uint2* __restrict__ postings, const uint64_t* segs, uint32_t first,
+                                              uint32_t n, uint32_t lane, uint4 (&v)[U], uint32_t (&cnt)[U])
+{
 #pragma unroll
-        for (int u = 0; u < U; ++u)
+    for (int u = 0; u < U; ++u)
+    {
+        cnt[u] = 0;
+        v[u] = make_uint4(0, 0, 0, 0);
+        if (first + u < n)
         {
-            cnt[u] = 0;
-            v[u] = make_uint4(0, 0, 0, 0);
-            if (h < nh)
-            {
-                const uint64_t off = cur >> LEN_BITS;
-                const uint32_t len = static_cast<uint32_t>(cur & LEN_MASK);
-                const uint32_t c = min(len - pos, 64u);
-                cnt[u] = c;
-                if (2 * lane < c)
-                {
-                    v[u] = __ldg(reinterpret_cast<const uint4*>(db.postings + off + pos) + lane);
-                }
-                pos += 64;
-                if (pos >= len)
-                {
-                    ++h;
-                    pos = 0;
-                    cur = h < nh ? hits[h] : 0;
-                }
-            }
-        }
-#pragma unroll
-        for (int u = 0; u < U; ++u)
-        {
+            const uint64_t d = segs[first + u];
+            cnt[u] = static_cast<uint32_t>(d) & 127u;
             if (2 * lane < cnt[u])
             {
-                add_entry(acc, v[u].x, v[u].y);
-                if (2 * lane + 1 < cnt[u]) { add_entry(acc, v[u].z, v[u].w); }
+                v[u] = __ldg(reinterpret_cast<const uint4*>(postings + (d >> 7)) + lane);
             }
-            n_entries += cnt[u];
-            __syncwarp();
         }
     }
-    return n_entries;
 }
 
-template<uint32_t TABLE, int KMAX, int U>
+// place.cpp:358-367 for up to 64 postings of one list (two per lane; branches are distinct)
+template<int U>
+__device__ __forceinline__ void apply_segments(float2* acc, uint32_t lane, const uint4 (&v)[U], const uint32_t (&cnt)[U])
+{
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+    {
+        if (cnt[u] == 0) { break; }
+        const bool p0 = 2 * lane < cnt[u];
+        const bool p1 = 2 * lane + 1 < cnt[u];
+        float2 a0 = make_float2(0.0f, 0.0f), a1 = make_float2(0.0f, 0.0f);
+        if (p0) { a0 = acc[v[u].x]; }
+        if (p1) { a1 = acc[v[u].z]; }
+        a0.x = __fadd_rn(a0.x, __uint_as_float(v[u].y));
+        a1.x = __fadd_rn(a1.x, __uint_as_float(v[u].w));
+        a0.y = __uint_as_float(__float_as_uint(a0.y) + 1u);
+        a1.y = __uint_as_float(__float_as_uint(a1.y) + 1u);
+        if (p0) { acc[v[u].x] = a0; }
+        if (p1) { acc[v[u].z] = a1; }
+        __syncwarp();
+    }
+}
+
+// Applies segs[0, n) in order; U segments are in flight while the previous U are applied.
+template<int U>
+__device__ __noinline__ void gather_segments(const uint2* __restrict__ postings, float2* acc, const uint64_t* segs,
+                                             uint32_t n, uint32_t lane)
+{
+    uint4 va[U], vb[U];
+    uint32_t ca[U], cb[U];
+    load_segments<U>(postings, segs, 0, n, lane, va, ca);
+    for (uint32_t first = 0; first < n; first += 2 * U)
+    {
+        if (first + U < n) { load_segments<U>(postings, segs, first + U, n, lane, vb, cb); }
+        apply_segments<U>(acc, lane, va, ca);
+        if (first + U >= n) { break; }
+        if (first + 2 * U < n) { load_segments<U>(postings, segs, first + 2 * U, n, lane, va, ca); }
+        apply_segments<U>(acc, lane, vb, cb);
+    }
+}
+
+// One long list on its own (only when a single chunk's lists overflow the segment buffer).
+__device__ __noinline__ void apply_list(const uint2* __restrict__ postings, float2* acc, uint64_t off, uint32_t len, uint32_t lane)
+{
+    for (uint32_t pos = 0; pos < len; pos += 4 * SEG_LEN)
+    {
+        uint4 v[4];
+        uint32_t cnt[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+        {
+            const uint32_t at = pos + u * SEG_LEN;
+            cnt[u] = at < len ? min(len - at, static_cast<uint32_t>(SEG_LEN)) : 0u;
+            v[u] = make_uint4(0, 0, 0, 0);
+            if (2 * lane < cnt[u]) { v[u] = __ldg(reinterpret_cast<const uint4*>(postings + off + at) + lane); }
+        }
+        apply_segments<4>(acc, lane, v, cnt);
+    }
+}
+
+// ---- top-k selection --------------------------------------------------------------------------
+
+// Candidates (score key, branch, count) live in three arrays of CAND_CAP words. Selects the best
+// `want` of the m buffered ones (higher score first, place.cpp:128-131; exact ties: lower branch
+// id first — the documented tie rule), leaves them sorted in slots [0, n_sel) and in the registers
+// of lanes [0, n_sel): lane i holds the i-th best. Returns n_sel = min(want, m).
+__device__ __forceinline__ uint32_t select_best(uint32_t* cand_key, uint32_t* cand_branch, uint32_t* cand_count, uint32_t m,
+                                                uint32_t want, uint32_t lane, uint32_t& my_key, uint32_t& my_branch,
+                                                uint32_t& my_count)
+{
+    constexpr int PER_LANE = CAND_CAP / 32;
+    uint32_t hi[PER_LANE], lo[PER_LANE], cn[PER_LANE];
+#pragma unroll
+    for (int i = 0; i < PER_LANE; ++i)
+    {
+        const uint32_t j = lane + 32u * i;
+        const bool have = j < m;
+        hi[i] = have ? cand_key[j] : 0u;
+        lo[i] = have ? ~cand_branch[j] : 0u;
+        cn[i] = have ? cand_count[j] : 0u;
+    }
+    __syncwarp();
+    my_key = 0;
+    my_branch = NO_BRANCH;
+    my_count = 0;
+    uint32_t n_sel = 0;
+    const uint32_t rounds = min(want, m);
+    for (uint32_t round = 0; round < rounds; ++round)
+    {
+        // my best remaining candidate: largest (hi, lo)
+        uint32_t bh = hi[0], bl = lo[0], bc = cn[0];
+#pragma unroll
+        for (int i = 1; i < PER_LANE; ++i)
+        {
+            const bool gt = hi[i] > bh || (hi[i] == bh && lo[i] > bl);
+            bh = gt ? hi[i] : bh;
+            bl = gt ? lo[i] : bl;
+            bc = gt ? cn[i] : bc;
+        }
+        const uint32_t top_hi = __reduce_max_sync(FULL, bh);
+        const uint32_t top_lo = __reduce_max_sync(FULL, bh == top_hi ? bl : 0u);
+        const bool mine = bh == top_hi && bl == top_lo && bl != 0u; // branches are distinct: one lane
+        const uint32_t src = __ffs(__ballot_sync(FULL, mine)) - 1u;
+        const uint32_t top_count = __shfl_sync(FULL, bc, src);
+        if (lane == round)
+        {
+            my_key = top_hi;
+            my_branch = ~top_lo;
+            my_count = top_count;
+        }
+        if (mine)
+        {
+#pragma unroll
+            for (int i = 0; i < PER_LANE; ++i)
+            {
+                if (hi[i] == top_hi && lo[i] == top_lo) { hi[i] = 0u; lo[i] = 0u; }
+            }
+        }
+        ++n_sel;
+    }
+    if (lane < n_sel)
+    {
+        cand_key[lane] = my_key;
+        cand_branch[lane] = my_branch;
+        cand_count[lane] = my_count;
+    }
+    __syncwarp();
+    return n_sel;
+}
+
+// ---- the kernel ----------------------------------------------------------------------------------
+
+template<uint32_t TABLE, int U>
 __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const place_params p)
 {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -181,22 +344,27 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
     const size_t seen_bytes = (seen_words * 4 + 15) & ~static_cast<size_t>(15);
     float2* acc = reinterpret_cast<float2*>(base);
     uint32_t* seen = reinterpret_cast<uint32_t*>(base + acc_bytes);
-    uint64_t* hits = reinterpret_cast<uint64_t*>(base + acc_bytes + seen_bytes);
-    uint8_t* codes = reinterpret_cast<uint8_t*>(base + acc_bytes + seen_bytes + CHUNK * 8);
+    uint64_t* segs = reinterpret_cast<uint64_t*>(base + acc_bytes + seen_bytes);
+    uint32_t* cand_key = reinterpret_cast<uint32_t*>(segs); // the segment buffer is idle during the sweeps
+    uint32_t* cand_branch = cand_key + CAND_CAP;
+    uint32_t* cand_count = cand_branch + CAND_CAP;
+    uint8_t* codes = reinterpret_cast<uint8_t*>(base + acc_bytes + seen_bytes + SEG_CAP * 8);
 
     for (uint32_t b = lane; b < N; b += 32) { acc[b] = make_float2(0.0f, 0.0f); }
     for (uint32_t i = lane; i < seen_words; i += 32) { seen[i] = 0; }
     __syncthreads();
 
     const float kf = static_cast<float>(k);
+    const float rcp_k = __frcp_rn(kf);
     const float logthr = db.log_threshold;
-    uint64_t ctr_windows = 0, ctr_hits = 0, ctr_entries = 0;
+    const uint32_t key_mask = db.key_mask;
+    uint64_t ctr_windows = 0, ctr_hits = 0, ctr_entries = 0; // per lane, folded once at the end
 
     while (true)
     {
         uint32_t q = 0;
         if (lane == 0) { q = static_cast<uint32_t>(atomicAdd(p.counters + CTR_CURSOR, 1ull)); }
-        q = __shfl_sync(0xFFFFFFFFu, q, 0);
+        q = __shfl_sync(FULL, q, 0);
         if (q >= p.n) { break; }
 
         const uint64_t s0 = p.seq_off[q];
@@ -214,51 +382,116 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
         const uint64_t n_windows = len + 1 - k; // place.cpp:322, counts skipped windows too
         const char* seq = p.seq + s0;
         bool has_ambiguous = false;
+        uint32_t nseg = 0;
+        if (lane == 0) { ctr_windows += n_windows; }
 
         // ---- exact k-mers, window order (place.cpp:294-304, 349-371) ----
         for (uint64_t c0 = 0; c0 < n_windows; c0 += CHUNK)
         {
             const uint32_t nw = static_cast<uint32_t>(min(n_windows - c0, static_cast<uint64_t>(CHUNK)));
             const uint32_t ncode = nw + k - 1;
+            __syncwarp();
             for (uint32_t i = lane; i < ncode; i += 32)
             {
                 codes[i] = static_cast<uint8_t>(letters[static_cast<uint8_t>(seq[c0 + i])]);
             }
             __syncwarp();
 
-            uint64_t slot[ROUNDS];
+            // lane L owns windows [L*WPL, L*WPL + WPL): one rolling code, WPL probes in flight
+            uint64_t slot[WPL];
 #pragma unroll
-            for (int r = 0; r < ROUNDS; ++r)
+            for (int r = 0; r < WPL; ++r) { slot[r] = 0; }
+            const uint32_t w0 = lane * WPL;
+            if (w0 < nw)
             {
-                slot[r] = 0;
-                const uint32_t w = r * 32 + lane;
-                if (w < nw)
+                uint32_t key = 0;
+                int last_gap = -1, last_amb = -1, prev_amb = -1; // positions of the latest such letters
+                for (uint32_t j = 0; j + 1 < k; ++j)
                 {
-                    const window_class c = classify_window(codes, w, k, bits);
-                    if (c.gaps == 0)
+                    const uint32_t l = codes[w0 + j];
+                    const int at = static_cast<int>(w0 + j);
+                    key = (key << bits) | (l & 31u);
+                    last_gap = (l & LETTER_GAP) ? at : last_gap;
+                    prev_amb = (l & LETTER_AMBIGUOUS) ? last_amb : prev_amb;
+                    last_amb = (l & LETTER_AMBIGUOUS) ? at : last_amb;
+                }
+#pragma unroll
+                for (int r = 0; r < WPL; ++r)
+                {
+                    const uint32_t w = w0 + r;
+                    if (w < nw)
                     {
-                        if (c.ambs == 0) { slot[r] = db_search<TABLE>(db, c.key); }
-                        else if (c.ambs == 1) { has_ambiguous = true; }
+                        const uint32_t l = codes[w + k - 1];
+                        const int at = static_cast<int>(w + k - 1);
+                        key = ((key << bits) | (l & 31u)) & key_mask;
+                        last_gap = (l & LETTER_GAP) ? at : last_gap;
+                        prev_amb = (l & LETTER_AMBIGUOUS) ? last_amb : prev_amb;
+                        last_amb = (l & LETTER_AMBIGUOUS) ? at : last_amb;
+                        if (last_gap < static_cast<int>(w))
+                        {
+                            if (last_amb < static_cast<int>(w)) { slot[r] = db_search<TABLE>(db, key); }
+                            else if (prev_amb < static_cast<int>(w)) { has_ambiguous = true; }
+                        }
                     }
                 }
             }
-            uint32_t nh = 0;
+
+            // segments of this chunk's hits; window order = lane-major
+            uint32_t my_segs = 0;
 #pragma unroll
-            for (int r = 0; r < ROUNDS; ++r)
+            for (int r = 0; r < WPL; ++r)
             {
-                const bool hit = (slot[r] & LEN_MASK) != 0;
-                const uint32_t ballot = __ballot_sync(0xFFFFFFFFu, hit);
-                if (hit) { hits[nh + __popc(ballot & ((1u << lane) - 1u))] = slot[r]; }
-                nh += __popc(ballot);
+                const uint32_t l = static_cast<uint32_t>(slot[r] & LEN_MASK);
+                my_segs += (l + SEG_LEN - 1) / SEG_LEN;
+                ctr_hits += l != 0;
+                ctr_entries += l;
             }
-            __syncwarp();
-            ctr_windows += nw;
-            ctr_hits += nh;
-            ctr_entries += gather_hits<U>(db, acc, hits, nh, lane);
+            const uint32_t incl = warp_inclusive_sum(my_segs, lane);
+            const uint32_t total = __shfl_sync(FULL, incl, 31);
+            if (total == 0) { continue; }
+            if (nseg + total > SEG_CAP)
+            {
+                __syncwarp();
+                gather_segments<U>(db.postings, acc, segs, nseg, lane);
+                nseg = 0;
+                __syncwarp();
+            }
+            if (total <= SEG_CAP)
+            {
+                uint32_t at = nseg + incl - my_segs;
+#pragma unroll
+                for (int r = 0; r < WPL; ++r)
+                {
+                    const uint32_t l = static_cast<uint32_t>(slot[r] & LEN_MASK);
+                    const uint64_t off = slot[r] >> LEN_BITS;
+                    for (uint32_t pos = 0; pos < l; pos += SEG_LEN)
+                    {
+                        segs[at++] = ((off + pos) << 7) | min(l - pos, static_cast<uint32_t>(SEG_LEN));
+                    }
+                }
+                nseg += total;
+            }
+            else
+            {
+                // more postings in one chunk than the buffer describes: list by list
+                for (uint32_t src = 0; src < 32; ++src)
+                {
+#pragma unroll
+                    for (int r = 0; r < WPL; ++r)
+                    {
+                        const uint64_t s = __shfl_sync(FULL, slot[r], src);
+                        const uint32_t l = static_cast<uint32_t>(s & LEN_MASK);
+                        if (l) { apply_list(db.postings, acc, s >> LEN_BITS, l, lane); }
+                    }
+                }
+            }
         }
+        __syncwarp();
+        if (nseg) { gather_segments<U>(db.postings, acc, segs, nseg, lane); }
+        __syncwarp();
 
         // ---- windows with exactly one ambiguous letter (place.cpp:306-313, 373-415) ----
-        has_ambiguous = __any_sync(0xFFFFFFFFu, has_ambiguous);
+        has_ambiguous = __any_sync(FULL, has_ambiguous);
         if (has_ambiguous)
         {
             const float thr_rest = __fmul_rn(static_cast<float>(k - 1), db.threshold);
@@ -272,18 +505,18 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
                     codes[i] = static_cast<uint8_t>(letters[static_cast<uint8_t>(seq[c0 + i])]);
                 }
                 __syncwarp();
-                for (uint32_t r = 0; r < ROUNDS && r * 32 < nw; ++r)
+                for (uint32_t r = 0; r * 32 < nw; ++r)
                 {
                     const uint32_t w = r * 32 + lane;
                     window_class c{ 0, 1, 0, 0 };
                     if (w < nw) { c = classify_window(codes, w, k, bits); }
-                    uint32_t todo = __ballot_sync(0xFFFFFFFFu, c.gaps == 0 && c.ambs == 1);
+                    uint32_t todo = __ballot_sync(FULL, c.gaps == 0 && c.ambs == 1);
                     while (todo)
                     {
                         const int src = __ffs(todo) - 1;
                         todo &= todo - 1;
-                        const uint32_t base_key = __shfl_sync(0xFFFFFFFFu, c.key, src);
-                        const uint32_t amb_at = __shfl_sync(0xFFFFFFFFu, c.amb_at, src);
+                        const uint32_t base_key = __shfl_sync(FULL, c.key, src);
+                        const uint32_t amb_at = __shfl_sync(FULL, c.amb_at, src);
                         const uint32_t letter = letters[static_cast<uint8_t>(seq[c0 + r * 32 + src + amb_at])];
                         uint32_t resolutions = letter >> 8;
                         const uint32_t shift = bits * (k - 1 - amb_at);
@@ -295,8 +528,11 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
                             const uint64_t found = db_search<TABLE>(db, base_key | (code << shift));
                             const uint32_t flen = static_cast<uint32_t>(found & LEN_MASK);
                             const uint2* list = db.postings + (found >> LEN_BITS);
-                            ctr_hits += flen != 0;
-                            ctr_entries += flen;
+                            if (lane == 0)
+                            {
+                                ctr_hits += flen != 0;
+                                ctr_entries += flen;
+                            }
                             for (uint32_t e = lane; e < flen; e += 32)
                             {
                                 const uint2 entry = __ldg(list + e);
@@ -320,94 +556,102 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
                 }
             }
             for (uint32_t i = lane; i < seen_words; i += 32) { seen[i] = 0; }
+            __syncwarp();
         }
 
-        // ---- correction, likelihood mass, per-lane top-K (place.cpp:417-422, 164-184, 134-159) ----
-        float top_s[KMAX];
-        uint32_t top_b[KMAX], top_c[KMAX];
-#pragma unroll
-        for (int i = 0; i < KMAX; ++i)
-        {
-            top_s[i] = -INFINITY;
-            top_b[i] = NO_BRANCH;
-            top_c[i] = 0;
-        }
+        // ---- pass A: correction (place.cpp:417-422), likelihood mass (:164-184), lane maxima ----
+        const uint32_t nw32 = static_cast<uint32_t>(min(n_windows, static_cast<uint64_t>(0xFFFFFFFFu)));
         double mass = 0.0;
         uint32_t touched = 0;
+        uint32_t lane_best = 0; // score key of my best branch, 0 = none
+#pragma unroll 4
         for (uint32_t b = lane; b < N; b += 32)
         {
             const float2 a = acc[b];
             const uint32_t c = __float_as_uint(a.y);
+            // the reference converts the size_t difference to float (place.cpp:420)
+            const float absent = n_windows > 0xFFFFFFFFull ? static_cast<float>(n_windows - c) : static_cast<float>(nw32 - c);
+            const float s = div_by_k(__fadd_rn(a.x, __fmul_rn(absent, logthr)), kf, rcp_k);
+            const double e = exp10_of_float(s);
             if (c != 0)
             {
-                acc[b] = make_float2(0.0f, 0.0f);
-                float s = __fadd_rn(a.x, __fmul_rn(static_cast<float>(n_windows - c), logthr));
-                s = __fdiv_rn(s, kf);
-                mass += exp10(static_cast<double>(s));
+                acc[b].x = s;
+                mass += e;
                 ++touched;
-                if (better(s, b, top_s[KMAX - 1], top_b[KMAX - 1]))
-                {
-                    top_s[KMAX - 1] = s;
-                    top_b[KMAX - 1] = b;
-                    top_c[KMAX - 1] = c;
-#pragma unroll
-                    for (int i = KMAX - 1; i > 0; --i)
-                    {
-                        if (better(top_s[i], top_b[i], top_s[i - 1], top_b[i - 1]))
-                        {
-                            const float ts = top_s[i]; top_s[i] = top_s[i - 1]; top_s[i - 1] = ts;
-                            const uint32_t tb = top_b[i]; top_b[i] = top_b[i - 1]; top_b[i - 1] = tb;
-                            const uint32_t tc = top_c[i]; top_c[i] = top_c[i - 1]; top_c[i - 1] = tc;
-                        }
-                    }
-                }
+                lane_best = max(lane_best, score_key(s));
             }
         }
 #pragma unroll
         for (int d = 16; d > 0; d >>= 1)
         {
-            mass += __shfl_xor_sync(0xFFFFFFFFu, mass, d);
-            touched += __shfl_xor_sync(0xFFFFFFFFu, touched, d);
+            mass += __shfl_xor_sync(FULL, mass, d);
+            touched += __shfl_xor_sync(FULL, touched, d);
         }
 
-        // ---- merge: round i elects the best remaining head; lane i keeps it ----
-        float my_s = 0.0f;
-        uint32_t my_b = NO_BRANCH, my_c = 0;
-        const uint32_t n_keep = min(K, touched);
-        for (uint32_t i = 0; i < n_keep; ++i)
+        // the K-th largest lane maximum bounds the K-th best score from below
+        uint32_t bar_key = 0, bar_branch = NO_BRANCH;
         {
-            float bs = top_s[0];
-            uint32_t bb = top_b[0];
-            uint32_t bl = lane;
-#pragma unroll
-            for (int d = 16; d > 0; d >>= 1)
+            uint32_t mine = lane_best, kth = 0;
+            for (uint32_t i = 0; i < K; ++i)
             {
-                const float os = __shfl_xor_sync(0xFFFFFFFFu, bs, d);
-                const uint32_t ob = __shfl_xor_sync(0xFFFFFFFFu, bb, d);
-                const uint32_t ol = __shfl_xor_sync(0xFFFFFFFFu, bl, d);
-                if (better(os, ob, bs, bb)) { bs = os; bb = ob; bl = ol; }
+                kth = __reduce_max_sync(FULL, mine);
+                if (kth == 0) { break; }
+                const uint32_t first = __ffs(__ballot_sync(FULL, mine == kth)) - 1u;
+                if (lane == first) { mine = 0; }
             }
-            const uint32_t bc = __shfl_sync(0xFFFFFFFFu, top_c[0], bl);
-            if (lane == i) { my_s = bs; my_b = bb; my_c = bc; }
-            if (lane == bl)
+            bar_key = kth;
+        }
+
+        // ---- pass B: collect the branches at or above the bar, clear the accumulators ----
+        __syncwarp();
+        uint32_t n_cand = 0;
+        uint32_t my_key = 0, my_b = NO_BRANCH, my_c = 0;
+        for (uint32_t b0 = 0; b0 < N; b0 += 32)
+        {
+            const uint32_t b = b0 + lane;
+            bool cand = false;
+            uint32_t key = 0, c = 0;
+            if (b < N)
             {
-#pragma unroll
-                for (int j = 0; j < KMAX - 1; ++j)
+                const float2 a = acc[b];
+                c = __float_as_uint(a.y);
+                acc[b] = make_float2(0.0f, 0.0f);
+                key = score_key(a.x);
+                cand = c != 0 && (key > bar_key || (key == bar_key && b < bar_branch));
+            }
+            const uint32_t ballot = __ballot_sync(FULL, cand);
+            if (ballot)
+            {
+                if (cand)
                 {
-                    top_s[j] = top_s[j + 1];
-                    top_b[j] = top_b[j + 1];
-                    top_c[j] = top_c[j + 1];
+                    const uint32_t at = n_cand + __popc(ballot & ((1u << lane) - 1u));
+                    cand_key[at] = key;
+                    cand_branch[at] = b;
+                    cand_count[at] = c;
                 }
-                top_s[KMAX - 1] = -INFINITY;
-                top_b[KMAX - 1] = NO_BRANCH;
+                n_cand += __popc(ballot);
+                __syncwarp();
+                if (n_cand > CAND_CAP - 32)
+                {
+                    // keep the best K, raise the bar to the K-th of them
+                    n_cand = select_best(cand_key, cand_branch, cand_count, n_cand, K, lane, my_key, my_b, my_c);
+                    if (n_cand == K)
+                    {
+                        bar_key = __shfl_sync(FULL, my_key, K - 1);
+                        bar_branch = __shfl_sync(FULL, my_b, K - 1);
+                    }
+                }
             }
         }
+        __syncwarp();
+        const uint32_t n_keep = select_best(cand_key, cand_branch, cand_count, n_cand, K, lane, my_key, my_b, my_c);
+        float my_s = key_score(my_key);
 
         // ---- likelihood weight ratios and keep_factor (place.cpp:164-184, 241-267) ----
         const float nwf = static_cast<float>(n_windows);
         const float absent_score = __fdiv_rn(__fmul_rn(nwf, logthr), kf);
         const double absent_mass = static_cast<double>(static_cast<float>(N) - static_cast<float>(touched))
-                                   * exp10(static_cast<double>(absent_score));
+                                   * exp10_of_float(absent_score);
         const double total = absent_mass + mass;
         uint32_t n_out = n_keep;
         if (touched == 0)
@@ -427,12 +671,12 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
         if (total == 0.0) { keep_factor = 0.0; }
         else if (lane < n_out)
         {
-            const double power = exp10(static_cast<double>(my_s));
+            const double power = exp10_of_float(my_s);
             ratio = power == 0.0 ? 0.0 : power / total;
         }
-        const double cut = __shfl_sync(0xFFFFFFFFu, ratio, 0) * keep_factor;
+        const double cut = __shfl_sync(FULL, ratio, 0) * keep_factor;
         const bool keep = lane < n_out && ratio >= cut;
-        const uint32_t kept = __ballot_sync(0xFFFFFFFFu, keep);
+        const uint32_t kept = __ballot_sync(FULL, keep);
         const uint32_t rank = __popc(kept & ((1u << lane) - 1u));
         const uint32_t n_kept = __popc(kept);
         const size_t row = static_cast<size_t>(q) * K;
@@ -454,6 +698,13 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
         __syncwarp();
     }
 
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1)
+    {
+        ctr_windows += __shfl_xor_sync(FULL, ctr_windows, d);
+        ctr_hits += __shfl_xor_sync(FULL, ctr_hits, d);
+        ctr_entries += __shfl_xor_sync(FULL, ctr_entries, d);
+    }
     if (lane == 0)
     {
         atomicAdd(p.counters + CTR_WINDOWS, static_cast<unsigned long long>(ctr_windows));

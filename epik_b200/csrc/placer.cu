@@ -123,12 +123,7 @@ namespace
 
     kernel_fn pick_kernel(const epk_placer& pl)
     {
-        const bool direct = pl.db->table_kind == TABLE_DIRECT;
-        if (pl.keep_at_most <= 8)
-        {
-            return direct ? place_kernel<TABLE_DIRECT, 8, 8> : place_kernel<TABLE_HASH, 8, 8>;
-        }
-        return direct ? place_kernel<TABLE_DIRECT, 32, 4> : place_kernel<TABLE_HASH, 32, 4>;
+        return pl.db->table_kind == TABLE_DIRECT ? place_kernel<TABLE_DIRECT, 8> : place_kernel<TABLE_HASH, 8>;
     }
 
     // one launch over n sequences already on the device
