@@ -9,7 +9,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libepik_b200.so")
+LIB_PATH = os.environ.get("EPIK_B200_LIB") or os.path.join(_HERE, "libepik_b200.so")  # override: kernel experiments
 
 EPK_OK, EPK_E_INVALID, EPK_E_CUDA, EPK_E_NOMEM, EPK_E_SHORT_SEQ, EPK_E_UNSUPPORTED = range(6)
 STATUS_NAMES = ["EPK_OK", "EPK_E_INVALID", "EPK_E_CUDA", "EPK_E_NOMEM", "EPK_E_SHORT_SEQ", "EPK_E_UNSUPPORTED"]

@@ -37,6 +37,7 @@ constexpr int CHUNK = 32 * WPL;        // windows staged per pass
 constexpr int CODE_BYTES = CHUNK + 32; // letter codes of one pass (k - 1 <= 31 extra letters)
 constexpr int SEG_CAP = 256;           // segment descriptors buffered per warp
 constexpr int SEG_LEN = 64;            // postings per segment: one 128-bit load per lane
+constexpr int SEG_PAD = 8;             // zero descriptors after the last one (= segments in flight)
 constexpr int CAND_CAP = 128;          // top-k candidates buffered per warp (aliases the segments)
 constexpr int MAX_WARPS_PER_CTA = 8;
 constexpr uint32_t NO_BRANCH = 0xFFFFFFFFu;
@@ -69,7 +70,7 @@ __host__ __device__ inline size_t warp_smem_bytes(uint32_t n_nodes)
 {
     size_t acc = (static_cast<size_t>(n_nodes) * 8 + 15) & ~static_cast<size_t>(15);
     size_t seen = ((static_cast<size_t>(n_nodes) + 31) / 32 * 4 + 15) & ~static_cast<size_t>(15);
-    return acc + seen + SEG_CAP * 8 + CODE_BYTES;
+    return acc + seen + (SEG_CAP + SEG_PAD) * 8 + CODE_BYTES;
 }
 constexpr size_t CTA_SMEM_FIXED = 1024; // letter table
 
@@ -104,52 +105,57 @@ __device__ __forceinline__ window_class classify_window(CodePtr codes, uint32_t 
 
 // ---- arithmetic helpers -------------------------------------------------------------------
 
-// 10^s in FP64 for a float exponent (sum_scores and the LWR loop call std::pow(10.0, double(s)),
-// place.cpp:44-47,175,254). 10^s = 2^n * 2^f with n = rint(s*log2(10)), |f| <= 1/2; 2^f by its
-// Taylor polynomial of degree 12 (truncation 1.7e-16 relative), log2(10) carried in two doubles
-// so that the reduction loses nothing. About 1.5 ulp; exponents near the FP64 range ends go to
-// the library routine (gradual underflow is part of the reference's behaviour for long queries).
-__device__ __forceinline__ double exp10_of_float(float s)
+// Taylor coefficients ln(2)^i / i!, i = 12 .. 1, of 2^f (constant bank: DFMA takes them as operands)
+__constant__ double EXP2_POLY[12] = {
+    2.5678435993488206e-11, 4.4455382718708116e-10, 7.054911620801123e-09, 1.01780860092397e-07,
+    1.321548679014431e-06,  1.5252733804059841e-05, 0.0001540353039338161, 0.0013333558146428443,
+    0.009618129107628477,   0.05550410866482158,    0.24022650695910072,   0.6931471805599453 };
+
+// 10^s in FP64 for a float exponent with |s| < 300 (sum_scores and the LWR loop call
+// std::pow(10.0, double(s)), place.cpp:44-47,175,254). 10^s = 2^n * 2^f with
+// n = rint(s*log2(10)), |f| <= 1/2, 2^f by its Taylor polynomial of degree 12. Relative error
+// below 1e-13, dominated by the single-double log2(10) in the reduction; it is common to all
+// terms of a ratio to first order. Straight-line code: callers interleave several of these.
+__device__ __forceinline__ double exp10_small(float s)
 {
-    if (!(fabsf(s) < 300.0f)) { return exp10(static_cast<double>(s)); }
-    const double x = static_cast<double>(s);
-    const double t = x * 3.321928094887362;
-    const double t_lo = fma(x, 1.661617516973592e-16, fma(x, 3.321928094887362, -t));
-    const double shifted = t + 6755399441055744.0; // 2^52 + 2^51: integer part lands in the low word
+    const double t = static_cast<double>(s) * 3.321928094887362;
+    const double shifted = t + 6755399441055744.0; // 2^52 + 2^51: the integer part lands in the low word
     const int n = __double2loint(shifted);
-    const double f = (t - (shifted - 6755399441055744.0)) + t_lo;
-    double p = 2.5678435993488206e-11;
-    p = fma(p, f, 4.4455382718708116e-10);
-    p = fma(p, f, 7.054911620801123e-09);
-    p = fma(p, f, 1.01780860092397e-07);
-    p = fma(p, f, 1.321548679014431e-06);
-    p = fma(p, f, 1.5252733804059841e-05);
-    p = fma(p, f, 0.0001540353039338161);
-    p = fma(p, f, 0.0013333558146428443);
-    p = fma(p, f, 0.009618129107628477);
-    p = fma(p, f, 0.05550410866482158);
-    p = fma(p, f, 0.24022650695910072);
-    p = fma(p, f, 0.6931471805599453);
+    const double f = t - (shifted - 6755399441055744.0);
+    double p = EXP2_POLY[0];
+#pragma unroll
+    for (int i = 1; i < 12; ++i) { p = fma(p, f, EXP2_POLY[i]); }
     p = fma(p, f, 1.0);
     return __hiloint2double(__double2hiint(p) + (n << 20), __double2loint(p));
+}
+__device__ __forceinline__ bool exp10_is_small(float s) { return fabsf(s) < 300.0f; }
+
+// any exponent: near the ends of the FP64 range the library routine takes over (gradual underflow
+// is part of the reference's behaviour for long queries)
+__device__ __forceinline__ double exp10_of_float(float s)
+{
+    return exp10_is_small(s) ? exp10_small(s) : exp10(static_cast<double>(s));
 }
 
 // x / kf, correctly rounded (place.cpp:421 divides the corrected score by the k-mer size):
 // q = x*r, one FMA residual step with r = RN(1/kf). Checked exhaustively against x / kf for
-// every float with 1e-30 < |x| < 1e30 and kf = 1..32; the rest takes the IEEE routine.
-__device__ __forceinline__ float div_by_k(float x, float kf, float rcp)
+// every float with 1e-30 < |x| < 1e30 and kf = 1..32 (div_is_plain); the rest takes __fdiv_rn.
+__device__ __forceinline__ float div_by_k_plain(float x, float kf, float rcp)
 {
-    const float ax = fabsf(x);
-    if (!(ax > 1e-30f && ax < 1e30f)) { return __fdiv_rn(x, kf); }
     const float q = __fmul_rn(x, rcp);
     return __fmaf_rn(__fmaf_rn(-q, kf, x), rcp, q);
+}
+__device__ __forceinline__ bool div_is_plain(float x)
+{
+    const float ax = fabsf(x);
+    return ax > 1e-30f && ax < 1e30f;
 }
 
 // order-preserving map float -> uint32 (and back); -0 and +0 are made one value first
 __device__ __forceinline__ uint32_t score_key(float s)
 {
     const uint32_t u = __float_as_uint(__fadd_rn(s, 0.0f));
-    return (u >> 31) ? ~u : (u | 0x80000000u);
+    return u ^ (static_cast<uint32_t>(static_cast<int32_t>(u) >> 31) | 0x80000000u);
 }
 __device__ __forceinline__ float key_score(uint32_t key)
 {
@@ -168,86 +174,155 @@ __device__ __forceinline__ uint32_t warp_inclusive_sum(uint32_t v, uint32_t lane
 }
 
 // ---- gathering posting lists ---------------------------------------------------------------
+//
+// A segment descriptor is {index of the segment's first posting / 2, number of postings (1..64)};
+// a zero count is padding. Lists start on 16-byte boundaries and segments on multiples of 64
+// postings, so a lane fetches postings 2*lane and 2*lane + 1 of a segment with one 128-bit load.
+// The hot loop is written in PTX: nvcc's version of it spent three quarters of its instructions
+// on moves and branches.
 
-// segment descriptor: (index of the first posting) << 7 | number of postings (1..64)
-template<int U>
-__device__ __forceinline__ void load_segments(const uint2* __restrict__ postings, const uint64_t* segs, uint32_t first,
-                                              uint32_t n, uint32_t lane, uint4 (&v)[U], uint32_t (&cnt)[U])
+struct seg_regs
 {
-#pragma unroll
-    for (int u = 0; u < U; ++u)
+    uint32_t b0, s0, b1, s1; // two postings: (branch, score bits) x 2
+    uint32_t cnt;
+};
+
+__device__ __forceinline__ void load_segment(const unsigned char* lane_base, uint32_t segs_shared, uint32_t idx,
+                                             uint32_t lane2, seg_regs& r)
+{
+#ifdef EPK_CXX_LOAD
+    extern __shared__ __align__(16) unsigned char smem_base[];
+    const uint32_t smem0 = static_cast<uint32_t>(__cvta_generic_to_shared(smem_base));
+    const uint2 d = *reinterpret_cast<const uint2*>(smem_base + (segs_shared + idx * 8u - smem0));
+    r.cnt = d.y;
+    if (lane2 < d.y)
     {
-        cnt[u] = 0;
-        v[u] = make_uint4(0, 0, 0, 0);
-        if (first + u < n)
-        {
-            const uint64_t d = segs[first + u];
-            cnt[u] = static_cast<uint32_t>(d) & 127u;
-            if (2 * lane < cnt[u])
-            {
-                v[u] = __ldg(reinterpret_cast<const uint4*>(postings + (d >> 7)) + lane);
-            }
-        }
+        const uint4 v = __ldg(reinterpret_cast<const uint4*>(lane_base + 16ull * d.x));
+        r.b0 = v.x; r.s0 = v.y; r.b1 = v.z; r.s1 = v.w;
     }
+    return;
+#endif
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        ".reg .b32 pair;\n\t"
+        ".reg .b64 addr;\n\t"
+        "ld.shared.v2.b32 {pair, %4}, [%5];\n\t"
+        "setp.lt.u32 p, %7, %4;\n\t"
+        "mad.wide.u32 addr, pair, 16, %6;\n\t"
+        "@p ld.global.nc.v4.b32 {%0, %1, %2, %3}, [addr];\n\t"
+        "}"
+        : "+r"(r.b0), "+r"(r.s0), "+r"(r.b1), "+r"(r.s1), "=&r"(r.cnt)
+        : "r"(segs_shared + idx * 8u), "l"(lane_base), "r"(lane2)
+        : "memory");
 }
 
-// place.cpp:358-367 for up to 64 postings of one list (two per lane; branches are distinct)
-template<int U>
-__device__ __forceinline__ void apply_segments(float2* acc, uint32_t lane, const uint4 (&v)[U], const uint32_t (&cnt)[U])
+// place.cpp:358-367 for the (up to) two postings a lane holds of one segment; branches of one
+// list are distinct, so the two read-modify-writes of a lane and those of different lanes are
+// independent.
+__device__ __forceinline__ void apply_segment(uint32_t acc_shared, uint32_t lane2, const seg_regs& r)
 {
-#pragma unroll
-    for (int u = 0; u < U; ++u)
-    {
-        if (cnt[u] == 0) { break; }
-        const bool p0 = 2 * lane < cnt[u];
-        const bool p1 = 2 * lane + 1 < cnt[u];
-        float2 a0 = make_float2(0.0f, 0.0f), a1 = make_float2(0.0f, 0.0f);
-        if (p0) { a0 = acc[v[u].x]; }
-        if (p1) { a1 = acc[v[u].z]; }
-        a0.x = __fadd_rn(a0.x, __uint_as_float(v[u].y));
-        a1.x = __fadd_rn(a1.x, __uint_as_float(v[u].w));
-        a0.y = __uint_as_float(__float_as_uint(a0.y) + 1u);
-        a1.y = __uint_as_float(__float_as_uint(a1.y) + 1u);
-        if (p0) { acc[v[u].x] = a0; }
-        if (p1) { acc[v[u].z] = a1; }
-        __syncwarp();
-    }
+#ifdef EPK_CXX_APPLY
+    extern __shared__ __align__(16) unsigned char smem_base[];
+    const uint32_t smem0 = static_cast<uint32_t>(__cvta_generic_to_shared(smem_base));
+    float2* acc = reinterpret_cast<float2*>(smem_base + (acc_shared - smem0));
+    const bool p0 = lane2 < r.cnt, p1 = lane2 + 1 < r.cnt;
+    float2 a0 = acc[r.b0], a1 = acc[r.b1];
+    a0.x = __fadd_rn(a0.x, __uint_as_float(r.s0));
+    a1.x = __fadd_rn(a1.x, __uint_as_float(r.s1));
+    a0.y = __uint_as_float(__float_as_uint(a0.y) + 1u);
+    a1.y = __uint_as_float(__float_as_uint(a1.y) + 1u);
+    if (p0) { acc[r.b0] = a0; }
+    if (p1) { acc[r.b1] = a1; }
+    __syncwarp();
+    return;
+#endif
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p0, p1;\n\t"
+        ".reg .b32 a0, a1, c0, c1, x0, x1;\n\t"
+        ".reg .f32 f0, f1;\n\t"
+        "setp.lt.u32 p0, %5, %4;\n\t"
+        "setp.lt.u32 p1, %6, %4;\n\t"
+        "shl.b32 a0, %0, 3;\n\t"
+        "shl.b32 a1, %2, 3;\n\t"
+        "add.u32 a0, a0, %7;\n\t"
+        "add.u32 a1, a1, %7;\n\t"
+        "ld.shared.v2.b32 {x0, c0}, [a0];\n\t" // lanes past the end hold 0 or an older, valid branch
+        "ld.shared.v2.b32 {x1, c1}, [a1];\n\t"
+        "mov.b32 f0, x0;\n\t"
+        "mov.b32 f1, x1;\n\t"
+        "add.rn.f32 f0, f0, %1;\n\t"
+        "add.rn.f32 f1, f1, %3;\n\t"
+        "add.u32 c0, c0, 1;\n\t"
+        "add.u32 c1, c1, 1;\n\t"
+        "mov.b32 x0, f0;\n\t"
+        "mov.b32 x1, f1;\n\t"
+        "@p0 st.shared.v2.b32 [a0], {x0, c0};\n\t"
+        "@p1 st.shared.v2.b32 [a1], {x1, c1};\n\t"
+        "}"
+        :
+        : "r"(r.b0), "f"(__uint_as_float(r.s0)), "r"(r.b1), "f"(__uint_as_float(r.s1)), "r"(r.cnt), "r"(lane2),
+          "r"(lane2 + 1u), "r"(acc_shared)
+        : "memory");
+    __syncwarp(); // the next segment may name the same branches from other lanes
 }
 
 // Applies segs[0, n) in order; U segments are in flight while the previous U are applied.
+// segs[n, n + U) must hold zero descriptors.
+#ifndef EPK_GATHER_INLINE
+#define EPK_GATHER_INLINE __noinline__
+#endif
 template<int U>
-__device__ __noinline__ void gather_segments(const uint2* __restrict__ postings, float2* acc, const uint64_t* segs,
+__device__ EPK_GATHER_INLINE void gather_segments(const uint2* __restrict__ postings, uint32_t acc_shared, uint32_t segs_shared,
                                              uint32_t n, uint32_t lane)
 {
-    uint4 va[U], vb[U];
-    uint32_t ca[U], cb[U];
-    load_segments<U>(postings, segs, 0, n, lane, va, ca);
+    const unsigned char* lane_base = reinterpret_cast<const unsigned char*>(postings) + 16u * lane;
+    const uint32_t lane2 = 2u * lane;
+    seg_regs a[U], b[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+    {
+        a[u] = seg_regs{ 0, 0, 0, 0, 0 };
+        b[u] = seg_regs{ 0, 0, 0, 0, 0 };
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) { load_segment(lane_base, segs_shared, u, lane2, a[u]); }
     for (uint32_t first = 0; first < n; first += 2 * U)
     {
-        if (first + U < n) { load_segments<U>(postings, segs, first + U, n, lane, vb, cb); }
-        apply_segments<U>(acc, lane, va, ca);
-        if (first + U >= n) { break; }
-        if (first + 2 * U < n) { load_segments<U>(postings, segs, first + 2 * U, n, lane, va, ca); }
-        apply_segments<U>(acc, lane, vb, cb);
+        const bool more_b = first + U < n;
+        if (more_b)
+        {
+#pragma unroll
+            for (int u = 0; u < U; ++u) { load_segment(lane_base, segs_shared, first + U + u, lane2, b[u]); }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) { apply_segment(acc_shared, lane2, a[u]); }
+        if (!more_b) { break; }
+        if (first + 2 * U < n)
+        {
+#pragma unroll
+            for (int u = 0; u < U; ++u) { load_segment(lane_base, segs_shared, first + 2 * U + u, lane2, a[u]); }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) { apply_segment(acc_shared, lane2, b[u]); }
     }
 }
 
 // One long list on its own (only when a single chunk's lists overflow the segment buffer).
-__device__ __noinline__ void apply_list(const uint2* __restrict__ postings, float2* acc, uint64_t off, uint32_t len, uint32_t lane)
+__device__ __noinline__ void apply_list(const uint2* __restrict__ postings, uint32_t acc_shared, uint64_t off, uint32_t len,
+                                        uint32_t lane)
 {
-    for (uint32_t pos = 0; pos < len; pos += 4 * SEG_LEN)
+    const uint32_t lane2 = 2u * lane;
+    for (uint32_t pos = 0; pos < len; pos += SEG_LEN)
     {
-        uint4 v[4];
-        uint32_t cnt[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u)
+        seg_regs r{ 0, 0, 0, 0, min(len - pos, static_cast<uint32_t>(SEG_LEN)) };
+        if (lane2 < r.cnt)
         {
-            const uint32_t at = pos + u * SEG_LEN;
-            cnt[u] = at < len ? min(len - at, static_cast<uint32_t>(SEG_LEN)) : 0u;
-            v[u] = make_uint4(0, 0, 0, 0);
-            if (2 * lane < cnt[u]) { v[u] = __ldg(reinterpret_cast<const uint4*>(postings + off + at) + lane); }
+            const uint4 v = __ldg(reinterpret_cast<const uint4*>(postings + off + pos) + lane);
+            r.b0 = v.x; r.s0 = v.y; r.b1 = v.z; r.s1 = v.w;
         }
-        apply_segments<4>(acc, lane, v, cnt);
+        apply_segment(acc_shared, lane2, r);
     }
 }
 
@@ -334,6 +409,7 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
     const uint32_t k = db.k;
     const uint32_t bits = db.bits;
     const uint32_t K = p.keep_at_most;
+    static_assert(U <= SEG_PAD, "zero padding of the segment buffer covers one batch of loads");
 
     uint32_t* letters = reinterpret_cast<uint32_t*>(smem);
     for (uint32_t i = threadIdx.x; i < 256; i += blockDim.x) { letters[i] = p.letters[i]; }
@@ -344,11 +420,13 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
     const size_t seen_bytes = (seen_words * 4 + 15) & ~static_cast<size_t>(15);
     float2* acc = reinterpret_cast<float2*>(base);
     uint32_t* seen = reinterpret_cast<uint32_t*>(base + acc_bytes);
-    uint64_t* segs = reinterpret_cast<uint64_t*>(base + acc_bytes + seen_bytes);
+    uint2* segs = reinterpret_cast<uint2*>(base + acc_bytes + seen_bytes);
+    const uint32_t segs_shared = static_cast<uint32_t>(__cvta_generic_to_shared(segs));
+    const uint32_t acc_shared = static_cast<uint32_t>(__cvta_generic_to_shared(acc));
     uint32_t* cand_key = reinterpret_cast<uint32_t*>(segs); // the segment buffer is idle during the sweeps
     uint32_t* cand_branch = cand_key + CAND_CAP;
     uint32_t* cand_count = cand_branch + CAND_CAP;
-    uint8_t* codes = reinterpret_cast<uint8_t*>(base + acc_bytes + seen_bytes + SEG_CAP * 8);
+    uint8_t* codes = reinterpret_cast<uint8_t*>(base + acc_bytes + seen_bytes + (SEG_CAP + SEG_PAD) * 8);
 
     for (uint32_t b = lane; b < N; b += 32) { acc[b] = make_float2(0.0f, 0.0f); }
     for (uint32_t i = lane; i < seen_words; i += 32) { seen[i] = 0; }
@@ -451,8 +529,9 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
             if (total == 0) { continue; }
             if (nseg + total > SEG_CAP)
             {
+                if (lane < SEG_PAD) { segs[nseg + lane] = make_uint2(0, 0); }
                 __syncwarp();
-                gather_segments<U>(db.postings, acc, segs, nseg, lane);
+                gather_segments<U>(db.postings, acc_shared, segs_shared, nseg, lane);
                 nseg = 0;
                 __syncwarp();
             }
@@ -463,10 +542,10 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
                 for (int r = 0; r < WPL; ++r)
                 {
                     const uint32_t l = static_cast<uint32_t>(slot[r] & LEN_MASK);
-                    const uint64_t off = slot[r] >> LEN_BITS;
+                    const uint32_t pair = static_cast<uint32_t>(slot[r] >> (LEN_BITS + 1));
                     for (uint32_t pos = 0; pos < l; pos += SEG_LEN)
                     {
-                        segs[at++] = ((off + pos) << 7) | min(l - pos, static_cast<uint32_t>(SEG_LEN));
+                        segs[at++] = make_uint2(pair + pos / 2, min(l - pos, static_cast<uint32_t>(SEG_LEN)));
                     }
                 }
                 nseg += total;
@@ -481,13 +560,17 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
                     {
                         const uint64_t s = __shfl_sync(FULL, slot[r], src);
                         const uint32_t l = static_cast<uint32_t>(s & LEN_MASK);
-                        if (l) { apply_list(db.postings, acc, s >> LEN_BITS, l, lane); }
+                        if (l) { apply_list(db.postings, acc_shared, s >> LEN_BITS, l, lane); }
                     }
                 }
             }
         }
-        __syncwarp();
-        if (nseg) { gather_segments<U>(db.postings, acc, segs, nseg, lane); }
+        if (nseg)
+        {
+            if (lane < SEG_PAD) { segs[nseg + lane] = make_uint2(0, 0); }
+            __syncwarp();
+            gather_segments<U>(db.postings, acc_shared, segs_shared, nseg, lane);
+        }
         __syncwarp();
 
         // ---- windows with exactly one ambiguous letter (place.cpp:306-313, 373-415) ----
@@ -560,25 +643,57 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
         }
 
         // ---- pass A: correction (place.cpp:417-422), likelihood mass (:164-184), lane maxima ----
-        const uint32_t nw32 = static_cast<uint32_t>(min(n_windows, static_cast<uint64_t>(0xFFFFFFFFu)));
+        // Four branches per lane and iteration, straight-line, so that the four FP64 chains overlap.
+        // The corrected score replaces S as its order-preserving key; C stays.
+        const uint32_t nw32 = static_cast<uint32_t>(n_windows);
         double mass = 0.0;
         uint32_t touched = 0;
         uint32_t lane_best = 0; // score key of my best branch, 0 = none
-#pragma unroll 4
-        for (uint32_t b = lane; b < N; b += 32)
+        for (uint32_t base0 = 0; base0 < N; base0 += 128) // warp-uniform trip count
         {
-            const float2 a = acc[b];
-            const uint32_t c = __float_as_uint(a.y);
-            // the reference converts the size_t difference to float (place.cpp:420)
-            const float absent = n_windows > 0xFFFFFFFFull ? static_cast<float>(n_windows - c) : static_cast<float>(nw32 - c);
-            const float s = div_by_k(__fadd_rn(a.x, __fmul_rn(absent, logthr)), kf, rcp_k);
-            const double e = exp10_of_float(s);
-            if (c != 0)
+            const uint32_t b0 = base0 + lane;
+            float2 a[4];
+            float x[4], s[4];
+            double e[4];
+            bool odd = false;
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
             {
-                acc[b].x = s;
-                mass += e;
-                ++touched;
-                lane_best = max(lane_best, score_key(s));
+                const uint32_t b = b0 + 32u * u;
+                a[u] = b < N ? acc[b] : make_float2(0.0f, 0.0f);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+            {
+                const uint32_t c = __float_as_uint(a[u].y);
+                // the reference converts the size_t difference to float (place.cpp:420)
+                x[u] = __fadd_rn(a[u].x, __fmul_rn(static_cast<float>(nw32 - c), logthr));
+                s[u] = div_by_k_plain(x[u], kf, rcp_k);
+                e[u] = exp10_small(s[u]);
+                odd |= c != 0 && !(div_is_plain(x[u]) && exp10_is_small(s[u]));
+            }
+            if (odd)
+            {
+                // outside what the short forms were checked for (very long queries): the IEEE routines
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                {
+                    s[u] = __fdiv_rn(x[u], kf);
+                    e[u] = exp10(static_cast<double>(s[u]));
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+            {
+                const uint32_t b = b0 + 32u * u;
+                if (__float_as_uint(a[u].y) != 0)
+                {
+                    const uint32_t key = score_key(s[u]);
+                    acc[b].x = __uint_as_float(key);
+                    mass += e[u];
+                    ++touched;
+                    lane_best = max(lane_best, key);
+                }
             }
         }
 #pragma unroll
@@ -606,39 +721,50 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
         __syncwarp();
         uint32_t n_cand = 0;
         uint32_t my_key = 0, my_b = NO_BRANCH, my_c = 0;
-        for (uint32_t b0 = 0; b0 < N; b0 += 32)
+        for (uint32_t base0 = 0; base0 < N; base0 += 128) // warp-uniform trip count
         {
-            const uint32_t b = b0 + lane;
-            bool cand = false;
-            uint32_t key = 0, c = 0;
-            if (b < N)
+            const uint32_t b0 = base0 + lane;
+            uint32_t key[4], cnt[4];
+            bool cand[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
             {
-                const float2 a = acc[b];
-                c = __float_as_uint(a.y);
-                acc[b] = make_float2(0.0f, 0.0f);
-                key = score_key(a.x);
-                cand = c != 0 && (key > bar_key || (key == bar_key && b < bar_branch));
-            }
-            const uint32_t ballot = __ballot_sync(FULL, cand);
-            if (ballot)
-            {
-                if (cand)
+                const uint32_t b = b0 + 32u * u;
+                float2 a = make_float2(0.0f, 0.0f);
+                if (b < N)
                 {
-                    const uint32_t at = n_cand + __popc(ballot & ((1u << lane) - 1u));
-                    cand_key[at] = key;
-                    cand_branch[at] = b;
-                    cand_count[at] = c;
+                    a = acc[b];
+                    acc[b] = make_float2(0.0f, 0.0f);
                 }
-                n_cand += __popc(ballot);
-                __syncwarp();
-                if (n_cand > CAND_CAP - 32)
+                key[u] = __float_as_uint(a.x);
+                cnt[u] = __float_as_uint(a.y);
+                cand[u] = (cnt[u] != 0) & ((key[u] > bar_key) | ((key[u] == bar_key) & (b < bar_branch)));
+            }
+            if (__any_sync(FULL, cand[0] | cand[1] | cand[2] | cand[3]))
+            {
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
                 {
-                    // keep the best K, raise the bar to the K-th of them
-                    n_cand = select_best(cand_key, cand_branch, cand_count, n_cand, K, lane, my_key, my_b, my_c);
-                    if (n_cand == K)
+                    const uint32_t ballot = __ballot_sync(FULL, cand[u]);
+                    if (cand[u])
                     {
-                        bar_key = __shfl_sync(FULL, my_key, K - 1);
-                        bar_branch = __shfl_sync(FULL, my_b, K - 1);
+                        const uint32_t at = n_cand + __popc(ballot & ((1u << lane) - 1u));
+                        cand_key[at] = key[u];
+                        cand_branch[at] = b0 + 32u * u;
+                        cand_count[at] = cnt[u];
+                    }
+                    n_cand += __popc(ballot);
+                    __syncwarp();
+                    if (n_cand > CAND_CAP - 32)
+                    {
+                        // keep the best K, raise the bar to the K-th of them. Later branches of this
+                        // group were tested against the old bar: a few extra candidates, never a miss.
+                        n_cand = select_best(cand_key, cand_branch, cand_count, n_cand, K, lane, my_key, my_b, my_c);
+                        if (n_cand == K)
+                        {
+                            bar_key = __shfl_sync(FULL, my_key, K - 1);
+                            bar_branch = __shfl_sync(FULL, my_b, K - 1);
+                        }
                     }
                 }
             }
