@@ -64,7 +64,7 @@ class Result(C.Structure):
 
 class Counters(C.Structure):
     _fields_ = [("n_reads", C.c_uint64), ("n_windows", C.c_uint64), ("n_hits", C.c_uint64), ("n_entries", C.c_uint64),
-                ("n_launches", C.c_uint64), ("n_short", C.c_uint64)]
+                ("n_launches", C.c_uint64), ("n_short", C.c_uint64), ("n_unsupported", C.c_uint64)]
 
 
 _lib = None

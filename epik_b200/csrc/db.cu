@@ -290,6 +290,15 @@ static void build_db(const epk_db_desc& d, const epk_load_filter* filter, int de
         validate_lists_kernel<<<1184, warps * 32, smem, stream>>>(db.postings.get(), new_len.get(), new_off.get(), n_keys,
                                                                   d.n_nodes, status.get());
     }
+    // ---- range of the loaded scores (which arithmetic the sweep of the placement kernel may use) ----
+    device_buffer<uint32_t> stats(4);
+    uint32_t h_stats[4] = { 0xFFFFFFFFu, 0u, 0x7F800000u, 0u };
+    EPK_CUDA(cudaMemcpyAsync(stats.get(), h_stats, sizeof(h_stats), cudaMemcpyHostToDevice, stream));
+    if (n_keys)
+    {
+        score_stats_kernel<<<1184, 256, 0, stream>>>(db.postings.get(), new_len.get(), new_off.get(), n_keys, stats.get());
+    }
+    EPK_CUDA(cudaMemcpyAsync(h_stats, stats.get(), sizeof(h_stats), cudaMemcpyDeviceToHost, stream));
     uint32_t h_status = 0;
     EPK_CUDA(cudaMemcpyAsync(&h_status, status.get(), 4, cudaMemcpyDeviceToHost, stream));
     EPK_CUDA(cudaStreamSynchronize(stream));
@@ -317,6 +326,14 @@ static void build_db(const epk_db_desc& d, const epk_load_filter* filter, int de
     dd.alphabet = d.alphabet;
     dd.threshold = score_threshold(d.alphabet, omega, d.kmer_size);
     dd.log_threshold = std::log10(dd.threshold); // place.cpp:88, float log10
+    {
+        const bool any = h_stats[0] <= h_stats[1];
+        dd.score_lo = any ? ordered_key_value(h_stats[0]) : 0.0f;
+        dd.score_hi = any ? ordered_key_value(h_stats[1]) : 0.0f;
+        float tiny;
+        std::memcpy(&tiny, &h_stats[2], 4);
+        dd.fast_ok = (h_stats[3] == 0 && dd.score_hi <= 0.0f && tiny >= 1e-20f) ? 1u : 0u;
+    }
 
     // place.cpp:98-125: distal = branch_length / 2, pendant = mean subtree branch length + distal
     db.distal.resize(d.n_nodes);

@@ -14,6 +14,7 @@
 #pragma once
 
 #include <cstdint>
+#include <cstring>
 #include <cuda_runtime.h>
 #include "device_db.cuh"
 
@@ -211,6 +212,60 @@ __global__ void validate_lists_kernel(const uint2* postings, const uint64_t* new
             if (b < n_nodes) { bitmap[b >> 5] = 0; }
         }
         __syncwarp();
+    }
+}
+
+// Range of the loaded scores, as order-preserving keys: stats[0] = min, stats[1] = max,
+// stats[2] = smallest non-zero magnitude (raw bits), stats[3] = 1 when a score is not finite.
+// stats must start as {0xFFFFFFFF, 0, 0x7F800000, 0}.
+__device__ __forceinline__ uint32_t ordered_key(float s)
+{
+    const uint32_t u = __float_as_uint(s);
+    return u ^ (static_cast<uint32_t>(static_cast<int32_t>(u) >> 31) | 0x80000000u);
+}
+__host__ __device__ inline float ordered_key_value(uint32_t key)
+{
+    const uint32_t u = (key >> 31) ? (key & 0x7FFFFFFFu) : ~key;
+#ifdef __CUDA_ARCH__
+    return __uint_as_float(u);
+#else
+    float f;
+    memcpy(&f, &u, 4);
+    return f;
+#endif
+}
+__global__ void score_stats_kernel(const uint2* postings, const uint64_t* new_len, const uint64_t* new_off,
+                                   uint64_t n_keys, uint32_t* stats)
+{
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint64_t warp = (blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x) >> 5;
+    const uint64_t n_warps = (static_cast<uint64_t>(gridDim.x) * blockDim.x) >> 5;
+    uint32_t lo = 0xFFFFFFFFu, hi = 0u, tiny = 0x7F800000u, bad = 0u;
+    for (uint64_t i = warp; i < n_keys; i += n_warps)
+    {
+        const uint64_t n = new_len[i];
+        const uint2* list = postings + new_off[i];
+        for (uint64_t j = lane; j < n; j += 32)
+        {
+            const float s = __uint_as_float(list[j].y);
+            const uint32_t mag = list[j].y & 0x7FFFFFFFu;
+            if (mag >= 0x7F800000u) { bad = 1u; continue; }
+            const uint32_t key = ordered_key(s);
+            lo = min(lo, key);
+            hi = max(hi, key);
+            if (mag != 0u) { tiny = min(tiny, mag); }
+        }
+    }
+    lo = __reduce_min_sync(0xFFFFFFFFu, lo);
+    hi = __reduce_max_sync(0xFFFFFFFFu, hi);
+    tiny = __reduce_min_sync(0xFFFFFFFFu, tiny);
+    bad = __reduce_max_sync(0xFFFFFFFFu, bad);
+    if (lane == 0)
+    {
+        atomicMin(stats + 0, lo);
+        atomicMax(stats + 1, hi);
+        atomicMin(stats + 2, tiny);
+        atomicMax(stats + 3, bad);
     }
 }
 

@@ -41,6 +41,10 @@ struct device_db
     uint32_t alphabet;
     float threshold;         // i2l::score_threshold(omega, k), place.cpp:87
     float log_threshold;     // std::log10 of it, place.cpp:88
+    float score_lo;          // smallest / largest score of the loaded postings (0 when there are none)
+    float score_hi;
+    uint32_t fast_ok;        // 1 when every score is finite, <= 0, and 0 or >= 1e-20 in magnitude:
+                             // the short arithmetic forms of the sweep then hold (place_kernel.cuh)
 };
 
 __host__ __device__ inline uint32_t hash_slot(uint32_t key, uint32_t shift)

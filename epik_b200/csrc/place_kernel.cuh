@@ -10,16 +10,18 @@
 //      independent loads in flight per lane);
 //   2. expands the hits, in window order, into segment descriptors (<= 64 postings each) and
 //      gathers them with 128-bit loads (two (branch, score) postings per lane), U segments in
-//      flight while the previous U are being applied to the per-branch accumulators
-//      {float S, uint32 C} in shared memory. Segments are applied in window order and a list
-//      never names a branch twice, so every S[b] sees exactly the additions of place.cpp:358-367
-//      in the same order: the sums are bit-identical to the reference's, without atomics;
+//      flight while the previous U are being applied to the per-branch accumulators in shared
+//      memory: float S[N] and a count C[N] whose width follows the number of windows of the
+//      query (uint8 up to 255 windows, uint16 up to 65535, uint32 beyond; one kernel
+//      instantiation per width, so that 150-bp reads pay 5 bytes per branch and 8 warps fit one
+//      SM at N = 5000). Segments are applied in window order and a list never names a branch
+//      twice, so every S[b] sees exactly the additions of place.cpp:358-367 in the same order:
+//      the sums are bit-identical to the reference's, without atomics;
 //   3. (only for reads that have windows with one ambiguous letter) replays place.cpp:373-415;
-//   4. sweeps the accumulators twice. Pass A: omega-threshold correction (place.cpp:417-422),
-//      FP64 10^S summed over all touched branches (sum_scores) and the per-lane maximum. The
-//      keep_at_most-th largest lane maximum is a lower bound of the keep_at_most-th best score,
-//      so pass B only has to collect the few branches at or above it (and clears the
-//      accumulators on the way);
+//   4. sweeps the accumulators ONCE, four consecutive branches per lane and step: omega-threshold
+//      correction (place.cpp:417-422), FP64 10^S summed over the touched branches (sum_scores),
+//      collection of the top-k candidates against a bar that rises as candidates accumulate, and
+//      clearing of the accumulators for the next query;
 //   5. picks the best keep_at_most candidates with warp reductions, computes the likelihood
 //      weight ratios in FP64 and applies keep_factor.
 // Float expressions that the reference evaluates without fused multiply-add are written with
@@ -40,12 +42,23 @@ constexpr int SEG_LEN = 64;            // postings per segment: one 128-bit load
 constexpr int SEG_PAD = 8;             // zero descriptors after the last one (= segments in flight)
 constexpr int CAND_CAP = 128;          // top-k candidates buffered per warp (aliases the segments)
 constexpr int MAX_WARPS_PER_CTA = 8;
+constexpr int SWEEP_STEP = 128;        // branches per warp and sweep step (4 per lane)
 constexpr uint32_t NO_BRANCH = 0xFFFFFFFFu;
 constexpr uint32_t FULL = 0xFFFFFFFFu;
 
 static_assert(CAND_CAP * 12 <= SEG_CAP * 8, "candidate arrays alias the segment buffer");
 
-enum counter_slot { CTR_CURSOR = 0, CTR_WINDOWS = 1, CTR_HITS = 2, CTR_ENTRIES = 3, CTR_SHORT = 4, CTR_COUNT = 8 };
+// One kernel instantiation per width of the hit counts: class c handles the queries with
+// CLASS_MIN_WINDOWS[c] <= windows <= CLASS_MAX_WINDOWS[c].
+constexpr int N_CLASSES = 3;
+__host__ __device__ constexpr uint64_t class_max_windows(int c) { return c == 0 ? 255ull : c == 1 ? 65535ull : 0xFFFFFFFFull; }
+__host__ __device__ constexpr uint32_t class_count_bytes(int c) { return c == 0 ? 1u : c == 1 ? 2u : 4u; }
+__host__ __device__ inline int class_of_windows(uint64_t n_windows)
+{
+    return n_windows <= class_max_windows(0) ? 0 : n_windows <= class_max_windows(1) ? 1 : 2;
+}
+
+enum counter_slot { CTR_CURSOR = 0, CTR_WINDOWS = 1, CTR_HITS = 2, CTR_ENTRIES = 3, CTR_SHORT = 4, CTR_TOO_LONG = 5, CTR_UNSUPPORTED = 6, CTR_COUNT = 8 };
 
 struct place_params
 {
@@ -62,17 +75,47 @@ struct place_params
     uint32_t* count;
     const uint32_t* letters;     // [256] letter table
     const uint32_t* fake_order;  // [keep_at_most] order of the zero-hit placements
-    unsigned long long* counters; // [CTR_COUNT]
+    unsigned long long* counters; // [CTR_COUNT] of this launch
+    const uint32_t* class_reads; // [N_CLASSES] queries per class (classify_kernel); NULL = unknown
+    uint32_t cls;                // class this launch handles
 };
 
-// bytes of shared memory one warp needs for a tree of n_nodes
-__host__ __device__ inline size_t warp_smem_bytes(uint32_t n_nodes)
+__host__ __device__ inline uint32_t padded_nodes(uint32_t n_nodes)
 {
-    size_t acc = (static_cast<size_t>(n_nodes) * 8 + 15) & ~static_cast<size_t>(15);
-    size_t seen = ((static_cast<size_t>(n_nodes) + 31) / 32 * 4 + 15) & ~static_cast<size_t>(15);
-    return acc + seen + (SEG_CAP + SEG_PAD) * 8 + CODE_BYTES;
+    return (n_nodes + SWEEP_STEP - 1) / SWEEP_STEP * SWEEP_STEP;
+}
+
+// bytes of shared memory one warp needs for a tree of n_nodes and counts of count_bytes
+__host__ __device__ inline size_t warp_smem_bytes(uint32_t n_nodes, uint32_t count_bytes)
+{
+    const size_t np = padded_nodes(n_nodes);
+    return np * 4 + np * count_bytes + np / 8 + (SEG_CAP + SEG_PAD) * 8 + CODE_BYTES;
 }
 constexpr size_t CTA_SMEM_FIXED = 1024; // letter table
+
+// Number of queries of each class (sequences shorter than k - 1 letters count for class 0, which
+// reports them). Classes in unsupported_mask have no launch: their rows get n_place = 0 here.
+__global__ void classify_kernel(const uint64_t* __restrict__ seq_off, uint32_t n, uint32_t k, uint32_t* class_reads,
+                                uint32_t unsupported_mask, uint32_t* n_place)
+{
+    uint32_t mine[N_CLASSES] = { 0, 0, 0 };
+    for (uint64_t i = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x; i < n;
+         i += static_cast<uint64_t>(gridDim.x) * blockDim.x)
+    {
+        const uint64_t len = seq_off[i + 1] - seq_off[i];
+        const int c = len + 1 < k ? 0 : class_of_windows(len + 1 - k);
+        if ((unsupported_mask >> c) & 1u) { n_place[i] = 0; } // no launch will write this row
+        mine[0] += c == 0;
+        mine[1] += c == 1;
+        mine[2] += c == 2;
+    }
+#pragma unroll
+    for (int c = 0; c < N_CLASSES; ++c)
+    {
+        const uint32_t total = __reduce_add_sync(FULL, mine[c]);
+        if ((threadIdx.x & 31u) == 0 && total) { atomicAdd(class_reads + c, total); }
+    }
+}
 
 struct window_class
 {
@@ -105,17 +148,18 @@ __device__ __forceinline__ window_class classify_window(CodePtr codes, uint32_t 
 
 // ---- arithmetic helpers -------------------------------------------------------------------
 
-// Taylor coefficients ln(2)^i / i!, i = 12 .. 1, of 2^f (constant bank: DFMA takes them as operands)
-__constant__ double EXP2_POLY[12] = {
-    2.5678435993488206e-11, 4.4455382718708116e-10, 7.054911620801123e-09, 1.01780860092397e-07,
-    1.321548679014431e-06,  1.5252733804059841e-05, 0.0001540353039338161, 0.0013333558146428443,
-    0.009618129107628477,   0.05550410866482158,    0.24022650695910072,   0.6931471805599453 };
+// Coefficients c8 .. c1 of a degree-8 near-minimax polynomial of 2^f on |f| <= 1/2 (c0 = 1);
+// relative error 2.2e-12 (tools/exp2_poly.py). Constant bank: DFMA takes them as operands.
+__constant__ double EXP2_POLY[8] = {
+    1.325522879405974e-06, 1.5303702622244995e-05, 0.0001540345583542578, 0.001333347846654947,
+    0.009618129159424775,  0.05550410906332551,    0.24022650695812914,   0.6931471805568318 };
 
 // 10^s in FP64 for a float exponent with |s| < 300 (sum_scores and the LWR loop call
 // std::pow(10.0, double(s)), place.cpp:44-47,175,254). 10^s = 2^n * 2^f with
-// n = rint(s*log2(10)), |f| <= 1/2, 2^f by its Taylor polynomial of degree 12. Relative error
-// below 1e-13, dominated by the single-double log2(10) in the reduction; it is common to all
-// terms of a ratio to first order. Straight-line code: callers interleave several of these.
+// n = rint(s*log2(10)), |f| <= 1/2, 2^f by the polynomial above. Relative error below 3e-12:
+// four orders of magnitude under what the float score itself resolves (an ulp of a score near
+// -60 moves 10^s by 9e-6) and under the 1e-9 the parity tests ask of the weight ratios.
+// Straight-line code: callers interleave several of these.
 __device__ __forceinline__ double exp10_small(float s)
 {
     const double t = static_cast<double>(s) * 3.321928094887362;
@@ -124,31 +168,27 @@ __device__ __forceinline__ double exp10_small(float s)
     const double f = t - (shifted - 6755399441055744.0);
     double p = EXP2_POLY[0];
 #pragma unroll
-    for (int i = 1; i < 12; ++i) { p = fma(p, f, EXP2_POLY[i]); }
+    for (int i = 1; i < 8; ++i) { p = fma(p, f, EXP2_POLY[i]); }
     p = fma(p, f, 1.0);
     return __hiloint2double(__double2hiint(p) + (n << 20), __double2loint(p));
 }
-__device__ __forceinline__ bool exp10_is_small(float s) { return fabsf(s) < 300.0f; }
+constexpr float EXP10_SMALL_LIMIT = 290.0f;
 
 // any exponent: near the ends of the FP64 range the library routine takes over (gradual underflow
 // is part of the reference's behaviour for long queries)
 __device__ __forceinline__ double exp10_of_float(float s)
 {
-    return exp10_is_small(s) ? exp10_small(s) : exp10(static_cast<double>(s));
+    return fabsf(s) < EXP10_SMALL_LIMIT ? exp10_small(s) : exp10(static_cast<double>(s));
 }
 
 // x / kf, correctly rounded (place.cpp:421 divides the corrected score by the k-mer size):
 // q = x*r, one FMA residual step with r = RN(1/kf). Checked exhaustively against x / kf for
-// every float with 1e-30 < |x| < 1e30 and kf = 1..32 (div_is_plain); the rest takes __fdiv_rn.
+// every float with 1e-30 < |x| < 1e30 and kf = 1..32 (tools/check_div.cu); +0 stays +0. Queries
+// whose scores could leave that range take the sweep with __fdiv_rn (see fast_sweep_ok).
 __device__ __forceinline__ float div_by_k_plain(float x, float kf, float rcp)
 {
     const float q = __fmul_rn(x, rcp);
     return __fmaf_rn(__fmaf_rn(-q, kf, x), rcp, q);
-}
-__device__ __forceinline__ bool div_is_plain(float x)
-{
-    const float ax = fabsf(x);
-    return ax > 1e-30f && ax < 1e30f;
 }
 
 // order-preserving map float -> uint32 (and back); -0 and +0 are made one value first
@@ -217,64 +257,64 @@ __device__ __forceinline__ void load_segment(const unsigned char* lane_base, uin
         : "memory");
 }
 
+// The accumulators of one warp: float S[np] and CT C[np] (np = padded_nodes(N)), as shared-window
+// addresses for the PTX below.
+struct acc_ref
+{
+    uint32_t s_shared; // S
+    uint32_t c_shared; // C
+};
+
 // place.cpp:358-367 for the (up to) two postings a lane holds of one segment; branches of one
 // list are distinct, so the two read-modify-writes of a lane and those of different lanes are
-// independent.
-__device__ __forceinline__ void apply_segment(uint32_t acc_shared, uint32_t lane2, const seg_regs& r)
-{
-#ifdef EPK_CXX_APPLY
-    extern __shared__ __align__(16) unsigned char smem_base[];
-    const uint32_t smem0 = static_cast<uint32_t>(__cvta_generic_to_shared(smem_base));
-    float2* acc = reinterpret_cast<float2*>(smem_base + (acc_shared - smem0));
-    const bool p0 = lane2 < r.cnt, p1 = lane2 + 1 < r.cnt;
-    float2 a0 = acc[r.b0], a1 = acc[r.b1];
-    a0.x = __fadd_rn(a0.x, __uint_as_float(r.s0));
-    a1.x = __fadd_rn(a1.x, __uint_as_float(r.s1));
-    a0.y = __uint_as_float(__float_as_uint(a0.y) + 1u);
-    a1.y = __uint_as_float(__float_as_uint(a1.y) + 1u);
-    if (p0) { acc[r.b0] = a0; }
-    if (p1) { acc[r.b1] = a1; }
-    __syncwarp();
-    return;
-#endif
-    asm volatile(
-        "{\n\t"
-        ".reg .pred p0, p1;\n\t"
-        ".reg .b32 a0, a1, c0, c1, x0, x1;\n\t"
-        ".reg .f32 f0, f1;\n\t"
-        "setp.lt.u32 p0, %5, %4;\n\t"
-        "setp.lt.u32 p1, %6, %4;\n\t"
-        "shl.b32 a0, %0, 3;\n\t"
-        "shl.b32 a1, %2, 3;\n\t"
-        "add.u32 a0, a0, %7;\n\t"
-        "add.u32 a1, a1, %7;\n\t"
-        "ld.shared.v2.b32 {x0, c0}, [a0];\n\t" // lanes past the end hold 0 or an older, valid branch
-        "ld.shared.v2.b32 {x1, c1}, [a1];\n\t"
-        "mov.b32 f0, x0;\n\t"
-        "mov.b32 f1, x1;\n\t"
-        "add.rn.f32 f0, f0, %1;\n\t"
-        "add.rn.f32 f1, f1, %3;\n\t"
-        "add.u32 c0, c0, 1;\n\t"
-        "add.u32 c1, c1, 1;\n\t"
-        "mov.b32 x0, f0;\n\t"
-        "mov.b32 x1, f1;\n\t"
-        "@p0 st.shared.v2.b32 [a0], {x0, c0};\n\t"
-        "@p1 st.shared.v2.b32 [a1], {x1, c1};\n\t"
-        "}"
-        :
-        : "r"(r.b0), "f"(__uint_as_float(r.s0)), "r"(r.b1), "f"(__uint_as_float(r.s1)), "r"(r.cnt), "r"(lane2),
-          "r"(lane2 + 1u), "r"(acc_shared)
-        : "memory");
-    __syncwarp(); // the next segment may name the same branches from other lanes
-}
+// independent. Lanes past the end of the segment hold 0 or an older, valid branch: they read it
+// and store nothing.
+#define EPK_APPLY_SEGMENT(CT, LD, ST)                                                                      \
+    __device__ __forceinline__ void apply_segment(const acc_ref& acc, uint32_t lane2, const seg_regs& r, CT) \
+    {                                                                                                      \
+        asm volatile(                                                                                      \
+            "{\n\t"                                                                                        \
+            ".reg .pred p0, p1;\n\t"                                                                       \
+            ".reg .b32 a0, a1, d0, d1, c0, c1;\n\t"                                                        \
+            ".reg .f32 f0, f1;\n\t"                                                                        \
+            "setp.lt.u32 p0, %5, %4;\n\t"                                                                  \
+            "setp.lt.u32 p1, %6, %4;\n\t"                                                                  \
+            "mad.lo.u32 a0, %0, 4, %7;\n\t"                                                                \
+            "mad.lo.u32 a1, %2, 4, %7;\n\t"                                                                \
+            "mad.lo.u32 d0, %0, %9, %8;\n\t"                                                               \
+            "mad.lo.u32 d1, %2, %9, %8;\n\t"                                                               \
+            "ld.shared.f32 f0, [a0];\n\t"                                                                  \
+            "ld.shared.f32 f1, [a1];\n\t"                                                                  \
+            "ld.shared." LD " c0, [d0];\n\t"                                                               \
+            "ld.shared." LD " c1, [d1];\n\t"                                                               \
+            "add.rn.f32 f0, f0, %1;\n\t"                                                                   \
+            "add.rn.f32 f1, f1, %3;\n\t"                                                                   \
+            "add.u32 c0, c0, 1;\n\t"                                                                       \
+            "add.u32 c1, c1, 1;\n\t"                                                                       \
+            "@p0 st.shared.f32 [a0], f0;\n\t"                                                              \
+            "@p1 st.shared.f32 [a1], f1;\n\t"                                                              \
+            "@p0 st.shared." ST " [d0], c0;\n\t"                                                           \
+            "@p1 st.shared." ST " [d1], c1;\n\t"                                                           \
+            "}"                                                                                            \
+            :                                                                                              \
+            : "r"(r.b0), "f"(__uint_as_float(r.s0)), "r"(r.b1), "f"(__uint_as_float(r.s1)), "r"(r.cnt),    \
+              "r"(lane2), "r"(lane2 + 1u), "r"(acc.s_shared), "r"(acc.c_shared),                           \
+              "n"(static_cast<int>(sizeof(CT)))                                                            \
+            : "memory");                                                                                   \
+        __syncwarp(); /* the next segment may name the same branches from other lanes */                  \
+    }
+EPK_APPLY_SEGMENT(uint8_t, "u8", "u8")
+EPK_APPLY_SEGMENT(uint16_t, "u16", "u16")
+EPK_APPLY_SEGMENT(uint32_t, "u32", "u32")
+#undef EPK_APPLY_SEGMENT
 
 // Applies segs[0, n) in order; U segments are in flight while the previous U are applied.
 // segs[n, n + U) must hold zero descriptors.
 #ifndef EPK_GATHER_INLINE
 #define EPK_GATHER_INLINE __noinline__
 #endif
-template<int U>
-__device__ EPK_GATHER_INLINE void gather_segments(const uint2* __restrict__ postings, uint32_t acc_shared, uint32_t segs_shared,
+template<int U, class CT>
+__device__ EPK_GATHER_INLINE void gather_segments(const uint2* __restrict__ postings, acc_ref acc, uint32_t segs_shared,
                                              uint32_t n, uint32_t lane)
 {
     const unsigned char* lane_base = reinterpret_cast<const unsigned char*>(postings) + 16u * lane;
@@ -297,7 +337,7 @@ __device__ EPK_GATHER_INLINE void gather_segments(const uint2* __restrict__ post
             for (int u = 0; u < U; ++u) { load_segment(lane_base, segs_shared, first + U + u, lane2, b[u]); }
         }
 #pragma unroll
-        for (int u = 0; u < U; ++u) { apply_segment(acc_shared, lane2, a[u]); }
+        for (int u = 0; u < U; ++u) { apply_segment(acc, lane2, a[u], CT{}); }
         if (!more_b) { break; }
         if (first + 2 * U < n)
         {
@@ -305,12 +345,13 @@ __device__ EPK_GATHER_INLINE void gather_segments(const uint2* __restrict__ post
             for (int u = 0; u < U; ++u) { load_segment(lane_base, segs_shared, first + 2 * U + u, lane2, a[u]); }
         }
 #pragma unroll
-        for (int u = 0; u < U; ++u) { apply_segment(acc_shared, lane2, b[u]); }
+        for (int u = 0; u < U; ++u) { apply_segment(acc, lane2, b[u], CT{}); }
     }
 }
 
 // One long list on its own (only when a single chunk's lists overflow the segment buffer).
-__device__ __noinline__ void apply_list(const uint2* __restrict__ postings, uint32_t acc_shared, uint64_t off, uint32_t len,
+template<class CT>
+__device__ __noinline__ void apply_list(const uint2* __restrict__ postings, acc_ref acc, uint64_t off, uint32_t len,
                                         uint32_t lane)
 {
     const uint32_t lane2 = 2u * lane;
@@ -322,7 +363,7 @@ __device__ __noinline__ void apply_list(const uint2* __restrict__ postings, uint
             const uint4 v = __ldg(reinterpret_cast<const uint4*>(postings + off + pos) + lane);
             r.b0 = v.x; r.s0 = v.y; r.b1 = v.z; r.s1 = v.w;
         }
-        apply_segment(acc_shared, lane2, r);
+        apply_segment(acc, lane2, r, CT{});
     }
 }
 
@@ -396,16 +437,165 @@ __device__ __forceinline__ uint32_t select_best(uint32_t* cand_key, uint32_t* ca
     return n_sel;
 }
 
+// ---- the sweep over the accumulators ---------------------------------------------------------------
+
+// four consecutive hit counts, and their clearing, by width
+__device__ __forceinline__ void load_counts4(const uint8_t* C, uint32_t j, uint32_t (&c)[4])
+{
+    const uint32_t w = *reinterpret_cast<const uint32_t*>(C + j);
+    c[0] = w & 0xFFu; c[1] = (w >> 8) & 0xFFu; c[2] = (w >> 16) & 0xFFu; c[3] = w >> 24;
+}
+__device__ __forceinline__ void load_counts4(const uint16_t* C, uint32_t j, uint32_t (&c)[4])
+{
+    const uint2 w = *reinterpret_cast<const uint2*>(C + j);
+    c[0] = w.x & 0xFFFFu; c[1] = w.x >> 16; c[2] = w.y & 0xFFFFu; c[3] = w.y >> 16;
+}
+__device__ __forceinline__ void load_counts4(const uint32_t* C, uint32_t j, uint32_t (&c)[4])
+{
+    const uint4 w = *reinterpret_cast<const uint4*>(C + j);
+    c[0] = w.x; c[1] = w.y; c[2] = w.z; c[3] = w.w;
+}
+__device__ __forceinline__ void clear_counts4(uint8_t* C, uint32_t j) { *reinterpret_cast<uint32_t*>(C + j) = 0u; }
+__device__ __forceinline__ void clear_counts4(uint16_t* C, uint32_t j) { *reinterpret_cast<uint2*>(C + j) = make_uint2(0u, 0u); }
+__device__ __forceinline__ void clear_counts4(uint32_t* C, uint32_t j) { *reinterpret_cast<uint4*>(C + j) = make_uint4(0u, 0u, 0u, 0u); }
+
+// Terms of the likelihood mass more than this many decades under a term already summed by the same
+// lane are left out: each is below 1e-20 of the total, all of them together below N * 1e-20.
+constexpr float MASS_CUTOFF_DECADES = 20.0f;
+
+struct sweep_result
+{
+    double mass;       // sum over the touched branches of 10^score            (place.cpp:174-175)
+    uint32_t touched;  // |L|: branches with at least one hit                   (place.cpp:166)
+    uint32_t n_keep;   // min(keep_at_most, touched); lane i < n_keep holds the i-th best in key/branch/count
+    uint32_t key, branch, count;
+};
+
+// One pass over S[0, np), C[0, np) of a query with nw windows; leaves both arrays zeroed.
+// Per branch b with C[b] != 0 (place.cpp:417-422):  S[b] += float(nw - C[b]) * log10thr;  S[b] /= k.
+// FAST: the short forms of the division and of 10^s (valid for the score range established by
+// fast_sweep_ok) and the mass cut-off; otherwise the IEEE division and the library exp10, every term.
+template<class CT, bool FAST>
+__device__ __forceinline__ sweep_result sweep(float* S, CT* C, uint32_t np, uint32_t nw32, float logthr, float kf,
+                                              float rcp_k, uint32_t K, uint32_t lane, uint32_t* cand_key,
+                                              uint32_t* cand_branch, uint32_t* cand_count)
+{
+    sweep_result out{ 0.0, 0u, 0u, 0u, NO_BRANCH, 0u };
+    double mass = 0.0;
+    uint32_t touched = 0, n_cand = 0;
+    uint32_t bar_key = 0, bar_branch = 0; // a candidate beats (bar_key, bar_branch); nothing beats key 0 / branch 0
+    uint32_t lane_max = 0;                // best score key this lane has seen
+    for (uint32_t j0 = 0; j0 < np; j0 += SWEEP_STEP) // warp-uniform trip count
+    {
+        const uint32_t j = j0 + 4u * lane;
+        const float4 s4 = *reinterpret_cast<const float4*>(S + j);
+        uint32_t c[4];
+        load_counts4(C, j, c);
+        *reinterpret_cast<float4*>(S + j) = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        clear_counts4(C, j);
+        const float sum[4] = { s4.x, s4.y, s4.z, s4.w };
+        float s[4];
+        uint32_t key[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+        {
+            // the reference converts the size_t difference to float (place.cpp:420)
+            const float x = __fadd_rn(sum[u], __fmul_rn(static_cast<float>(nw32 - c[u]), logthr));
+            s[u] = FAST ? div_by_k_plain(x, kf, rcp_k) : __fdiv_rn(x, kf);
+            key[u] = c[u] != 0 ? score_key(s[u]) : 0u;
+            touched += c[u] != 0;
+            lane_max = max(lane_max, key[u]);
+        }
+        // ---- likelihood mass (place.cpp:164-184) ----
+        bool in[4];
+        if (FAST)
+        {
+            const uint32_t cut = score_key(key_score(lane_max) - MASS_CUTOFF_DECADES);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { in[u] = key[u] != 0 && key[u] >= cut; }
+        }
+        else
+        {
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { in[u] = key[u] != 0; }
+        }
+        if (__any_sync(FULL, in[0] | in[1] | in[2] | in[3]))
+        {
+            double e[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { e[u] = FAST ? exp10_small(s[u]) : exp10(static_cast<double>(s[u])); }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { mass += in[u] ? e[u] : 0.0; }
+        }
+        // ---- top-k candidates (place.cpp:134-159) ----
+        bool cand[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) { cand[u] = (key[u] > bar_key) | ((key[u] == bar_key) & (j + u < bar_branch)); }
+        if (__any_sync(FULL, cand[0] | cand[1] | cand[2] | cand[3]))
+        {
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+            {
+                const uint32_t ballot = __ballot_sync(FULL, cand[u]);
+                if (cand[u])
+                {
+                    const uint32_t at = n_cand + __popc(ballot & ((1u << lane) - 1u));
+                    cand_key[at] = key[u];
+                    cand_branch[at] = j + u;
+                    cand_count[at] = c[u];
+                }
+                n_cand += __popc(ballot);
+                __syncwarp();
+                if (n_cand > CAND_CAP - 32)
+                {
+                    // keep the best K, raise the bar to the K-th of them. Later branches of this
+                    // step were tested against the old bar: a few extra candidates, never a miss.
+                    n_cand = select_best(cand_key, cand_branch, cand_count, n_cand, K, lane, out.key, out.branch, out.count);
+                    if (n_cand == K)
+                    {
+                        bar_key = __shfl_sync(FULL, out.key, K - 1);
+                        bar_branch = __shfl_sync(FULL, out.branch, K - 1);
+                    }
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1)
+    {
+        mass += __shfl_xor_sync(FULL, mass, d);
+        touched += __shfl_xor_sync(FULL, touched, d);
+    }
+    __syncwarp();
+    out.n_keep = select_best(cand_key, cand_branch, cand_count, n_cand, K, lane, out.key, out.branch, out.count);
+    out.mass = mass;
+    out.touched = touched;
+    return out;
+}
+
+// Whether every score a query with nwf windows can end up with stays inside what the short forms
+// of the sweep were checked for: |score| < EXP10_SMALL_LIMIT, and a corrected sum that is 0 or has
+// 1e-30 < |x| < 1e30 (the database guarantees the latter through fast_ok: finite scores <= 0 with
+// magnitude 0 or >= 1e-20).
+__device__ __forceinline__ bool fast_sweep_ok(const device_db& db, float nwf, float kf)
+{
+    const float lo = nwf * fminf(db.score_lo, db.log_threshold) / kf;
+    const float hi = (nwf * fmaxf(db.log_threshold, 0.0f) + 1.0f) / kf; // ambiguous windows add at most 1 (a probability)
+    return db.fast_ok != 0 && lo > -EXP10_SMALL_LIMIT && hi < EXP10_SMALL_LIMIT;
+}
+
 // ---- the kernel ----------------------------------------------------------------------------------
 
-template<uint32_t TABLE, int U>
+template<uint32_t TABLE, int U, class CT>
 __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const place_params p)
 {
     extern __shared__ __align__(16) unsigned char smem[];
+    if (p.class_reads && p.class_reads[p.cls] == 0) { return; } // no query of this class in the batch
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t warp = threadIdx.x >> 5;
     const device_db& db = p.db;
     const uint32_t N = db.n_nodes;
+    const uint32_t np = padded_nodes(N);
     const uint32_t k = db.k;
     const uint32_t bits = db.bits;
     const uint32_t K = p.keep_at_most;
@@ -414,21 +604,25 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
     uint32_t* letters = reinterpret_cast<uint32_t*>(smem);
     for (uint32_t i = threadIdx.x; i < 256; i += blockDim.x) { letters[i] = p.letters[i]; }
 
-    unsigned char* base = smem + CTA_SMEM_FIXED + warp * warp_smem_bytes(N);
-    const size_t acc_bytes = (static_cast<size_t>(N) * 8 + 15) & ~static_cast<size_t>(15);
-    const size_t seen_words = (static_cast<size_t>(N) + 31) / 32;
-    const size_t seen_bytes = (seen_words * 4 + 15) & ~static_cast<size_t>(15);
-    float2* acc = reinterpret_cast<float2*>(base);
-    uint32_t* seen = reinterpret_cast<uint32_t*>(base + acc_bytes);
-    uint2* segs = reinterpret_cast<uint2*>(base + acc_bytes + seen_bytes);
+    // per warp: float S[np] | CT C[np] | seen bitmap np/8 bytes | segment descriptors | letter codes
+    unsigned char* base = smem + CTA_SMEM_FIXED + warp * warp_smem_bytes(N, sizeof(CT));
+    float* S = reinterpret_cast<float*>(base);
+    CT* C = reinterpret_cast<CT*>(base + static_cast<size_t>(np) * 4);
+    uint32_t* seen = reinterpret_cast<uint32_t*>(base + static_cast<size_t>(np) * (4 + sizeof(CT)));
+    const uint32_t seen_words = np / 32;
+    uint2* segs = reinterpret_cast<uint2*>(reinterpret_cast<unsigned char*>(seen) + np / 8);
     const uint32_t segs_shared = static_cast<uint32_t>(__cvta_generic_to_shared(segs));
-    const uint32_t acc_shared = static_cast<uint32_t>(__cvta_generic_to_shared(acc));
-    uint32_t* cand_key = reinterpret_cast<uint32_t*>(segs); // the segment buffer is idle during the sweeps
+    const acc_ref acc{ static_cast<uint32_t>(__cvta_generic_to_shared(S)), static_cast<uint32_t>(__cvta_generic_to_shared(C)) };
+    uint32_t* cand_key = reinterpret_cast<uint32_t*>(segs); // the segment buffer is idle during the sweep
     uint32_t* cand_branch = cand_key + CAND_CAP;
     uint32_t* cand_count = cand_branch + CAND_CAP;
-    uint8_t* codes = reinterpret_cast<uint8_t*>(base + acc_bytes + seen_bytes + (SEG_CAP + SEG_PAD) * 8);
+    uint8_t* codes = reinterpret_cast<uint8_t*>(segs + SEG_CAP + SEG_PAD);
 
-    for (uint32_t b = lane; b < N; b += 32) { acc[b] = make_float2(0.0f, 0.0f); }
+    for (uint32_t b = lane; b < np; b += 32)
+    {
+        S[b] = 0.0f;
+        C[b] = 0;
+    }
     for (uint32_t i = lane; i < seen_words; i += 32) { seen[i] = 0; }
     __syncthreads();
 
@@ -450,7 +644,7 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
         if (len + 1 < k)
         {
             // the reference dies here (size_t wrap at place.cpp:291); reported as EPK_E_SHORT_SEQ
-            if (lane == 0)
+            if (lane == 0 && p.cls == 0)
             {
                 atomicAdd(p.counters + CTR_SHORT, 1ull);
                 p.n_place[q] = 0;
@@ -458,6 +652,16 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
             continue;
         }
         const uint64_t n_windows = len + 1 - k; // place.cpp:322, counts skipped windows too
+        if (class_of_windows(n_windows) != static_cast<int>(p.cls)) { continue; } // another launch's query
+        if (n_windows > class_max_windows(N_CLASSES - 1))
+        {
+            if (lane == 0)
+            {
+                atomicAdd(p.counters + CTR_TOO_LONG, 1ull);
+                p.n_place[q] = 0;
+            }
+            continue;
+        }
         const char* seq = p.seq + s0;
         bool has_ambiguous = false;
         uint32_t nseg = 0;
@@ -531,7 +735,7 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
             {
                 if (lane < SEG_PAD) { segs[nseg + lane] = make_uint2(0, 0); }
                 __syncwarp();
-                gather_segments<U>(db.postings, acc_shared, segs_shared, nseg, lane);
+                gather_segments<U, CT>(db.postings, acc, segs_shared, nseg, lane);
                 nseg = 0;
                 __syncwarp();
             }
@@ -560,7 +764,7 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
                     {
                         const uint64_t s = __shfl_sync(FULL, slot[r], src);
                         const uint32_t l = static_cast<uint32_t>(s & LEN_MASK);
-                        if (l) { apply_list(db.postings, acc_shared, s >> LEN_BITS, l, lane); }
+                        if (l) { apply_list<CT>(db.postings, acc, s >> LEN_BITS, l, lane); }
                     }
                 }
             }
@@ -569,7 +773,7 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
         {
             if (lane < SEG_PAD) { segs[nseg + lane] = make_uint2(0, 0); }
             __syncwarp();
-            gather_segments<U>(db.postings, acc_shared, segs_shared, nseg, lane);
+            gather_segments<U, CT>(db.postings, acc, segs_shared, nseg, lane);
         }
         __syncwarp();
 
@@ -627,10 +831,8 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
                                     // added to the LOG score (place.cpp:391,400-410)
                                     const float prob = static_cast<float>(pow(10.0, static_cast<double>(__uint_as_float(entry.y))));
                                     const float mean = __fdiv_rn(__fadd_rn(prob, thr_rest), kf);
-                                    float2 a = acc[entry.x];
-                                    a.x = __fadd_rn(a.x, mean);
-                                    a.y = __uint_as_float(__float_as_uint(a.y) + 1u);
-                                    acc[entry.x] = a;
+                                    S[entry.x] = __fadd_rn(S[entry.x], mean);
+                                    C[entry.x] = static_cast<CT>(C[entry.x] + 1u);
                                 }
                             }
                             __syncwarp();
@@ -642,144 +844,22 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
             __syncwarp();
         }
 
-        // ---- pass A: correction (place.cpp:417-422), likelihood mass (:164-184), lane maxima ----
-        // Four branches per lane and iteration, straight-line, so that the four FP64 chains overlap.
-        // The corrected score replaces S as its order-preserving key; C stays.
+        // ---- correction, likelihood mass, top-k (place.cpp:417-422, 164-184, 134-159) ----
         const uint32_t nw32 = static_cast<uint32_t>(n_windows);
-        double mass = 0.0;
-        uint32_t touched = 0;
-        uint32_t lane_best = 0; // score key of my best branch, 0 = none
-        for (uint32_t base0 = 0; base0 < N; base0 += 128) // warp-uniform trip count
-        {
-            const uint32_t b0 = base0 + lane;
-            float2 a[4];
-            float x[4], s[4];
-            double e[4];
-            bool odd = false;
-#pragma unroll
-            for (int u = 0; u < 4; ++u)
-            {
-                const uint32_t b = b0 + 32u * u;
-                a[u] = b < N ? acc[b] : make_float2(0.0f, 0.0f);
-            }
-#pragma unroll
-            for (int u = 0; u < 4; ++u)
-            {
-                const uint32_t c = __float_as_uint(a[u].y);
-                // the reference converts the size_t difference to float (place.cpp:420)
-                x[u] = __fadd_rn(a[u].x, __fmul_rn(static_cast<float>(nw32 - c), logthr));
-                s[u] = div_by_k_plain(x[u], kf, rcp_k);
-                e[u] = exp10_small(s[u]);
-                odd |= c != 0 && !(div_is_plain(x[u]) && exp10_is_small(s[u]));
-            }
-            if (odd)
-            {
-                // outside what the short forms were checked for (very long queries): the IEEE routines
-#pragma unroll
-                for (int u = 0; u < 4; ++u)
-                {
-                    s[u] = __fdiv_rn(x[u], kf);
-                    e[u] = exp10(static_cast<double>(s[u]));
-                }
-            }
-#pragma unroll
-            for (int u = 0; u < 4; ++u)
-            {
-                const uint32_t b = b0 + 32u * u;
-                if (__float_as_uint(a[u].y) != 0)
-                {
-                    const uint32_t key = score_key(s[u]);
-                    acc[b].x = __uint_as_float(key);
-                    mass += e[u];
-                    ++touched;
-                    lane_best = max(lane_best, key);
-                }
-            }
-        }
-#pragma unroll
-        for (int d = 16; d > 0; d >>= 1)
-        {
-            mass += __shfl_xor_sync(FULL, mass, d);
-            touched += __shfl_xor_sync(FULL, touched, d);
-        }
-
-        // the K-th largest lane maximum bounds the K-th best score from below
-        uint32_t bar_key = 0, bar_branch = NO_BRANCH;
-        {
-            uint32_t mine = lane_best, kth = 0;
-            for (uint32_t i = 0; i < K; ++i)
-            {
-                kth = __reduce_max_sync(FULL, mine);
-                if (kth == 0) { break; }
-                const uint32_t first = __ffs(__ballot_sync(FULL, mine == kth)) - 1u;
-                if (lane == first) { mine = 0; }
-            }
-            bar_key = kth;
-        }
-
-        // ---- pass B: collect the branches at or above the bar, clear the accumulators ----
-        __syncwarp();
-        uint32_t n_cand = 0;
-        uint32_t my_key = 0, my_b = NO_BRANCH, my_c = 0;
-        for (uint32_t base0 = 0; base0 < N; base0 += 128) // warp-uniform trip count
-        {
-            const uint32_t b0 = base0 + lane;
-            uint32_t key[4], cnt[4];
-            bool cand[4];
-#pragma unroll
-            for (int u = 0; u < 4; ++u)
-            {
-                const uint32_t b = b0 + 32u * u;
-                float2 a = make_float2(0.0f, 0.0f);
-                if (b < N)
-                {
-                    a = acc[b];
-                    acc[b] = make_float2(0.0f, 0.0f);
-                }
-                key[u] = __float_as_uint(a.x);
-                cnt[u] = __float_as_uint(a.y);
-                cand[u] = (cnt[u] != 0) & ((key[u] > bar_key) | ((key[u] == bar_key) & (b < bar_branch)));
-            }
-            if (__any_sync(FULL, cand[0] | cand[1] | cand[2] | cand[3]))
-            {
-#pragma unroll
-                for (int u = 0; u < 4; ++u)
-                {
-                    const uint32_t ballot = __ballot_sync(FULL, cand[u]);
-                    if (cand[u])
-                    {
-                        const uint32_t at = n_cand + __popc(ballot & ((1u << lane) - 1u));
-                        cand_key[at] = key[u];
-                        cand_branch[at] = b0 + 32u * u;
-                        cand_count[at] = cnt[u];
-                    }
-                    n_cand += __popc(ballot);
-                    __syncwarp();
-                    if (n_cand > CAND_CAP - 32)
-                    {
-                        // keep the best K, raise the bar to the K-th of them. Later branches of this
-                        // group were tested against the old bar: a few extra candidates, never a miss.
-                        n_cand = select_best(cand_key, cand_branch, cand_count, n_cand, K, lane, my_key, my_b, my_c);
-                        if (n_cand == K)
-                        {
-                            bar_key = __shfl_sync(FULL, my_key, K - 1);
-                            bar_branch = __shfl_sync(FULL, my_b, K - 1);
-                        }
-                    }
-                }
-            }
-        }
-        __syncwarp();
-        const uint32_t n_keep = select_best(cand_key, cand_branch, cand_count, n_cand, K, lane, my_key, my_b, my_c);
-        float my_s = key_score(my_key);
+        const float nwf = static_cast<float>(n_windows);
+        const sweep_result sw = fast_sweep_ok(db, nwf, kf)
+                                    ? sweep<CT, true>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cand_key, cand_branch, cand_count)
+                                    : sweep<CT, false>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cand_key, cand_branch, cand_count);
+        const uint32_t touched = sw.touched;
+        uint32_t my_b = sw.branch, my_c = sw.count;
+        float my_s = key_score(sw.key);
 
         // ---- likelihood weight ratios and keep_factor (place.cpp:164-184, 241-267) ----
-        const float nwf = static_cast<float>(n_windows);
         const float absent_score = __fdiv_rn(__fmul_rn(nwf, logthr), kf);
         const double absent_mass = static_cast<double>(static_cast<float>(N) - static_cast<float>(touched))
                                    * exp10_of_float(absent_score);
-        const double total = absent_mass + mass;
-        uint32_t n_out = n_keep;
+        const double total = absent_mass + sw.mass;
+        uint32_t n_out = sw.n_keep;
         if (touched == 0)
         {
             // no k-mer found: keep_at_most placements on the first branches (place.cpp:141-152), in the

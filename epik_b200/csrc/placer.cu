@@ -18,9 +18,16 @@ namespace
 {
     constexpr int N_SLOTS = 3; // chunks in flight in epk_place: copy in / compute / copy out
 
-    __global__ void fold_counters_kernel(const unsigned long long* launch, unsigned long long* totals)
+    // adds the work counters of the (up to N_CLASSES) launches of one batch to the running totals;
+    // queries of a class this placer cannot run (accumulators larger than shared memory) are reported
+    __global__ void fold_counters_kernel(const unsigned long long* launch, const uint32_t* class_reads,
+                                         uint32_t unsupported_mask, unsigned long long* totals)
     {
-        for (int i = 1; i < CTR_COUNT; ++i) { atomicAdd(totals + i, launch[i]); }
+        for (int c = 0; c < N_CLASSES; ++c)
+        {
+            for (int i = 1; i < CTR_COUNT; ++i) { atomicAdd(totals + i, launch[c * CTR_COUNT + i]); }
+            if ((unsupported_mask >> c) & 1u) { atomicAdd(totals + CTR_UNSUPPORTED, static_cast<unsigned long long>(class_reads[c])); }
+        }
     }
 
     // letter codes straight from the sequence bytes (the placement kernel stages them in shared memory)
@@ -83,7 +90,8 @@ namespace
         device_buffer<char> seq;
         device_buffer<uint64_t> off;
         out_arrays out;
-        device_buffer<unsigned long long> counters;
+        device_buffer<unsigned long long> counters; // [N_CLASSES][CTR_COUNT]
+        device_buffer<uint32_t> class_reads;         // [N_CLASSES]
         pinned_buffer<char> h_seq;        // staging when the caller's memory is pageable
         pinned_buffer<uint64_t> h_off;
         pinned_buffer<unsigned char> h_out;
@@ -106,11 +114,13 @@ struct epk_placer
     uint32_t variant = 0;
     uint32_t chunk_reads = 0;
     int n_sms = 0;
-    uint32_t warps_per_cta = 0;
-    size_t smem_bytes = 0;
+    uint32_t warps_per_cta[N_CLASSES] = { 0, 0, 0 }; // 0: the accumulators of this class do not fit shared memory
+    size_t smem_bytes[N_CLASSES] = { 0, 0, 0 };
+    uint32_t unsupported_mask = 0;
     device_buffer<uint32_t> fake_order;
     device_buffer<unsigned long long> totals;          // folded work counters
     device_buffer<unsigned long long> device_counters; // per-launch counters of epk_place_device
+    device_buffer<uint32_t> device_class_reads;
     chunk_slot slots[N_SLOTS];
     uint64_t n_launches = 0, n_reads = 0;
     cudaStream_t last_stream = nullptr;
@@ -121,14 +131,23 @@ namespace
 {
     using kernel_fn = void (*)(const place_params);
 
-    kernel_fn pick_kernel(const epk_placer& pl)
+    kernel_fn pick_kernel(const epk_placer& pl, int cls)
     {
-        return pl.db->table_kind == TABLE_DIRECT ? place_kernel<TABLE_DIRECT, 8> : place_kernel<TABLE_HASH, 8>;
+        if (pl.db->table_kind == TABLE_DIRECT)
+        {
+            return cls == 0 ? place_kernel<TABLE_DIRECT, 8, uint8_t> : cls == 1 ? place_kernel<TABLE_DIRECT, 8, uint16_t>
+                                                                                 : place_kernel<TABLE_DIRECT, 8, uint32_t>;
+        }
+        return cls == 0 ? place_kernel<TABLE_HASH, 8, uint8_t> : cls == 1 ? place_kernel<TABLE_HASH, 8, uint16_t>
+                                                                           : place_kernel<TABLE_HASH, 8, uint32_t>;
     }
 
-    // one launch over n sequences already on the device
+    // One batch of n sequences already on the device: a count of the queries per class, then one
+    // launch of the placement kernel per class (uint8 / uint16 / uint32 hit counts; a launch whose
+    // class is empty returns at once), then the counters. `class_mask` names the classes the caller
+    // knows to be present (all of them when it does not know).
     void launch(epk_placer& pl, const char* d_seq, const uint64_t* d_off, uint32_t n, const epk_result& d_out,
-                unsigned long long* counters, cudaStream_t stream)
+                unsigned long long* counters, uint32_t* class_reads, uint32_t class_mask, cudaStream_t stream)
     {
         place_params p{};
         p.db = pl.db->d;
@@ -144,24 +163,49 @@ namespace
         p.count = d_out.count;
         p.letters = pl.db->letters.get();
         p.fake_order = pl.fake_order.get();
-        p.counters = counters;
-        EPK_CUDA(cudaMemsetAsync(counters, 0, CTR_COUNT * sizeof(unsigned long long), stream));
+        p.class_reads = class_reads;
+        EPK_CUDA(cudaMemsetAsync(counters, 0, N_CLASSES * CTR_COUNT * sizeof(unsigned long long), stream));
+        EPK_CUDA(cudaMemsetAsync(class_reads, 0, N_CLASSES * sizeof(uint32_t), stream));
         {
             const cudaError_t stale = cudaGetLastError();
             if (stale != cudaSuccess) { throw error(EPK_E_CUDA, std::string("stale CUDA error before launch: ") + cudaGetErrorString(stale)); }
         }
         if (n)
         {
-            const unsigned grid = static_cast<unsigned>(std::min<uint64_t>(pl.n_sms, (n + pl.warps_per_cta - 1) / pl.warps_per_cta));
-            pick_kernel(pl)<<<grid, pl.warps_per_cta * 32, pl.smem_bytes, stream>>>(p);
+            const unsigned cgrid = static_cast<unsigned>(std::min<uint64_t>(4ull * pl.n_sms, (static_cast<uint64_t>(n) + 255) / 256));
+            classify_kernel<<<cgrid, 256, 0, stream>>>(d_off, n, pl.db->d.k, class_reads, pl.unsupported_mask, d_out.n_place);
             EPK_CUDA(cudaGetLastError());
-            fold_counters_kernel<<<1, 1, 0, stream>>>(counters, pl.totals.get());
+            ++pl.n_launches;
+            for (int c = 0; c < N_CLASSES; ++c)
+            {
+                if (!((class_mask >> c) & 1u) || pl.warps_per_cta[c] == 0) { continue; }
+                p.cls = static_cast<uint32_t>(c);
+                p.counters = counters + c * CTR_COUNT;
+                const unsigned grid = static_cast<unsigned>(
+                    std::min<uint64_t>(pl.n_sms, (static_cast<uint64_t>(n) + pl.warps_per_cta[c] - 1) / pl.warps_per_cta[c]));
+                pick_kernel(pl, c)<<<grid, pl.warps_per_cta[c] * 32, pl.smem_bytes[c], stream>>>(p);
+                EPK_CUDA(cudaGetLastError());
+                ++pl.n_launches;
+            }
+            fold_counters_kernel<<<1, 1, 0, stream>>>(counters, class_reads, pl.unsupported_mask, pl.totals.get());
             EPK_CUDA(cudaGetLastError());
-            pl.n_launches += 2;
+            ++pl.n_launches;
         }
         pl.n_reads += n;
         pl.totals_dirty = true;
         pl.last_stream = stream;
+    }
+
+    // classes present among sequences [first, last) (host offsets)
+    uint32_t classes_of(const uint64_t* seq_off, uint32_t first, uint32_t last, uint32_t k)
+    {
+        uint32_t mask = 0;
+        for (uint32_t i = first; i < last && mask != (1u << N_CLASSES) - 1u; ++i)
+        {
+            const uint64_t len = seq_off[i + 1] - seq_off[i];
+            mask |= 1u << (len + 1 < k ? 0 : class_of_windows(len + 1 - k));
+        }
+        return mask;
     }
 
     void reserve_slot(epk_placer& pl, chunk_slot& s, size_t reads, size_t bytes, bool stage_in, bool stage_out)
@@ -262,16 +306,26 @@ extern "C" epk_status epk_placer_create(const epk_db* db, uint64_t keep_at_most,
         int max_smem = 0;
         EPK_CUDA(cudaDeviceGetAttribute(&pl->n_sms, cudaDevAttrMultiProcessorCount, db->device));
         EPK_CUDA(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, db->device));
-        const size_t per_warp = warp_smem_bytes(db->d.n_nodes);
-        if (CTA_SMEM_FIXED + per_warp > static_cast<size_t>(max_smem))
+        // warps per CTA by class of hit-count width; a class whose accumulators do not fit one SM's
+        // shared memory is unsupported (its queries are reported, not placed)
+        for (int c = 0; c < N_CLASSES; ++c)
+        {
+            const size_t per_warp = warp_smem_bytes(db->d.n_nodes, class_count_bytes(c));
+            if (CTA_SMEM_FIXED + per_warp > static_cast<size_t>(max_smem))
+            {
+                pl->unsupported_mask |= 1u << c;
+                continue;
+            }
+            pl->warps_per_cta[c] = static_cast<uint32_t>(
+                std::min<size_t>(MAX_WARPS_PER_CTA, (static_cast<size_t>(max_smem) - CTA_SMEM_FIXED) / per_warp));
+            pl->smem_bytes[c] = CTA_SMEM_FIXED + pl->warps_per_cta[c] * per_warp;
+            EPK_CUDA(cudaFuncSetAttribute(pick_kernel(*pl, c), cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          static_cast<int>(pl->smem_bytes[c])));
+        }
+        if (pl->warps_per_cta[0] == 0)
         {
             throw error(EPK_E_UNSUPPORTED, "tree too large for the shared-memory accumulators of this build");
         }
-        pl->warps_per_cta = static_cast<uint32_t>(
-            std::min<size_t>(MAX_WARPS_PER_CTA, (static_cast<size_t>(max_smem) - CTA_SMEM_FIXED) / per_warp));
-        pl->smem_bytes = CTA_SMEM_FIXED + pl->warps_per_cta * per_warp;
-        EPK_CUDA(cudaFuncSetAttribute(pick_kernel(*pl), cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      static_cast<int>(pl->smem_bytes)));
 
         // zero-hit queries: keep_at_most placements on branches 0..K-1, all tied, pushed through
         // std::partial_sort (place.cpp:141-156). The order it leaves them in is the library's; ask it.
@@ -285,12 +339,14 @@ extern "C" epk_status epk_placer_create(const epk_db* db, uint64_t keep_at_most,
         EPK_CUDA(cudaMemcpy(pl->fake_order.get(), order.data(), order.size() * 4, cudaMemcpyHostToDevice));
 
         pl->totals.resize(CTR_COUNT);
-        pl->device_counters.resize(CTR_COUNT);
+        pl->device_counters.resize(N_CLASSES * CTR_COUNT);
+        pl->device_class_reads.resize(N_CLASSES);
         EPK_CUDA(cudaMemset(pl->totals.get(), 0, pl->totals.bytes()));
         for (auto& s : pl->slots)
         {
             EPK_CUDA(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
-            s.counters.resize(CTR_COUNT);
+            s.counters.resize(N_CLASSES * CTR_COUNT);
+            s.class_reads.resize(N_CLASSES);
         }
         *out = pl.release();
     });
@@ -325,7 +381,8 @@ extern "C" epk_status epk_place_device(epk_placer* pl, const char* d_seq, const 
         EPK_CUDA(cudaMemsetAsync(pl->totals.get(), 0, pl->totals.bytes(), s));
         pl->n_launches = 0;
         pl->n_reads = 0;
-        launch(*pl, d_seq, d_seq_off, n, *d_out, pl->device_counters.get(), s);
+        launch(*pl, d_seq, d_seq_off, n, *d_out, pl->device_counters.get(), pl->device_class_reads.get(),
+               (1u << N_CLASSES) - 1u, s);
     });
 }
 
@@ -386,7 +443,8 @@ extern "C" epk_status epk_place(epk_placer* pl, const char* seq, const uint64_t*
             d.lwr = s.out.lwr.get();
             d.count = s.out.count.get();
             // offsets stay absolute: bias the base pointer instead of rewriting them
-            launch(*pl, s.seq.get() - seq_off[first], s.off.get(), m, d, s.counters.get(), s.stream);
+            launch(*pl, s.seq.get() - seq_off[first], s.off.get(), m, d, s.counters.get(), s.class_reads.get(),
+                   classes_of(seq_off, first, last, k), s.stream);
 
             if (out_pinned)
             {
@@ -422,6 +480,12 @@ extern "C" epk_status epk_place(epk_placer* pl, const char* seq, const uint64_t*
             throw error(EPK_E_SHORT_SEQ, std::to_string(totals[CTR_SHORT]) + " sequence(s) shorter than k - 1 = "
                                              + std::to_string(k - 1) + " letters");
         }
+        if (totals[CTR_UNSUPPORTED] + totals[CTR_TOO_LONG] != 0)
+        {
+            throw error(EPK_E_UNSUPPORTED, std::to_string(totals[CTR_UNSUPPORTED] + totals[CTR_TOO_LONG])
+                                               + " sequence(s) too long for the shared-memory accumulators of a tree of "
+                                               + std::to_string(pl->db->d.n_nodes) + " nodes");
+        }
         // distal / pendant are look-ups by branch (place.cpp:434-437); zero for the zero-hit placements
         if (out->distal || out->pendant)
         {
@@ -453,6 +517,7 @@ extern "C" epk_status epk_placer_counters(epk_placer* pl, epk_counters* out)
         out->n_hits = totals[CTR_HITS];
         out->n_entries = totals[CTR_ENTRIES];
         out->n_short = totals[CTR_SHORT];
+        out->n_unsupported = totals[CTR_UNSUPPORTED] + totals[CTR_TOO_LONG];
         out->n_launches = pl->n_launches;
     });
 }

@@ -170,7 +170,9 @@ epk_status epk_kmers(const epk_db* db, const char* seq, uint64_t len, uint64_t c
 typedef struct epk_counters
 {
     uint64_t n_reads, n_windows, n_hits, n_entries, n_launches;
-    uint64_t n_short; /* sequences shorter than k - 1 letters (left with n_place = 0) */
+    uint64_t n_short;       /* sequences shorter than k - 1 letters (left with n_place = 0)            */
+    uint64_t n_unsupported; /* sequences with more windows than the shared-memory accumulators of this */
+                            /* tree size can count (left with n_place = 0)                             */
 } epk_counters;
 epk_status epk_placer_counters(epk_placer* placer, epk_counters* out);
 

@@ -173,7 +173,7 @@ def test_pinned_and_pageable_host_buffers_and_chunking_agree():
     # small chunks: many launches, three slots in flight
     p = Placer(db, chunk_reads=257)
     r = p.place_packed(data, off)
-    assert p.counters()["n_launches"] == 2 * ((5000 + 256) // 257)
+    assert p.counters()["n_launches"] == 3 * ((5000 + 256) // 257)  # per chunk: classify, one class of reads, counters
     # pinned in/out
     from epik_b200.placer import PinnedArray
     pd, po = PinnedArray(data.shape, np.uint8), PinnedArray(off.shape, np.uint64)
@@ -210,7 +210,7 @@ def test_device_resident_call_matches_host_call():
     assert np.array_equal(d_out["score"].cpu().numpy().reshape(-1, K), base["score"])
     assert np.array_equal(d_out["lwr"].cpu().numpy().reshape(-1, K), base["lwr"])
     c = p.counters()
-    assert c["n_reads"] == 4000 and c["n_launches"] == 2
+    assert c["n_reads"] == 4000 and c["n_launches"] == 5  # classify, three count widths, counters
 
 
 def test_database_validation_errors():
@@ -232,3 +232,45 @@ def test_database_validation_errors():
         Placer(Database(flat), keep_at_most=33)
     with pytest.raises(capi.EpkError):
         Database(flat, mu=1.5)  # check_mu, main.cpp:196-202
+
+
+def test_hit_count_widths_and_mixed_lengths():
+    """One kernel instantiation per width of the hit counts (uint8 up to 255 windows, uint16 up to
+    65535, uint32 beyond): a batch mixing all three must come out as if placed one by one."""
+    flat = synth.make_db(0, 8, 120, 0.6, 8.0, seed=51)
+    rng = np.random.default_rng(9)
+    lens = [7, 8, 100, 262, 263, 264, 300, 5000, 65542, 65543, 70000, 150, 65000]
+    seqs = ["".join(rng.choice(list("ACGT"), size=L)) for L in lens]
+    seqs += ["".join(rng.choice(list("ACGTN"), size=int(L), p=[0.245, 0.245, 0.245, 0.245, 0.02])) for L in rng.integers(200, 330, size=60)]
+    p = Placer(Database(flat))
+    got = p.place_packed(*pack_sequences(seqs))
+    oracle, kind = best_oracle(flat, threads=4)
+    want = oracle.place(seqs, threads=4)
+    helpers.assert_same_placements(got, want, what="mixed widths " + kind)
+    valid = np.arange(7)[None, :] < want["n_place"][:, None]
+    assert np.array_equal(got["score"][valid], want["score"][valid])
+    c = p.counters()
+    assert c["n_unsupported"] == 0 and c["n_launches"] == 5 and c["n_windows"] == sum(L - 7 for L in lens) + sum(len(s) - 7 for s in seqs[len(lens):])
+
+
+@pytest.mark.parametrize("tweak", ["positive", "tiny", "zero", "below_threshold"])
+def test_databases_outside_the_short_arithmetic_forms(tweak):
+    """Scores the fast sweep was not checked for (positive, denormal-range, far below the threshold)
+    switch the kernel to IEEE division + library exp10; zeros stay on the fast path."""
+    flat = synth.make_db(0, 7, 100, 0.6, 8.0, seed=61)
+    e = flat.entries
+    if tweak == "positive":
+        e["score"][::97] = 0.25
+    elif tweak == "tiny":
+        e["score"][::89] = -1e-33
+    elif tweak == "zero":
+        e["score"][::5] = 0.0
+    else:
+        e["score"][::101] = -250.0
+    data, off = synth.make_reads(0, 400, 120, seed=62, amb_rate=0.01)
+    got = Placer(Database(flat)).place_packed(data, off)
+    oracle, kind = best_oracle(flat, threads=2)
+    want = oracle.place_packed(data, off, threads=2)
+    helpers.assert_same_placements(got, want, what=tweak + " " + kind)
+    valid = np.arange(7)[None, :] < want["n_place"][:, None]
+    assert np.array_equal(got["score"][valid], want["score"][valid])
