@@ -42,7 +42,11 @@ constexpr int SEG_LEN = 64;            // postings per segment: one 128-bit load
 constexpr int SEG_PAD = 8;             // zero descriptors after the last one (= segments in flight)
 constexpr int CAND_CAP = 128;          // top-k candidates buffered per warp (aliases the segments)
 constexpr int MAX_WARPS_PER_CTA = 8;
-constexpr int SWEEP_STEP = 128;        // branches per warp and sweep step (4 per lane)
+constexpr int SWEEP_STEP = 128;        // branches per warp and run of the sweep (4 consecutive ones per lane)
+#ifndef EPK_SWEEP_Q
+#define EPK_SWEEP_Q 1
+#endif
+constexpr int SWEEP_Q = EPK_SWEEP_Q;   // runs per sweep step: 4 * SWEEP_Q independent chains per lane
 constexpr uint32_t NO_BRANCH = 0xFFFFFFFFu;
 constexpr uint32_t FULL = 0xFFFFFFFFu;
 
@@ -82,7 +86,7 @@ struct place_params
 
 __host__ __device__ inline uint32_t padded_nodes(uint32_t n_nodes)
 {
-    return (n_nodes + SWEEP_STEP - 1) / SWEEP_STEP * SWEEP_STEP;
+    return (n_nodes + SWEEP_STEP * SWEEP_Q - 1) / (SWEEP_STEP * SWEEP_Q) * (SWEEP_STEP * SWEEP_Q);
 }
 
 // bytes of shared memory one warp needs for a tree of n_nodes and counts of count_bytes
@@ -195,6 +199,12 @@ __device__ __forceinline__ float div_by_k_plain(float x, float kf, float rcp)
 __device__ __forceinline__ uint32_t score_key(float s)
 {
     const uint32_t u = __float_as_uint(__fadd_rn(s, 0.0f));
+    return u ^ (static_cast<uint32_t>(static_cast<int32_t>(u) >> 31) | 0x80000000u);
+}
+// the same without folding -0 into +0 (for scores known not to be -0)
+__device__ __forceinline__ uint32_t score_key_raw(float s)
+{
+    const uint32_t u = __float_as_uint(s);
     return u ^ (static_cast<uint32_t>(static_cast<int32_t>(u) >> 31) | 0x80000000u);
 }
 __device__ __forceinline__ float key_score(uint32_t key)
@@ -373,11 +383,11 @@ __device__ __noinline__ void apply_list(const uint2* __restrict__ postings, acc_
 // `want` of the m buffered ones (higher score first, place.cpp:128-131; exact ties: lower branch
 // id first — the documented tie rule), leaves them sorted in slots [0, n_sel) and in the registers
 // of lanes [0, n_sel): lane i holds the i-th best. Returns n_sel = min(want, m).
-__device__ __forceinline__ uint32_t select_best(uint32_t* cand_key, uint32_t* cand_branch, uint32_t* cand_count, uint32_t m,
-                                                uint32_t want, uint32_t lane, uint32_t& my_key, uint32_t& my_branch,
-                                                uint32_t& my_count)
+template<int PER_LANE>
+__device__ __forceinline__ uint32_t select_best_n(uint32_t* cand_key, uint32_t* cand_branch, uint32_t* cand_count, uint32_t m,
+                                                  uint32_t want, uint32_t lane, uint32_t& my_key, uint32_t& my_branch,
+                                                  uint32_t& my_count)
 {
-    constexpr int PER_LANE = CAND_CAP / 32;
     uint32_t hi[PER_LANE], lo[PER_LANE], cn[PER_LANE];
 #pragma unroll
     for (int i = 0; i < PER_LANE; ++i)
@@ -437,6 +447,16 @@ __device__ __forceinline__ uint32_t select_best(uint32_t* cand_key, uint32_t* ca
     return n_sel;
 }
 
+// m <= CAND_CAP candidates: the fewer there are, the fewer each lane has to look at per round
+__device__ __noinline__ uint32_t select_best(uint32_t* cand_key, uint32_t* cand_branch, uint32_t* cand_count, uint32_t m,
+                                             uint32_t want, uint32_t lane, uint32_t& my_key, uint32_t& my_branch,
+                                             uint32_t& my_count)
+{
+    if (m <= 32) { return select_best_n<1>(cand_key, cand_branch, cand_count, m, want, lane, my_key, my_branch, my_count); }
+    if (m <= 64) { return select_best_n<2>(cand_key, cand_branch, cand_count, m, want, lane, my_key, my_branch, my_count); }
+    return select_best_n<CAND_CAP / 32>(cand_key, cand_branch, cand_count, m, want, lane, my_key, my_branch, my_count);
+}
+
 // ---- the sweep over the accumulators ---------------------------------------------------------------
 
 // four consecutive hit counts, and their clearing, by width
@@ -459,8 +479,8 @@ __device__ __forceinline__ void clear_counts4(uint8_t* C, uint32_t j) { *reinter
 __device__ __forceinline__ void clear_counts4(uint16_t* C, uint32_t j) { *reinterpret_cast<uint2*>(C + j) = make_uint2(0u, 0u); }
 __device__ __forceinline__ void clear_counts4(uint32_t* C, uint32_t j) { *reinterpret_cast<uint4*>(C + j) = make_uint4(0u, 0u, 0u, 0u); }
 
-// Terms of the likelihood mass more than this many decades under a term already summed by the same
-// lane are left out: each is below 1e-20 of the total, all of them together below N * 1e-20.
+// Terms of the likelihood mass more than this many decades under the best score the warp has seen
+// are left out: each is below 1e-20 of the total, all of them together below N * 1e-20.
 constexpr float MASS_CUTOFF_DECADES = 20.0f;
 
 struct sweep_result
@@ -475,7 +495,7 @@ struct sweep_result
 // Per branch b with C[b] != 0 (place.cpp:417-422):  S[b] += float(nw - C[b]) * log10thr;  S[b] /= k.
 // FAST: the short forms of the division and of 10^s (valid for the score range established by
 // fast_sweep_ok) and the mass cut-off; otherwise the IEEE division and the library exp10, every term.
-template<class CT, bool FAST>
+template<class CT, bool FAST, int Q>
 __device__ __forceinline__ sweep_result sweep(float* S, CT* C, uint32_t np, uint32_t nw32, float logthr, float kf,
                                               float rcp_k, uint32_t K, uint32_t lane, uint32_t* cand_key,
                                               uint32_t* cand_branch, uint32_t* cand_count)
@@ -483,73 +503,108 @@ __device__ __forceinline__ sweep_result sweep(float* S, CT* C, uint32_t np, uint
     sweep_result out{ 0.0, 0u, 0u, 0u, NO_BRANCH, 0u };
     double mass = 0.0;
     uint32_t touched = 0, n_cand = 0;
-    uint32_t bar_key = 0, bar_branch = 0; // a candidate beats (bar_key, bar_branch); nothing beats key 0 / branch 0
+    // A candidate beats (bar_key, bar_branch): higher key, or the same key and a lower branch id. The
+    // bar is a lower bound of the K-th best score: the K-th largest of the lanes' best keys so far
+    // (refreshed after steps 1, 2, 4, 8 ...), or the K-th best candidate when the buffer was squeezed.
+    uint32_t bar_key = 0, bar_branch = 0; // nothing beats key 0 / branch 0: untouched branches have key 0
+    uint32_t cut_key = 1;                 // mass terms below this key are negligible; 1 admits every touched branch
     uint32_t lane_max = 0;                // best score key this lane has seen
-    for (uint32_t j0 = 0; j0 < np; j0 += SWEEP_STEP) // warp-uniform trip count
+    uint32_t step = 0;
+    constexpr int B = 4 * Q; // branches per lane and step: Q runs of 4 consecutive ones, 128 apart
+    for (uint32_t j0 = 0; j0 < np; j0 += SWEEP_STEP * Q, ++step) // warp-uniform trip count
     {
         const uint32_t j = j0 + 4u * lane;
-        const float4 s4 = *reinterpret_cast<const float4*>(S + j);
-        uint32_t c[4];
-        load_counts4(C, j, c);
-        *reinterpret_cast<float4*>(S + j) = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-        clear_counts4(C, j);
-        const float sum[4] = { s4.x, s4.y, s4.z, s4.w };
-        float s[4];
-        uint32_t key[4];
+        float sum[B];
+        uint32_t c[B];
 #pragma unroll
-        for (int u = 0; u < 4; ++u)
+        for (int g = 0; g < Q; ++g)
+        {
+            const uint32_t jg = j + SWEEP_STEP * g;
+            const float4 s4 = *reinterpret_cast<const float4*>(S + jg);
+            uint32_t cg[4];
+            load_counts4(C, jg, cg);
+            *reinterpret_cast<float4*>(S + jg) = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            clear_counts4(C, jg);
+            sum[4 * g] = s4.x; sum[4 * g + 1] = s4.y; sum[4 * g + 2] = s4.z; sum[4 * g + 3] = s4.w;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { c[4 * g + u] = cg[u]; }
+        }
+        float s[B];
+        uint32_t key[B];
+#pragma unroll
+        for (int u = 0; u < B; ++u)
         {
             // the reference converts the size_t difference to float (place.cpp:420)
             const float x = __fadd_rn(sum[u], __fmul_rn(static_cast<float>(nw32 - c[u]), logthr));
             s[u] = FAST ? div_by_k_plain(x, kf, rcp_k) : __fdiv_rn(x, kf);
-            key[u] = c[u] != 0 ? score_key(s[u]) : 0u;
+            // FAST: no -0 can come out of the division (x is 0 or |x| > 1e-30), the key needs no folding
+            key[u] = c[u] != 0 ? (FAST ? score_key_raw(s[u]) : score_key(s[u])) : 0u;
             touched += c[u] != 0;
             lane_max = max(lane_max, key[u]);
         }
+        if ((step & (step + 1)) == 0)
+        {
+            // K-th largest of the lanes' maxima (0 while fewer than K lanes have a touched branch)
+            uint32_t mine = lane_max, kth = 0;
+            const uint32_t top = __reduce_max_sync(FULL, mine);
+            for (uint32_t i = 0; i < K; ++i)
+            {
+                kth = __reduce_max_sync(FULL, mine);
+                if (kth == 0) { break; }
+                const uint32_t first = __ffs(__ballot_sync(FULL, mine == kth)) - 1u;
+                if (lane == first) { mine = 0; }
+            }
+            if (kth > bar_key)
+            {
+                bar_key = kth;
+                bar_branch = NO_BRANCH;
+            }
+            if (FAST && top != 0) { cut_key = max(cut_key, score_key_raw(key_score(top) - MASS_CUTOFF_DECADES)); }
+        }
         // ---- likelihood mass (place.cpp:164-184) ----
-        bool in[4];
-        if (FAST)
+        bool in_any = false;
+#pragma unroll
+        for (int u = 0; u < B; ++u) { in_any |= key[u] >= cut_key; }
+        if (__any_sync(FULL, in_any))
         {
-            const uint32_t cut = score_key(key_score(lane_max) - MASS_CUTOFF_DECADES);
+            double e[B];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) { in[u] = key[u] != 0 && key[u] >= cut; }
-        }
-        else
-        {
+            for (int u = 0; u < B; ++u) { e[u] = FAST ? exp10_small(s[u]) : exp10(static_cast<double>(s[u])); }
 #pragma unroll
-            for (int u = 0; u < 4; ++u) { in[u] = key[u] != 0; }
-        }
-        if (__any_sync(FULL, in[0] | in[1] | in[2] | in[3]))
-        {
-            double e[4];
-#pragma unroll
-            for (int u = 0; u < 4; ++u) { e[u] = FAST ? exp10_small(s[u]) : exp10(static_cast<double>(s[u])); }
-#pragma unroll
-            for (int u = 0; u < 4; ++u) { mass += in[u] ? e[u] : 0.0; }
+            for (int u = 0; u < B; ++u)
+            {
+                if (key[u] >= cut_key) { mass += e[u]; }
+            }
         }
         // ---- top-k candidates (place.cpp:134-159) ----
-        bool cand[4];
+        bool cand_any = false;
 #pragma unroll
-        for (int u = 0; u < 4; ++u) { cand[u] = (key[u] > bar_key) | ((key[u] == bar_key) & (j + u < bar_branch)); }
-        if (__any_sync(FULL, cand[0] | cand[1] | cand[2] | cand[3]))
+        for (int u = 0; u < B; ++u)
+        {
+            const uint32_t b = j + SWEEP_STEP * (u / 4) + (u % 4);
+            cand_any |= (key[u] > bar_key) | ((key[u] == bar_key) & (b < bar_branch));
+        }
+        if (__any_sync(FULL, cand_any))
         {
 #pragma unroll
-            for (int u = 0; u < 4; ++u)
+            for (int u = 0; u < B; ++u)
             {
-                const uint32_t ballot = __ballot_sync(FULL, cand[u]);
-                if (cand[u])
+                const uint32_t b = j + SWEEP_STEP * (u / 4) + (u % 4);
+                const bool cand = (key[u] > bar_key) | ((key[u] == bar_key) & (b < bar_branch));
+                const uint32_t ballot = __ballot_sync(FULL, cand);
+                if (ballot == 0) { continue; }
+                if (cand)
                 {
                     const uint32_t at = n_cand + __popc(ballot & ((1u << lane) - 1u));
                     cand_key[at] = key[u];
-                    cand_branch[at] = j + u;
+                    cand_branch[at] = b;
                     cand_count[at] = c[u];
                 }
                 n_cand += __popc(ballot);
                 __syncwarp();
                 if (n_cand > CAND_CAP - 32)
                 {
-                    // keep the best K, raise the bar to the K-th of them. Later branches of this
-                    // step were tested against the old bar: a few extra candidates, never a miss.
+                    // keep the best K, raise the bar to the K-th of them
                     n_cand = select_best(cand_key, cand_branch, cand_count, n_cand, K, lane, out.key, out.branch, out.count);
                     if (n_cand == K)
                     {
@@ -571,6 +626,15 @@ __device__ __forceinline__ sweep_result sweep(float* S, CT* C, uint32_t np, uint
     out.mass = mass;
     out.touched = touched;
     return out;
+}
+
+// the general form, out of line: it is cold and long
+template<class CT>
+__device__ __noinline__ sweep_result sweep_ieee(float* S, CT* C, uint32_t np, uint32_t nw32, float logthr, float kf,
+                                                float rcp_k, uint32_t K, uint32_t lane, uint32_t* cand_key,
+                                                uint32_t* cand_branch, uint32_t* cand_count)
+{
+    return sweep<CT, false, 1>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cand_key, cand_branch, cand_count);
 }
 
 // Whether every score a query with nwf windows can end up with stays inside what the short forms
@@ -848,8 +912,8 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
         const uint32_t nw32 = static_cast<uint32_t>(n_windows);
         const float nwf = static_cast<float>(n_windows);
         const sweep_result sw = fast_sweep_ok(db, nwf, kf)
-                                    ? sweep<CT, true>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cand_key, cand_branch, cand_count)
-                                    : sweep<CT, false>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cand_key, cand_branch, cand_count);
+                                    ? sweep<CT, true, SWEEP_Q>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cand_key, cand_branch, cand_count)
+                                    : sweep_ieee<CT>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cand_key, cand_branch, cand_count);
         const uint32_t touched = sw.touched;
         uint32_t my_b = sw.branch, my_c = sw.count;
         float my_s = key_score(sw.key);
