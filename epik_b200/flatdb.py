@@ -73,3 +73,63 @@ def from_dict(alphabet, kmer_size, omega, kmers: dict, branch_length, subtree_nu
     return FlatDB(alphabet, kmer_size, omega, np.asarray(keys, np.uint32), np.asarray(offs, np.uint64), e,
                   np.asarray(branch_length, np.float64), np.asarray(subtree_num_nodes, np.uint64),
                   np.asarray(subtree_total_length, np.float64))
+
+
+# ------------------------------------------------------------------------- .epkdb container -----
+# The on-disk form the C++ host layer reads (epik_b200/host/include/epik/flat_db.h, load_epkdb). The
+# reference's `.ipk` format is defined only inside the absent i2l submodule.
+EPKDB_MAGIC = b"EPKDB1\0\0"
+
+
+def _pad8(n: int) -> bytes:
+    return b"\0" * ((8 - n % 8) % 8)
+
+
+def save_epkdb(db: FlatDB, path: str, newick: str = "") -> None:
+    import struct
+    db.validate()
+    has_filter = db.filter_value is not None
+    nw = newick.encode()
+    with open(path, "wb") as f:
+        f.write(EPKDB_MAGIC)
+        f.write(struct.pack("<IIfIQQQQ", int(db.alphabet), int(db.kmer_size), float(db.omega), db.n_nodes, db.n_keys,
+                            db.n_entries, int(has_filter), len(nw)))
+        keys = np.ascontiguousarray(db.keys, np.uint32).tobytes()
+        f.write(keys + _pad8(len(keys)))
+        f.write(np.ascontiguousarray(db.offsets, np.uint64).tobytes())
+        f.write(np.ascontiguousarray(db.entries, ENTRY_DTYPE).tobytes())
+        if has_filter:
+            fv = np.ascontiguousarray(db.filter_value, np.float32).tobytes()
+            f.write(fv + _pad8(len(fv)))
+        f.write(np.ascontiguousarray(db.branch_length, np.float64).tobytes())
+        f.write(np.ascontiguousarray(db.subtree_num_nodes, np.uint64).tobytes())
+        f.write(np.ascontiguousarray(db.subtree_total_length, np.float64).tobytes())
+        f.write(nw)
+
+
+def load_epkdb(path: str):
+    """-> (FlatDB, newick string)."""
+    import struct
+    with open(path, "rb") as f:
+        buf = f.read()
+    if buf[:8] != EPKDB_MAGIC:
+        raise ValueError("not an .epkdb file: %s" % path)
+    alphabet, k, omega, n_nodes, n_keys, n_entries, has_filter, nw_len = struct.unpack_from("<IIfIQQQQ", buf, 8)
+    at = 8 + struct.calcsize("<IIfIQQQQ")
+
+    def take(dtype, count, pad=False):
+        nonlocal at
+        nbytes = np.dtype(dtype).itemsize * count
+        a = np.frombuffer(buf, dtype, count, at).copy()
+        at += nbytes + (len(_pad8(nbytes)) if pad else 0)
+        return a
+
+    keys = take(np.uint32, n_keys, True)
+    offsets = take(np.uint64, n_keys + 1)
+    entries = take(ENTRY_DTYPE, n_entries)
+    fv = take(np.float32, n_keys, True) if has_filter else None
+    bl = take(np.float64, n_nodes)
+    sn = take(np.uint64, n_nodes)
+    st = take(np.float64, n_nodes)
+    newick = buf[at:at + nw_len].decode()
+    return FlatDB(alphabet, k, omega, keys, offsets, entries, bl, sn, st, fv), newick

@@ -1,0 +1,292 @@
+// jplace (v3) output with the reference's layout: epik/src/epik/jplace.cpp:9-158, which drives a RapidJSON
+// PrettyWriter (4-space indent) and flips kFormatSingleLineArray on and off to put every placement row
+// and every [name, multiplicity] pair on one line. RapidJSON is not a dependency here: json_pretty_writer
+// below restates the layout rules of that writer (where a value gets a newline, an indent, ", " or ": "),
+// and the numbers are printed as RapidJSON prints them (shortest round-trip digits, plain notation for
+// decimal exponents in (-6, 21], `d.ddde-7` otherwise, `0.0` / `-0.0` for zeros). Digits come from
+// std::to_chars (shortest round trip); RapidJSON's Grisu2 is shortest for all but about 0.1 % of doubles,
+// where it prints one more digit — those numbers parse to the same double but are not byte-identical.
+#ifndef EPIK_B200_HOST_JPLACE_H
+#define EPIK_B200_HOST_JPLACE_H
+
+#include <charconv>
+#include <cmath>
+#include <cstdint>
+#include <cstdlib>
+#include <cstring>
+#include <fstream>
+#include <stdexcept>
+#include <string>
+#include <string_view>
+#include <vector>
+
+#include <epik/place.h>
+
+namespace epik::io
+{
+    /// The subset of a pretty-printing JSON writer jplace.cpp uses.
+    class json_pretty_writer
+    {
+    public:
+        explicit json_pretty_writer(std::string& out) : _out(out) {}
+
+        void single_line_arrays(bool on) noexcept { _single_line = on; }
+
+        void start_object() { prefix(); _levels.push_back({ 0, false }); _out.push_back('{'); }
+        void end_object()
+        {
+            const bool empty = _levels.back().count == 0;
+            _levels.pop_back();
+            if (!empty) { _out.push_back('\n'); indent(); }
+            _out.push_back('}');
+        }
+        void start_array() { prefix(); _levels.push_back({ 0, true }); _out.push_back('['); }
+        void end_array()
+        {
+            const bool empty = _levels.back().count == 0;
+            _levels.pop_back();
+            if (!empty && !_single_line) { _out.push_back('\n'); indent(); }
+            _out.push_back(']');
+        }
+        void key(std::string_view s) { string(s); }
+        void string(std::string_view s)
+        {
+            prefix();
+            static const char hex[] = "0123456789ABCDEF";
+            _out.push_back('"');
+            for (const char ch : s)
+            {
+                const unsigned char c = static_cast<unsigned char>(ch);
+                switch (c)
+                {
+                    case '"': _out += "\\\""; break;
+                    case '\\': _out += "\\\\"; break;
+                    case '\b': _out += "\\b"; break;
+                    case '\f': _out += "\\f"; break;
+                    case '\n': _out += "\\n"; break;
+                    case '\r': _out += "\\r"; break;
+                    case '\t': _out += "\\t"; break;
+                    default:
+                        if (c < 0x20)
+                        {
+                            _out += "\\u00";
+                            _out.push_back(hex[c >> 4]);
+                            _out.push_back(hex[c & 15]);
+                        }
+                        else { _out.push_back(ch); }
+                }
+            }
+            _out.push_back('"');
+        }
+        void uint(uint64_t v)
+        {
+            prefix();
+            char buf[24];
+            const auto r = std::to_chars(buf, buf + sizeof(buf), v);
+            _out.append(buf, r.ptr);
+        }
+        void number(double v)
+        {
+            prefix();
+            if (std::isnan(v) || std::isinf(v)) { return; } // RapidJSON refuses them after the prefix
+            if (v == 0.0)
+            {
+                _out += std::signbit(v) ? "-0.0" : "0.0";
+                return;
+            }
+            if (v < 0.0)
+            {
+                _out.push_back('-');
+                v = -v;
+            }
+            // shortest round-trip digits and decimal exponent: d.ddddde[+-]XX
+            char sci[40];
+            const auto r = std::to_chars(sci, sci + sizeof(sci), v, std::chars_format::scientific);
+            const char* e = static_cast<const char*>(std::memchr(sci, 'e', static_cast<size_t>(r.ptr - sci)));
+            char digits[24];
+            int length = 0;
+            for (const char* p = sci; p < e; ++p)
+            {
+                if (*p != '.') { digits[length++] = *p; }
+            }
+            int exp10 = 0;
+            std::from_chars(e[1] == '+' ? e + 2 : e + 1, r.ptr, exp10);
+            const int kk = exp10 + 1;      // 10^(kk-1) <= v < 10^kk
+            const int k = kk - length;     // v = digits * 10^k
+            if (0 <= k && kk <= 21)
+            {
+                _out.append(digits, static_cast<size_t>(length));
+                _out.append(static_cast<size_t>(k), '0');
+                _out += ".0";
+            }
+            else if (0 < kk && kk <= 21)
+            {
+                _out.append(digits, static_cast<size_t>(kk));
+                _out.push_back('.');
+                _out.append(digits + kk, static_cast<size_t>(length - kk));
+            }
+            else if (-6 < kk && kk <= 0)
+            {
+                _out += "0.";
+                _out.append(static_cast<size_t>(-kk), '0');
+                _out.append(digits, static_cast<size_t>(length));
+            }
+            else
+            {
+                _out.push_back(digits[0]);
+                if (length > 1)
+                {
+                    _out.push_back('.');
+                    _out.append(digits + 1, static_cast<size_t>(length - 1));
+                }
+                _out.push_back('e');
+                int x = kk - 1;
+                if (x < 0)
+                {
+                    _out.push_back('-');
+                    x = -x;
+                }
+                _out += std::to_string(x);
+            }
+        }
+
+    private:
+        struct level { size_t count; bool in_array; };
+
+        void indent() { _out.append(_levels.size() * 4, ' '); }
+        void prefix()
+        {
+            if (_levels.empty()) { return; }
+            level& l = _levels.back();
+            if (l.in_array)
+            {
+                if (l.count > 0)
+                {
+                    _out.push_back(',');
+                    if (_single_line) { _out.push_back(' '); }
+                }
+                if (!_single_line) { _out.push_back('\n'); indent(); }
+            }
+            else
+            {
+                if (l.count > 0)
+                {
+                    if (l.count % 2 == 0) { _out += ",\n"; }
+                    else { _out += ": "; }
+                }
+                else { _out.push_back('\n'); }
+                if (l.count % 2 == 0) { indent(); }
+            }
+            ++l.count;
+        }
+
+        std::string& _out;
+        std::vector<level> _levels;
+        bool _single_line = false;
+    };
+
+    /// \brief Writes a collection of placements to a .jplace formatted file (jplace.h:19-53): same
+    /// constructor, start(), operator<<, end(); the buffer is appended to the file per batch (jplace.cpp:33-36).
+    class jplace_writer
+    {
+    public:
+        jplace_writer(const std::string& filename, const std::string& invocation, std::string_view newick_tree)
+            : _filename(filename), _out(filename), _writer(_buffer), _invocation(invocation), _tree(newick_tree)
+        {
+            if (!_out) { throw std::runtime_error("Could not create file " + filename); }
+        }
+        jplace_writer(const jplace_writer&) = delete;
+        jplace_writer& operator=(const jplace_writer&) = delete;
+
+        void start()
+        {
+            _writer.single_line_arrays(true);
+            _writer.start_object();
+            _writer.key("metadata");
+            _writer.start_object();
+            _writer.key("invocation");
+            _writer.string(_invocation);
+            _writer.end_object();
+            _writer.key("tree");
+            _writer.string(_tree);
+            _writer.key("version");
+            _writer.uint(3);
+            _writer.key("fields");
+            _writer.start_array();
+            for (const char* f : { "edge_num", "likelihood", "like_weight_ratio", "distal_length", "pendant_length" })
+            {
+                _writer.string(f);
+            }
+            _writer.end_array();
+            _writer.single_line_arrays(false);
+            _writer.key("placements");
+            _writer.start_array();
+            flush();
+        }
+
+        jplace_writer& operator<<(const impl::placed_collection& placed)
+        {
+            for (const auto& placed_seq : placed.placed_seqs)
+            {
+                _writer.start_object();
+                _writer.key("p");
+                _writer.start_array();
+                for (const auto& p : placed_seq.placements)
+                {
+                    _writer.single_line_arrays(false);
+                    _writer.start_array();
+                    _writer.single_line_arrays(true);
+                    _writer.uint(p.branch_id);
+                    _writer.number(static_cast<double>(p.score)); // float widened to double (jplace.cpp:131)
+                    _writer.number(p.weight_ratio);
+                    _writer.number(p.distal_length);
+                    _writer.number(p.pendant_length);
+                    _writer.end_array();
+                }
+                _writer.single_line_arrays(false);
+                _writer.end_array();
+                _writer.key("nm");
+                _writer.start_array();
+                for (const auto header : placed.sequence_map.at(placed_seq.sequence))
+                {
+                    _writer.single_line_arrays(false);
+                    _writer.start_array();
+                    _writer.single_line_arrays(true);
+                    _writer.string(header);
+                    _writer.uint(1);
+                    _writer.end_array();
+                }
+                _writer.single_line_arrays(false);
+                _writer.end_array();
+                _writer.end_object();
+            }
+            flush();
+            return *this;
+        }
+
+        void end()
+        {
+            _writer.end_array();
+            _writer.end_object();
+            flush();
+        }
+
+    private:
+        void flush()
+        {
+            if (!_out.is_open()) { _out.open(_filename, std::ios_base::app); }
+            _out << _buffer;
+            _buffer.clear();
+            _out.close();
+        }
+
+        std::string _filename;
+        std::ofstream _out;
+        std::string _buffer;
+        json_pretty_writer _writer;
+        std::string _invocation;
+        std::string _tree;
+    };
+}
+
+#endif

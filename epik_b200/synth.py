@@ -73,10 +73,28 @@ def make_tree(n_leaves: int, seed: int = SEED_TREE, mean_length: float = 0.05):
     return length, num, tot, parent
 
 
+def tree_newick(length: np.ndarray, parent: np.ndarray) -> str:
+    """The tree of make_tree as a jplace tree string: `(child,child)name:length{edge}`, edge numbers =
+    post-order ids (what the reference obtains from i2l::io::to_newick(tree, true), main.cpp:297; the exact
+    upstream spelling is [UNVERIFIED], the jplace standard only asks for `{edge_num}` after the length)."""
+    n = len(length)
+    kids = [[] for _ in range(n)]
+    for i in range(n):
+        if parent[i] >= 0:
+            kids[int(parent[i])].append(i)
+    text = [""] * n
+    for i in range(n):  # post-order: children come before their parent
+        inner = "(" + ",".join(text[c] for c in kids[i]) + ")" if kids[i] else "L%d" % i
+        text[i] = "%s:%.6g{%d}" % (inner, float(length[i]), i)
+        for c in kids[i]:
+            text[c] = ""
+    return text[n - 1] + ";"
+
+
 # -------------------------------------------------------------------------------- database -----
 def make_db(alphabet: int, k: int, n_leaves: int, p_occ: float, m: float, omega: float = 1.5,
             seed: int = SEED_DB, max_len: int | None = None, key_space_limit: int | None = None) -> FlatDB:
-    length, num, tot, _ = make_tree(n_leaves, seed ^ 0x7EE)
+    length, num, tot, parent = make_tree(n_leaves, seed ^ 0x7EE)
     n_nodes = len(length)
     if alphabet == DNA:
         n_space = 4 ** k
@@ -127,7 +145,7 @@ def make_db(alphabet: int, k: int, n_leaves: int, p_occ: float, m: float, omega:
     entries["branch"], entries["score"] = branch, score
     fv = _unit(_stream(seed, 9, kk)).astype(np.float32)
     db = FlatDB(alphabet, k, omega, keys, offsets, entries, length, num, tot, fv,
-                meta=dict(p_occ=p_occ, m=m, n_leaves=n_leaves, seed=seed, n_space=n_space))
+                meta=dict(p_occ=p_occ, m=m, n_leaves=n_leaves, seed=seed, n_space=n_space, parent=parent))
     return db
 
 

@@ -17,5 +17,6 @@ def built():
     """Builds the native pieces once per session (no-op when up to date)."""
     import __graft_entry__ as g
     g.build_cuda()
+    g.build_host()
     g.build_oracle()
     return g
