@@ -85,6 +85,26 @@ namespace i2l
             _num_entries_loaded += n;
         }
 
+        /// Iteration over (key, entries) pairs — what a consumer that flattens the database needs (the
+        /// placer of the reference never iterates; upstream's iteration API is [UNVERIFIED]).
+        class const_iterator
+        {
+        public:
+            const_iterator(const phylo_kmer_db* db, size_t slot) : _db(db), _slot(slot) { skip(); }
+            std::pair<key_type, const value_type&> operator*() const
+            {
+                return { _db->_slots[_slot].key, _db->_values[_db->_slots[_slot].value] };
+            }
+            const_iterator& operator++() { ++_slot; skip(); return *this; }
+            bool operator!=(const const_iterator& o) const noexcept { return _slot != o._slot; }
+        private:
+            void skip() { while (_slot < _db->_slots.size() && _db->_slots[_slot].value == npos) { ++_slot; } }
+            const phylo_kmer_db* _db;
+            size_t _slot;
+        };
+        const_iterator begin() const { return const_iterator(this, 0); }
+        const_iterator end() const { return const_iterator(this, _slots.size()); }
+
         size_t size() const noexcept { return _values.size(); }
         size_t kmer_size() const noexcept { return _kmer_size; }
         phylo_kmer::score_type omega() const noexcept { return _omega; }

@@ -152,3 +152,28 @@ def test_driver_errors_and_filters(built, tmp_path):
     assert "Max-RAM provided: will be loaded not more than 65.5K phylo-k-mers." in r.stdout
     loaded = [l for l in r.stdout.split("\n") if l.startswith("Loaded ")][0]
     assert " of %s phylo-k-mers" % ("%.1fK" % (flat.n_entries / 1e3)) in loaded
+
+
+@pytest.mark.gpu
+def test_reference_driver_loop_against_the_facade(built, tmp_path):
+    """main.cpp:294-366 written against epik_b200's headers with i2l-shaped db/tree types (tests/cpp/facade_main.cpp):
+    epik::placer(db, tree, ...) flattens and uploads the database; the jplace equals the driver binary's."""
+    from epik_b200 import flatdb, synth
+    subprocess.run(["make", "-s", "-C", os.path.join(ROOT, "epik_b200", "host")], check=True)
+    exe = compile_cpp(tmp_path, "facade", OURS + ["-I" + os.path.join(ROOT, "oracle", "shim")],
+                      [os.path.join(CPP, "facade_main.cpp")], LINK)
+    flat = synth.make_db(0, 8, 150, 0.6, 10.0, seed=81)
+    data, off = synth.make_reads(0, 700, 90, seed=82, amb_rate=0.005)
+    db_path, q_path = str(tmp_path / "db.epkdb"), str(tmp_path / "q.fasta")
+    flatdb.save_epkdb(flat, db_path, synth.tree_newick(flat.branch_length, flat.meta["parent"]))
+    with open(q_path, "w") as f:
+        for i in range(700):
+            f.write(">r%d\n%s\n" % (i % 650, bytes(data[int(off[i % 650]):int(off[i % 650 + 1])]).decode()))
+    a = str(tmp_path / "facade.jplace")
+    r = subprocess.run([exe, db_path, q_path, a, "256"], capture_output=True, text=True)
+    assert r.returncode == 0 and "placed 700" in r.stdout, r.stderr
+    r = subprocess.run([os.path.join(ROOT, "bin", "epik", "epik-dna"), "-d", db_path, "-q", q_path, "-o", str(tmp_path),
+                        "--batch-size", "256"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    ja, jb = json.load(open(a)), json.load(open(str(tmp_path / "placements_q.fasta.jplace")))
+    assert ja["placements"] == jb["placements"] and ja["tree"] == jb["tree"] and len(ja["placements"]) > 600
