@@ -274,3 +274,39 @@ def test_databases_outside_the_short_arithmetic_forms(tweak):
     helpers.assert_same_placements(got, want, what=tweak + " " + kind)
     valid = np.arange(7)[None, :] < want["n_place"][:, None]
     assert np.array_equal(got["score"][valid], want["score"][valid])
+
+
+@pytest.mark.parametrize("mu,omega,max_entries", [
+    (0.5, 1.5, None),          # --mu 0.5
+    (1.0, 1.5, 20000),         # --max-ram
+    (0.5, 1.8, 30000),         # both, and a stricter omega (BASELINE config 3 combines them, main.cpp:277)
+    (0.3, 1.2, None),          # a looser omega than the database's: nothing dropped by score
+    (1.0, 2.5, None),          # omega only
+    (0.0, 1.5, None),          # nothing loaded: every query gets the zero-hit placements
+])
+def test_load_filter_matches_its_restatement(mu, omega, max_entries):
+    """--mu / --omega / --max-ram applied on the device at load time (device sort by filter value, prefix cut,
+    per-entry threshold, compaction) against the numpy restatement in oracle/load_filter.py."""
+    from oracle import load_filter
+    flat = synth.make_db(0, 8, 200, 0.6, 10.0, seed=91)
+    data, off = synth.make_reads(0, 1500, 120, seed=92, amb_rate=0.003)
+    probe = synth.make_db(0, 8, 200, 0.001, 2.0, omega=omega, seed=91)   # only to ask the C++ oracle for the thresholds
+    _, log_thr = best_oracle(probe)[0].thresholds()
+    want_db = load_filter.apply(flat, mu, omega, max_entries, float(log_thr))
+    db = Database(flat, mu=mu, omega=omega, max_entries=max_entries)
+    assert db.info["n_entries_total"] == flat.n_entries
+    assert db.info["n_entries_loaded"] == want_db.n_entries and db.info["n_keys_loaded"] == want_db.n_keys
+    assert db.info["omega"] == np.float32(omega) and db.info["log10_threshold"] == log_thr
+    if 0 < mu < 1 and max_entries is None:
+        assert abs(want_db.n_entries - mu * flat.n_entries) < 0.2 * flat.n_entries
+    got = Placer(db).place_packed(data, off)
+    oracle, kind = best_oracle(want_db, threads=2)
+    want = oracle.place_packed(data, off, threads=2)
+    helpers.assert_same_placements(got, want, what="filter " + kind)
+    valid = np.arange(7)[None, :] < want["n_place"][:, None]
+    assert np.array_equal(got["score"][valid], want["score"][valid])
+    # hits seen by the kernel = hits in the filtered database
+    for i in range(3):
+        seq = bytes(data[int(off[i]):int(off[i + 1])])
+        for x, y in zip(db.kmers(seq), oracle.kmers(seq)):
+            assert np.array_equal(x, y)
