@@ -41,7 +41,7 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="C2", choices=["C2", "C4", "C1p"])
+    ap.add_argument("--workload", default="C2", choices=["C2", "C3", "C4", "C1p"])
     ap.add_argument("--reads", type=int, default=0, help="reads per GPU per step (default: the workload's)")
     ap.add_argument("--variant", type=int, default=0)
     ap.add_argument("--no-e2e", action="store_true")
@@ -49,15 +49,17 @@ def parse_args():
     return ap.parse_args()
 
 
-WORKLOAD_READS = {"C2": 10_000_000, "C4": 1_000_000, "C1p": 100_000}
+WORKLOAD_READS = {"C2": 10_000_000, "C3": 10_000_000, "C4": 1_000_000, "C1p": 100_000}
 
 
 def workload_config(name, n_reads, world):
     from epik_b200 import synth
     alphabet, k, n_leaves, p_occ, m, read_len = synth.CONFIGS[name]
+    flt = synth.LOAD_FILTERS.get(name)
     return {
-        "workload": "%s: synthetic %s DB k=%d, %d branches, p_occ=%.2f, m=%.0f; %d x %d-letter reads per GPU per step"
-                    % (name, "amino" if alphabet else "nucl", k, 2 * n_leaves - 1, p_occ, m, n_reads, read_len),
+        "workload": "%s: synthetic %s DB k=%d, %d branches, p_occ=%.2f, m=%.0f%s; %d x %d-letter reads per GPU per step"
+                    % (name, "amino" if alphabet else "nucl", k, 2 * n_leaves - 1, p_occ, m,
+                       " loaded with mu=%g omega=%g max_entries=%d" % flt if flt else "", n_reads, read_len),
         "reads_per_gpu": n_reads, "read_len": read_len, "k": k, "branches": 2 * n_leaves - 1,
         "keep_at_most": 7, "keep_factor": 0.01, "omega": 1.5,
         "parallelism": "query-sharded x%d, DB replicated" % world,
@@ -133,13 +135,20 @@ def host_threads():
         return os.cpu_count() or 1
 
 
-def cpu_reference(db, alphabet, read_len, seconds_target, steps=1, warmup=0):
+def cpu_reference(db, alphabet, read_len, seconds_target, steps=1, warmup=0, load_filter=None):
     """Times the reference's CPU placer (oracle/_ref if built, else the port) on a bounded sample.
     Returns (reads/s of the timed steps, kind, cores, sample description)."""
     from epik_b200 import synth
     from oracle import oracle as O
     kind = "reference" if O.available("reference", alphabet) else "port"
     cores = host_threads()
+    if load_filter is not None:
+        # what i2l::load would hand the placer (main.cpp:277): the filter applied before the timed region
+        from oracle import load_filter as LF
+        mu, omega, max_entries = load_filter
+        probe = synth.make_db(alphabet, db.kmer_size, 8, 0.001, 2.0, omega=omega, key_space_limit=4096)
+        _, log_thr = O.Oracle(probe, kind=kind).thresholds()
+        db = LF.apply(db, mu, omega, max_entries, float(log_thr))
     o = O.Oracle(db, 7, 0.01, cores, kind=kind)
     probe_n = 4000 * max(1, cores // 4)
     data, off = synth.make_reads(alphabet, probe_n, read_len, first=900_000_000)
@@ -171,7 +180,8 @@ def run_reference(args):
     db = synth.make_config_db(args.workload)
     total = max(args.steps + args.warmup, 1)
     value, kind, cores, sample, step_s = cpu_reference(db, alphabet, read_len, seconds_target=min(20.0, 150.0 / total),
-                                                       steps=args.steps, warmup=args.warmup)
+                                                       steps=args.steps, warmup=args.warmup,
+                                                       load_filter=synth.LOAD_FILTERS.get(args.workload))
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": step_s * 1e3, "higher_is_better": True, "scaling": "weak",
@@ -228,7 +238,8 @@ def run_ours(args):
     n = args.reads or WORKLOAD_READS[args.workload]
     K = 7
     flat = synth.make_config_db(args.workload)
-    db = Database(flat, device=local)
+    flt = synth.LOAD_FILTERS.get(args.workload)
+    db = Database(flat, device=local) if flt is None else Database(flat, mu=flt[0], omega=flt[1], max_entries=flt[2], device=local)
     placer = Placer(db, K, 0.01, variant=args.variant)
 
     # ---- inputs: pinned host copies (for e2e) and device-resident copies (for value) ----
@@ -316,7 +327,7 @@ def run_ours(args):
     # ---- CPU baseline: rank 0, N = 1 only ----
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        v, kind, cores, sample, _ = cpu_reference(flat, alphabet, read_len, seconds_target=15.0)
+        v, kind, cores, sample, _ = cpu_reference(flat, alphabet, read_len, seconds_target=15.0, load_filter=flt)
         cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample}
 
     total_reads = sum_over_ranks(float(n))

@@ -175,9 +175,15 @@ CONFIGS = {
     # name: (alphabet, k, n_leaves, p_occ, m, read_len)
     "C1p": (DNA, 10, 652, 0.6, 24.0, 1500),    # D652-shaped stand-in for config 1 (N = 1303)
     "C2": (DNA, 10, 2500, 0.6, 32.0, 150),     # N = 4999, ~33 M entries
+    "C3": (DNA, 10, 2500, 0.6, 32.0, 150),     # C2 loaded with --mu 0.5 --max-ram 4G (LOAD_FILTERS)
     "C4": (AA, 6, 1000, 0.05, 16.0, 100),      # N = 1999, 64 M-key space
     "C5": (DNA, 12, 10000, 0.9, 160.0, 150),   # N = 19999, ~4 G entries (device-generated only)
 }
+
+
+# (mu, omega, max_entries) of i2l::load for the configs that filter at load time; --max-ram 4G is
+# 4 * 2^30 / sizeof(pkdb_value) entries (main.cpp:252-265)
+LOAD_FILTERS = {"C3": (0.5, 1.5, (4 << 30) // 8)}
 
 
 def make_config_db(name: str, **kw) -> FlatDB:
