@@ -35,6 +35,14 @@ METRIC = "placed queries/sec"
 UNIT = "reads/s"
 
 
+T0 = time.time()
+
+
+def log(msg):
+    """progress to stderr (stdout carries only the JSON line)"""
+    print("[bench %6.1fs rank %s] %s" % (time.time() - T0, os.environ.get("RANK", "0"), msg), file=sys.stderr, flush=True)
+
+
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -237,11 +245,13 @@ def run_ours(args):
     alphabet, k, n_leaves, p_occ, m, read_len = synth.CONFIGS[args.workload]
     n = args.reads or WORKLOAD_READS[args.workload]
     K = 7
+    log("world %d, device %d: generating database %s" % (world, local, args.workload))
     flat = synth.make_config_db(args.workload)
     flt = synth.LOAD_FILTERS.get(args.workload)
     db = Database(flat, device=local) if flt is None else Database(flat, mu=flt[0], omega=flt[1], max_entries=flt[2], device=local)
     placer = Placer(db, K, 0.01, variant=args.variant)
 
+    log("database on the device: %d entries; generating %d reads" % (db.info["n_entries_loaded"], n))
     # ---- inputs: pinned host copies (for e2e) and device-resident copies (for value) ----
     h_seq = PinnedArray((n * read_len,), np.uint8)
     h_off = PinnedArray((n + 1,), np.uint64)
@@ -256,6 +266,7 @@ def run_ours(args):
              "count": torch.zeros(n * K, dtype=torch.int32, device=dev)}
     stream = torch.cuda.Stream(device=dev)
 
+    log("reads ready; timing the device-resident path")
     # ---- value: everything resident in HBM ----
     for _ in range(args.warmup):
         placer.place_device(d_seq, d_off, n, d_out, stream=stream)
@@ -302,6 +313,7 @@ def run_ours(args):
                 "launch_ms": kernel_s * 1e3, "peak_source": peak_src,
                 "entries_per_read": counters["n_entries"] / n, "hits_per_read": counters["n_hits"] / n}
 
+    log("device-resident: %.1f ms/step; timing the host path" % (total_s / args.steps * 1e3))
     # ---- e2e: pinned host buffers through epk_place, copies inside the timed region ----
     e2e = None
     if not args.no_e2e:

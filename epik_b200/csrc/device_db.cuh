@@ -78,6 +78,24 @@ __device__ __forceinline__ uint64_t db_search(const device_db& db, uint32_t key)
     }
 }
 
+// The same for the hashed table when the first slot of the probe sequence has already been fetched
+// (the placement kernel issues the first probes of all the windows of a lane before resolving any).
+__device__ __forceinline__ uint64_t db_search_from(const device_db& db, uint32_t key, uint4 s)
+{
+    uint64_t h = hash_slot(key, db.hash_shift);
+    while (true)
+    {
+        if (s.y == HASH_EMPTY) { return 0; }
+        if (s.x == key)
+        {
+            const uint64_t off = (static_cast<uint64_t>(s.w) << 32) | s.z;
+            return (off << LEN_BITS) | s.y;
+        }
+        h = (h + 1) & db.hash_mask;
+        s = __ldg(db.hashed + h);
+    }
+}
+
 // Letter tables: the 2-bit / 5-bit codes of i2l (absent submodule; SURVEY.md Appendix B, the same
 // tables the oracle shim states with switch statements). Filled by make_letter_table on the host.
 void make_letter_table(uint32_t alphabet, uint32_t* table /*[256]*/);

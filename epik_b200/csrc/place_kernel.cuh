@@ -43,10 +43,6 @@ constexpr int SEG_PAD = 8;             // zero descriptors after the last one (=
 constexpr int CAND_CAP = 128;          // top-k candidates buffered per warp (aliases the segments)
 constexpr int MAX_WARPS_PER_CTA = 8;
 constexpr int SWEEP_STEP = 128;        // branches per warp and run of the sweep (4 consecutive ones per lane)
-#ifndef EPK_SWEEP_Q
-#define EPK_SWEEP_Q 1
-#endif
-constexpr int SWEEP_Q = EPK_SWEEP_Q;   // runs per sweep step: 4 * SWEEP_Q independent chains per lane
 constexpr uint32_t NO_BRANCH = 0xFFFFFFFFu;
 constexpr uint32_t FULL = 0xFFFFFFFFu;
 
@@ -86,7 +82,7 @@ struct place_params
 
 __host__ __device__ inline uint32_t padded_nodes(uint32_t n_nodes)
 {
-    return (n_nodes + SWEEP_STEP * SWEEP_Q - 1) / (SWEEP_STEP * SWEEP_Q) * (SWEEP_STEP * SWEEP_Q);
+    return (n_nodes + SWEEP_STEP - 1) / SWEEP_STEP * SWEEP_STEP;
 }
 
 // bytes of shared memory one warp needs for a tree of n_nodes and counts of count_bytes
@@ -475,6 +471,17 @@ __device__ __forceinline__ void load_counts4(const uint32_t* C, uint32_t j, uint
     const uint4 w = *reinterpret_cast<const uint4*>(C + j);
     c[0] = w.x; c[1] = w.y; c[2] = w.z; c[3] = w.w;
 }
+__device__ __forceinline__ bool any_count4(const uint8_t* C, uint32_t j) { return *reinterpret_cast<const uint32_t*>(C + j) != 0u; }
+__device__ __forceinline__ bool any_count4(const uint16_t* C, uint32_t j)
+{
+    const uint2 w = *reinterpret_cast<const uint2*>(C + j);
+    return (w.x | w.y) != 0u;
+}
+__device__ __forceinline__ bool any_count4(const uint32_t* C, uint32_t j)
+{
+    const uint4 w = *reinterpret_cast<const uint4*>(C + j);
+    return (w.x | w.y | w.z | w.w) != 0u;
+}
 __device__ __forceinline__ void clear_counts4(uint8_t* C, uint32_t j) { *reinterpret_cast<uint32_t*>(C + j) = 0u; }
 __device__ __forceinline__ void clear_counts4(uint16_t* C, uint32_t j) { *reinterpret_cast<uint2*>(C + j) = make_uint2(0u, 0u); }
 __device__ __forceinline__ void clear_counts4(uint32_t* C, uint32_t j) { *reinterpret_cast<uint4*>(C + j) = make_uint4(0u, 0u, 0u, 0u); }
@@ -482,6 +489,10 @@ __device__ __forceinline__ void clear_counts4(uint32_t* C, uint32_t j) { *reinte
 // Terms of the likelihood mass more than this many decades under the best score the warp has seen
 // are left out: each is below 1e-20 of the total, all of them together below N * 1e-20.
 constexpr float MASS_CUTOFF_DECADES = 20.0f;
+
+// a scan step with at least this many touched quads (of 32) is processed in place rather than queued
+constexpr uint32_t DENSE_QUADS = 24;
+static_assert(3 * CAND_CAP * 4 + 64 * 4 <= (SEG_CAP + SEG_PAD) * 8, "candidates and the quad queue alias the segment buffer");
 
 struct sweep_result
 {
@@ -495,7 +506,7 @@ struct sweep_result
 // Per branch b with C[b] != 0 (place.cpp:417-422):  S[b] += float(nw - C[b]) * log10thr;  S[b] /= k.
 // FAST: the short forms of the division and of 10^s (valid for the score range established by
 // fast_sweep_ok) and the mass cut-off; otherwise the IEEE division and the library exp10, every term.
-template<class CT, bool FAST, int Q>
+template<class CT, bool FAST, bool DENSE>
 __device__ __forceinline__ sweep_result sweep(float* S, CT* C, uint32_t np, uint32_t nw32, float logthr, float kf,
                                               float rcp_k, uint32_t K, uint32_t lane, uint32_t* cand_key,
                                               uint32_t* cand_branch, uint32_t* cand_count)
@@ -510,29 +521,82 @@ __device__ __forceinline__ sweep_result sweep(float* S, CT* C, uint32_t np, uint
     uint32_t cut_key = 1;                 // mass terms below this key are negligible; 1 admits every touched branch
     uint32_t lane_max = 0;                // best score key this lane has seen
     uint32_t step = 0;
-    constexpr int B = 4 * Q; // branches per lane and step: Q runs of 4 consecutive ones, 128 apart
-    for (uint32_t j0 = 0; j0 < np; j0 += SWEEP_STEP * Q, ++step) // warp-uniform trip count
+    // The accumulators are looked at in runs of 4 consecutive branches ("quads"), 32 quads per scan step.
+    // `dense` (the query gathered at least a sixth as many postings as there are branches): every step is
+    // processed as it stands, lane l takes quad l. Otherwise the count words are scanned first: a step
+    // with many touched quads is still processed in place, the touched quads of sparse steps are queued
+    // and processed 32 at a time, so that a query that touched few branches pays for those only (a
+    // 100-residue protein read touches a few dozen of the 2000 branches of its tree).
+    uint32_t* pending = cand_key + 3 * CAND_CAP; // [64] first branch of queued quads
+    uint32_t n_pending = 0, scan = 0;
+    while (true)
     {
-        const uint32_t j = j0 + 4u * lane;
-        float sum[B];
-        uint32_t c[B];
-#pragma unroll
-        for (int g = 0; g < Q; ++g)
+        // ---- next 32 quads to process: j = first branch of this lane's quad ----
+        uint32_t j = 0;
+        bool active = DENSE, have = false;
+        if (DENSE)
         {
-            const uint32_t jg = j + SWEEP_STEP * g;
-            const float4 s4 = *reinterpret_cast<const float4*>(S + jg);
-            uint32_t cg[4];
-            load_counts4(C, jg, cg);
-            *reinterpret_cast<float4*>(S + jg) = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-            clear_counts4(C, jg);
-            sum[4 * g] = s4.x; sum[4 * g + 1] = s4.y; sum[4 * g + 2] = s4.z; sum[4 * g + 3] = s4.w;
-#pragma unroll
-            for (int u = 0; u < 4; ++u) { c[4 * g + u] = cg[u]; }
+            // a query with many postings touched most quads: every step as it stands, no scan
+            if (scan >= np) { break; }
+            j = scan + 4u * lane;
+            scan += SWEEP_STEP;
+            have = true;
         }
-        float s[B];
-        uint32_t key[B];
+        while (!DENSE && !have && scan < np)
+        {
+            const uint32_t mine = scan + 4u * lane;
+            const bool hit = any_count4(C, mine);
+            const uint32_t ballot = __ballot_sync(FULL, hit);
+            const uint32_t n_hit = __popc(ballot);
+            scan += SWEEP_STEP;
+            if (n_hit >= DENSE_QUADS)
+            {
+                j = mine;
+                active = true;
+                have = true;
+            }
+            else if (n_hit)
+            {
+                if (hit) { pending[n_pending + __popc(ballot & ((1u << lane) - 1u))] = mine; }
+                n_pending += n_hit;
+                __syncwarp();
+                if (n_pending >= 32)
+                {
+                    j = pending[lane];
+                    const uint32_t rest = n_pending - 32;
+                    const uint32_t moved = lane < rest ? pending[32 + lane] : 0u;
+                    __syncwarp();
+                    if (lane < rest) { pending[lane] = moved; }
+                    __syncwarp();
+                    n_pending = rest;
+                    active = true;
+                    have = true;
+                }
+            }
+        }
+        if (!DENSE && !have)
+        {
+            if (n_pending == 0) { break; }
+            active = lane < n_pending;
+            j = active ? pending[lane] : 0u;
+            n_pending = 0;
+        }
+
+        // ---- the quad: correction, keys ----
+        float4 s4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        uint32_t c[4] = { 0u, 0u, 0u, 0u };
+        if (DENSE || active)
+        {
+            s4 = *reinterpret_cast<const float4*>(S + j);
+            load_counts4(C, j, c);
+            *reinterpret_cast<float4*>(S + j) = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            clear_counts4(C, j);
+        }
+        const float sum[4] = { s4.x, s4.y, s4.z, s4.w };
+        float s[4];
+        uint32_t key[4];
 #pragma unroll
-        for (int u = 0; u < B; ++u)
+        for (int u = 0; u < 4; ++u)
         {
             // the reference converts the size_t difference to float (place.cpp:420)
             const float x = __fadd_rn(sum[u], __fmul_rn(static_cast<float>(nw32 - c[u]), logthr));
@@ -561,17 +625,18 @@ __device__ __forceinline__ sweep_result sweep(float* S, CT* C, uint32_t np, uint
             }
             if (FAST && top != 0) { cut_key = max(cut_key, score_key_raw(key_score(top) - MASS_CUTOFF_DECADES)); }
         }
+        ++step;
         // ---- likelihood mass (place.cpp:164-184) ----
         bool in_any = false;
 #pragma unroll
-        for (int u = 0; u < B; ++u) { in_any |= key[u] >= cut_key; }
+        for (int u = 0; u < 4; ++u) { in_any |= key[u] >= cut_key; }
         if (__any_sync(FULL, in_any))
         {
-            double e[B];
+            double e[4];
 #pragma unroll
-            for (int u = 0; u < B; ++u) { e[u] = FAST ? exp10_small(s[u]) : exp10(static_cast<double>(s[u])); }
+            for (int u = 0; u < 4; ++u) { e[u] = FAST ? exp10_small(s[u]) : exp10(static_cast<double>(s[u])); }
 #pragma unroll
-            for (int u = 0; u < B; ++u)
+            for (int u = 0; u < 4; ++u)
             {
                 if (key[u] >= cut_key) { mass += e[u]; }
             }
@@ -579,25 +644,20 @@ __device__ __forceinline__ sweep_result sweep(float* S, CT* C, uint32_t np, uint
         // ---- top-k candidates (place.cpp:134-159) ----
         bool cand_any = false;
 #pragma unroll
-        for (int u = 0; u < B; ++u)
-        {
-            const uint32_t b = j + SWEEP_STEP * (u / 4) + (u % 4);
-            cand_any |= (key[u] > bar_key) | ((key[u] == bar_key) & (b < bar_branch));
-        }
+        for (int u = 0; u < 4; ++u) { cand_any |= (key[u] > bar_key) | ((key[u] == bar_key) & (j + u < bar_branch)); }
         if (__any_sync(FULL, cand_any))
         {
 #pragma unroll
-            for (int u = 0; u < B; ++u)
+            for (int u = 0; u < 4; ++u)
             {
-                const uint32_t b = j + SWEEP_STEP * (u / 4) + (u % 4);
-                const bool cand = (key[u] > bar_key) | ((key[u] == bar_key) & (b < bar_branch));
+                const bool cand = (key[u] > bar_key) | ((key[u] == bar_key) & (j + u < bar_branch));
                 const uint32_t ballot = __ballot_sync(FULL, cand);
                 if (ballot == 0) { continue; }
                 if (cand)
                 {
                     const uint32_t at = n_cand + __popc(ballot & ((1u << lane) - 1u));
                     cand_key[at] = key[u];
-                    cand_branch[at] = b;
+                    cand_branch[at] = j + u;
                     cand_count[at] = c[u];
                 }
                 n_cand += __popc(ballot);
@@ -628,13 +688,21 @@ __device__ __forceinline__ sweep_result sweep(float* S, CT* C, uint32_t np, uint
     return out;
 }
 
-// the general form, out of line: it is cold and long
+// The forms off the beaten track, out of line (they are long, and cold for 150-bp reads on a 5000-branch
+// tree): IEEE arithmetic; scan-and-queue for queries that touched few branches.
 template<class CT>
 __device__ __noinline__ sweep_result sweep_ieee(float* S, CT* C, uint32_t np, uint32_t nw32, float logthr, float kf,
                                                 float rcp_k, uint32_t K, uint32_t lane, uint32_t* cand_key,
                                                 uint32_t* cand_branch, uint32_t* cand_count)
 {
-    return sweep<CT, false, 1>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cand_key, cand_branch, cand_count);
+    return sweep<CT, false, false>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cand_key, cand_branch, cand_count);
+}
+template<class CT>
+__device__ __noinline__ sweep_result sweep_sparse(float* S, CT* C, uint32_t np, uint32_t nw32, float logthr, float kf,
+                                                  float rcp_k, uint32_t K, uint32_t lane, uint32_t* cand_key,
+                                                  uint32_t* cand_branch, uint32_t* cand_count)
+{
+    return sweep<CT, true, false>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cand_key, cand_branch, cand_count);
 }
 
 // Whether every score a query with nwf windows can end up with stays inside what the short forms
@@ -715,6 +783,7 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
             }
             continue;
         }
+        const uint64_t entries_before = ctr_entries;
         const uint64_t n_windows = len + 1 - k; // place.cpp:322, counts skipped windows too
         if (class_of_windows(n_windows) != static_cast<int>(p.cls)) { continue; } // another launch's query
         if (n_windows > class_max_windows(N_CLASSES - 1))
@@ -743,11 +812,14 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
             }
             __syncwarp();
 
-            // lane L owns windows [L*WPL, L*WPL + WPL): one rolling code, WPL probes in flight
             uint64_t slot[WPL];
 #pragma unroll
             for (int r = 0; r < WPL; ++r) { slot[r] = 0; }
-            const uint32_t w0 = lane * WPL;
+            // lane L owns windows [L*wpl, L*wpl + wpl): short queries spread over all the lanes
+            const uint32_t wpl = min(static_cast<uint32_t>(WPL), (nw + 31u) / 32u);
+            const uint32_t w0 = lane * wpl;
+            uint32_t keys[WPL];
+            uint32_t look = 0; // bit r: window w0 + r is an exact k-mer to look up
             if (w0 < nw)
             {
                 uint32_t key = 0;
@@ -765,20 +837,46 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
                 for (int r = 0; r < WPL; ++r)
                 {
                     const uint32_t w = w0 + r;
-                    if (w < nw)
+                    keys[r] = 0;
+                    if (static_cast<uint32_t>(r) < wpl && w < nw)
                     {
                         const uint32_t l = codes[w + k - 1];
                         const int at = static_cast<int>(w + k - 1);
                         key = ((key << bits) | (l & 31u)) & key_mask;
+                        keys[r] = key;
                         last_gap = (l & LETTER_GAP) ? at : last_gap;
                         prev_amb = (l & LETTER_AMBIGUOUS) ? last_amb : prev_amb;
                         last_amb = (l & LETTER_AMBIGUOUS) ? at : last_amb;
                         if (last_gap < static_cast<int>(w))
                         {
-                            if (last_amb < static_cast<int>(w)) { slot[r] = db_search<TABLE>(db, key); }
+                            if (last_amb < static_cast<int>(w)) { look |= 1u << r; }
                             else if (prev_amb < static_cast<int>(w)) { has_ambiguous = true; }
                         }
                     }
+                }
+            }
+            // all the look-ups of the lane go out before any of them is waited for
+            if (TABLE == TABLE_DIRECT)
+            {
+#pragma unroll
+                for (int r = 0; r < WPL; ++r)
+                {
+                    if ((look >> r) & 1u) { slot[r] = __ldg(db.direct + keys[r]); }
+                }
+            }
+            else
+            {
+                uint4 first[WPL];
+#pragma unroll
+                for (int r = 0; r < WPL; ++r)
+                {
+                    first[r] = make_uint4(0u, HASH_EMPTY, 0u, 0u);
+                    if ((look >> r) & 1u) { first[r] = __ldg(db.hashed + hash_slot(keys[r], db.hash_shift)); }
+                }
+#pragma unroll
+                for (int r = 0; r < WPL; ++r)
+                {
+                    if ((look >> r) & 1u) { slot[r] = db_search_from(db, keys[r], first[r]); }
                 }
             }
 
@@ -911,9 +1009,11 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
         // ---- correction, likelihood mass, top-k (place.cpp:417-422, 164-184, 134-159) ----
         const uint32_t nw32 = static_cast<uint32_t>(n_windows);
         const float nwf = static_cast<float>(n_windows);
-        const sweep_result sw = fast_sweep_ok(db, nwf, kf)
-                                    ? sweep<CT, true, SWEEP_Q>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cand_key, cand_branch, cand_count)
-                                    : sweep_ieee<CT>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cand_key, cand_branch, cand_count);
+        const bool dense = 6ull * __reduce_add_sync(FULL, static_cast<uint32_t>(min(static_cast<unsigned long long>(ctr_entries - entries_before), 0xFFFFFFull))) >= np;
+        const sweep_result sw =
+            !fast_sweep_ok(db, nwf, kf) ? sweep_ieee<CT>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cand_key, cand_branch, cand_count)
+            : dense                     ? sweep<CT, true, true>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cand_key, cand_branch, cand_count)
+                                        : sweep_sparse<CT>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cand_key, cand_branch, cand_count);
         const uint32_t touched = sw.touched;
         uint32_t my_b = sw.branch, my_c = sw.count;
         float my_s = key_score(sw.key);

@@ -31,13 +31,13 @@ exit 0
 fi
 
 echo "== ncu launch list"
-CMD="python bench.py --reads $NCU_READS --steps 2 --warmup 1 --no-e2e --no-cpu-baseline"
+CMD="python bench.py ${BENCH_ARGS:-} --reads $NCU_READS --steps 2 --warmup 1 --no-e2e --no-cpu-baseline"
 $CMD > $OUT/${TAG}_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/${TAG}_launches.csv $CMD > $OUT/${TAG}_ncu_launches.log 2>&1
 echo "launch list rc=$?"
 
 echo "== ncu full capture of the placement kernel"
-CMD2="python bench.py --reads $NCU_READS --steps 1 --warmup 1 --no-e2e --no-cpu-baseline"
+CMD2="python bench.py ${BENCH_ARGS:-} --reads $NCU_READS --steps 1 --warmup 1 --no-e2e --no-cpu-baseline"
 $CMD2 > $OUT/${TAG}_plain2.log 2>&1 &&
 ncu --set full --clock-control none --import-source on -k "regex:$KREGEX" -s 3 -c 1 -f -o $OUT/${TAG}_prof $CMD2 > $OUT/${TAG}_ncu_full.log 2>&1
 echo "full capture rc=$?"
