@@ -43,6 +43,15 @@ def log(msg):
     print("[bench %6.1fs rank %s] %s" % (time.time() - T0, os.environ.get("RANK", "0"), msg), file=sys.stderr, flush=True)
 
 
+REAL_STDOUT = None
+
+
+def emit(line):
+    out = REAL_STDOUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -202,7 +211,7 @@ def run_reference(args):
             "reference place.cpp compiled unmodified over the i2l shim (oracle/_ref)" if kind == "reference"
             else "oracle port (oracle/_ref not built)"),
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def run_ours(args):
@@ -353,12 +362,18 @@ def run_ours(args):
             "dtype_note": "scores accumulate in f32 (bit-identical to the reference), likelihood weight ratios in f64",
             "db": {k2: int(v2) if isinstance(v2, (int, np.integer)) else float(v2) for k2, v2 in db.info.items()},
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
 def main():
+    # stdout carries ONE JSON line: anything libraries print there (NCCL announces its version on stdout) is
+    # sent to stderr instead, and the line is written to the real stdout at the end
+    global REAL_STDOUT
+    sys.stdout.flush()
+    REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     args = parse_args()
     if args.impl == "reference":
         run_reference(args)
