@@ -20,6 +20,8 @@ SYMBOLS = [
     "epk_abi_version", "epk_last_error", "epk_device_count", "epk_db_create", "epk_db_get_info", "epk_db_destroy",
     "epk_placer_create", "epk_placer_destroy", "epk_place", "epk_place_device", "epk_group_batch", "epk_kmers",
     "epk_placer_counters", "epk_host_alloc", "epk_host_free",
+    "epk_db_create_shard", "epk_shard_of_key", "epk_partial_row_bytes", "epk_place_partial_device",
+    "epk_place_finalize_device",
 ]
 
 
@@ -104,6 +106,19 @@ def lib():
                             C.c_void_p, C.POINTER(C.c_uint64)]
     l.epk_placer_counters.restype = C.c_int
     l.epk_placer_counters.argtypes = [C.c_void_p, C.POINTER(Counters)]
+    l.epk_db_create_shard.restype = C.c_int
+    l.epk_db_create_shard.argtypes = [C.POINTER(DbDesc), C.POINTER(LoadFilter), C.c_int, C.c_uint32, C.c_uint32,
+                                      C.POINTER(C.c_void_p)]
+    l.epk_shard_of_key.restype = C.c_uint32
+    l.epk_shard_of_key.argtypes = [C.c_uint32, C.c_uint32]
+    l.epk_partial_row_bytes.restype = C.c_uint64
+    l.epk_partial_row_bytes.argtypes = [C.c_void_p]
+    l.epk_place_partial_device.restype = C.c_int
+    l.epk_place_partial_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p,
+                                           C.c_void_p, C.c_void_p]
+    l.epk_place_finalize_device.restype = C.c_int
+    l.epk_place_finalize_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint64, C.c_void_p, C.c_uint32,
+                                            C.POINTER(Result), C.c_void_p]
     l.epk_host_alloc.restype = C.c_void_p
     l.epk_host_alloc.argtypes = [C.c_size_t]
     l.epk_host_free.argtypes = [C.c_void_p]

@@ -127,8 +127,10 @@ float score_threshold(uint32_t alphabet, float omega, uint32_t k)
 
 using namespace epk;
 
-static void build_db(const epk_db_desc& d, const epk_load_filter* filter, int device, epk_db& db)
+static void build_db(const epk_db_desc& d, const epk_load_filter* filter, int device, uint32_t shard_index,
+                     uint32_t shard_count, epk_db& db)
 {
+    if (shard_count == 0 || shard_count > 65536 || shard_index >= shard_count) { throw error(EPK_E_INVALID, "bad shard index / count"); }
     if (d.alphabet != EPK_DNA && d.alphabet != EPK_AA) { throw error(EPK_E_INVALID, "unknown alphabet"); }
     const uint32_t bits = d.alphabet == EPK_AA ? 5 : 2;
     if (d.kmer_size == 0 || d.kmer_size * bits > 32) { throw error(EPK_E_INVALID, "k-mer size does not fit a 32-bit key"); }
@@ -216,6 +218,14 @@ static void build_db(const epk_db_desc& d, const epk_load_filter* filter, int de
             keep.resize(n_keys);
             prefix_cut_kernel<<<blocks_for(n_keys, T), T, 0, stream>>>(before.get(), order.get(), n_keys, budget, keep.get());
             EPK_CUDA(cudaStreamSynchronize(stream));
+        }
+        // ---- database-sharded mode: after the (global) informative prefix, only this shard's keys stay ----
+        if (shard_count > 1)
+        {
+            device_buffer<uint8_t> mine(n_keys);
+            shard_keep_kernel<<<blocks_for(n_keys, T), T, 0, stream>>>(keys.get(), n_keys, shard_index, shard_count, keep.get(), mine.get());
+            EPK_CUDA(cudaStreamSynchronize(stream));
+            keep = std::move(mine);
         }
         // ---- per-entry omega threshold, packed layout ----
         surviving_lengths_kernel<<<blocks_for(n_keys * 32, T), T, 0, stream>>>(
@@ -359,9 +369,26 @@ extern "C" epk_status epk_db_create(const epk_db_desc* desc, const epk_load_filt
         if (!desc || !out) { throw error(EPK_E_INVALID, "null argument"); }
         *out = nullptr;
         auto db = std::make_unique<epk_db>();
-        build_db(*desc, filter, device, *db);
+        build_db(*desc, filter, device, 0, 1, *db);
         *out = db.release();
     });
+}
+
+extern "C" epk_status epk_db_create_shard(const epk_db_desc* desc, const epk_load_filter* filter, int device,
+                                          uint32_t shard_index, uint32_t shard_count, epk_db** out)
+{
+    return guarded([&] {
+        if (!desc || !out) { throw error(EPK_E_INVALID, "null argument"); }
+        *out = nullptr;
+        auto db = std::make_unique<epk_db>();
+        build_db(*desc, filter, device, shard_index, shard_count, *db);
+        *out = db.release();
+    });
+}
+
+extern "C" uint32_t epk_shard_of_key(uint32_t key, uint32_t shard_count)
+{
+    return shard_count ? epk::shard_of_key(key, shard_count) : 0;
 }
 
 extern "C" epk_status epk_db_get_info(const epk_db* db, epk_db_info* info)

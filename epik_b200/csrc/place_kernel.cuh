@@ -43,6 +43,7 @@ constexpr int SEG_PAD = 8;             // zero descriptors after the last one (=
 constexpr int CAND_CAP = 128;          // top-k candidates buffered per warp (aliases the segments)
 constexpr int MAX_WARPS_PER_CTA = 8;
 constexpr int SWEEP_STEP = 128;        // branches per warp and run of the sweep (4 consecutive ones per lane)
+constexpr int MAX_OWNERS = 8;          // ranks of a database-sharded group (one NVSwitch domain)
 constexpr uint32_t NO_BRANCH = 0xFFFFFFFFu;
 constexpr uint32_t FULL = 0xFFFFFFFFu;
 
@@ -78,6 +79,13 @@ struct place_params
     unsigned long long* counters; // [CTR_COUNT] of this launch
     const uint32_t* class_reads; // [N_CLASSES] queries per class (classify_kernel); NULL = unknown
     uint32_t cls;                // class this launch handles
+    // ---- database-sharded mode (partial rows out / partial rows in), see "partial rows" below ----
+    unsigned char* rows_out[MAX_OWNERS]; // partial launch: where the rows of owner g's queries go
+    uint32_t owner_first[MAX_OWNERS + 1]; // queries [owner_first[g], owner_first[g + 1]) are finalised by owner g
+    uint32_t n_owners;
+    const unsigned char* rows_in;        // finalize launch: n_shards slabs of n rows each
+    uint64_t shard_stride;               // bytes from a row of shard g to the same row of shard g + 1
+    uint32_t n_shards;
 };
 
 __host__ __device__ inline uint32_t padded_nodes(uint32_t n_nodes)
@@ -104,7 +112,7 @@ __global__ void classify_kernel(const uint64_t* __restrict__ seq_off, uint32_t n
     {
         const uint64_t len = seq_off[i + 1] - seq_off[i];
         const int c = len + 1 < k ? 0 : class_of_windows(len + 1 - k);
-        if ((unsupported_mask >> c) & 1u) { n_place[i] = 0; } // no launch will write this row
+        if (n_place && ((unsupported_mask >> c) & 1u)) { n_place[i] = 0; } // no launch will write this row
         mine[0] += c == 0;
         mine[1] += c == 1;
         mine[2] += c == 2;
@@ -716,9 +724,136 @@ __device__ __forceinline__ bool fast_sweep_ok(const device_db& db, float nwf, fl
     return db.fast_ok != 0 && lo > -EXP10_SMALL_LIMIT && hi < EXP10_SMALL_LIMIT;
 }
 
+// ---- the end of a query ---------------------------------------------------------------------------
+//
+// The accumulators S, C of one query with n_windows windows are complete (place.cpp:349-415 done):
+// correction + likelihood mass + top-k (the sweep), weight ratios, keep_factor, the rows of query q.
+// `gathered` = postings the query gathered (warp-uniform; only steers dense / scan-and-queue).
+template<class CT>
+__device__ __forceinline__ void finish_query(const place_params& p, float* S, CT* C, uint32_t np, uint64_t n_windows,
+                                             uint32_t gathered, uint32_t q, uint32_t lane, uint32_t* cand_key,
+                                             uint32_t* cand_branch, uint32_t* cand_count)
+{
+    const device_db& db = p.db;
+    const uint32_t N = db.n_nodes;
+    const uint32_t K = p.keep_at_most;
+    const float kf = static_cast<float>(db.k);
+    const float rcp_k = __frcp_rn(kf);
+    const float logthr = db.log_threshold;
+    // ---- correction, likelihood mass, top-k (place.cpp:417-422, 164-184, 134-159) ----
+    const uint32_t nw32 = static_cast<uint32_t>(n_windows);
+    const float nwf = static_cast<float>(n_windows);
+    const bool dense = 6ull * gathered >= np;
+    const sweep_result sw =
+        !fast_sweep_ok(db, nwf, kf) ? sweep_ieee<CT>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cand_key, cand_branch, cand_count)
+        : dense                     ? sweep<CT, true, true>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cand_key, cand_branch, cand_count)
+                                    : sweep_sparse<CT>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cand_key, cand_branch, cand_count);
+    const uint32_t touched = sw.touched;
+    uint32_t my_b = sw.branch, my_c = sw.count;
+    float my_s = key_score(sw.key);
+
+    // ---- likelihood weight ratios and keep_factor (place.cpp:164-184, 241-267) ----
+    const float absent_score = __fdiv_rn(__fmul_rn(nwf, logthr), kf);
+    const double absent_mass = static_cast<double>(static_cast<float>(N) - static_cast<float>(touched))
+                               * exp10_of_float(absent_score);
+    const double total = absent_mass + sw.mass;
+    uint32_t n_out = sw.n_keep;
+    if (touched == 0)
+    {
+        // no k-mer found: keep_at_most placements on the first branches (place.cpp:141-152), in the
+        // order std::partial_sort leaves all-tied elements in (precomputed on the host)
+        n_out = K;
+        if (lane < K)
+        {
+            my_s = absent_score;
+            my_b = p.fake_order[lane];
+            my_c = 0;
+        }
+    }
+    double ratio = 0.0;
+    double keep_factor = p.keep_factor;
+    if (total == 0.0) { keep_factor = 0.0; }
+    else if (lane < n_out)
+    {
+        const double power = exp10_of_float(my_s);
+        ratio = power == 0.0 ? 0.0 : power / total;
+    }
+    const double cut = __shfl_sync(FULL, ratio, 0) * keep_factor;
+    const bool keep = lane < n_out && ratio >= cut;
+    const uint32_t kept = __ballot_sync(FULL, keep);
+    const uint32_t rank = __popc(kept & ((1u << lane) - 1u));
+    const uint32_t n_kept = __popc(kept);
+    const size_t row = static_cast<size_t>(q) * K;
+    if (keep)
+    {
+        p.branch[row + rank] = my_b;
+        p.score[row + rank] = my_s;
+        p.lwr[row + rank] = ratio;
+        p.count[row + rank] = my_c;
+    }
+    if (lane >= n_kept && lane < K)
+    {
+        p.branch[row + lane] = 0;
+        p.score[row + lane] = 0.0f;
+        p.lwr[row + lane] = 0.0;
+        p.count[row + lane] = 0;
+    }
+    if (lane == 0) { p.n_place[q] = n_kept; }
+    __syncwarp();
+}
+
+// ---- partial rows (database-sharded mode) ---------------------------------------------------------
+//
+// When the database is split by key over the GPUs of a group (second row), every GPU
+// runs the encode / probe / gather phases of EVERY query against its shard and leaves, per query, a
+// row   { uint32 flags, uint32 postings gathered, 0, 0 | float S[np] | uint16 C[np] }
+// in the memory of the GPU that finalises that query (its own, a send buffer, or a peer's slab mapped
+// over NVLink). The owner adds the rows of all shards in shard order and runs finish_query on the sums.
+// The additions of one branch are no longer in window order: scores agree with the reference to
+// float rounding of a differently associated sum (asserted at 1e-5 relative), not bit for bit.
+constexpr uint32_t ROW_HEADER_BYTES = 16;
+constexpr uint32_t ROW_FLAG_AMBIGUOUS = 1u; // the query has windows with one ambiguous letter: the
+                                            // first-key-wins rule of place.cpp:391 needs the global key
+                                            // order, which a shard does not have -> reported unsupported
+__host__ __device__ inline uint64_t partial_row_bytes(uint32_t n_nodes)
+{
+    return ROW_HEADER_BYTES + 6ull * padded_nodes(n_nodes);
+}
+
+__device__ __forceinline__ void store_counts4_u16(unsigned char* at, const uint32_t (&c)[4])
+{
+    *reinterpret_cast<uint2*>(at) = make_uint2(c[0] | (c[1] << 16), c[2] | (c[3] << 16));
+}
+
+// S, C of query q -> its row at the owner; leaves both arrays zeroed
+template<class CT>
+__device__ __forceinline__ void dump_partial_row(const place_params& p, float* S, CT* C, uint32_t np, uint32_t q,
+                                                 uint32_t flags, uint32_t gathered, uint32_t lane)
+{
+    uint32_t g = 0;
+    while (g + 1 < p.n_owners && q >= p.owner_first[g + 1]) { ++g; }
+    unsigned char* row = p.rows_out[g] + static_cast<uint64_t>(q - p.owner_first[g]) * partial_row_bytes(p.db.n_nodes);
+    if (lane == 0) { *reinterpret_cast<uint4*>(row) = make_uint4(flags, gathered, 0u, 0u); }
+    unsigned char* s_out = row + ROW_HEADER_BYTES;
+    unsigned char* c_out = s_out + 4ull * np;
+    for (uint32_t j = 4u * lane; j < np; j += SWEEP_STEP)
+    {
+        const float4 s4 = *reinterpret_cast<const float4*>(S + j);
+        uint32_t c[4];
+        load_counts4(C, j, c);
+        *reinterpret_cast<float4*>(S + j) = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        clear_counts4(C, j);
+        *reinterpret_cast<float4*>(s_out + 4ull * j) = s4;
+        store_counts4_u16(c_out + 2ull * j, c);
+    }
+    __syncwarp();
+}
+
 // ---- the kernel ----------------------------------------------------------------------------------
 
-template<uint32_t TABLE, int U, class CT>
+// PARTIAL: database-sharded mode, the accumulators of a query leave as a partial row instead of being
+// swept (queries with ambiguous windows are flagged, their ambiguous windows left out).
+template<uint32_t TABLE, int U, class CT, bool PARTIAL = false>
 __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const place_params p)
 {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -730,7 +865,6 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
     const uint32_t np = padded_nodes(N);
     const uint32_t k = db.k;
     const uint32_t bits = db.bits;
-    const uint32_t K = p.keep_at_most;
     static_assert(U <= SEG_PAD, "zero padding of the segment buffer covers one batch of loads");
 
     uint32_t* letters = reinterpret_cast<uint32_t*>(smem);
@@ -759,8 +893,6 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
     __syncthreads();
 
     const float kf = static_cast<float>(k);
-    const float rcp_k = __frcp_rn(kf);
-    const float logthr = db.log_threshold;
     const uint32_t key_mask = db.key_mask;
     uint64_t ctr_windows = 0, ctr_hits = 0, ctr_entries = 0; // per lane, folded once at the end
 
@@ -776,7 +908,7 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
         if (len + 1 < k)
         {
             // the reference dies here (size_t wrap at place.cpp:291); reported as EPK_E_SHORT_SEQ
-            if (lane == 0 && p.cls == 0)
+            if (lane == 0 && p.cls == 0 && !PARTIAL) // (sharded mode: the finalising launch reports it)
             {
                 atomicAdd(p.counters + CTR_SHORT, 1ull);
                 p.n_place[q] = 0;
@@ -788,7 +920,7 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
         if (class_of_windows(n_windows) != static_cast<int>(p.cls)) { continue; } // another launch's query
         if (n_windows > class_max_windows(N_CLASSES - 1))
         {
-            if (lane == 0)
+            if (lane == 0 && !PARTIAL)
             {
                 atomicAdd(p.counters + CTR_TOO_LONG, 1ull);
                 p.n_place[q] = 0;
@@ -941,6 +1073,12 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
 
         // ---- windows with exactly one ambiguous letter (place.cpp:306-313, 373-415) ----
         has_ambiguous = __any_sync(FULL, has_ambiguous);
+        if (PARTIAL)
+        {
+            const uint32_t gathered_here = __reduce_add_sync(FULL, static_cast<uint32_t>(min(static_cast<unsigned long long>(ctr_entries - entries_before), 0xFFFFFFull)));
+            dump_partial_row<CT>(p, S, C, np, q, has_ambiguous ? ROW_FLAG_AMBIGUOUS : 0u, gathered_here, lane);
+            continue;
+        }
         if (has_ambiguous)
         {
             const float thr_rest = __fmul_rn(static_cast<float>(k - 1), db.threshold);
@@ -1006,66 +1144,9 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
             __syncwarp();
         }
 
-        // ---- correction, likelihood mass, top-k (place.cpp:417-422, 164-184, 134-159) ----
-        const uint32_t nw32 = static_cast<uint32_t>(n_windows);
-        const float nwf = static_cast<float>(n_windows);
-        const bool dense = 6ull * __reduce_add_sync(FULL, static_cast<uint32_t>(min(static_cast<unsigned long long>(ctr_entries - entries_before), 0xFFFFFFull))) >= np;
-        const sweep_result sw =
-            !fast_sweep_ok(db, nwf, kf) ? sweep_ieee<CT>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cand_key, cand_branch, cand_count)
-            : dense                     ? sweep<CT, true, true>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cand_key, cand_branch, cand_count)
-                                        : sweep_sparse<CT>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cand_key, cand_branch, cand_count);
-        const uint32_t touched = sw.touched;
-        uint32_t my_b = sw.branch, my_c = sw.count;
-        float my_s = key_score(sw.key);
-
-        // ---- likelihood weight ratios and keep_factor (place.cpp:164-184, 241-267) ----
-        const float absent_score = __fdiv_rn(__fmul_rn(nwf, logthr), kf);
-        const double absent_mass = static_cast<double>(static_cast<float>(N) - static_cast<float>(touched))
-                                   * exp10_of_float(absent_score);
-        const double total = absent_mass + sw.mass;
-        uint32_t n_out = sw.n_keep;
-        if (touched == 0)
-        {
-            // no k-mer found: keep_at_most placements on the first branches (place.cpp:141-152), in the
-            // order std::partial_sort leaves all-tied elements in (precomputed on the host)
-            n_out = K;
-            if (lane < K)
-            {
-                my_s = absent_score;
-                my_b = p.fake_order[lane];
-                my_c = 0;
-            }
-        }
-        double ratio = 0.0;
-        double keep_factor = p.keep_factor;
-        if (total == 0.0) { keep_factor = 0.0; }
-        else if (lane < n_out)
-        {
-            const double power = exp10_of_float(my_s);
-            ratio = power == 0.0 ? 0.0 : power / total;
-        }
-        const double cut = __shfl_sync(FULL, ratio, 0) * keep_factor;
-        const bool keep = lane < n_out && ratio >= cut;
-        const uint32_t kept = __ballot_sync(FULL, keep);
-        const uint32_t rank = __popc(kept & ((1u << lane) - 1u));
-        const uint32_t n_kept = __popc(kept);
-        const size_t row = static_cast<size_t>(q) * K;
-        if (keep)
-        {
-            p.branch[row + rank] = my_b;
-            p.score[row + rank] = my_s;
-            p.lwr[row + rank] = ratio;
-            p.count[row + rank] = my_c;
-        }
-        if (lane >= n_kept && lane < K)
-        {
-            p.branch[row + lane] = 0;
-            p.score[row + lane] = 0.0f;
-            p.lwr[row + lane] = 0.0;
-            p.count[row + lane] = 0;
-        }
-        if (lane == 0) { p.n_place[q] = n_kept; }
-        __syncwarp();
+        // ---- correction, likelihood mass, top-k, weight ratios (place.cpp:417-422, 164-184, 134-159, 241-267) ----
+        const uint32_t gathered = __reduce_add_sync(FULL, static_cast<uint32_t>(min(static_cast<unsigned long long>(ctr_entries - entries_before), 0xFFFFFFull)));
+        finish_query<CT>(p, S, C, np, n_windows, gathered, q, lane, cand_key, cand_branch, cand_count);
     }
 
 #pragma unroll
@@ -1080,6 +1161,81 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
         atomicAdd(p.counters + CTR_WINDOWS, static_cast<unsigned long long>(ctr_windows));
         atomicAdd(p.counters + CTR_HITS, static_cast<unsigned long long>(ctr_hits));
         atomicAdd(p.counters + CTR_ENTRIES, static_cast<unsigned long long>(ctr_entries));
+    }
+}
+// Database-sharded mode, the owner's side: adds the partial rows of the n_shards shards of each of its
+// queries (shard order: a fixed association, the same on every run), then finishes the query exactly
+// like place_kernel does. One warp per query; shared memory per warp as for uint16 counts.
+__global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) finalize_kernel(const place_params p)
+{
+    using CT = uint16_t;
+    extern __shared__ __align__(16) unsigned char smem[];
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t warp = threadIdx.x >> 5;
+    const device_db& db = p.db;
+    const uint32_t N = db.n_nodes;
+    const uint32_t np = padded_nodes(N);
+    const uint32_t k = db.k;
+    unsigned char* base = smem + CTA_SMEM_FIXED + warp * warp_smem_bytes(N, sizeof(CT));
+    float* S = reinterpret_cast<float*>(base);
+    CT* C = reinterpret_cast<CT*>(base + static_cast<size_t>(np) * 4);
+    uint32_t* cand_key = reinterpret_cast<uint32_t*>(base + static_cast<size_t>(np) * (4 + sizeof(CT)) + np / 8);
+    uint32_t* cand_branch = cand_key + CAND_CAP;
+    uint32_t* cand_count = cand_branch + CAND_CAP;
+    const uint64_t row_bytes = partial_row_bytes(N);
+
+    while (true)
+    {
+        uint32_t q = 0;
+        if (lane == 0) { q = static_cast<uint32_t>(atomicAdd(p.counters + CTR_CURSOR, 1ull)); }
+        q = __shfl_sync(FULL, q, 0);
+        if (q >= p.n) { break; }
+        const uint64_t len = p.seq_off[q + 1] - p.seq_off[q];
+        const unsigned char* row0 = p.rows_in + static_cast<uint64_t>(q) * row_bytes;
+        uint32_t flags = 0, gathered = 0;
+        if (lane < p.n_shards)
+        {
+            const uint4 h = *reinterpret_cast<const uint4*>(row0 + lane * p.shard_stride);
+            flags = h.x;
+            gathered = h.y;
+        }
+        flags = __reduce_or_sync(FULL, flags);
+        gathered = __reduce_add_sync(FULL, gathered);
+        const bool too_short = len + 1 < k;
+        const uint64_t n_windows = too_short ? 0 : len + 1 - k;
+        if (too_short || n_windows > class_max_windows(1) || (flags & ROW_FLAG_AMBIGUOUS))
+        {
+            if (lane == 0)
+            {
+                atomicAdd(p.counters + (too_short ? CTR_SHORT : CTR_UNSUPPORTED), 1ull);
+                p.n_place[q] = 0;
+            }
+            continue;
+        }
+        if (lane == 0)
+        {
+            atomicAdd(p.counters + CTR_WINDOWS, static_cast<unsigned long long>(n_windows));
+            atomicAdd(p.counters + CTR_ENTRIES, static_cast<unsigned long long>(gathered));
+        }
+        for (uint32_t j = 4u * lane; j < np; j += SWEEP_STEP)
+        {
+            const unsigned char* s_in = row0 + ROW_HEADER_BYTES + 4ull * j;
+            const unsigned char* c_in = row0 + ROW_HEADER_BYTES + 4ull * np + 2ull * j;
+            float4 s4 = __ldcs(reinterpret_cast<const float4*>(s_in));
+            uint2 c2 = __ldcs(reinterpret_cast<const uint2*>(c_in));
+            for (uint32_t g = 1; g < p.n_shards; ++g)
+            {
+                const float4 t = __ldcs(reinterpret_cast<const float4*>(s_in + g * p.shard_stride));
+                const uint2 u = __ldcs(reinterpret_cast<const uint2*>(c_in + g * p.shard_stride));
+                s4.x = __fadd_rn(s4.x, t.x); s4.y = __fadd_rn(s4.y, t.y);
+                s4.z = __fadd_rn(s4.z, t.z); s4.w = __fadd_rn(s4.w, t.w);
+                c2.x += u.x; c2.y += u.y; // 16-bit halves cannot carry: a branch is hit at most n_windows <= 65535 times
+            }
+            *reinterpret_cast<float4*>(S + j) = s4;
+            *reinterpret_cast<uint2*>(C + j) = c2;
+        }
+        __syncwarp();
+        finish_query<CT>(p, S, C, np, n_windows, gathered, q, lane, cand_key, cand_branch, cand_count);
     }
 }
 } // namespace epk

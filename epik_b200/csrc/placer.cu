@@ -131,6 +131,16 @@ namespace
 {
     using kernel_fn = void (*)(const place_params);
 
+    // the launch of database-sharded mode that leaves partial rows (classes 0 and 1 only)
+    kernel_fn pick_partial_kernel(const epk_placer& pl, int cls)
+    {
+        if (pl.db->table_kind == TABLE_DIRECT)
+        {
+            return cls == 0 ? place_kernel<TABLE_DIRECT, 8, uint8_t, true> : place_kernel<TABLE_DIRECT, 8, uint16_t, true>;
+        }
+        return cls == 0 ? place_kernel<TABLE_HASH, 8, uint8_t, true> : place_kernel<TABLE_HASH, 8, uint16_t, true>;
+    }
+
     kernel_fn pick_kernel(const epk_placer& pl, int cls)
     {
         if (pl.db->table_kind == TABLE_DIRECT)
@@ -321,6 +331,16 @@ extern "C" epk_status epk_placer_create(const epk_db* db, uint64_t keep_at_most,
             pl->smem_bytes[c] = CTA_SMEM_FIXED + pl->warps_per_cta[c] * per_warp;
             EPK_CUDA(cudaFuncSetAttribute(pick_kernel(*pl, c), cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           static_cast<int>(pl->smem_bytes[c])));
+            if (c < 2)
+            {
+                EPK_CUDA(cudaFuncSetAttribute(pick_partial_kernel(*pl, c), cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              static_cast<int>(pl->smem_bytes[c])));
+            }
+            if (c == 1)
+            {
+                EPK_CUDA(cudaFuncSetAttribute(finalize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              static_cast<int>(pl->smem_bytes[c])));
+            }
         }
         if (pl->warps_per_cta[0] == 0)
         {
@@ -501,6 +521,130 @@ extern "C" epk_status epk_place(epk_placer* pl, const char* seq, const uint64_t*
                 }
             }
         }
+    });
+}
+
+// ---- database-sharded mode -----------------------------------------------------------------------
+
+extern "C" uint64_t epk_partial_row_bytes(const epk_placer* pl)
+{
+    return pl ? partial_row_bytes(pl->db->d.n_nodes) : 0;
+}
+
+extern "C" epk_status epk_place_partial_device(epk_placer* pl, const char* d_seq, const uint64_t* d_seq_off, uint32_t n,
+                                               uint32_t n_owners, const uint32_t* owner_first, void* const* d_rows,
+                                               void* stream)
+{
+    return guarded([&] {
+        if (!pl || (n && (!d_seq_off || !owner_first || !d_rows))) { throw error(EPK_E_INVALID, "null argument"); }
+        if (n_owners == 0 || n_owners > static_cast<uint32_t>(MAX_OWNERS)) { throw error(EPK_E_INVALID, "n_owners must be in [1, 8]"); }
+        if (pl->warps_per_cta[1] == 0)
+        {
+            throw error(EPK_E_UNSUPPORTED, "tree too large for the shared-memory accumulators of database-sharded mode");
+        }
+        EPK_CUDA(cudaSetDevice(pl->db->device));
+        const cudaStream_t s = static_cast<cudaStream_t>(stream);
+        place_params p{};
+        p.db = pl->db->d;
+        p.seq = d_seq;
+        p.seq_off = d_seq_off;
+        p.n = n;
+        p.keep_at_most = pl->keep_at_most;
+        p.keep_factor = pl->keep_factor;
+        p.letters = pl->db->letters.get();
+        p.fake_order = pl->fake_order.get();
+        p.n_owners = n_owners;
+        for (uint32_t g = 0; g < n_owners; ++g)
+        {
+            if (owner_first[g] > owner_first[g + 1]) { throw error(EPK_E_INVALID, "owner_first must be non-decreasing"); }
+            if (owner_first[g] < owner_first[g + 1] && !d_rows[g]) { throw error(EPK_E_INVALID, "null row buffer"); }
+            p.owner_first[g] = owner_first[g];
+            p.rows_out[g] = static_cast<unsigned char*>(d_rows[g]);
+        }
+        p.owner_first[n_owners] = owner_first[n_owners];
+        if (owner_first[0] != 0 || owner_first[n_owners] != n) { throw error(EPK_E_INVALID, "owner_first must span [0, n]"); }
+
+        unsigned long long* counters = pl->device_counters.get();
+        uint32_t* class_reads = pl->device_class_reads.get();
+        EPK_CUDA(cudaMemsetAsync(pl->totals.get(), 0, pl->totals.bytes(), s));
+        EPK_CUDA(cudaMemsetAsync(counters, 0, N_CLASSES * CTR_COUNT * sizeof(unsigned long long), s));
+        EPK_CUDA(cudaMemsetAsync(class_reads, 0, N_CLASSES * sizeof(uint32_t), s));
+        pl->n_launches = 0;
+        pl->n_reads = n;
+        if (n)
+        {
+            const unsigned cgrid = static_cast<unsigned>(std::min<uint64_t>(4ull * pl->n_sms, (static_cast<uint64_t>(n) + 255) / 256));
+            classify_kernel<<<cgrid, 256, 0, s>>>(d_seq_off, n, pl->db->d.k, class_reads, 0u, nullptr);
+            EPK_CUDA(cudaGetLastError());
+            ++pl->n_launches;
+            p.class_reads = class_reads;
+            for (int c = 0; c < 2; ++c)
+            {
+                p.cls = static_cast<uint32_t>(c);
+                p.counters = counters + c * CTR_COUNT;
+                const unsigned grid = static_cast<unsigned>(
+                    std::min<uint64_t>(pl->n_sms, (static_cast<uint64_t>(n) + pl->warps_per_cta[c] - 1) / pl->warps_per_cta[c]));
+                pick_partial_kernel(*pl, c)<<<grid, pl->warps_per_cta[c] * 32, pl->smem_bytes[c], s>>>(p);
+                EPK_CUDA(cudaGetLastError());
+                ++pl->n_launches;
+            }
+            fold_counters_kernel<<<1, 1, 0, s>>>(counters, class_reads, 0u, pl->totals.get());
+            EPK_CUDA(cudaGetLastError());
+            ++pl->n_launches;
+        }
+        pl->totals_dirty = true;
+        pl->last_stream = s;
+    });
+}
+
+extern "C" epk_status epk_place_finalize_device(epk_placer* pl, const void* d_rows, uint32_t n_shards,
+                                                uint64_t shard_stride_bytes, const uint64_t* d_seq_off, uint32_t n,
+                                                const epk_result* d_out, void* stream)
+{
+    return guarded([&] {
+        if (!pl || !d_out || (n && (!d_rows || !d_seq_off || !d_out->n_place || !d_out->branch || !d_out->score || !d_out->lwr || !d_out->count)))
+        {
+            throw error(EPK_E_INVALID, "null argument");
+        }
+        if (n_shards == 0 || n_shards > 32) { throw error(EPK_E_INVALID, "n_shards must be in [1, 32]"); }
+        if (d_out->distal || d_out->pendant) { throw error(EPK_E_INVALID, "distal/pendant must be NULL for device results"); }
+        if (pl->warps_per_cta[1] == 0)
+        {
+            throw error(EPK_E_UNSUPPORTED, "tree too large for the shared-memory accumulators of database-sharded mode");
+        }
+        if (shard_stride_bytes % 16 != 0 || (reinterpret_cast<uintptr_t>(d_rows) & 15u)) { throw error(EPK_E_INVALID, "rows must be 16-byte aligned"); }
+        EPK_CUDA(cudaSetDevice(pl->db->device));
+        const cudaStream_t s = static_cast<cudaStream_t>(stream);
+        place_params p{};
+        p.db = pl->db->d;
+        p.seq_off = d_seq_off;
+        p.n = n;
+        p.keep_at_most = pl->keep_at_most;
+        p.keep_factor = pl->keep_factor;
+        p.n_place = d_out->n_place;
+        p.branch = d_out->branch;
+        p.score = d_out->score;
+        p.lwr = d_out->lwr;
+        p.count = d_out->count;
+        p.fake_order = pl->fake_order.get();
+        p.rows_in = static_cast<const unsigned char*>(d_rows);
+        p.n_shards = n_shards;
+        p.shard_stride = shard_stride_bytes;
+        // the counters of this call replace those of the partial launch: they now describe whole queries
+        EPK_CUDA(cudaMemsetAsync(pl->totals.get(), 0, pl->totals.bytes(), s));
+        p.counters = pl->totals.get();
+        pl->n_launches = 0;
+        pl->n_reads = n;
+        if (n)
+        {
+            const unsigned grid = static_cast<unsigned>(
+                std::min<uint64_t>(pl->n_sms, (static_cast<uint64_t>(n) + pl->warps_per_cta[1] - 1) / pl->warps_per_cta[1]));
+            finalize_kernel<<<grid, pl->warps_per_cta[1] * 32, pl->smem_bytes[1], s>>>(p);
+            EPK_CUDA(cudaGetLastError());
+            ++pl->n_launches;
+        }
+        pl->totals_dirty = true;
+        pl->last_stream = s;
     });
 }
 

@@ -1,0 +1,151 @@
+"""Database-sharded placement (second row): the k-mer keys are split by hash range over the
+GPUs of a group, every GPU looks every query up in its shard, and the per-branch partial sums are brought
+together on the GPU that owns the query before the threshold correction, the likelihood mass, the top-k and
+the weight ratios (place.cpp:417-422, 164-199, 238-267) run there.
+
+Needed only when a database exceeds one GPU's HBM; the default is query sharding (shard.py) with the
+database replicated. The reference has nothing like it (one phylo_kmer_db in one address space,
+main.cpp:277): what is preserved is the result, within float rounding of a re-associated sum.
+
+Two transports for the partial rows (include/epik_b200.h, "database-sharded mode"):
+  * "a2a"  — every rank writes the rows of all queries into a send buffer ordered by owner and one
+             all_to_all_single (NCCL over NVLink; gloo in the CPU tests of the layout) delivers the slabs;
+  * "local" — all shards live on ONE device (tests, and databases that merely do not fit one table build):
+             the rows are written straight into the slab the finalising launch reads.
+All computing is in libepik_b200.so; this module only sizes buffers and calls the collective.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from .placer import Database, Placer
+from .shard import slice_for_rank
+
+RESULT_FIELDS = ("n_place", "branch", "score", "lwr", "count")
+
+
+def owner_bounds(n: int, world: int) -> np.ndarray:
+    """owner_first[g] .. owner_first[g + 1]: the queries of a batch of n that rank g finalises."""
+    return np.array([slice_for_rank(n, g, world)[0] for g in range(world)] + [n], dtype=np.uint32)
+
+
+def exchange_rows(send, n: int, rank: int, world: int, group=None):
+    """send: uint8 tensor [n, row_bytes], rows ordered by query (hence by owner). Returns the tensor
+    [world, m, row_bytes] of the rows of this rank's m queries, one slab per shard, in shard order."""
+    import torch
+    import torch.distributed as dist
+    bounds = owner_bounds(n, world)
+    sizes = [int(bounds[g + 1] - bounds[g]) for g in range(world)]
+    m = sizes[rank]
+    recv = torch.empty((world * m, send.shape[1]), dtype=send.dtype, device=send.device)
+    dist.all_to_all_single(recv, send, output_split_sizes=[m] * world, input_split_sizes=sizes, group=group)
+    return recv.view(world, m, send.shape[1])
+
+
+def _alloc_out(torch, n: int, K: int, device):
+    return {"n_place": torch.zeros(n, dtype=torch.int32, device=device),
+            "branch": torch.zeros((n, K), dtype=torch.int32, device=device),
+            "score": torch.zeros((n, K), dtype=torch.float32, device=device),
+            "lwr": torch.zeros((n, K), dtype=torch.float64, device=device),
+            "count": torch.zeros((n, K), dtype=torch.int32, device=device)}
+
+
+def _to_host(out: dict) -> dict:
+    res = {k: v.cpu().numpy() for k, v in out.items()}
+    for k in ("n_place", "branch", "count"):
+        res[k] = res[k].view(np.uint32)
+    return res
+
+
+class LocalShardedPlacer:
+    """All n_shards shards on one device: partial launches write into the slab the finalising launch reads."""
+
+    def __init__(self, flat, n_shards: int, device: int = 0, keep_at_most: int = 7, keep_factor: float = 0.01, **load):
+        self.dbs = [Database(flat, device=device, shard=(g, n_shards), **load) for g in range(n_shards)]
+        self.placers = [Placer(db, keep_at_most, keep_factor) for db in self.dbs]
+        self.n_shards = n_shards
+        self.device = device
+        self.keep_at_most = keep_at_most
+
+    def place_packed(self, data, offsets, max_rows: int = 1 << 15):
+        import torch
+        dev = torch.device("cuda", self.device)
+        n = len(offsets) - 1
+        d_seq = torch.from_numpy(np.ascontiguousarray(data, np.uint8)).to(dev) if len(data) else torch.zeros(1, dtype=torch.uint8, device=dev)
+        d_off = torch.from_numpy(np.ascontiguousarray(offsets, np.uint64).view(np.int64)).to(dev)
+        out = _alloc_out(torch, n, self.keep_at_most, dev)
+        row_bytes = self.placers[0].partial_row_bytes()
+        step = max(1, min(n, max_rows))
+        slab = torch.empty((self.n_shards, step, row_bytes), dtype=torch.uint8, device=dev)
+        self.unsupported = 0
+        self.short = 0
+        for first in range(0, n, step):
+            m = min(step, n - first)
+            off_ptr = d_off.data_ptr() + 8 * first
+            for g, pl in enumerate(self.placers):
+                # absolute offsets: the sequence base stays, the offsets pointer moves
+                pl.place_partial_device(d_seq, _Ptr(off_ptr), m, [0, m], [slab[g].data_ptr()])
+            piece = {k: v[first:first + m] for k, v in out.items()}
+            self.placers[0].place_finalize_device(slab.data_ptr(), self.n_shards, step * row_bytes, off_ptr, m, piece)
+            c = self.placers[0].counters()
+            self.unsupported += c["n_unsupported"]
+            self.short += c["n_short"]
+        torch.cuda.synchronize(dev)
+        return _to_host(out)
+
+
+class _Ptr:
+    """Minimal .data_ptr() carrier for an address inside a tensor."""
+
+    def __init__(self, p: int):
+        self._p = int(p)
+
+    def data_ptr(self) -> int:
+        return self._p
+
+
+class ShardedPlacer:
+    """One rank of a database-sharded group (torch.distributed, one process per GPU). Every rank passes the
+    SAME batch; rank r gets back the placements of its slice [first, last) of the batch."""
+
+    def __init__(self, flat, rank: int, world: int, group=None, device: int = 0, keep_at_most: int = 7,
+                 keep_factor: float = 0.01, **load):
+        self.db = Database(flat, device=device, shard=(rank, world), **load)
+        self.placer = Placer(self.db, keep_at_most, keep_factor)
+        self.rank, self.world, self.group, self.device = rank, world, group, device
+        self.keep_at_most = keep_at_most
+        self.row_bytes = self.placer.partial_row_bytes()
+        self._send = None
+        self.unsupported = 0
+        self.short = 0
+
+    def place_device(self, d_seq, d_off, n: int, out: dict | None = None):
+        """d_seq (uint8) / d_off (int64 view of uint64 offsets, n + 1) on this rank's device; the whole batch.
+        Returns (out, first, last): device tensors with the rows of queries [first, last)."""
+        import torch
+        dev = d_off.device
+        bounds = owner_bounds(n, self.world)
+        first, last = int(bounds[self.rank]), int(bounds[self.rank + 1])
+        if self._send is None or self._send.shape[0] < n:
+            self._send = torch.empty((n, self.row_bytes), dtype=torch.uint8, device=dev)
+        send = self._send[:n]
+        base = send.data_ptr()
+        self.placer.place_partial_device(d_seq, d_off, n, bounds, [base + int(bounds[g]) * self.row_bytes for g in range(self.world)])
+        slabs = exchange_rows(send, n, self.rank, self.world, self.group)
+        m = last - first
+        if out is None:
+            out = _alloc_out(torch, m, self.keep_at_most, dev)
+        self.placer.place_finalize_device(slabs.data_ptr(), self.world, m * self.row_bytes, d_off.data_ptr() + 8 * first, m, out)
+        return out, first, last
+
+    def place_packed(self, data, offsets):
+        import torch
+        dev = torch.device("cuda", self.device)
+        n = len(offsets) - 1
+        d_seq = torch.from_numpy(np.ascontiguousarray(data, np.uint8)).to(dev) if len(data) else torch.zeros(1, dtype=torch.uint8, device=dev)
+        d_off = torch.from_numpy(np.ascontiguousarray(offsets, np.uint64).view(np.int64)).to(dev)
+        out, first, last = self.place_device(d_seq, d_off, n)
+        torch.cuda.synchronize(dev)
+        c = self.placer.counters()
+        self.unsupported, self.short = c["n_unsupported"], c["n_short"]
+        return _to_host(out), first, last

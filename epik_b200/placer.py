@@ -62,10 +62,11 @@ class PinnedArray:
 
 class Database:
     """HBM-resident phylo-k-mer database (epk_db). `mu`, `omega`, `max_entries` are the load-filter
-    arguments of i2l::load (main.cpp:277); leave all three None to load everything."""
+    arguments of i2l::load (main.cpp:277); leave all three None to load everything. `shard` = (index, count)
+    keeps only the keys of one shard (database-sharded mode, epk_db_create_shard)."""
 
     def __init__(self, db: FlatDB, mu: float | None = None, omega: float | None = None,
-                 max_entries: int | None = None, device: int = 0):
+                 max_entries: int | None = None, device: int = 0, shard: tuple[int, int] | None = None):
         l = capi.lib()
         db.validate()
         self.flat = db
@@ -83,7 +84,12 @@ class Database:
             flt = capi.LoadFilter(1.0 if mu is None else float(mu), float(db.omega if omega is None else omega),
                                   capi.UINT64_MAX if max_entries is None else int(max_entries))
         handle = C.c_void_p()
-        capi.check(l.epk_db_create(C.byref(desc), C.byref(flt) if flt is not None else None, int(device), C.byref(handle)))
+        fref = C.byref(flt) if flt is not None else None
+        if shard is None:
+            capi.check(l.epk_db_create(C.byref(desc), fref, int(device), C.byref(handle)))
+        else:
+            capi.check(l.epk_db_create_shard(C.byref(desc), fref, int(device), int(shard[0]), int(shard[1]), C.byref(handle)))
+        self.shard = shard
         self.handle = handle
         self.device = int(device)
         info = capi.DbInfo()
@@ -197,6 +203,29 @@ class Placer:
                           d_out["lwr"].data_ptr(), d_out["count"].data_ptr(), None, None)
         s = None if stream is None else C.c_void_p(stream.cuda_stream)
         capi.check(capi.lib().epk_place_device(self.handle, d_seq.data_ptr(), d_off.data_ptr(), int(n), C.byref(res), s))
+
+    # ------------------------------------------------------------- database-sharded mode -----
+    def partial_row_bytes(self) -> int:
+        return int(capi.lib().epk_partial_row_bytes(self.handle))
+
+    def place_partial_device(self, d_seq, d_off, n: int, owner_first, row_ptrs, stream=None):
+        """epk_place_partial_device: the partial row of query i goes to row_ptrs[g] + (i - owner_first[g]) * row_bytes
+        for the owner g with owner_first[g] <= i < owner_first[g + 1]. row_ptrs are device addresses (ints)."""
+        first = np.ascontiguousarray(owner_first, np.uint32)
+        ptrs = (C.c_void_p * len(row_ptrs))(*[C.c_void_p(int(p)) for p in row_ptrs])
+        s = None if stream is None else C.c_void_p(stream.cuda_stream)
+        capi.check(capi.lib().epk_place_partial_device(self.handle, d_seq.data_ptr(), d_off.data_ptr(), int(n),
+                                                       len(row_ptrs), _ptr(first), ptrs, s))
+
+    def place_finalize_device(self, rows_ptr: int, n_shards: int, shard_stride: int, d_off_ptr: int, n: int, d_out: dict,
+                              stream=None):
+        """epk_place_finalize_device over n queries whose rows of shard g start at rows_ptr + g * shard_stride."""
+        res = capi.Result(d_out["n_place"].data_ptr(), d_out["branch"].data_ptr(), d_out["score"].data_ptr(),
+                          d_out["lwr"].data_ptr(), d_out["count"].data_ptr(), None, None)
+        s = None if stream is None else C.c_void_p(stream.cuda_stream)
+        capi.check(capi.lib().epk_place_finalize_device(self.handle, C.c_void_p(int(rows_ptr)), int(n_shards),
+                                                        int(shard_stride), C.c_void_p(int(d_off_ptr)), int(n),
+                                                        C.byref(res), s))
 
     def counters(self) -> dict:
         c = capi.Counters()

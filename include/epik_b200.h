@@ -176,6 +176,45 @@ typedef struct epk_counters
 } epk_counters;
 epk_status epk_placer_counters(epk_placer* placer, epk_counters* out);
 
+/* ---- database-sharded mode (used when a database exceeds one GPU's HBM) -----------
+ *
+ * The reference has one phylo_kmer_db in one address space (main.cpp:277); when it does not fit one
+ * HBM the keys are split over the G GPUs of a group by a hash range. Every GPU runs the encode /
+ * probe / accumulate phases (place.cpp:278-316,349-371) of EVERY query against its shard and leaves a
+ * partial row per query  { u32 flags, u32 postings, 0, 0 | f32 S[Np] | u16 C[Np] }  (Np = n_nodes
+ * rounded up to 128) in the memory of the GPU that owns the query; the owner adds the G rows in shard
+ * order and finishes the query (place.cpp:417-422, 164-199, 238-267). Transport between the two calls
+ * is the caller's: an NCCL all-to-all of the row buffers, or row buffers that ARE the owners' memory
+ * (CUDA IPC / peer pointers over NVLink), in which case the partial launch is the exchange.
+ * Scores agree with the reference within float rounding of a re-associated sum (1e-5 relative), not
+ * bit for bit. Queries with ambiguous windows (place.cpp:373-415 needs the global key order) and
+ * queries with more than 65535 windows are reported through epk_counters.n_unsupported, n_place = 0. */
+
+/* epk_db_create keeping only the keys of shard `shard_index` of `shard_count`; the load filter's
+ * informative prefix (mu / max_entries) is still taken over the whole description. */
+epk_status epk_db_create_shard(const epk_db_desc* desc, const epk_load_filter* filter, int device,
+                               uint32_t shard_index, uint32_t shard_count, epk_db** out);
+/* The shard a k-mer code belongs to. */
+uint32_t epk_shard_of_key(uint32_t key, uint32_t shard_count);
+
+/* Bytes of one partial row for this placer's tree: 16 + 6 * Np. */
+uint64_t epk_partial_row_bytes(const epk_placer* placer);
+
+/* Phases 1-3 of placer::place_seq for n queries against this placer's (shard) database. Query i with
+ * owner_first[g] <= i < owner_first[g+1] leaves its row at d_rows[g] + (i - owner_first[g]) * row_bytes.
+ * owner_first [n_owners + 1] and d_rows [n_owners] are HOST arrays; d_rows[g] are DEVICE pointers
+ * (16-byte aligned; local or peer memory). d_seq / d_seq_off are DEVICE memory. Asynchronous on `stream`. */
+epk_status epk_place_partial_device(epk_placer* placer, const char* d_seq, const uint64_t* d_seq_off, uint32_t n,
+                                    uint32_t n_owners, const uint32_t* owner_first, void* const* d_rows,
+                                    void* stream);
+
+/* The owner's side: row i of shard g is at d_rows + g * shard_stride_bytes + i * row_bytes. Adds the
+ * n_shards rows of each of the n queries and writes their placements to d_out (DEVICE memory, rows
+ * [0, n)). d_seq_off[0 .. n] are the offsets of these n queries (only their differences are used). */
+epk_status epk_place_finalize_device(epk_placer* placer, const void* d_rows, uint32_t n_shards,
+                                     uint64_t shard_stride_bytes, const uint64_t* d_seq_off, uint32_t n,
+                                     const epk_result* d_out, void* stream);
+
 /* Pinned host memory for the buffers of epk_place. */
 void* epk_host_alloc(size_t bytes);
 void epk_host_free(void* p);

@@ -1,0 +1,209 @@
+"""Database-sharded mode (epik_b200/dbshard.py, include/epik_b200.h "database-sharded mode").
+
+CPU part (gloo, world_size 2 and 3): the key -> shard rule exported by the library, the owner slices, and the
+all-to-all layout of the partial rows; the rows themselves come from a numpy restatement of the exact
+accumulation (place.cpp:349-371) over one shard, so that what is checked is: the shards partition the hits,
+every row reaches its owner in shard order, and the summed rows equal the unsharded accumulators.
+GPU part: the CUDA partial + finalize launches against the oracle (1e-5 relative: the per-branch sums are
+re-associated by shard), and the one-shard case bit for bit against the fused kernel."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from epik_b200 import capi, dbshard, synth
+
+from .helpers import assert_close_placements
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def test_shard_rule_partitions_the_keys(built):
+    l = capi.lib()
+    keys = np.arange(0, 1 << 20, 7, dtype=np.uint32)
+    for world in (1, 2, 3, 8):
+        owner = np.array([l.epk_shard_of_key(int(k), world) for k in keys[:20000]])
+        assert owner.min() >= 0 and owner.max() == world - 1
+        # the python statement of the rule used below agrees with the library
+        assert np.array_equal(owner, _shard_of(keys[:20000], world))
+        share = np.bincount(owner, minlength=world) / len(owner)
+        assert np.all(np.abs(share - 1.0 / world) < 0.02)
+
+
+def test_owner_bounds():
+    for n in (0, 1, 5, 1000):
+        for world in (1, 2, 3, 8):
+            b = dbshard.owner_bounds(n, world)
+            assert b[0] == 0 and b[-1] == n and np.all(np.diff(b.astype(np.int64)) >= 0) and len(b) == world + 1
+
+
+def _shard_of(keys, world):
+    h = (keys.astype(np.uint64) * np.uint64(0x9E3779B1)) & np.uint64(0xFFFFFFFF)
+    return (((h >> np.uint64(16)) * np.uint64(world)) >> np.uint64(16)).astype(np.int64)
+
+
+def _rows_numpy(flat, data, off, shard, world, n_pad):
+    """Partial rows {S f32[n_pad] | C u16[n_pad]} of every read over the keys of one shard (unambiguous reads)."""
+    k = flat.kmer_size
+    code = np.full(256, -1, np.int64)
+    for i, ch in enumerate(b"ACGT"):
+        code[ch] = i
+    lookup = {int(key): i for i, key in enumerate(flat.keys)}
+    n = len(off) - 1
+    S = np.zeros((n, n_pad), np.float32)
+    C = np.zeros((n, n_pad), np.uint16)
+    for r in range(n):
+        seq = code[data[int(off[r]):int(off[r + 1])]]
+        for w in range(len(seq) - k + 1):
+            key = 0
+            for c in seq[w:w + k]:
+                key = (key << 2) | int(c)
+            i = lookup.get(key)
+            if i is None or (world > 1 and _shard_of(np.array([key], np.uint32), world)[0] != shard):
+                continue
+            for e in flat.entries[int(flat.offsets[i]):int(flat.offsets[i + 1])]:
+                S[r, e["branch"]] = np.float32(S[r, e["branch"]] + e["score"])
+                C[r, e["branch"]] += 1
+    return S, C
+
+
+def _worker(rank, world, port, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    flat = synth.make_db(0, 5, 20, 0.7, 4.0, seed=3)
+    data, off = synth.make_reads(0, 23, 40, seed=4)
+    n = len(off) - 1
+    n_pad = 128
+    S, C = _rows_numpy(flat, data, off, rank, world, n_pad)
+    rows = np.concatenate([S.view(np.uint8).reshape(n, -1), C.view(np.uint8).reshape(n, -1)], axis=1)
+    slabs = dbshard.exchange_rows(torch.from_numpy(rows.copy()), n, rank, world).numpy()
+    np.save(os.path.join(out_dir, "slabs%d.npy" % rank), slabs)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_rows_reach_their_owner_in_shard_order(built, tmp_path, world):
+    mp.spawn(_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    flat = synth.make_db(0, 5, 20, 0.7, 4.0, seed=3)
+    data, off = synth.make_reads(0, 23, 40, seed=4)
+    n, n_pad = len(off) - 1, 128
+    S_full, C_full = _rows_numpy(flat, data, off, 0, 1, n_pad)
+    per_shard = [_rows_numpy(flat, data, off, g, world, n_pad) for g in range(world)]
+    assert np.array_equal(sum(c.astype(np.int64) for _, c in per_shard), C_full.astype(np.int64))  # the shards partition the hits
+    bounds = dbshard.owner_bounds(n, world)
+    for rank in range(world):
+        slabs = np.load(str(tmp_path / ("slabs%d.npy" % rank)))
+        first, last = int(bounds[rank]), int(bounds[rank + 1])
+        assert slabs.shape == (world, last - first, 6 * n_pad)
+        S = slabs[:, :, :4 * n_pad].copy().view(np.float32)
+        C = slabs[:, :, 4 * n_pad:].copy().view(np.uint16)
+        for g in range(world):
+            assert np.array_equal(S[g], per_shard[g][0][first:last]) and np.array_equal(C[g], per_shard[g][1][first:last])
+        total = np.zeros_like(S[0])
+        for g in range(world):
+            total = (total + S[g]).astype(np.float32)
+        np.testing.assert_allclose(total, S_full[first:last], rtol=1e-5, atol=1e-6)
+        assert np.array_equal(C.sum(axis=0), C_full[first:last])
+
+
+# ------------------------------------------------------------------------------------------ GPU -----
+
+def _oracle(flat):
+    from oracle import oracle as O
+    return O.Oracle(flat, kind="reference" if O.available("reference", flat.alphabet) else "port")
+
+
+@pytest.mark.gpu
+def test_one_shard_equals_the_fused_kernel_bit_for_bit(built):
+    from epik_b200.placer import Database, Placer
+    flat = synth.make_db(0, 8, 300, 0.6, 12.0, seed=21)
+    data, off = synth.make_reads(0, 3000, 150, seed=22)
+    want = Placer(Database(flat)).place_packed(data, off)
+    sp = dbshard.LocalShardedPlacer(flat, 1)
+    got = sp.place_packed(data, off, max_rows=1024)
+    assert sp.unsupported == 0 and sp.short == 0
+    for name in dbshard.RESULT_FIELDS:
+        assert np.array_equal(got[name], want[name]), name
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("alphabet,k,leaves,p_occ,m,length,shards", [(0, 8, 300, 0.6, 12.0, 150, 3), (0, 10, 2500, 0.6, 32.0, 150, 2),
+                                                                  (1, 6, 200, 0.05, 8.0, 100, 4), (0, 8, 100, 0.5, 6.0, 700, 2)])
+def test_sharded_database_matches_the_oracle(built, alphabet, k, leaves, p_occ, m, length, shards):
+    flat = synth.make_db(alphabet, k, leaves, p_occ, m, seed=31)
+    data, off = synth.make_reads(alphabet, 2000, length, seed=32)
+    sp = dbshard.LocalShardedPlacer(flat, shards)
+    got = sp.place_packed(data, off, max_rows=777)
+    assert sp.unsupported == 0 and sp.short == 0
+    want = _oracle(flat).place_packed(data, off)
+    assert_close_placements(got, want, what="dbshard x%d" % shards)
+    loaded = sum(db.info["n_entries_loaded"] for db in sp.dbs)
+    assert loaded == len(flat.entries)  # the shards partition the database
+
+
+@pytest.mark.gpu
+def test_sharded_load_filter_cuts_globally(built):
+    from epik_b200.placer import Database
+    flat = synth.make_db(0, 8, 300, 0.6, 12.0, seed=41)
+    whole = Database(flat, mu=0.5, omega=1.5)
+    parts = [Database(flat, mu=0.5, omega=1.5, shard=(g, 3)) for g in range(3)]
+    assert sum(p.info["n_entries_loaded"] for p in parts) == whole.info["n_entries_loaded"]
+    assert sum(p.info["n_keys_loaded"] for p in parts) == whole.info["n_keys_loaded"]
+
+
+@pytest.mark.gpu
+def test_ambiguous_and_short_reads_are_reported(built):
+    flat = synth.make_db(0, 8, 300, 0.6, 12.0, seed=21)
+    seqs = [b"ACGTACGTACGTAACCGGTTACGT" * 4, b"ACGTACGTACGNAACCGGTTACGT" * 4, b"ACG", b"ACGTACGTACGTAACCGGTTACGT" * 4]
+    from epik_b200.placer import pack_sequences
+    data, off = pack_sequences(seqs)
+    sp = dbshard.LocalShardedPlacer(flat, 2)
+    got = sp.place_packed(data, off)
+    assert sp.unsupported == 1 and sp.short == 1
+    assert got["n_place"][1] == 0 and got["n_place"][2] == 0 and got["n_place"][0] > 0
+    assert np.array_equal(got["branch"][0], got["branch"][3]) and np.array_equal(got["score"][0], got["score"][3])
+
+
+def _nccl_worker(rank, world, port, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    flat = synth.make_db(0, 8, 300, 0.6, 12.0, seed=31)
+    data, off = synth.make_reads(0, 2001, 150, seed=32)
+    sp = dbshard.ShardedPlacer(flat, rank, world, device=rank)
+    for _ in range(2):  # twice: buffers are reused
+        got, first, last = sp.place_packed(data, off)
+    assert sp.unsupported == 0
+    np.savez(os.path.join(out_dir, "part%d.npz" % rank), first=first, last=last, **got)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+def test_two_gpus_nccl_exchange(built, tmp_path):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    world = 2
+    mp.spawn(_nccl_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    flat = synth.make_db(0, 8, 300, 0.6, 12.0, seed=31)
+    data, off = synth.make_reads(0, 2001, 150, seed=32)
+    want = _oracle(flat).place_packed(data, off)
+    local = dbshard.LocalShardedPlacer(flat, world).place_packed(data, off)
+    for rank in range(world):
+        part = np.load(str(tmp_path / ("part%d.npz" % rank)))
+        first, last = int(part["first"]), int(part["last"])
+        piece = {k: want[k][first:last] for k in dbshard.RESULT_FIELDS}
+        assert_close_placements({k: part[k] for k in dbshard.RESULT_FIELDS}, piece, what="rank %d" % rank)
+        for k in dbshard.RESULT_FIELDS:  # the transport does not change a bit: same sums in the same shard order
+            assert np.array_equal(part[k], local[k][first:last]), k
