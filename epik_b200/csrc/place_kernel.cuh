@@ -48,6 +48,7 @@ constexpr uint32_t NO_BRANCH = 0xFFFFFFFFu;
 constexpr uint32_t FULL = 0xFFFFFFFFu;
 
 static_assert(CAND_CAP * 12 <= SEG_CAP * 8, "candidate arrays alias the segment buffer");
+static_assert(MAX_WARPS_PER_CTA * 32 <= 256, "one mailbox per accumulator set");
 
 // One kernel instantiation per width of the hit counts: class c handles the queries with
 // CLASS_MIN_WINDOWS[c] <= windows <= CLASS_MAX_WINDOWS[c].
@@ -99,7 +100,8 @@ __host__ __device__ inline size_t warp_smem_bytes(uint32_t n_nodes, uint32_t cou
     const size_t np = padded_nodes(n_nodes);
     return np * 4 + np * count_bytes + np / 8 + (SEG_CAP + SEG_PAD) * 8 + CODE_BYTES;
 }
-constexpr size_t CTA_SMEM_FIXED = 1024; // letter table
+constexpr size_t CTA_SMEM_FIXED = 1024 + 256; // letter table | one 32-byte mailbox per accumulator set (paired warps)
+constexpr int PAIR_CAND_CAP = 64;      // candidates buffered per warp when two warps sweep one query
 
 // Number of queries of each class (sequences shorter than k - 1 letters count for class 0, which
 // reports them). Classes in unsupported_mask have no launch: their rows get n_place = 0 here.
@@ -461,6 +463,19 @@ __device__ __noinline__ uint32_t select_best(uint32_t* cand_key, uint32_t* cand_
     return select_best_n<CAND_CAP / 32>(cand_key, cand_branch, cand_count, m, want, lane, my_key, my_branch, my_count);
 }
 
+// Where a warp keeps its candidates and the quad queue of the scan-and-queue sweep: CAP words each of
+// key / branch / count, then 64 words of queue.
+template<int CAP>
+struct cand_buffers
+{
+    uint32_t* key;
+    uint32_t* branch;
+    uint32_t* count;
+    uint32_t* pending;
+    __device__ explicit cand_buffers(uint32_t* base) : key(base), branch(base + CAP), count(base + 2 * CAP), pending(base + 3 * CAP) {}
+    static constexpr uint32_t WORDS = 3 * CAP + 64;
+};
+
 // ---- the sweep over the accumulators ---------------------------------------------------------------
 
 // four consecutive hit counts, and their clearing, by width
@@ -514,11 +529,15 @@ struct sweep_result
 // Per branch b with C[b] != 0 (place.cpp:417-422):  S[b] += float(nw - C[b]) * log10thr;  S[b] /= k.
 // FAST: the short forms of the division and of 10^s (valid for the score range established by
 // fast_sweep_ok) and the mass cut-off; otherwise the IEEE division and the library exp10, every term.
-template<class CT, bool FAST, bool DENSE>
+// The warp looks at the steps scan0, scan0 + stride, ... (two warps of a pair take alternate steps).
+template<class CT, bool FAST, bool DENSE, int CAP>
 __device__ __forceinline__ sweep_result sweep(float* S, CT* C, uint32_t np, uint32_t nw32, float logthr, float kf,
-                                              float rcp_k, uint32_t K, uint32_t lane, uint32_t* cand_key,
-                                              uint32_t* cand_branch, uint32_t* cand_count)
+                                              float rcp_k, uint32_t K, uint32_t lane, const cand_buffers<CAP>& cb,
+                                              uint32_t scan0, uint32_t stride)
 {
+    uint32_t* const cand_key = cb.key;
+    uint32_t* const cand_branch = cb.branch;
+    uint32_t* const cand_count = cb.count;
     sweep_result out{ 0.0, 0u, 0u, 0u, NO_BRANCH, 0u };
     double mass = 0.0;
     uint32_t touched = 0, n_cand = 0;
@@ -535,8 +554,8 @@ __device__ __forceinline__ sweep_result sweep(float* S, CT* C, uint32_t np, uint
     // with many touched quads is still processed in place, the touched quads of sparse steps are queued
     // and processed 32 at a time, so that a query that touched few branches pays for those only (a
     // 100-residue protein read touches a few dozen of the 2000 branches of its tree).
-    uint32_t* pending = cand_key + 3 * CAND_CAP; // [64] first branch of queued quads
-    uint32_t n_pending = 0, scan = 0;
+    uint32_t* pending = cb.pending; // [64] first branch of queued quads
+    uint32_t n_pending = 0, scan = scan0;
     while (true)
     {
         // ---- next 32 quads to process: j = first branch of this lane's quad ----
@@ -547,7 +566,7 @@ __device__ __forceinline__ sweep_result sweep(float* S, CT* C, uint32_t np, uint
             // a query with many postings touched most quads: every step as it stands, no scan
             if (scan >= np) { break; }
             j = scan + 4u * lane;
-            scan += SWEEP_STEP;
+            scan += stride;
             have = true;
         }
         while (!DENSE && !have && scan < np)
@@ -556,7 +575,7 @@ __device__ __forceinline__ sweep_result sweep(float* S, CT* C, uint32_t np, uint
             const bool hit = any_count4(C, mine);
             const uint32_t ballot = __ballot_sync(FULL, hit);
             const uint32_t n_hit = __popc(ballot);
-            scan += SWEEP_STEP;
+            scan += stride;
             if (n_hit >= DENSE_QUADS)
             {
                 j = mine;
@@ -670,7 +689,7 @@ __device__ __forceinline__ sweep_result sweep(float* S, CT* C, uint32_t np, uint
                 }
                 n_cand += __popc(ballot);
                 __syncwarp();
-                if (n_cand > CAND_CAP - 32)
+                if (n_cand > CAP - 32)
                 {
                     // keep the best K, raise the bar to the K-th of them
                     n_cand = select_best(cand_key, cand_branch, cand_count, n_cand, K, lane, out.key, out.branch, out.count);
@@ -698,19 +717,19 @@ __device__ __forceinline__ sweep_result sweep(float* S, CT* C, uint32_t np, uint
 
 // The forms off the beaten track, out of line (they are long, and cold for 150-bp reads on a 5000-branch
 // tree): IEEE arithmetic; scan-and-queue for queries that touched few branches.
-template<class CT>
+template<class CT, int CAP>
 __device__ __noinline__ sweep_result sweep_ieee(float* S, CT* C, uint32_t np, uint32_t nw32, float logthr, float kf,
-                                                float rcp_k, uint32_t K, uint32_t lane, uint32_t* cand_key,
-                                                uint32_t* cand_branch, uint32_t* cand_count)
+                                                float rcp_k, uint32_t K, uint32_t lane, const cand_buffers<CAP>& cb,
+                                                uint32_t scan0, uint32_t stride)
 {
-    return sweep<CT, false, false>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cand_key, cand_branch, cand_count);
+    return sweep<CT, false, false, CAP>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride);
 }
-template<class CT>
+template<class CT, int CAP>
 __device__ __noinline__ sweep_result sweep_sparse(float* S, CT* C, uint32_t np, uint32_t nw32, float logthr, float kf,
-                                                  float rcp_k, uint32_t K, uint32_t lane, uint32_t* cand_key,
-                                                  uint32_t* cand_branch, uint32_t* cand_count)
+                                                  float rcp_k, uint32_t K, uint32_t lane, const cand_buffers<CAP>& cb,
+                                                  uint32_t scan0, uint32_t stride)
 {
-    return sweep<CT, true, false>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cand_key, cand_branch, cand_count);
+    return sweep<CT, true, false, CAP>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride);
 }
 
 // Whether every score a query with nwf windows can end up with stays inside what the short forms
@@ -729,30 +748,36 @@ __device__ __forceinline__ bool fast_sweep_ok(const device_db& db, float nwf, fl
 // The accumulators S, C of one query with n_windows windows are complete (place.cpp:349-415 done):
 // correction + likelihood mass + top-k (the sweep), weight ratios, keep_factor, the rows of query q.
 // `gathered` = postings the query gathered (warp-uniform; only steers dense / scan-and-queue).
-template<class CT>
-__device__ __forceinline__ void finish_query(const place_params& p, float* S, CT* C, uint32_t np, uint64_t n_windows,
-                                             uint32_t gathered, uint32_t q, uint32_t lane, uint32_t* cand_key,
-                                             uint32_t* cand_branch, uint32_t* cand_count)
+
+// the sweep form that fits the query; this warp takes the steps scan0, scan0 + stride, ...
+template<class CT, int CAP>
+__device__ __forceinline__ sweep_result run_sweep(const device_db& db, float* S, CT* C, uint32_t np, uint32_t nw32,
+                                                  uint32_t gathered, uint32_t K, uint32_t lane, const cand_buffers<CAP>& cb,
+                                                  uint32_t scan0, uint32_t stride)
+{
+    const float kf = static_cast<float>(db.k);
+    const float rcp_k = __frcp_rn(kf);
+    const float logthr = db.log_threshold;
+    const float nwf = static_cast<float>(nw32);
+    const bool dense = 6ull * gathered >= np;
+    return !fast_sweep_ok(db, nwf, kf) ? sweep_ieee<CT, CAP>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride)
+           : dense                     ? sweep<CT, true, true, CAP>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride)
+                                       : sweep_sparse<CT, CAP>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride);
+}
+
+// likelihood weight ratios and keep_factor (place.cpp:164-184, 241-267), rows of query q
+__device__ __forceinline__ void emit_query(const place_params& p, const sweep_result& sw, uint32_t nw32, uint32_t q, uint32_t lane)
 {
     const device_db& db = p.db;
     const uint32_t N = db.n_nodes;
     const uint32_t K = p.keep_at_most;
     const float kf = static_cast<float>(db.k);
-    const float rcp_k = __frcp_rn(kf);
     const float logthr = db.log_threshold;
-    // ---- correction, likelihood mass, top-k (place.cpp:417-422, 164-184, 134-159) ----
-    const uint32_t nw32 = static_cast<uint32_t>(n_windows);
-    const float nwf = static_cast<float>(n_windows);
-    const bool dense = 6ull * gathered >= np;
-    const sweep_result sw =
-        !fast_sweep_ok(db, nwf, kf) ? sweep_ieee<CT>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cand_key, cand_branch, cand_count)
-        : dense                     ? sweep<CT, true, true>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cand_key, cand_branch, cand_count)
-                                    : sweep_sparse<CT>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cand_key, cand_branch, cand_count);
+    const float nwf = static_cast<float>(nw32);
     const uint32_t touched = sw.touched;
     uint32_t my_b = sw.branch, my_c = sw.count;
     float my_s = key_score(sw.key);
 
-    // ---- likelihood weight ratios and keep_factor (place.cpp:164-184, 241-267) ----
     const float absent_score = __fdiv_rn(__fmul_rn(nwf, logthr), kf);
     const double absent_mass = static_cast<double>(static_cast<float>(N) - static_cast<float>(touched))
                                * exp10_of_float(absent_score);
@@ -800,6 +825,93 @@ __device__ __forceinline__ void finish_query(const place_params& p, float* S, CT
     }
     if (lane == 0) { p.n_place[q] = n_kept; }
     __syncwarp();
+}
+
+// one warp does it all; cand_base: CAND_CAP * 3 + 64 words (the idle segment buffer)
+template<class CT>
+__device__ __forceinline__ void finish_query(const place_params& p, float* S, CT* C, uint32_t np, uint64_t n_windows,
+                                             uint32_t gathered, uint32_t q, uint32_t lane, uint32_t* cand_base)
+{
+    const cand_buffers<CAND_CAP> cb(cand_base);
+    const uint32_t nw32 = static_cast<uint32_t>(n_windows);
+    const sweep_result sw = run_sweep<CT, CAND_CAP>(p.db, S, C, np, nw32, gathered, p.keep_at_most, lane, cb, 0u, SWEEP_STEP);
+    emit_query(p, sw, nw32, q, lane);
+}
+
+// ---- two warps per query --------------------------------------------------------------------------
+//
+// At N = 5000 eight accumulator sets fill the shared memory of an SM, and eight warps leave the issue
+// slots 60 % idle (ncu, profiles/r1e): the sweep is two thirds of a query's instructions and splits
+// cleanly, so every accumulator set gets a second warp. The leader (even warp) encodes, probes and
+// gathers as before - the order of the additions per branch is untouched - then both warps sweep
+// alternate 128-branch steps; the helper leaves its mass, its count of touched branches and its best
+// keep_at_most candidates in shared memory and the leader merges them (mass = leader's + helper's, a
+// fixed order). The pair meets on a named barrier (id 1 + set): A = accumulators complete, B = helper done.
+struct pair_mailbox
+{
+    uint32_t q, nw32, gathered, pad; // leader -> helper (q == NO_BRANCH: no more queries)
+    uint32_t mass_lo, mass_hi, touched, n_keep; // helper -> leader
+};
+static_assert(sizeof(pair_mailbox) == 32, "mailbox");
+
+__device__ __forceinline__ void pair_sync(uint32_t set)
+{
+    asm volatile("bar.sync %0, 64;" ::"r"(set + 1u) : "memory");
+}
+
+// helper's candidate buffers sit after the leader's in the idle segment + code area
+constexpr uint32_t PAIR_CAND_WORDS = cand_buffers<PAIR_CAND_CAP>::WORDS;
+static_assert(2 * PAIR_CAND_WORDS * 4 <= (SEG_CAP + SEG_PAD) * 8 + CODE_BYTES, "two candidate sets alias the segment buffer and the codes");
+
+template<class CT>
+__device__ __forceinline__ void finish_query_leader(const place_params& p, float* S, CT* C, uint32_t np, uint32_t nw32,
+                                                    uint32_t gathered, uint32_t q, uint32_t lane, uint32_t* cand_base,
+                                                    pair_mailbox* box, uint32_t set)
+{
+    const uint32_t K = p.keep_at_most;
+    const cand_buffers<PAIR_CAND_CAP> cb(cand_base), hb(cand_base + PAIR_CAND_WORDS);
+    sweep_result sw = run_sweep<CT, PAIR_CAND_CAP>(p.db, S, C, np, nw32, gathered, K, lane, cb, 0u, 2u * SWEEP_STEP);
+    __syncwarp();
+    pair_sync(set); // B: the helper's half is in its buffers and the mailbox
+    const uint32_t n_h = box->n_keep;
+    sw.mass += __hiloint2double(static_cast<int>(box->mass_hi), static_cast<int>(box->mass_lo));
+    sw.touched += box->touched;
+    if (n_h)
+    {
+        if (lane < n_h)
+        {
+            cb.key[sw.n_keep + lane] = hb.key[lane];
+            cb.branch[sw.n_keep + lane] = hb.branch[lane];
+            cb.count[sw.n_keep + lane] = hb.count[lane];
+        }
+        __syncwarp();
+        sw.n_keep = select_best(cb.key, cb.branch, cb.count, sw.n_keep + n_h, K, lane, sw.key, sw.branch, sw.count);
+    }
+    emit_query(p, sw, nw32, q, lane);
+}
+
+template<class CT>
+__device__ __forceinline__ void helper_loop(const place_params& p, float* S, CT* C, uint32_t np, uint32_t lane,
+                                            uint32_t* cand_base, pair_mailbox* box, uint32_t set)
+{
+    const cand_buffers<PAIR_CAND_CAP> hb(cand_base + PAIR_CAND_WORDS);
+    while (true)
+    {
+        pair_sync(set); // A
+        const uint32_t q = box->q, nw32 = box->nw32, gathered = box->gathered;
+        if (q == NO_BRANCH) { break; }
+        const sweep_result sw = run_sweep<CT, PAIR_CAND_CAP>(p.db, S, C, np, nw32, gathered, p.keep_at_most, lane, hb,
+                                                             SWEEP_STEP, 2u * SWEEP_STEP);
+        if (lane == 0)
+        {
+            box->mass_lo = static_cast<uint32_t>(__double2loint(sw.mass));
+            box->mass_hi = static_cast<uint32_t>(__double2hiint(sw.mass));
+            box->touched = sw.touched;
+            box->n_keep = sw.n_keep;
+        }
+        __syncwarp();
+        pair_sync(set); // B
+    }
 }
 
 // ---- partial rows (database-sharded mode) ---------------------------------------------------------
@@ -853,13 +965,16 @@ __device__ __forceinline__ void dump_partial_row(const place_params& p, float* S
 
 // PARTIAL: database-sharded mode, the accumulators of a query leave as a partial row instead of being
 // swept (queries with ambiguous windows are flagged, their ambiguous windows left out).
-template<uint32_t TABLE, int U, class CT, bool PARTIAL = false>
-__global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const place_params p)
+// PAIRED: two warps per accumulator set (see "two warps per query"); blockDim = 64 * sets.
+template<uint32_t TABLE, int U, class CT, bool PARTIAL = false, bool PAIRED = false>
+__global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32 * (PAIRED ? 2 : 1), 1) place_kernel(const place_params p)
 {
+    static_assert(!(PARTIAL && PAIRED), "partial rows are written by one warp per query");
     extern __shared__ __align__(16) unsigned char smem[];
     if (p.class_reads && p.class_reads[p.cls] == 0) { return; } // no query of this class in the batch
     const uint32_t lane = threadIdx.x & 31u;
-    const uint32_t warp = threadIdx.x >> 5;
+    const uint32_t warp = PAIRED ? threadIdx.x >> 6 : threadIdx.x >> 5; // accumulator set
+    const bool helper = PAIRED && ((threadIdx.x >> 5) & 1u);
     const device_db& db = p.db;
     const uint32_t N = db.n_nodes;
     const uint32_t np = padded_nodes(N);
@@ -879,18 +994,25 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
     uint2* segs = reinterpret_cast<uint2*>(reinterpret_cast<unsigned char*>(seen) + np / 8);
     const uint32_t segs_shared = static_cast<uint32_t>(__cvta_generic_to_shared(segs));
     const acc_ref acc{ static_cast<uint32_t>(__cvta_generic_to_shared(S)), static_cast<uint32_t>(__cvta_generic_to_shared(C)) };
-    uint32_t* cand_key = reinterpret_cast<uint32_t*>(segs); // the segment buffer is idle during the sweep
-    uint32_t* cand_branch = cand_key + CAND_CAP;
-    uint32_t* cand_count = cand_branch + CAND_CAP;
+    uint32_t* cand_base = reinterpret_cast<uint32_t*>(segs); // the segment buffer is idle during the sweep
     uint8_t* codes = reinterpret_cast<uint8_t*>(segs + SEG_CAP + SEG_PAD);
+    pair_mailbox* box = reinterpret_cast<pair_mailbox*>(smem + 1024) + warp;
 
-    for (uint32_t b = lane; b < np; b += 32)
+    if (!helper)
     {
-        S[b] = 0.0f;
-        C[b] = 0;
+        for (uint32_t b = lane; b < np; b += 32)
+        {
+            S[b] = 0.0f;
+            C[b] = 0;
+        }
+        for (uint32_t i = lane; i < seen_words; i += 32) { seen[i] = 0; }
     }
-    for (uint32_t i = lane; i < seen_words; i += 32) { seen[i] = 0; }
     __syncthreads();
+    if (helper)
+    {
+        helper_loop<CT>(p, S, C, np, lane, cand_base, box, warp);
+        return;
+    }
 
     const float kf = static_cast<float>(k);
     const uint32_t key_mask = db.key_mask;
@@ -901,7 +1023,16 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
         uint32_t q = 0;
         if (lane == 0) { q = static_cast<uint32_t>(atomicAdd(p.counters + CTR_CURSOR, 1ull)); }
         q = __shfl_sync(FULL, q, 0);
-        if (q >= p.n) { break; }
+        if (q >= p.n)
+        {
+            if (PAIRED)
+            {
+                if (lane == 0) { box->q = NO_BRANCH; }
+                __syncwarp();
+                pair_sync(warp); // A: tells the helper to leave
+            }
+            break;
+        }
 
         const uint64_t s0 = p.seq_off[q];
         const uint64_t len = p.seq_off[q + 1] - s0;
@@ -1146,7 +1277,19 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
 
         // ---- correction, likelihood mass, top-k, weight ratios (place.cpp:417-422, 164-184, 134-159, 241-267) ----
         const uint32_t gathered = __reduce_add_sync(FULL, static_cast<uint32_t>(min(static_cast<unsigned long long>(ctr_entries - entries_before), 0xFFFFFFull)));
-        finish_query<CT>(p, S, C, np, n_windows, gathered, q, lane, cand_key, cand_branch, cand_count);
+        if (PAIRED)
+        {
+            if (lane == 0)
+            {
+                box->q = q;
+                box->nw32 = static_cast<uint32_t>(n_windows);
+                box->gathered = gathered;
+            }
+            __syncwarp();
+            pair_sync(warp); // A: the accumulators are complete
+            finish_query_leader<CT>(p, S, C, np, static_cast<uint32_t>(n_windows), gathered, q, lane, cand_base, box, warp);
+        }
+        else { finish_query<CT>(p, S, C, np, n_windows, gathered, q, lane, cand_base); }
     }
 
 #pragma unroll
@@ -1179,9 +1322,7 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) finalize_kernel(con
     unsigned char* base = smem + CTA_SMEM_FIXED + warp * warp_smem_bytes(N, sizeof(CT));
     float* S = reinterpret_cast<float*>(base);
     CT* C = reinterpret_cast<CT*>(base + static_cast<size_t>(np) * 4);
-    uint32_t* cand_key = reinterpret_cast<uint32_t*>(base + static_cast<size_t>(np) * (4 + sizeof(CT)) + np / 8);
-    uint32_t* cand_branch = cand_key + CAND_CAP;
-    uint32_t* cand_count = cand_branch + CAND_CAP;
+    uint32_t* cand_base = reinterpret_cast<uint32_t*>(base + static_cast<size_t>(np) * (4 + sizeof(CT)) + np / 8);
     const uint64_t row_bytes = partial_row_bytes(N);
 
     while (true)
@@ -1235,7 +1376,7 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) finalize_kernel(con
             *reinterpret_cast<uint2*>(C + j) = c2;
         }
         __syncwarp();
-        finish_query<CT>(p, S, C, np, n_windows, gathered, q, lane, cand_key, cand_branch, cand_count);
+        finish_query<CT>(p, S, C, np, n_windows, gathered, q, lane, cand_base);
     }
 }
 } // namespace epk
