@@ -58,7 +58,12 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="C2", choices=["C2", "C3", "C4", "C1p"])
+    ap.add_argument("--workload", default="C2", choices=["C2", "C3", "C4", "C1p", "C5r"])
+    ap.add_argument("--mode", default="replicated", choices=["replicated", "dbshard"],
+                    help="replicated: queries sharded over the ranks, database in every HBM (default); "
+                         "dbshard: database sharded by key over the ranks, every rank sees every query, partial rows "
+                         "exchanged with an all-to-all (SURVEY.md 8e second row)")
+    ap.add_argument("--dbshard-rows", type=int, default=32768, help="queries per exchange step in dbshard mode")
     ap.add_argument("--reads", type=int, default=0, help="reads per GPU per step (default: the workload's)")
     ap.add_argument("--variant", type=int, default=0)
     ap.add_argument("--no-e2e", action="store_true")
@@ -66,7 +71,7 @@ def parse_args():
     return ap.parse_args()
 
 
-WORKLOAD_READS = {"C2": 10_000_000, "C3": 10_000_000, "C4": 1_000_000, "C1p": 100_000}
+WORKLOAD_READS = {"C2": 10_000_000, "C3": 10_000_000, "C4": 1_000_000, "C1p": 100_000, "C5r": 1_000_000}
 
 
 def workload_config(name, n_reads, world):
@@ -322,6 +327,29 @@ def run_ours(args):
                 "launch_ms": kernel_s * 1e3, "peak_source": peak_src,
                 "entries_per_read": counters["n_entries"] / n, "hits_per_read": counters["n_hits"] / n}
 
+    # ---- the random-gather ceiling: the same launch with loads only (epk_gather_ceiling_device) ----
+    d_sum = torch.zeros(n, dtype=torch.int32, device=dev)
+    for _ in range(2):
+        placer.gather_ceiling_device(d_seq, d_off, n, d_sum, stream=stream)
+    stream.synchronize()
+    g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = max(2, min(args.steps, 5))
+    with torch.cuda.stream(stream):
+        g0.record(stream)
+        for _ in range(reps):
+            placer.gather_ceiling_device(d_seq, d_off, n, d_sum, stream=stream)
+        g1.record(stream)
+    stream.synchronize()
+    gather_s = g0.elapsed_time(g1) / reps / 1e3
+    gather_gbs = bytes_per_launch / gather_s / 1e9
+    roofline["gather_ceiling"] = {
+        "achieved": gather_gbs, "unit": "GB/s", "launch_ms": gather_s * 1e3, "frac_of_peak": gather_gbs / peak,
+        "what": "same kernel, same reads: encode + probe + posting gathers, accumulator updates replaced by a register "
+                "XOR, no sweep (epk_gather_ceiling_device); same algorithmic bytes"}
+    roofline["frac_of_gather_ceiling"] = achieved / gather_gbs
+    roofline["frac_of_8TBs_nominal"] = achieved / 8000.0
+    del d_sum
+
     log("device-resident: %.1f ms/step; timing the host path" % (total_s / args.steps * 1e3))
     # ---- e2e: pinned host buffers through epk_place, copies inside the timed region ----
     e2e = None
@@ -367,6 +395,95 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+def run_dbshard(args):
+    """Database-sharded variant: rank r holds shard r of the keys, EVERY rank sees the whole read set of a step;
+    value = reads of the step / time (strong scaling of the database, not of the queries)."""
+    import torch
+    import torch.distributed as dist
+    from epik_b200 import dbshard, synth
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    alphabet, k, n_leaves, p_occ, m, read_len = synth.CONFIGS[args.workload]
+    n = args.reads or WORKLOAD_READS[args.workload]
+    K = 7
+    log("dbshard: world %d, generating database %s" % (world, args.workload))
+    flat = synth.make_config_db(args.workload)
+    if world > 1:
+        sp = dbshard.ShardedPlacer(flat, rank, world, device=local, keep_at_most=K)
+        info = sp.db.info
+    else:
+        sp = dbshard.LocalShardedPlacer(flat, 1, device=local, keep_at_most=K)
+        info = sp.dbs[0].info
+    h_seq = np.zeros(n * read_len, np.uint8)
+    make_reads_chunked(alphabet, n, read_len, 0, h_seq)  # the SAME reads on every rank
+    d_seq = torch.from_numpy(h_seq).to(dev)
+    d_off = torch.from_numpy((np.arange(n + 1, dtype=np.uint64) * np.uint64(read_len)).view(np.int64)).to(dev)
+    rows = args.dbshard_rows
+    row_bytes = (sp.placer if world > 1 else sp.placers[0]).partial_row_bytes()
+
+    def step():
+        got = 0
+        for first in range(0, n, rows):
+            mrows = min(rows, n - first)
+            off = d_off[first:first + mrows + 1]
+            if world > 1:
+                out, f, l = sp.place_device(d_seq, off, mrows)
+            else:
+                pl = sp.placers[0]
+                if getattr(sp, "_slab", None) is None:
+                    sp._slab = torch.empty((rows, row_bytes), dtype=torch.uint8, device=dev)
+                    sp._out = dbshard._alloc_out(torch, rows, K, dev)
+                pl.place_partial_device(d_seq, off, mrows, [0, mrows], [sp._slab.data_ptr()])
+                pl.place_finalize_device(sp._slab.data_ptr(), 1, rows * row_bytes, off.data_ptr(), mrows, sp._out)
+                out = sp._out
+            got += 1
+        return out
+
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        out = step()
+    e1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    clocks = sampler.stop()
+    secs = e0.elapsed_time(e1) / 1e3
+    if world > 1:
+        t = torch.tensor([secs], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        secs = float(t.item())
+    assert int(out["n_place"].sum().item()) > 0
+    value = n * args.steps / secs
+    if rank == 0:
+        cfg = workload_config(args.workload, n, world)
+        cfg["parallelism"] = "database sharded by key hash x%d, every rank sees every query; partial rows (%d B per query) " \
+                             "exchanged by all_to_all_single (NCCL), %d queries per exchange" % (world, row_bytes, rows)
+        cfg["reads_per_gpu"] = n
+        emit({"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+              "ms_per_step": secs / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+              "dtype": "f32", "data": "synthetic", "mode": "dbshard", "config": cfg, "clocks": clocks,
+              "exchange_bytes_per_query": row_bytes * (world - 1) / max(world, 1),
+              "db_shard": {k2: int(v2) if isinstance(v2, (int, np.integer)) else float(v2) for k2, v2 in info.items()}})
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     # stdout carries ONE JSON line: anything libraries print there (NCCL announces its version on stdout) is
     # sent to stderr instead, and the line is written to the real stdout at the end
@@ -377,6 +494,8 @@ def main():
     args = parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif args.mode == "dbshard":
+        run_dbshard(args)
     else:
         run_ours(args)
 

@@ -21,7 +21,7 @@ SYMBOLS = [
     "epk_placer_create", "epk_placer_destroy", "epk_place", "epk_place_device", "epk_group_batch", "epk_kmers",
     "epk_placer_counters", "epk_host_alloc", "epk_host_free",
     "epk_db_create_shard", "epk_shard_of_key", "epk_partial_row_bytes", "epk_place_partial_device",
-    "epk_place_finalize_device",
+    "epk_place_finalize_device", "epk_gather_ceiling_device",
 ]
 
 
@@ -119,6 +119,8 @@ def lib():
     l.epk_place_finalize_device.restype = C.c_int
     l.epk_place_finalize_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint64, C.c_void_p, C.c_uint32,
                                             C.POINTER(Result), C.c_void_p]
+    l.epk_gather_ceiling_device.restype = C.c_int
+    l.epk_gather_ceiling_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]
     l.epk_host_alloc.restype = C.c_void_p
     l.epk_host_alloc.argtypes = [C.c_size_t]
     l.epk_host_free.argtypes = [C.c_void_p]

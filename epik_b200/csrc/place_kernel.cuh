@@ -48,7 +48,6 @@ constexpr uint32_t NO_BRANCH = 0xFFFFFFFFu;
 constexpr uint32_t FULL = 0xFFFFFFFFu;
 
 static_assert(CAND_CAP * 12 <= SEG_CAP * 8, "candidate arrays alias the segment buffer");
-static_assert(MAX_WARPS_PER_CTA * 32 <= 256, "one mailbox per accumulator set");
 
 // One kernel instantiation per width of the hit counts: class c handles the queries with
 // CLASS_MIN_WINDOWS[c] <= windows <= CLASS_MAX_WINDOWS[c].
@@ -100,8 +99,7 @@ __host__ __device__ inline size_t warp_smem_bytes(uint32_t n_nodes, uint32_t cou
     const size_t np = padded_nodes(n_nodes);
     return np * 4 + np * count_bytes + np / 8 + (SEG_CAP + SEG_PAD) * 8 + CODE_BYTES;
 }
-constexpr size_t CTA_SMEM_FIXED = 1024 + 256; // letter table | one 32-byte mailbox per accumulator set (paired warps)
-constexpr int PAIR_CAND_CAP = 64;      // candidates buffered per warp when two warps sweep one query
+constexpr size_t CTA_SMEM_FIXED = 1024; // letter table
 
 // Number of queries of each class (sequences shorter than k - 1 letters count for class 0, which
 // reports them). Classes in unsupported_mask have no launch: their rows get n_place = 0 here.
@@ -329,10 +327,17 @@ EPK_APPLY_SEGMENT(uint32_t, "u32", "u32")
 #ifndef EPK_GATHER_INLINE
 #define EPK_GATHER_INLINE __noinline__
 #endif
-template<int U, class CT>
-__device__ EPK_GATHER_INLINE void gather_segments(const uint2* __restrict__ postings, acc_ref acc, uint32_t segs_shared,
-                                             uint32_t n, uint32_t lane)
+// load-only stand-in for apply_segment (MODE_GATHER_ONLY): the postings are consumed, nothing is stored
+__device__ __forceinline__ void sink_segment(uint32_t& sink, uint32_t lane2, const seg_regs& r)
 {
+    if (lane2 < r.cnt) { sink ^= r.b0 ^ r.s0 ^ r.b1 ^ r.s1; }
+}
+
+template<int U, class CT, bool SINK = false>
+__device__ EPK_GATHER_INLINE void gather_segments(const uint2* __restrict__ postings, acc_ref acc, uint32_t segs_shared,
+                                             uint32_t n, uint32_t lane, uint32_t* sink_out = nullptr)
+{
+    uint32_t sink = 0;
     const unsigned char* lane_base = reinterpret_cast<const unsigned char*>(postings) + 16u * lane;
     const uint32_t lane2 = 2u * lane;
     seg_regs a[U], b[U];
@@ -353,7 +358,11 @@ __device__ EPK_GATHER_INLINE void gather_segments(const uint2* __restrict__ post
             for (int u = 0; u < U; ++u) { load_segment(lane_base, segs_shared, first + U + u, lane2, b[u]); }
         }
 #pragma unroll
-        for (int u = 0; u < U; ++u) { apply_segment(acc, lane2, a[u], CT{}); }
+        for (int u = 0; u < U; ++u)
+        {
+            if (SINK) { sink_segment(sink, lane2, a[u]); }
+            else { apply_segment(acc, lane2, a[u], CT{}); }
+        }
         if (!more_b) { break; }
         if (first + 2 * U < n)
         {
@@ -361,8 +370,13 @@ __device__ EPK_GATHER_INLINE void gather_segments(const uint2* __restrict__ post
             for (int u = 0; u < U; ++u) { load_segment(lane_base, segs_shared, first + 2 * U + u, lane2, a[u]); }
         }
 #pragma unroll
-        for (int u = 0; u < U; ++u) { apply_segment(acc, lane2, b[u], CT{}); }
+        for (int u = 0; u < U; ++u)
+        {
+            if (SINK) { sink_segment(sink, lane2, b[u]); }
+            else { apply_segment(acc, lane2, b[u], CT{}); }
+        }
     }
+    if (SINK) { *sink_out ^= sink; }
 }
 
 // One long list on its own (only when a single chunk's lists overflow the segment buffer).
@@ -529,11 +543,9 @@ struct sweep_result
 // Per branch b with C[b] != 0 (place.cpp:417-422):  S[b] += float(nw - C[b]) * log10thr;  S[b] /= k.
 // FAST: the short forms of the division and of 10^s (valid for the score range established by
 // fast_sweep_ok) and the mass cut-off; otherwise the IEEE division and the library exp10, every term.
-// The warp looks at the steps scan0, scan0 + stride, ... (two warps of a pair take alternate steps).
 template<class CT, bool FAST, bool DENSE, int CAP>
 __device__ __forceinline__ sweep_result sweep(float* S, CT* C, uint32_t np, uint32_t nw32, float logthr, float kf,
-                                              float rcp_k, uint32_t K, uint32_t lane, const cand_buffers<CAP>& cb,
-                                              uint32_t scan0, uint32_t stride)
+                                              float rcp_k, uint32_t K, uint32_t lane, const cand_buffers<CAP>& cb)
 {
     uint32_t* const cand_key = cb.key;
     uint32_t* const cand_branch = cb.branch;
@@ -555,7 +567,7 @@ __device__ __forceinline__ sweep_result sweep(float* S, CT* C, uint32_t np, uint
     // and processed 32 at a time, so that a query that touched few branches pays for those only (a
     // 100-residue protein read touches a few dozen of the 2000 branches of its tree).
     uint32_t* pending = cb.pending; // [64] first branch of queued quads
-    uint32_t n_pending = 0, scan = scan0;
+    uint32_t n_pending = 0, scan = 0;
     while (true)
     {
         // ---- next 32 quads to process: j = first branch of this lane's quad ----
@@ -566,7 +578,7 @@ __device__ __forceinline__ sweep_result sweep(float* S, CT* C, uint32_t np, uint
             // a query with many postings touched most quads: every step as it stands, no scan
             if (scan >= np) { break; }
             j = scan + 4u * lane;
-            scan += stride;
+            scan += SWEEP_STEP;
             have = true;
         }
         while (!DENSE && !have && scan < np)
@@ -575,7 +587,7 @@ __device__ __forceinline__ sweep_result sweep(float* S, CT* C, uint32_t np, uint
             const bool hit = any_count4(C, mine);
             const uint32_t ballot = __ballot_sync(FULL, hit);
             const uint32_t n_hit = __popc(ballot);
-            scan += stride;
+            scan += SWEEP_STEP;
             if (n_hit >= DENSE_QUADS)
             {
                 j = mine;
@@ -719,17 +731,15 @@ __device__ __forceinline__ sweep_result sweep(float* S, CT* C, uint32_t np, uint
 // tree): IEEE arithmetic; scan-and-queue for queries that touched few branches.
 template<class CT, int CAP>
 __device__ __noinline__ sweep_result sweep_ieee(float* S, CT* C, uint32_t np, uint32_t nw32, float logthr, float kf,
-                                                float rcp_k, uint32_t K, uint32_t lane, const cand_buffers<CAP>& cb,
-                                                uint32_t scan0, uint32_t stride)
+                                                float rcp_k, uint32_t K, uint32_t lane, const cand_buffers<CAP>& cb)
 {
-    return sweep<CT, false, false, CAP>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride);
+    return sweep<CT, false, false, CAP>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cb);
 }
 template<class CT, int CAP>
 __device__ __noinline__ sweep_result sweep_sparse(float* S, CT* C, uint32_t np, uint32_t nw32, float logthr, float kf,
-                                                  float rcp_k, uint32_t K, uint32_t lane, const cand_buffers<CAP>& cb,
-                                                  uint32_t scan0, uint32_t stride)
+                                                  float rcp_k, uint32_t K, uint32_t lane, const cand_buffers<CAP>& cb)
 {
-    return sweep<CT, true, false, CAP>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride);
+    return sweep<CT, true, false, CAP>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cb);
 }
 
 // Whether every score a query with nwf windows can end up with stays inside what the short forms
@@ -749,20 +759,19 @@ __device__ __forceinline__ bool fast_sweep_ok(const device_db& db, float nwf, fl
 // correction + likelihood mass + top-k (the sweep), weight ratios, keep_factor, the rows of query q.
 // `gathered` = postings the query gathered (warp-uniform; only steers dense / scan-and-queue).
 
-// the sweep form that fits the query; this warp takes the steps scan0, scan0 + stride, ...
+// the sweep form that fits the query
 template<class CT, int CAP>
 __device__ __forceinline__ sweep_result run_sweep(const device_db& db, float* S, CT* C, uint32_t np, uint32_t nw32,
-                                                  uint32_t gathered, uint32_t K, uint32_t lane, const cand_buffers<CAP>& cb,
-                                                  uint32_t scan0, uint32_t stride)
+                                                  uint32_t gathered, uint32_t K, uint32_t lane, const cand_buffers<CAP>& cb)
 {
     const float kf = static_cast<float>(db.k);
     const float rcp_k = __frcp_rn(kf);
     const float logthr = db.log_threshold;
     const float nwf = static_cast<float>(nw32);
     const bool dense = 6ull * gathered >= np;
-    return !fast_sweep_ok(db, nwf, kf) ? sweep_ieee<CT, CAP>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride)
-           : dense                     ? sweep<CT, true, true, CAP>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride)
-                                       : sweep_sparse<CT, CAP>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride);
+    return !fast_sweep_ok(db, nwf, kf) ? sweep_ieee<CT, CAP>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cb)
+           : dense                     ? sweep<CT, true, true, CAP>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cb)
+                                       : sweep_sparse<CT, CAP>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cb);
 }
 
 // likelihood weight ratios and keep_factor (place.cpp:164-184, 241-267), rows of query q
@@ -834,84 +843,8 @@ __device__ __forceinline__ void finish_query(const place_params& p, float* S, CT
 {
     const cand_buffers<CAND_CAP> cb(cand_base);
     const uint32_t nw32 = static_cast<uint32_t>(n_windows);
-    const sweep_result sw = run_sweep<CT, CAND_CAP>(p.db, S, C, np, nw32, gathered, p.keep_at_most, lane, cb, 0u, SWEEP_STEP);
+    const sweep_result sw = run_sweep<CT, CAND_CAP>(p.db, S, C, np, nw32, gathered, p.keep_at_most, lane, cb);
     emit_query(p, sw, nw32, q, lane);
-}
-
-// ---- two warps per query --------------------------------------------------------------------------
-//
-// At N = 5000 eight accumulator sets fill the shared memory of an SM, and eight warps leave the issue
-// slots 60 % idle (ncu, profiles/r1e): the sweep is two thirds of a query's instructions and splits
-// cleanly, so every accumulator set gets a second warp. The leader (even warp) encodes, probes and
-// gathers as before - the order of the additions per branch is untouched - then both warps sweep
-// alternate 128-branch steps; the helper leaves its mass, its count of touched branches and its best
-// keep_at_most candidates in shared memory and the leader merges them (mass = leader's + helper's, a
-// fixed order). The pair meets on a named barrier (id 1 + set): A = accumulators complete, B = helper done.
-struct pair_mailbox
-{
-    uint32_t q, nw32, gathered, pad; // leader -> helper (q == NO_BRANCH: no more queries)
-    uint32_t mass_lo, mass_hi, touched, n_keep; // helper -> leader
-};
-static_assert(sizeof(pair_mailbox) == 32, "mailbox");
-
-__device__ __forceinline__ void pair_sync(uint32_t set)
-{
-    asm volatile("bar.sync %0, 64;" ::"r"(set + 1u) : "memory");
-}
-
-// helper's candidate buffers sit after the leader's in the idle segment + code area
-constexpr uint32_t PAIR_CAND_WORDS = cand_buffers<PAIR_CAND_CAP>::WORDS;
-static_assert(2 * PAIR_CAND_WORDS * 4 <= (SEG_CAP + SEG_PAD) * 8 + CODE_BYTES, "two candidate sets alias the segment buffer and the codes");
-
-template<class CT>
-__device__ __forceinline__ void finish_query_leader(const place_params& p, float* S, CT* C, uint32_t np, uint32_t nw32,
-                                                    uint32_t gathered, uint32_t q, uint32_t lane, uint32_t* cand_base,
-                                                    pair_mailbox* box, uint32_t set)
-{
-    const uint32_t K = p.keep_at_most;
-    const cand_buffers<PAIR_CAND_CAP> cb(cand_base), hb(cand_base + PAIR_CAND_WORDS);
-    sweep_result sw = run_sweep<CT, PAIR_CAND_CAP>(p.db, S, C, np, nw32, gathered, K, lane, cb, 0u, 2u * SWEEP_STEP);
-    __syncwarp();
-    pair_sync(set); // B: the helper's half is in its buffers and the mailbox
-    const uint32_t n_h = box->n_keep;
-    sw.mass += __hiloint2double(static_cast<int>(box->mass_hi), static_cast<int>(box->mass_lo));
-    sw.touched += box->touched;
-    if (n_h)
-    {
-        if (lane < n_h)
-        {
-            cb.key[sw.n_keep + lane] = hb.key[lane];
-            cb.branch[sw.n_keep + lane] = hb.branch[lane];
-            cb.count[sw.n_keep + lane] = hb.count[lane];
-        }
-        __syncwarp();
-        sw.n_keep = select_best(cb.key, cb.branch, cb.count, sw.n_keep + n_h, K, lane, sw.key, sw.branch, sw.count);
-    }
-    emit_query(p, sw, nw32, q, lane);
-}
-
-template<class CT>
-__device__ __forceinline__ void helper_loop(const place_params& p, float* S, CT* C, uint32_t np, uint32_t lane,
-                                            uint32_t* cand_base, pair_mailbox* box, uint32_t set)
-{
-    const cand_buffers<PAIR_CAND_CAP> hb(cand_base + PAIR_CAND_WORDS);
-    while (true)
-    {
-        pair_sync(set); // A
-        const uint32_t q = box->q, nw32 = box->nw32, gathered = box->gathered;
-        if (q == NO_BRANCH) { break; }
-        const sweep_result sw = run_sweep<CT, PAIR_CAND_CAP>(p.db, S, C, np, nw32, gathered, p.keep_at_most, lane, hb,
-                                                             SWEEP_STEP, 2u * SWEEP_STEP);
-        if (lane == 0)
-        {
-            box->mass_lo = static_cast<uint32_t>(__double2loint(sw.mass));
-            box->mass_hi = static_cast<uint32_t>(__double2hiint(sw.mass));
-            box->touched = sw.touched;
-            box->n_keep = sw.n_keep;
-        }
-        __syncwarp();
-        pair_sync(set); // B
-    }
 }
 
 // ---- partial rows (database-sharded mode) ---------------------------------------------------------
@@ -963,18 +896,22 @@ __device__ __forceinline__ void dump_partial_row(const place_params& p, float* S
 
 // ---- the kernel ----------------------------------------------------------------------------------
 
-// PARTIAL: database-sharded mode, the accumulators of a query leave as a partial row instead of being
-// swept (queries with ambiguous windows are flagged, their ambiguous windows left out).
-// PAIRED: two warps per accumulator set (see "two warps per query"); blockDim = 64 * sets.
-template<uint32_t TABLE, int U, class CT, bool PARTIAL = false, bool PAIRED = false>
-__global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32 * (PAIRED ? 2 : 1), 1) place_kernel(const place_params p)
+// MODE_PARTIAL: database-sharded mode, the accumulators of a query leave as a partial row instead of
+// being swept (queries with ambiguous windows are flagged, their ambiguous windows left out).
+// MODE_GATHER_ONLY: the measuring stick of the roofline - the same encode / probe / segment / gather
+// instruction stream with the read-modify-write of the accumulators replaced by an XOR into registers
+// and no sweep: what the memory system delivers for this access pattern (one word per query comes out).
+enum kernel_mode { MODE_FULL = 0, MODE_PARTIAL = 1, MODE_GATHER_ONLY = 2 };
+
+template<uint32_t TABLE, int U, class CT, int MODE = MODE_FULL>
+__global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const place_params p)
 {
-    static_assert(!(PARTIAL && PAIRED), "partial rows are written by one warp per query");
+    constexpr bool PARTIAL = MODE == MODE_PARTIAL;
+    constexpr bool GATHER_ONLY = MODE == MODE_GATHER_ONLY;
     extern __shared__ __align__(16) unsigned char smem[];
     if (p.class_reads && p.class_reads[p.cls] == 0) { return; } // no query of this class in the batch
     const uint32_t lane = threadIdx.x & 31u;
-    const uint32_t warp = PAIRED ? threadIdx.x >> 6 : threadIdx.x >> 5; // accumulator set
-    const bool helper = PAIRED && ((threadIdx.x >> 5) & 1u);
+    const uint32_t warp = threadIdx.x >> 5;
     const device_db& db = p.db;
     const uint32_t N = db.n_nodes;
     const uint32_t np = padded_nodes(N);
@@ -996,23 +933,14 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32 * (PAIRED ? 2 : 1), 1) 
     const acc_ref acc{ static_cast<uint32_t>(__cvta_generic_to_shared(S)), static_cast<uint32_t>(__cvta_generic_to_shared(C)) };
     uint32_t* cand_base = reinterpret_cast<uint32_t*>(segs); // the segment buffer is idle during the sweep
     uint8_t* codes = reinterpret_cast<uint8_t*>(segs + SEG_CAP + SEG_PAD);
-    pair_mailbox* box = reinterpret_cast<pair_mailbox*>(smem + 1024) + warp;
 
-    if (!helper)
+    for (uint32_t b = lane; b < np; b += 32)
     {
-        for (uint32_t b = lane; b < np; b += 32)
-        {
-            S[b] = 0.0f;
-            C[b] = 0;
-        }
-        for (uint32_t i = lane; i < seen_words; i += 32) { seen[i] = 0; }
+        S[b] = 0.0f;
+        C[b] = 0;
     }
+    for (uint32_t i = lane; i < seen_words; i += 32) { seen[i] = 0; }
     __syncthreads();
-    if (helper)
-    {
-        helper_loop<CT>(p, S, C, np, lane, cand_base, box, warp);
-        return;
-    }
 
     const float kf = static_cast<float>(k);
     const uint32_t key_mask = db.key_mask;
@@ -1023,16 +951,7 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32 * (PAIRED ? 2 : 1), 1) 
         uint32_t q = 0;
         if (lane == 0) { q = static_cast<uint32_t>(atomicAdd(p.counters + CTR_CURSOR, 1ull)); }
         q = __shfl_sync(FULL, q, 0);
-        if (q >= p.n)
-        {
-            if (PAIRED)
-            {
-                if (lane == 0) { box->q = NO_BRANCH; }
-                __syncwarp();
-                pair_sync(warp); // A: tells the helper to leave
-            }
-            break;
-        }
+        if (q >= p.n) { break; }
 
         const uint64_t s0 = p.seq_off[q];
         const uint64_t len = p.seq_off[q + 1] - s0;
@@ -1060,7 +979,7 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32 * (PAIRED ? 2 : 1), 1) 
         }
         const char* seq = p.seq + s0;
         bool has_ambiguous = false;
-        uint32_t nseg = 0;
+        uint32_t nseg = 0, sink = 0;
         if (lane == 0) { ctr_windows += n_windows; }
 
         // ---- exact k-mers, window order (place.cpp:294-304, 349-371) ----
@@ -1160,7 +1079,7 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32 * (PAIRED ? 2 : 1), 1) 
             {
                 if (lane < SEG_PAD) { segs[nseg + lane] = make_uint2(0, 0); }
                 __syncwarp();
-                gather_segments<U, CT>(db.postings, acc, segs_shared, nseg, lane);
+                gather_segments<U, CT, GATHER_ONLY>(db.postings, acc, segs_shared, nseg, lane, &sink);
                 nseg = 0;
                 __syncwarp();
             }
@@ -1198,9 +1117,15 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32 * (PAIRED ? 2 : 1), 1) 
         {
             if (lane < SEG_PAD) { segs[nseg + lane] = make_uint2(0, 0); }
             __syncwarp();
-            gather_segments<U, CT>(db.postings, acc, segs_shared, nseg, lane);
+            gather_segments<U, CT, GATHER_ONLY>(db.postings, acc, segs_shared, nseg, lane, &sink);
         }
         __syncwarp();
+        if (GATHER_ONLY)
+        {
+            sink = __reduce_xor_sync(FULL, sink);
+            if (lane == 0) { p.n_place[q] = sink; }
+            continue;
+        }
 
         // ---- windows with exactly one ambiguous letter (place.cpp:306-313, 373-415) ----
         has_ambiguous = __any_sync(FULL, has_ambiguous);
@@ -1277,19 +1202,7 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32 * (PAIRED ? 2 : 1), 1) 
 
         // ---- correction, likelihood mass, top-k, weight ratios (place.cpp:417-422, 164-184, 134-159, 241-267) ----
         const uint32_t gathered = __reduce_add_sync(FULL, static_cast<uint32_t>(min(static_cast<unsigned long long>(ctr_entries - entries_before), 0xFFFFFFull)));
-        if (PAIRED)
-        {
-            if (lane == 0)
-            {
-                box->q = q;
-                box->nw32 = static_cast<uint32_t>(n_windows);
-                box->gathered = gathered;
-            }
-            __syncwarp();
-            pair_sync(warp); // A: the accumulators are complete
-            finish_query_leader<CT>(p, S, C, np, static_cast<uint32_t>(n_windows), gathered, q, lane, cand_base, box, warp);
-        }
-        else { finish_query<CT>(p, S, C, np, n_windows, gathered, q, lane, cand_base); }
+        finish_query<CT>(p, S, C, np, n_windows, gathered, q, lane, cand_base);
     }
 
 #pragma unroll

@@ -136,9 +136,16 @@ namespace
     {
         if (pl.db->table_kind == TABLE_DIRECT)
         {
-            return cls == 0 ? place_kernel<TABLE_DIRECT, 8, uint8_t, true> : place_kernel<TABLE_DIRECT, 8, uint16_t, true>;
+            return cls == 0 ? place_kernel<TABLE_DIRECT, 8, uint8_t, MODE_PARTIAL> : place_kernel<TABLE_DIRECT, 8, uint16_t, MODE_PARTIAL>;
         }
-        return cls == 0 ? place_kernel<TABLE_HASH, 8, uint8_t, true> : place_kernel<TABLE_HASH, 8, uint16_t, true>;
+        return cls == 0 ? place_kernel<TABLE_HASH, 8, uint8_t, MODE_PARTIAL> : place_kernel<TABLE_HASH, 8, uint16_t, MODE_PARTIAL>;
+    }
+
+    // the load-only form of the class-0 launch (roofline ceiling, epk_gather_ceiling_device)
+    kernel_fn pick_gather_only_kernel(const epk_placer& pl)
+    {
+        return pl.db->table_kind == TABLE_DIRECT ? place_kernel<TABLE_DIRECT, 8, uint8_t, MODE_GATHER_ONLY>
+                                                 : place_kernel<TABLE_HASH, 8, uint8_t, MODE_GATHER_ONLY>;
     }
 
     kernel_fn pick_kernel(const epk_placer& pl, int cls)
@@ -331,6 +338,11 @@ extern "C" epk_status epk_placer_create(const epk_db* db, uint64_t keep_at_most,
             pl->smem_bytes[c] = CTA_SMEM_FIXED + pl->warps_per_cta[c] * per_warp;
             EPK_CUDA(cudaFuncSetAttribute(pick_kernel(*pl, c), cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           static_cast<int>(pl->smem_bytes[c])));
+            if (c == 0)
+            {
+                EPK_CUDA(cudaFuncSetAttribute(pick_gather_only_kernel(*pl), cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              static_cast<int>(pl->smem_bytes[c])));
+            }
             if (c < 2)
             {
                 EPK_CUDA(cudaFuncSetAttribute(pick_partial_kernel(*pl, c), cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -521,6 +533,45 @@ extern "C" epk_status epk_place(epk_placer* pl, const char* seq, const uint64_t*
                 }
             }
         }
+    });
+}
+
+// ---- the random-gather ceiling of the roofline -----------------------------------------------------
+
+extern "C" epk_status epk_gather_ceiling_device(epk_placer* pl, const char* d_seq, const uint64_t* d_seq_off, uint32_t n,
+                                                uint32_t* d_checksum, void* stream)
+{
+    return guarded([&] {
+        if (!pl || (n && (!d_seq_off || !d_checksum))) { throw error(EPK_E_INVALID, "null argument"); }
+        EPK_CUDA(cudaSetDevice(pl->db->device));
+        const cudaStream_t s = static_cast<cudaStream_t>(stream);
+        place_params p{};
+        p.db = pl->db->d;
+        p.seq = d_seq;
+        p.seq_off = d_seq_off;
+        p.n = n;
+        p.keep_at_most = pl->keep_at_most;
+        p.n_place = d_checksum;
+        p.letters = pl->db->letters.get();
+        p.cls = 0;
+        p.counters = pl->device_counters.get();
+        EPK_CUDA(cudaMemsetAsync(pl->totals.get(), 0, pl->totals.bytes(), s));
+        EPK_CUDA(cudaMemsetAsync(p.counters, 0, N_CLASSES * CTR_COUNT * sizeof(unsigned long long), s));
+        EPK_CUDA(cudaMemsetAsync(pl->device_class_reads.get(), 0, N_CLASSES * sizeof(uint32_t), s));
+        pl->n_launches = 0;
+        pl->n_reads = n;
+        if (n)
+        {
+            const unsigned grid = static_cast<unsigned>(
+                std::min<uint64_t>(pl->n_sms, (static_cast<uint64_t>(n) + pl->warps_per_cta[0] - 1) / pl->warps_per_cta[0]));
+            pick_gather_only_kernel(*pl)<<<grid, pl->warps_per_cta[0] * 32, pl->smem_bytes[0], s>>>(p);
+            EPK_CUDA(cudaGetLastError());
+            fold_counters_kernel<<<1, 1, 0, s>>>(p.counters, pl->device_class_reads.get(), 0u, pl->totals.get());
+            EPK_CUDA(cudaGetLastError());
+            pl->n_launches = 2;
+        }
+        pl->totals_dirty = true;
+        pl->last_stream = s;
     });
 }
 

@@ -227,6 +227,12 @@ class Placer:
                                                         int(shard_stride), C.c_void_p(int(d_off_ptr)), int(n),
                                                         C.byref(res), s))
 
+    def gather_ceiling_device(self, d_seq, d_off, n: int, d_checksum, stream=None):
+        """epk_gather_ceiling_device: the load-only form of the placement launch (roofline measuring stick)."""
+        s = None if stream is None else C.c_void_p(stream.cuda_stream)
+        capi.check(capi.lib().epk_gather_ceiling_device(self.handle, d_seq.data_ptr(), d_off.data_ptr(), int(n),
+                                                        d_checksum.data_ptr(), s))
+
     def counters(self) -> dict:
         c = capi.Counters()
         capi.check(capi.lib().epk_placer_counters(self.handle, C.byref(c)))

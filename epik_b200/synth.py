@@ -178,6 +178,8 @@ CONFIGS = {
     "C3": (DNA, 10, 2500, 0.6, 32.0, 150),     # C2 loaded with --mu 0.5 --max-ram 4G (LOAD_FILTERS)
     "C4": (AA, 6, 1000, 0.05, 16.0, 100),      # N = 1999, 64 M-key space
     "C5": (DNA, 12, 10000, 0.9, 160.0, 150),   # N = 19999, ~4 G entries (device-generated only)
+    "C5r": (DNA, 10, 10000, 0.9, 160.0, 150),  # C5's tree and per-read work (~33 k postings per read) over the
+                                               # 4^10 key space: ~250 M entries, 2 GB (what numpy generates in a minute)
 }
 
 

@@ -215,6 +215,14 @@ epk_status epk_place_finalize_device(epk_placer* placer, const void* d_rows, uin
                                      uint64_t shard_stride_bytes, const uint64_t* d_seq_off, uint32_t n,
                                      const epk_result* d_out, void* stream);
 
+/* Measuring stick for the roofline ("measured random-gather ceiling"): runs the same
+ * encode / probe / posting-gather instruction stream as epk_place_device for the queries with up to
+ * 255 windows, with the accumulator updates replaced by an XOR into registers and no sweep, so that
+ * its duration is what the memory system allows for this access pattern. d_checksum [n] (DEVICE)
+ * receives one word per query; epk_placer_counters reports the postings gathered. */
+epk_status epk_gather_ceiling_device(epk_placer* placer, const char* d_seq, const uint64_t* d_seq_off, uint32_t n,
+                                     uint32_t* d_checksum, void* stream);
+
 /* Pinned host memory for the buffers of epk_place. */
 void* epk_host_alloc(size_t bytes);
 void epk_host_free(void* p);

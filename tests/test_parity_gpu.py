@@ -310,3 +310,24 @@ def test_load_filter_matches_its_restatement(mu, omega, max_entries):
         seq = bytes(data[int(off[i]):int(off[i + 1])])
         for x, y in zip(db.kmers(seq), oracle.kmers(seq)):
             assert np.array_equal(x, y)
+
+
+def test_gather_ceiling_launch_moves_the_same_postings():
+    """epk_gather_ceiling_device (the roofline's measuring stick) walks the same probes and posting lists as the
+    placement launch: same windows / hits / entries counters, one checksum word per query, deterministic."""
+    import torch
+    flat = synth.make_db(0, 8, 300, 0.6, 12.0, seed=11)
+    data, off = synth.make_reads(0, 2000, 150, seed=12)
+    p = Placer(Database(flat))
+    p.place_packed(data, off)
+    full = p.counters()
+    dev = torch.device("cuda", 0)
+    d_seq = torch.from_numpy(data).to(dev)
+    d_off = torch.from_numpy(off.view(np.int64)).to(dev)
+    sums = [torch.zeros(len(off) - 1, dtype=torch.int32, device=dev) for _ in range(2)]
+    for s in sums:
+        p.gather_ceiling_device(d_seq, d_off, len(off) - 1, s)
+    torch.cuda.synchronize()
+    c = p.counters()
+    assert (c["n_windows"], c["n_hits"], c["n_entries"]) == (full["n_windows"], full["n_hits"], full["n_entries"])
+    assert torch.equal(sums[0], sums[1]) and int((sums[0] != 0).sum()) > 1900
