@@ -1075,42 +1075,55 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
             const uint32_t incl = warp_inclusive_sum(my_segs, lane);
             const uint32_t total = __shfl_sync(FULL, incl, 31);
             if (total == 0) { continue; }
-            if (nseg + total > SEG_CAP)
+            // Descriptors are emitted lane by lane (= in window order), as many lanes at a time as the
+            // buffer has room for; a full buffer is gathered and the emission goes on. Only a lane whose own
+            // windows need more than SEG_CAP descriptors (lists of tens of thousands of postings) is
+            // walked list by list.
+            const uint32_t excl = incl - my_segs;
+            uint32_t done = 0; // lanes [0, done) have been emitted
+            while (done < 32)
             {
-                if (lane < SEG_PAD) { segs[nseg + lane] = make_uint2(0, 0); }
-                __syncwarp();
-                gather_segments<U, CT, GATHER_ONLY>(db.postings, acc, segs_shared, nseg, lane, &sink);
-                nseg = 0;
-                __syncwarp();
-            }
-            if (total <= SEG_CAP)
-            {
-                uint32_t at = nseg + incl - my_segs;
-#pragma unroll
-                for (int r = 0; r < WPL; ++r)
+                const uint32_t start = __shfl_sync(FULL, excl, done);
+                const uint32_t space = SEG_CAP - nseg;
+                const bool fit = lane >= done && incl - start <= space; // monotone in the lane: a run from `done`
+                const uint32_t n_fit = __popc(__ballot_sync(FULL, fit));
+                if (n_fit == 0)
                 {
-                    const uint32_t l = static_cast<uint32_t>(slot[r] & LEN_MASK);
-                    const uint32_t pair = static_cast<uint32_t>(slot[r] >> (LEN_BITS + 1));
-                    for (uint32_t pos = 0; pos < l; pos += SEG_LEN)
+                    if (nseg)
                     {
-                        segs[at++] = make_uint2(pair + pos / 2, min(l - pos, static_cast<uint32_t>(SEG_LEN)));
+                        if (lane < SEG_PAD) { segs[nseg + lane] = make_uint2(0, 0); }
+                        __syncwarp();
+                        gather_segments<U, CT, GATHER_ONLY>(db.postings, acc, segs_shared, nseg, lane, &sink);
+                        nseg = 0;
+                        __syncwarp();
+                        continue;
                     }
-                }
-                nseg += total;
-            }
-            else
-            {
-                // more postings in one chunk than the buffer describes: list by list
-                for (uint32_t src = 0; src < 32; ++src)
-                {
 #pragma unroll
                     for (int r = 0; r < WPL; ++r)
                     {
-                        const uint64_t s = __shfl_sync(FULL, slot[r], src);
+                        const uint64_t s = __shfl_sync(FULL, slot[r], done);
                         const uint32_t l = static_cast<uint32_t>(s & LEN_MASK);
                         if (l) { apply_list<CT>(db.postings, acc, s >> LEN_BITS, l, lane); }
                     }
+                    ++done;
+                    continue;
                 }
+                if (fit)
+                {
+                    uint32_t at = nseg + excl - start;
+#pragma unroll
+                    for (int r = 0; r < WPL; ++r)
+                    {
+                        const uint32_t l = static_cast<uint32_t>(slot[r] & LEN_MASK);
+                        const uint32_t pair = static_cast<uint32_t>(slot[r] >> (LEN_BITS + 1));
+                        for (uint32_t pos = 0; pos < l; pos += SEG_LEN)
+                        {
+                            segs[at++] = make_uint2(pair + pos / 2, min(l - pos, static_cast<uint32_t>(SEG_LEN)));
+                        }
+                    }
+                }
+                nseg += __shfl_sync(FULL, incl, done + n_fit - 1) - start;
+                done += n_fit;
             }
         }
         if (nseg)

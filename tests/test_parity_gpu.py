@@ -91,6 +91,8 @@ def test_golden_cases(case):
     (0, 14, 300, 0.0002, 10.0, 200, 0.01),  # k = 14: hashed table for DNA
     (1, 6, 1000, 0.002, 16.0, 100, 0.01),   # C4-shaped: amino acids, hashed table
     (1, 4, 200, 0.3, 10.0, 60, 0.03),       # amino acids, direct table
+    (0, 6, 3000, 0.9, 300.0, 150, 0.0),     # C5-shaped lists: more segment descriptors per chunk than the buffer holds
+    (0, 5, 3000, 0.9, 4000.0, 300, 0.002),  # lists of thousands of postings: one lane's windows overflow the buffer
 ])
 def test_oracle_parity_on_synthetic_shapes(alphabet, k, n_leaves, p_occ, m, read_len, amb):
     flat = synth.make_db(alphabet, k, n_leaves, p_occ, m, seed=1000 + k)
