@@ -336,23 +336,18 @@ extern "C" epk_status epk_placer_create(const epk_db* db, uint64_t keep_at_most,
             pl->warps_per_cta[c] = static_cast<uint32_t>(
                 std::min<size_t>(MAX_WARPS_PER_CTA, (static_cast<size_t>(max_smem) - CTA_SMEM_FIXED) / per_warp));
             pl->smem_bytes[c] = CTA_SMEM_FIXED + pl->warps_per_cta[c] * per_warp;
-            EPK_CUDA(cudaFuncSetAttribute(pick_kernel(*pl, c), cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          static_cast<int>(pl->smem_bytes[c])));
+            // the attribute belongs to the function, not to this placer: always the device's limit, so that
+            // placers for trees of different sizes can live side by side
+            EPK_CUDA(cudaFuncSetAttribute(pick_kernel(*pl, c), cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
             if (c == 0)
             {
-                EPK_CUDA(cudaFuncSetAttribute(pick_gather_only_kernel(*pl), cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                              static_cast<int>(pl->smem_bytes[c])));
+                EPK_CUDA(cudaFuncSetAttribute(pick_gather_only_kernel(*pl), cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
             }
             if (c < 2)
             {
-                EPK_CUDA(cudaFuncSetAttribute(pick_partial_kernel(*pl, c), cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                              static_cast<int>(pl->smem_bytes[c])));
+                EPK_CUDA(cudaFuncSetAttribute(pick_partial_kernel(*pl, c), cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
             }
-            if (c == 1)
-            {
-                EPK_CUDA(cudaFuncSetAttribute(finalize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                              static_cast<int>(pl->smem_bytes[c])));
-            }
+            if (c == 1) { EPK_CUDA(cudaFuncSetAttribute(finalize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem)); }
         }
         if (pl->warps_per_cta[0] == 0)
         {
