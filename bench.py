@@ -64,6 +64,9 @@ def parse_args():
                          "dbshard: database sharded by key over the ranks, every rank sees every query, partial rows "
                          "exchanged with an all-to-all (SURVEY.md 8e second row)")
     ap.add_argument("--dbshard-rows", type=int, default=32768, help="queries per exchange step in dbshard mode")
+    ap.add_argument("--transport", default="p2p", choices=["p2p", "a2a"],
+                    help="dbshard mode: p2p = the partial launch stores its rows into the owner's HBM over NVLink (CUDA "
+                         "IPC), a2a = NCCL all_to_all_single of staged rows")
     ap.add_argument("--reads", type=int, default=0, help="reads per GPU per step (default: the workload's)")
     ap.add_argument("--variant", type=int, default=0)
     ap.add_argument("--no-e2e", action="store_true")
@@ -416,7 +419,8 @@ def run_dbshard(args):
     log("dbshard: world %d, generating database %s" % (world, args.workload))
     flat = synth.make_config_db(args.workload)
     if world > 1:
-        sp = dbshard.ShardedPlacer(flat, rank, world, device=local, keep_at_most=K)
+        sp = dbshard.ShardedPlacer(flat, rank, world, device=local, keep_at_most=K, transport=args.transport,
+                                   max_rows=args.dbshard_rows)
         info = sp.db.info
     else:
         sp = dbshard.LocalShardedPlacer(flat, 1, device=local, keep_at_most=K)
@@ -472,15 +476,20 @@ def run_dbshard(args):
     value = n * args.steps / secs
     if rank == 0:
         cfg = workload_config(args.workload, n, world)
+        how = "stored by the partial launch straight into the owner's HBM (CUDA IPC peer memory over NVLink), one " \
+              "1-element all_reduce per step as the barrier" if (world > 1 and args.transport == "p2p") else \
+              "exchanged by all_to_all_single (NCCL)" if world > 1 else "left in local HBM (one shard)"
         cfg["parallelism"] = "database sharded by key hash x%d, every rank sees every query; partial rows (%d B per query) " \
-                             "exchanged by all_to_all_single (NCCL), %d queries per exchange" % (world, row_bytes, rows)
+                             "%s, %d queries per step" % (world, row_bytes, how, rows)
         cfg["reads_per_gpu"] = n
         emit({"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
               "ms_per_step": secs / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-              "dtype": "f32", "data": "synthetic", "mode": "dbshard", "config": cfg, "clocks": clocks,
+              "dtype": "f32", "data": "synthetic", "mode": "dbshard", "transport": args.transport if world > 1 else "local",
+              "config": cfg, "clocks": clocks,
               "exchange_bytes_per_query": row_bytes * (world - 1) / max(world, 1),
               "db_shard": {k2: int(v2) if isinstance(v2, (int, np.integer)) else float(v2) for k2, v2 in info.items()}})
     if world > 1:
+        sp.close()
         dist.destroy_process_group()
 
 

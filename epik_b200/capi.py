@@ -22,6 +22,7 @@ SYMBOLS = [
     "epk_placer_counters", "epk_host_alloc", "epk_host_free",
     "epk_db_create_shard", "epk_shard_of_key", "epk_partial_row_bytes", "epk_place_partial_device",
     "epk_place_finalize_device", "epk_gather_ceiling_device",
+    "epk_device_alloc", "epk_device_free", "epk_ipc_export", "epk_ipc_import", "epk_ipc_close",
 ]
 
 
@@ -121,6 +122,16 @@ def lib():
                                             C.POINTER(Result), C.c_void_p]
     l.epk_gather_ceiling_device.restype = C.c_int
     l.epk_gather_ceiling_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]
+    l.epk_device_alloc.restype = C.c_int
+    l.epk_device_alloc.argtypes = [C.c_int, C.c_uint64, C.POINTER(C.c_void_p)]
+    l.epk_device_free.restype = None
+    l.epk_device_free.argtypes = [C.c_int, C.c_void_p]
+    l.epk_ipc_export.restype = C.c_int
+    l.epk_ipc_export.argtypes = [C.c_void_p, C.c_char_p]
+    l.epk_ipc_import.restype = C.c_int
+    l.epk_ipc_import.argtypes = [C.c_int, C.c_char_p, C.POINTER(C.c_void_p)]
+    l.epk_ipc_close.restype = None
+    l.epk_ipc_close.argtypes = [C.c_int, C.c_void_p]
     l.epk_host_alloc.restype = C.c_void_p
     l.epk_host_alloc.argtypes = [C.c_size_t]
     l.epk_host_free.argtypes = [C.c_void_p]

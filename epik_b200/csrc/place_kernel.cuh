@@ -523,6 +523,59 @@ __device__ __forceinline__ void clear_counts4(uint8_t* C, uint32_t j) { *reinter
 __device__ __forceinline__ void clear_counts4(uint16_t* C, uint32_t j) { *reinterpret_cast<uint2*>(C + j) = make_uint2(0u, 0u); }
 __device__ __forceinline__ void clear_counts4(uint32_t* C, uint32_t j) { *reinterpret_cast<uint4*>(C + j) = make_uint4(0u, 0u, 0u, 0u); }
 
+// Where the sweep finds the accumulators of its query. shared_acc: the warp's S / C in shared memory
+// (taking a quad clears it for the next query). rows_acc (database-sharded mode, the owner's side): the
+// partial rows of the shards in global memory, added in shard order as they are read - the sum never
+// exists anywhere but in registers.
+template<class CT>
+struct shared_acc
+{
+    float* S;
+    CT* C;
+    __device__ __forceinline__ bool any(uint32_t j) const { return any_count4(C, j); }
+    __device__ __forceinline__ float4 take(uint32_t j, uint32_t (&c)[4]) const
+    {
+        const float4 s4 = *reinterpret_cast<const float4*>(S + j);
+        load_counts4(C, j, c);
+        *reinterpret_cast<float4*>(S + j) = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        clear_counts4(C, j);
+        return s4;
+    }
+};
+
+struct rows_acc
+{
+    const unsigned char* s_rows; // S of shard 0; shard g is g * stride further
+    const unsigned char* c_rows; // C (uint16) of shard 0
+    uint64_t stride;
+    uint32_t n_shards;
+    __device__ __forceinline__ bool any(uint32_t j) const
+    {
+        uint32_t seen = 0;
+        for (uint32_t g = 0; g < n_shards; ++g)
+        {
+            const uint2 u = __ldg(reinterpret_cast<const uint2*>(c_rows + g * stride + 2ull * j));
+            seen |= u.x | u.y;
+        }
+        return seen != 0u;
+    }
+    __device__ __forceinline__ float4 take(uint32_t j, uint32_t (&c)[4]) const
+    {
+        float4 s4 = __ldg(reinterpret_cast<const float4*>(s_rows + 4ull * j));
+        uint2 c2 = __ldg(reinterpret_cast<const uint2*>(c_rows + 2ull * j));
+        for (uint32_t g = 1; g < n_shards; ++g)
+        {
+            const float4 t = __ldg(reinterpret_cast<const float4*>(s_rows + g * stride + 4ull * j));
+            const uint2 u = __ldg(reinterpret_cast<const uint2*>(c_rows + g * stride + 2ull * j));
+            s4.x = __fadd_rn(s4.x, t.x); s4.y = __fadd_rn(s4.y, t.y);
+            s4.z = __fadd_rn(s4.z, t.z); s4.w = __fadd_rn(s4.w, t.w);
+            c2.x += u.x; c2.y += u.y; // 16-bit halves cannot carry: a branch is hit at most n_windows <= 65535 times
+        }
+        c[0] = c2.x & 0xFFFFu; c[1] = c2.x >> 16; c[2] = c2.y & 0xFFFFu; c[3] = c2.y >> 16;
+        return s4;
+    }
+};
+
 // Terms of the likelihood mass more than this many decades under the best score the warp has seen
 // are left out: each is below 1e-20 of the total, all of them together below N * 1e-20.
 constexpr float MASS_CUTOFF_DECADES = 20.0f;
@@ -543,8 +596,8 @@ struct sweep_result
 // Per branch b with C[b] != 0 (place.cpp:417-422):  S[b] += float(nw - C[b]) * log10thr;  S[b] /= k.
 // FAST: the short forms of the division and of 10^s (valid for the score range established by
 // fast_sweep_ok) and the mass cut-off; otherwise the IEEE division and the library exp10, every term.
-template<class CT, bool FAST, bool DENSE, int CAP>
-__device__ __forceinline__ sweep_result sweep(float* S, CT* C, uint32_t np, uint32_t nw32, float logthr, float kf,
+template<class ACC, bool FAST, bool DENSE, int CAP>
+__device__ __forceinline__ sweep_result sweep(const ACC acc, uint32_t np, uint32_t nw32, float logthr, float kf,
                                               float rcp_k, uint32_t K, uint32_t lane, const cand_buffers<CAP>& cb)
 {
     uint32_t* const cand_key = cb.key;
@@ -584,7 +637,7 @@ __device__ __forceinline__ sweep_result sweep(float* S, CT* C, uint32_t np, uint
         while (!DENSE && !have && scan < np)
         {
             const uint32_t mine = scan + 4u * lane;
-            const bool hit = any_count4(C, mine);
+            const bool hit = acc.any(mine);
             const uint32_t ballot = __ballot_sync(FULL, hit);
             const uint32_t n_hit = __popc(ballot);
             scan += SWEEP_STEP;
@@ -624,13 +677,7 @@ __device__ __forceinline__ sweep_result sweep(float* S, CT* C, uint32_t np, uint
         // ---- the quad: correction, keys ----
         float4 s4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
         uint32_t c[4] = { 0u, 0u, 0u, 0u };
-        if (DENSE || active)
-        {
-            s4 = *reinterpret_cast<const float4*>(S + j);
-            load_counts4(C, j, c);
-            *reinterpret_cast<float4*>(S + j) = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-            clear_counts4(C, j);
-        }
+        if (DENSE || active) { s4 = acc.take(j, c); }
         const float sum[4] = { s4.x, s4.y, s4.z, s4.w };
         float s[4];
         uint32_t key[4];
@@ -729,17 +776,17 @@ __device__ __forceinline__ sweep_result sweep(float* S, CT* C, uint32_t np, uint
 
 // The forms off the beaten track, out of line (they are long, and cold for 150-bp reads on a 5000-branch
 // tree): IEEE arithmetic; scan-and-queue for queries that touched few branches.
-template<class CT, int CAP>
-__device__ __noinline__ sweep_result sweep_ieee(float* S, CT* C, uint32_t np, uint32_t nw32, float logthr, float kf,
+template<class ACC, int CAP>
+__device__ __noinline__ sweep_result sweep_ieee(const ACC acc, uint32_t np, uint32_t nw32, float logthr, float kf,
                                                 float rcp_k, uint32_t K, uint32_t lane, const cand_buffers<CAP>& cb)
 {
-    return sweep<CT, false, false, CAP>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cb);
+    return sweep<ACC, false, false, CAP>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb);
 }
-template<class CT, int CAP>
-__device__ __noinline__ sweep_result sweep_sparse(float* S, CT* C, uint32_t np, uint32_t nw32, float logthr, float kf,
+template<class ACC, int CAP>
+__device__ __noinline__ sweep_result sweep_sparse(const ACC acc, uint32_t np, uint32_t nw32, float logthr, float kf,
                                                   float rcp_k, uint32_t K, uint32_t lane, const cand_buffers<CAP>& cb)
 {
-    return sweep<CT, true, false, CAP>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cb);
+    return sweep<ACC, true, false, CAP>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb);
 }
 
 // Whether every score a query with nwf windows can end up with stays inside what the short forms
@@ -760,8 +807,8 @@ __device__ __forceinline__ bool fast_sweep_ok(const device_db& db, float nwf, fl
 // `gathered` = postings the query gathered (warp-uniform; only steers dense / scan-and-queue).
 
 // the sweep form that fits the query
-template<class CT, int CAP>
-__device__ __forceinline__ sweep_result run_sweep(const device_db& db, float* S, CT* C, uint32_t np, uint32_t nw32,
+template<class ACC, int CAP>
+__device__ __forceinline__ sweep_result run_sweep(const device_db& db, const ACC acc, uint32_t np, uint32_t nw32,
                                                   uint32_t gathered, uint32_t K, uint32_t lane, const cand_buffers<CAP>& cb)
 {
     const float kf = static_cast<float>(db.k);
@@ -769,9 +816,9 @@ __device__ __forceinline__ sweep_result run_sweep(const device_db& db, float* S,
     const float logthr = db.log_threshold;
     const float nwf = static_cast<float>(nw32);
     const bool dense = 6ull * gathered >= np;
-    return !fast_sweep_ok(db, nwf, kf) ? sweep_ieee<CT, CAP>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cb)
-           : dense                     ? sweep<CT, true, true, CAP>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cb)
-                                       : sweep_sparse<CT, CAP>(S, C, np, nw32, logthr, kf, rcp_k, K, lane, cb);
+    return !fast_sweep_ok(db, nwf, kf) ? sweep_ieee<ACC, CAP>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb)
+           : dense                     ? sweep<ACC, true, true, CAP>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb)
+                                       : sweep_sparse<ACC, CAP>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb);
 }
 
 // likelihood weight ratios and keep_factor (place.cpp:164-184, 241-267), rows of query q
@@ -837,13 +884,13 @@ __device__ __forceinline__ void emit_query(const place_params& p, const sweep_re
 }
 
 // one warp does it all; cand_base: CAND_CAP * 3 + 64 words (the idle segment buffer)
-template<class CT>
-__device__ __forceinline__ void finish_query(const place_params& p, float* S, CT* C, uint32_t np, uint64_t n_windows,
+template<class ACC>
+__device__ __forceinline__ void finish_query(const place_params& p, const ACC acc, uint32_t np, uint64_t n_windows,
                                              uint32_t gathered, uint32_t q, uint32_t lane, uint32_t* cand_base)
 {
     const cand_buffers<CAND_CAP> cb(cand_base);
     const uint32_t nw32 = static_cast<uint32_t>(n_windows);
-    const sweep_result sw = run_sweep<CT, CAND_CAP>(p.db, S, C, np, nw32, gathered, p.keep_at_most, lane, cb);
+    const sweep_result sw = run_sweep<ACC, CAND_CAP>(p.db, acc, np, nw32, gathered, p.keep_at_most, lane, cb);
     emit_query(p, sw, nw32, q, lane);
 }
 
@@ -1215,7 +1262,7 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
 
         // ---- correction, likelihood mass, top-k, weight ratios (place.cpp:417-422, 164-184, 134-159, 241-267) ----
         const uint32_t gathered = __reduce_add_sync(FULL, static_cast<uint32_t>(min(static_cast<unsigned long long>(ctr_entries - entries_before), 0xFFFFFFull)));
-        finish_query<CT>(p, S, C, np, n_windows, gathered, q, lane, cand_base);
+        finish_query(p, shared_acc<CT>{ S, C }, np, n_windows, gathered, q, lane, cand_base);
     }
 
 #pragma unroll
@@ -1232,12 +1279,15 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
         atomicAdd(p.counters + CTR_ENTRIES, static_cast<unsigned long long>(ctr_entries));
     }
 }
-// Database-sharded mode, the owner's side: adds the partial rows of the n_shards shards of each of its
-// queries (shard order: a fixed association, the same on every run), then finishes the query exactly
-// like place_kernel does. One warp per query; shared memory per warp as for uint16 counts.
-__global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) finalize_kernel(const place_params p)
+// Database-sharded mode, the owner's side: the sweep of finish_query runs straight over the partial rows
+// of the n_shards shards (rows_acc adds them in shard order as it reads: a fixed association, the same
+// on every run). One warp per query; shared memory only holds the candidate buffers, so the launch is
+// not limited by the size of the tree.
+constexpr size_t FINALIZE_WARP_SMEM = cand_buffers<CAND_CAP>::WORDS * 4;
+constexpr int FINALIZE_WARPS = 8;
+
+__global__ void __launch_bounds__(FINALIZE_WARPS * 32, 2) finalize_kernel(const place_params p)
 {
-    using CT = uint16_t;
     extern __shared__ __align__(16) unsigned char smem[];
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t warp = threadIdx.x >> 5;
@@ -1245,10 +1295,7 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) finalize_kernel(con
     const uint32_t N = db.n_nodes;
     const uint32_t np = padded_nodes(N);
     const uint32_t k = db.k;
-    unsigned char* base = smem + CTA_SMEM_FIXED + warp * warp_smem_bytes(N, sizeof(CT));
-    float* S = reinterpret_cast<float*>(base);
-    CT* C = reinterpret_cast<CT*>(base + static_cast<size_t>(np) * 4);
-    uint32_t* cand_base = reinterpret_cast<uint32_t*>(base + static_cast<size_t>(np) * (4 + sizeof(CT)) + np / 8);
+    uint32_t* cand_base = reinterpret_cast<uint32_t*>(smem + warp * FINALIZE_WARP_SMEM);
     const uint64_t row_bytes = partial_row_bytes(N);
 
     while (true)
@@ -1284,25 +1331,8 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) finalize_kernel(con
             atomicAdd(p.counters + CTR_WINDOWS, static_cast<unsigned long long>(n_windows));
             atomicAdd(p.counters + CTR_ENTRIES, static_cast<unsigned long long>(gathered));
         }
-        for (uint32_t j = 4u * lane; j < np; j += SWEEP_STEP)
-        {
-            const unsigned char* s_in = row0 + ROW_HEADER_BYTES + 4ull * j;
-            const unsigned char* c_in = row0 + ROW_HEADER_BYTES + 4ull * np + 2ull * j;
-            float4 s4 = __ldcs(reinterpret_cast<const float4*>(s_in));
-            uint2 c2 = __ldcs(reinterpret_cast<const uint2*>(c_in));
-            for (uint32_t g = 1; g < p.n_shards; ++g)
-            {
-                const float4 t = __ldcs(reinterpret_cast<const float4*>(s_in + g * p.shard_stride));
-                const uint2 u = __ldcs(reinterpret_cast<const uint2*>(c_in + g * p.shard_stride));
-                s4.x = __fadd_rn(s4.x, t.x); s4.y = __fadd_rn(s4.y, t.y);
-                s4.z = __fadd_rn(s4.z, t.z); s4.w = __fadd_rn(s4.w, t.w);
-                c2.x += u.x; c2.y += u.y; // 16-bit halves cannot carry: a branch is hit at most n_windows <= 65535 times
-            }
-            *reinterpret_cast<float4*>(S + j) = s4;
-            *reinterpret_cast<uint2*>(C + j) = c2;
-        }
-        __syncwarp();
-        finish_query<CT>(p, S, C, np, n_windows, gathered, q, lane, cand_base);
+        const rows_acc acc{ row0 + ROW_HEADER_BYTES, row0 + ROW_HEADER_BYTES + 4ull * np, p.shard_stride, p.n_shards };
+        finish_query(p, acc, np, n_windows, gathered, q, lane, cand_base);
     }
 }
 } // namespace epk

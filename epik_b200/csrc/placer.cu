@@ -347,7 +347,6 @@ extern "C" epk_status epk_placer_create(const epk_db* db, uint64_t keep_at_most,
             {
                 EPK_CUDA(cudaFuncSetAttribute(pick_partial_kernel(*pl, c), cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
             }
-            if (c == 1) { EPK_CUDA(cudaFuncSetAttribute(finalize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem)); }
         }
         if (pl->warps_per_cta[0] == 0)
         {
@@ -654,10 +653,6 @@ extern "C" epk_status epk_place_finalize_device(epk_placer* pl, const void* d_ro
         }
         if (n_shards == 0 || n_shards > 32) { throw error(EPK_E_INVALID, "n_shards must be in [1, 32]"); }
         if (d_out->distal || d_out->pendant) { throw error(EPK_E_INVALID, "distal/pendant must be NULL for device results"); }
-        if (pl->warps_per_cta[1] == 0)
-        {
-            throw error(EPK_E_UNSUPPORTED, "tree too large for the shared-memory accumulators of database-sharded mode");
-        }
         if (shard_stride_bytes % 16 != 0 || (reinterpret_cast<uintptr_t>(d_rows) & 15u)) { throw error(EPK_E_INVALID, "rows must be 16-byte aligned"); }
         EPK_CUDA(cudaSetDevice(pl->db->device));
         const cudaStream_t s = static_cast<cudaStream_t>(stream);
@@ -684,14 +679,67 @@ extern "C" epk_status epk_place_finalize_device(epk_placer* pl, const void* d_ro
         if (n)
         {
             const unsigned grid = static_cast<unsigned>(
-                std::min<uint64_t>(pl->n_sms, (static_cast<uint64_t>(n) + pl->warps_per_cta[1] - 1) / pl->warps_per_cta[1]));
-            finalize_kernel<<<grid, pl->warps_per_cta[1] * 32, pl->smem_bytes[1], s>>>(p);
+                std::min<uint64_t>(2ull * pl->n_sms, (static_cast<uint64_t>(n) + FINALIZE_WARPS - 1) / FINALIZE_WARPS));
+            finalize_kernel<<<grid, FINALIZE_WARPS * 32, FINALIZE_WARPS * FINALIZE_WARP_SMEM, s>>>(p);
             EPK_CUDA(cudaGetLastError());
             ++pl->n_launches;
         }
         pl->totals_dirty = true;
         pl->last_stream = s;
     });
+}
+
+// ---- peer memory for the fused exchange of database-sharded mode -------------------------------------
+
+extern "C" epk_status epk_device_alloc(int device, uint64_t bytes, void** out)
+{
+    return guarded([&] {
+        if (!out) { throw error(EPK_E_INVALID, "null argument"); }
+        *out = nullptr;
+        EPK_CUDA(cudaSetDevice(device));
+        EPK_CUDA(cudaMalloc(out, bytes ? bytes : 1));
+    });
+}
+
+extern "C" void epk_device_free(int device, void* p)
+{
+    if (p)
+    {
+        cudaSetDevice(device);
+        cudaFree(p);
+    }
+}
+
+extern "C" epk_status epk_ipc_export(const void* d_ptr, unsigned char* handle_out)
+{
+    return guarded([&] {
+        if (!d_ptr || !handle_out) { throw error(EPK_E_INVALID, "null argument"); }
+        static_assert(sizeof(cudaIpcMemHandle_t) == EPK_IPC_HANDLE_BYTES, "handle size");
+        cudaIpcMemHandle_t h;
+        EPK_CUDA(cudaIpcGetMemHandle(&h, const_cast<void*>(d_ptr)));
+        std::memcpy(handle_out, &h, sizeof(h));
+    });
+}
+
+extern "C" epk_status epk_ipc_import(int device, const unsigned char* handle, void** out)
+{
+    return guarded([&] {
+        if (!handle || !out) { throw error(EPK_E_INVALID, "null argument"); }
+        *out = nullptr;
+        EPK_CUDA(cudaSetDevice(device));
+        cudaIpcMemHandle_t h;
+        std::memcpy(&h, handle, sizeof(h));
+        EPK_CUDA(cudaIpcOpenMemHandle(out, h, cudaIpcMemLazyEnablePeerAccess));
+    });
+}
+
+extern "C" void epk_ipc_close(int device, void* p)
+{
+    if (p)
+    {
+        cudaSetDevice(device);
+        cudaIpcCloseMemHandle(p);
+    }
 }
 
 extern "C" epk_status epk_placer_counters(epk_placer* pl, epk_counters* out)

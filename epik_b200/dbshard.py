@@ -7,7 +7,12 @@ Needed only when a database exceeds one GPU's HBM; the default is query sharding
 database replicated. The reference has nothing like it (one phylo_kmer_db in one address space,
 main.cpp:277): what is preserved is the result, within float rounding of a re-associated sum.
 
-Two transports for the partial rows (include/epik_b200.h, "database-sharded mode"):
+Three transports for the partial rows (include/epik_b200.h, "database-sharded mode"):
+  * "p2p"  — the fused form: every owner's slab is mapped into its peers (CUDA IPC over NVLink / NVSwitch) and
+             the partial launch stores each row straight into the HBM of the GPU that finalises it - the
+             launch IS the exchange, nothing is staged or copied. A one-element all_reduce on the stream is the
+             only collective (it orders "all partial launches done" before the finalising launch); two slabs
+             alternate so that a step's stores never land in a slab a peer is still reading;
   * "a2a"  — every rank writes the rows of all queries into a send buffer ordered by owner and one
              all_to_all_single (NCCL over NVLink; gloo in the CPU tests of the layout) delivers the slabs;
   * "local" — all shards live on ONE device (tests, and databases that merely do not fit one table build):
@@ -109,20 +114,107 @@ class ShardedPlacer:
     SAME batch; rank r gets back the placements of its slice [first, last) of the batch."""
 
     def __init__(self, flat, rank: int, world: int, group=None, device: int = 0, keep_at_most: int = 7,
-                 keep_factor: float = 0.01, **load):
+                 keep_factor: float = 0.01, transport: str = "a2a", max_rows: int = 1 << 15, **load):
+        if transport not in ("a2a", "p2p"):
+            raise ValueError("transport must be 'a2a' or 'p2p'")
         self.db = Database(flat, device=device, shard=(rank, world), **load)
         self.placer = Placer(self.db, keep_at_most, keep_factor)
         self.rank, self.world, self.group, self.device = rank, world, group, device
         self.keep_at_most = keep_at_most
         self.row_bytes = self.placer.partial_row_bytes()
+        self.transport = transport
+        self.max_rows = int(max_rows)
         self._send = None
         self.unsupported = 0
         self.short = 0
+        self._slabs, self._peer = [], []
+        self._turn = 0
+        if transport == "p2p":
+            self._open_peer_slabs()
+
+    # ------------------------------------------------------------------ fused exchange -----
+    def _slab_rows(self) -> int:
+        """rows of one shard's part of a slab: the largest slice a rank can own of max_rows queries"""
+        return slice_for_rank(self.max_rows, 0, self.world)[1]
+
+    def _open_peer_slabs(self):
+        """Two slabs [world][slab_rows][row_bytes] in this rank's HBM, exported to every peer; the peers' slabs mapped here."""
+        import ctypes as C
+        import torch.distributed as dist
+        from . import capi
+        l = capi.lib()
+        bytes_ = self.world * self._slab_rows() * self.row_bytes
+        handles = []
+        for _ in range(2):
+            p = C.c_void_p()
+            capi.check(l.epk_device_alloc(self.device, bytes_, C.byref(p)))
+            self._slabs.append(p.value)
+            h = C.create_string_buffer(64)
+            capi.check(l.epk_ipc_export(C.c_void_p(p.value), h))
+            handles.append(h.raw)
+        everyone = [None] * self.world
+        dist.all_gather_object(everyone, handles, group=self.group)
+        for turn in range(2):
+            mapped = []
+            for r in range(self.world):
+                if r == self.rank:
+                    mapped.append(self._slabs[turn])
+                    continue
+                q = C.c_void_p()
+                capi.check(l.epk_ipc_import(self.device, everyone[r][turn], C.byref(q)))
+                mapped.append(q.value)
+            self._peer.append(mapped)
+
+    def close(self):
+        if not self._slabs and not self._peer:
+            return
+        from . import capi
+        l = capi.lib()
+        for turn, mapped in enumerate(self._peer):
+            for r, p in enumerate(mapped):
+                if r != self.rank:
+                    l.epk_ipc_close(self.device, p)
+        self._peer = []
+        if self._slabs:
+            import torch
+            import torch.distributed as dist
+            torch.cuda.synchronize(self.device)
+            if dist.is_initialized():
+                dist.barrier(group=self.group)  # nobody unmaps-then-frees under a peer that still stores
+        for p in self._slabs:
+            l.epk_device_free(self.device, p)
+        self._slabs = []
+
+    def _place_p2p(self, d_seq, d_off, n: int, out):
+        import torch
+        import torch.distributed as dist
+        if n > self.max_rows:
+            raise ValueError("p2p transport: at most max_rows = %d queries per call" % self.max_rows)
+        bounds = owner_bounds(n, self.world)
+        first, last = int(bounds[self.rank]), int(bounds[self.rank + 1])
+        turn = self._turn
+        self._turn ^= 1
+        stride = self._slab_rows() * self.row_bytes
+        # owner g's slab, part `rank`: where this rank's rows of g's queries go
+        dest = [self._peer[turn][g] + self.rank * stride for g in range(self.world)]
+        self.placer.place_partial_device(d_seq, d_off, n, bounds, dest)
+        if self._flag is None:
+            self._flag = torch.zeros(1, dtype=torch.int32, device=d_off.device)
+        dist.all_reduce(self._flag, group=self.group)  # stream-ordered: every rank's partial launch has completed
+        m = last - first
+        if out is None:
+            out = _alloc_out(torch, m, self.keep_at_most, d_off.device)
+        self.placer.place_finalize_device(self._slabs[turn], self.world, stride, d_off.data_ptr() + 8 * first, m, out)
+        return out, first, last
+
+    _flag = None
 
     def place_device(self, d_seq, d_off, n: int, out: dict | None = None):
         """d_seq (uint8) / d_off (int64 view of uint64 offsets, n + 1) on this rank's device; the whole batch.
         Returns (out, first, last): device tensors with the rows of queries [first, last)."""
         import torch
+        if self.transport == "p2p":
+            return self._place_p2p(d_seq, d_off, n, out)
         dev = d_off.device
         bounds = owner_bounds(n, self.world)
         first, last = int(bounds[self.rank]), int(bounds[self.rank + 1])
@@ -139,13 +231,26 @@ class ShardedPlacer:
         return out, first, last
 
     def place_packed(self, data, offsets):
+        """The whole batch in host memory (the same on every rank) -> (host arrays of this rank's queries, first, last).
+        Batches larger than max_rows go through in pieces; the rank then owns a slice of every piece and
+        (first, last) are lists."""
         import torch
         dev = torch.device("cuda", self.device)
         n = len(offsets) - 1
         d_seq = torch.from_numpy(np.ascontiguousarray(data, np.uint8)).to(dev) if len(data) else torch.zeros(1, dtype=torch.uint8, device=dev)
         d_off = torch.from_numpy(np.ascontiguousarray(offsets, np.uint64).view(np.int64)).to(dev)
-        out, first, last = self.place_device(d_seq, d_off, n)
-        torch.cuda.synchronize(dev)
-        c = self.placer.counters()
-        self.unsupported, self.short = c["n_unsupported"], c["n_short"]
-        return _to_host(out), first, last
+        self.unsupported = self.short = 0
+        pieces, firsts, lasts = [], [], []
+        for at in range(0, max(n, 1), self.max_rows):
+            m = min(self.max_rows, n - at)
+            out, first, last = self.place_device(d_seq, d_off[at:at + m + 1], m)
+            torch.cuda.synchronize(dev)
+            c = self.placer.counters()
+            self.unsupported += c["n_unsupported"]
+            self.short += c["n_short"]
+            pieces.append(_to_host(out))
+            firsts.append(at + first)
+            lasts.append(at + last)
+        if len(pieces) == 1:
+            return pieces[0], firsts[0], lasts[0]
+        return {k: np.concatenate([p[k] for p in pieces]) for k in pieces[0]}, firsts, lasts

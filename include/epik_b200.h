@@ -215,6 +215,17 @@ epk_status epk_place_finalize_device(epk_placer* placer, const void* d_rows, uin
                                      uint64_t shard_stride_bytes, const uint64_t* d_seq_off, uint32_t n,
                                      const epk_result* d_out, void* stream);
 
+/* Peer memory for the fused exchange: with one process per GPU, each owner allocates its slab with
+ * epk_device_alloc, exports it (64-byte CUDA IPC handle, sent to the peers by any means), the peers
+ * import it and pass the mapped address as d_rows[owner] of epk_place_partial_device: the partial
+ * launch then stores its rows straight into the owner's HBM over NVLink. */
+#define EPK_IPC_HANDLE_BYTES 64
+epk_status epk_device_alloc(int device, uint64_t bytes, void** out);
+void epk_device_free(int device, void* p);
+epk_status epk_ipc_export(const void* d_ptr, unsigned char* handle_out /* [EPK_IPC_HANDLE_BYTES] */);
+epk_status epk_ipc_import(int device, const unsigned char* handle, void** out);
+void epk_ipc_close(int device, void* p);
+
 /* Measuring stick for the roofline ("measured random-gather ceiling"): runs the same
  * encode / probe / posting-gather instruction stream as epk_place_device for the queries with up to
  * 255 windows, with the accumulator updates replaced by an XOR into registers and no sweep, so that

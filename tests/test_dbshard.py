@@ -174,28 +174,31 @@ def test_ambiguous_and_short_reads_are_reported(built):
     assert np.array_equal(got["branch"][0], got["branch"][3]) and np.array_equal(got["score"][0], got["score"][3])
 
 
-def _nccl_worker(rank, world, port, out_dir):
+def _nccl_worker(rank, world, port, out_dir, transport):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     flat = synth.make_db(0, 8, 300, 0.6, 12.0, seed=31)
     data, off = synth.make_reads(0, 2001, 150, seed=32)
-    sp = dbshard.ShardedPlacer(flat, rank, world, device=rank)
-    for _ in range(2):  # twice: buffers are reused
+    sp = dbshard.ShardedPlacer(flat, rank, world, device=rank, transport=transport, max_rows=4096)
+    for _ in range(3):  # several times: buffers are reused, the two peer slabs alternate
         got, first, last = sp.place_packed(data, off)
     assert sp.unsupported == 0
+    sp.close()
     np.savez(os.path.join(out_dir, "part%d.npz" % rank), first=first, last=last, **got)
     dist.barrier()
     dist.destroy_process_group()
 
 
 @pytest.mark.gpu
-def test_two_gpus_nccl_exchange(built, tmp_path):
+@pytest.mark.parametrize("transport", ["a2a", "p2p"])
+def test_two_gpus_exchange(built, tmp_path, transport):
+    """a2a: NCCL all_to_all_single of the row buffers; p2p: the partial launch stores into the owner's HBM (CUDA IPC)."""
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     world = 2
-    mp.spawn(_nccl_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    mp.spawn(_nccl_worker, args=(world, _free_port(), str(tmp_path), transport), nprocs=world, join=True)
     flat = synth.make_db(0, 8, 300, 0.6, 12.0, seed=31)
     data, off = synth.make_reads(0, 2001, 150, seed=32)
     want = _oracle(flat).place_packed(data, off)
