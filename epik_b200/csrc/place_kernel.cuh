@@ -86,6 +86,7 @@ struct place_params
     const unsigned char* rows_in;        // finalize launch: n_shards slabs of n rows each
     uint64_t shard_stride;               // bytes from a row of shard g to the same row of shard g + 1
     uint32_t n_shards;
+    uint32_t team;                       // warps per accumulator set (TEAM launches)
 };
 
 __host__ __device__ inline uint32_t padded_nodes(uint32_t n_nodes)
@@ -596,9 +597,11 @@ struct sweep_result
 // Per branch b with C[b] != 0 (place.cpp:417-422):  S[b] += float(nw - C[b]) * log10thr;  S[b] /= k.
 // FAST: the short forms of the division and of 10^s (valid for the score range established by
 // fast_sweep_ok) and the mass cut-off; otherwise the IEEE division and the library exp10, every term.
+// The warp looks at the steps scan0, scan0 + stride, ... (the warps of a team take interleaved steps).
 template<class ACC, bool FAST, bool DENSE, int CAP>
 __device__ __forceinline__ sweep_result sweep(const ACC acc, uint32_t np, uint32_t nw32, float logthr, float kf,
-                                              float rcp_k, uint32_t K, uint32_t lane, const cand_buffers<CAP>& cb)
+                                              float rcp_k, uint32_t K, uint32_t lane, const cand_buffers<CAP>& cb,
+                                              uint32_t scan0, uint32_t stride)
 {
     uint32_t* const cand_key = cb.key;
     uint32_t* const cand_branch = cb.branch;
@@ -620,7 +623,7 @@ __device__ __forceinline__ sweep_result sweep(const ACC acc, uint32_t np, uint32
     // and processed 32 at a time, so that a query that touched few branches pays for those only (a
     // 100-residue protein read touches a few dozen of the 2000 branches of its tree).
     uint32_t* pending = cb.pending; // [64] first branch of queued quads
-    uint32_t n_pending = 0, scan = 0;
+    uint32_t n_pending = 0, scan = scan0;
     while (true)
     {
         // ---- next 32 quads to process: j = first branch of this lane's quad ----
@@ -631,7 +634,7 @@ __device__ __forceinline__ sweep_result sweep(const ACC acc, uint32_t np, uint32
             // a query with many postings touched most quads: every step as it stands, no scan
             if (scan >= np) { break; }
             j = scan + 4u * lane;
-            scan += SWEEP_STEP;
+            scan += stride;
             have = true;
         }
         while (!DENSE && !have && scan < np)
@@ -640,7 +643,7 @@ __device__ __forceinline__ sweep_result sweep(const ACC acc, uint32_t np, uint32
             const bool hit = acc.any(mine);
             const uint32_t ballot = __ballot_sync(FULL, hit);
             const uint32_t n_hit = __popc(ballot);
-            scan += SWEEP_STEP;
+            scan += stride;
             if (n_hit >= DENSE_QUADS)
             {
                 j = mine;
@@ -778,15 +781,17 @@ __device__ __forceinline__ sweep_result sweep(const ACC acc, uint32_t np, uint32
 // tree): IEEE arithmetic; scan-and-queue for queries that touched few branches.
 template<class ACC, int CAP>
 __device__ __noinline__ sweep_result sweep_ieee(const ACC acc, uint32_t np, uint32_t nw32, float logthr, float kf,
-                                                float rcp_k, uint32_t K, uint32_t lane, const cand_buffers<CAP>& cb)
+                                                float rcp_k, uint32_t K, uint32_t lane, const cand_buffers<CAP>& cb,
+                                                uint32_t scan0, uint32_t stride)
 {
-    return sweep<ACC, false, false, CAP>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb);
+    return sweep<ACC, false, false, CAP>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride);
 }
 template<class ACC, int CAP>
 __device__ __noinline__ sweep_result sweep_sparse(const ACC acc, uint32_t np, uint32_t nw32, float logthr, float kf,
-                                                  float rcp_k, uint32_t K, uint32_t lane, const cand_buffers<CAP>& cb)
+                                                  float rcp_k, uint32_t K, uint32_t lane, const cand_buffers<CAP>& cb,
+                                                  uint32_t scan0, uint32_t stride)
 {
-    return sweep<ACC, true, false, CAP>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb);
+    return sweep<ACC, true, false, CAP>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride);
 }
 
 // Whether every score a query with nwf windows can end up with stays inside what the short forms
@@ -809,16 +814,17 @@ __device__ __forceinline__ bool fast_sweep_ok(const device_db& db, float nwf, fl
 // the sweep form that fits the query
 template<class ACC, int CAP>
 __device__ __forceinline__ sweep_result run_sweep(const device_db& db, const ACC acc, uint32_t np, uint32_t nw32,
-                                                  uint32_t gathered, uint32_t K, uint32_t lane, const cand_buffers<CAP>& cb)
+                                                  uint32_t gathered, uint32_t K, uint32_t lane, const cand_buffers<CAP>& cb,
+                                                  uint32_t scan0 = 0, uint32_t stride = SWEEP_STEP)
 {
     const float kf = static_cast<float>(db.k);
     const float rcp_k = __frcp_rn(kf);
     const float logthr = db.log_threshold;
     const float nwf = static_cast<float>(nw32);
     const bool dense = 6ull * gathered >= np;
-    return !fast_sweep_ok(db, nwf, kf) ? sweep_ieee<ACC, CAP>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb)
-           : dense                     ? sweep<ACC, true, true, CAP>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb)
-                                       : sweep_sparse<ACC, CAP>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb);
+    return !fast_sweep_ok(db, nwf, kf) ? sweep_ieee<ACC, CAP>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride)
+           : dense                     ? sweep<ACC, true, true, CAP>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride)
+                                       : sweep_sparse<ACC, CAP>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride);
 }
 
 // likelihood weight ratios and keep_factor (place.cpp:164-184, 241-267), rows of query q
@@ -894,6 +900,100 @@ __device__ __forceinline__ void finish_query(const place_params& p, const ACC ac
     emit_query(p, sw, nw32, q, lane);
 }
 
+// ---- teams: several warps sweep one query ---------------------------------------------------------
+//
+// A large tree leaves room for few accumulator sets per SM (N = 20 000: two), and a lone warp per set
+// then spends two thirds of its time in the sweep with the SM idle around it (ncu, profiles/r1w). In
+// team mode every set has T warps (T * sets = 8): the leader (member 0) encodes, probes and gathers as
+// before - the order of the additions per branch is untouched - then all T members sweep interleaved
+// 128-branch steps through ONE out-of-line copy of the sweep (the two-warps experiment of DESIGN.md 3.1
+// died of instruction-cache misses with two inlined copies), each with its own candidate buffer; the
+// leader adds the members' masses in member order and merges their best keep_at_most candidates. The
+// team meets on a named barrier (id 1 + set): A = accumulators complete, B = members done.
+constexpr int TEAM_CAND_CAP = 64;
+constexpr uint32_t TEAM_MEMBER_WORDS = cand_buffers<TEAM_CAND_CAP>::WORDS;     // candidate buffer of one member
+struct team_mailbox { uint32_t q, nw32, gathered, pad; };                      // leader -> members (q == NO_BRANCH: leave)
+struct team_result { uint32_t mass_lo, mass_hi, touched, n_keep; };            // member -> leader
+__host__ __device__ inline size_t team_smem_bytes(uint32_t team)
+{
+    return team <= 1 ? 0 : team * (TEAM_MEMBER_WORDS * 4 + sizeof(team_result)) + sizeof(team_mailbox);
+}
+
+__device__ __forceinline__ void team_sync(uint32_t set, uint32_t team)
+{
+    asm volatile("bar.sync %0, %1;" ::"r"(set + 1u), "r"(team * 32u) : "memory");
+}
+
+// one member's share of the sweep; out of line so that all members of all teams run the same code
+template<class CT>
+__device__ __noinline__ sweep_result team_sweep(const device_db& db, float* S, CT* C, uint32_t np, uint32_t nw32,
+                                                uint32_t gathered, uint32_t K, uint32_t lane, uint32_t* member_base,
+                                                uint32_t member, uint32_t team)
+{
+    const cand_buffers<TEAM_CAND_CAP> cb(member_base);
+    return run_sweep<shared_acc<CT>, TEAM_CAND_CAP>(db, shared_acc<CT>{ S, C }, np, nw32, gathered, K, lane, cb,
+                                                    member * SWEEP_STEP, team * SWEEP_STEP);
+}
+
+template<class CT>
+__device__ __forceinline__ void team_helper_loop(const place_params& p, float* S, CT* C, uint32_t np, uint32_t lane,
+                                                 unsigned char* team_area, uint32_t set, uint32_t member, uint32_t team)
+{
+    const team_mailbox* box = reinterpret_cast<const team_mailbox*>(team_area);
+    team_result* results = reinterpret_cast<team_result*>(team_area + sizeof(team_mailbox));
+    uint32_t* member_base = reinterpret_cast<uint32_t*>(team_area + sizeof(team_mailbox) + team * sizeof(team_result))
+                            + member * TEAM_MEMBER_WORDS;
+    while (true)
+    {
+        team_sync(set, team); // A
+        const uint32_t q = box->q, nw32 = box->nw32, gathered = box->gathered;
+        if (q == NO_BRANCH) { break; }
+        const sweep_result sw = team_sweep<CT>(p.db, S, C, np, nw32, gathered, p.keep_at_most, lane, member_base, member, team);
+        if (lane == 0)
+        {
+            results[member] = team_result{ static_cast<uint32_t>(__double2loint(sw.mass)),
+                                           static_cast<uint32_t>(__double2hiint(sw.mass)), sw.touched, sw.n_keep };
+        }
+        __syncwarp();
+        team_sync(set, team); // B
+    }
+}
+
+template<class CT>
+__device__ __forceinline__ void finish_query_leader(const place_params& p, float* S, CT* C, uint32_t np, uint32_t nw32,
+                                                    uint32_t gathered, uint32_t q, uint32_t lane, unsigned char* team_area,
+                                                    uint32_t set, uint32_t team)
+{
+    const uint32_t K = p.keep_at_most;
+    team_mailbox* box = reinterpret_cast<team_mailbox*>(team_area);
+    const team_result* results = reinterpret_cast<const team_result*>(team_area + sizeof(team_mailbox));
+    uint32_t* bases = reinterpret_cast<uint32_t*>(team_area + sizeof(team_mailbox) + team * sizeof(team_result));
+    if (lane == 0) { *box = team_mailbox{ q, nw32, gathered, 0u }; }
+    __syncwarp();
+    team_sync(set, team); // A: the accumulators are complete
+    sweep_result sw = team_sweep<CT>(p.db, S, C, np, nw32, gathered, K, lane, bases, 0u, team);
+    __syncwarp();
+    team_sync(set, team); // B: every member's share is in its buffer and its result slot
+    const cand_buffers<TEAM_CAND_CAP> mine(bases);
+    for (uint32_t m = 1; m < team; ++m)
+    {
+        const team_result r = results[m];
+        sw.mass += __hiloint2double(static_cast<int>(r.mass_hi), static_cast<int>(r.mass_lo));
+        sw.touched += r.touched;
+        if (r.n_keep == 0) { continue; }
+        const cand_buffers<TEAM_CAND_CAP> theirs(bases + m * TEAM_MEMBER_WORDS);
+        if (lane < r.n_keep)
+        {
+            mine.key[sw.n_keep + lane] = theirs.key[lane];
+            mine.branch[sw.n_keep + lane] = theirs.branch[lane];
+            mine.count[sw.n_keep + lane] = theirs.count[lane];
+        }
+        __syncwarp();
+        sw.n_keep = select_best(mine.key, mine.branch, mine.count, sw.n_keep + r.n_keep, K, lane, sw.key, sw.branch, sw.count);
+    }
+    emit_query(p, sw, nw32, q, lane);
+}
+
 // ---- partial rows (database-sharded mode) ---------------------------------------------------------
 //
 // When the database is split by key over the GPUs of a group (second row), every GPU
@@ -950,15 +1050,19 @@ __device__ __forceinline__ void dump_partial_row(const place_params& p, float* S
 // and no sweep: what the memory system delivers for this access pattern (one word per query comes out).
 enum kernel_mode { MODE_FULL = 0, MODE_PARTIAL = 1, MODE_GATHER_ONLY = 2 };
 
-template<uint32_t TABLE, int U, class CT, int MODE = MODE_FULL>
+// TEAM: p.team warps per accumulator set (see "teams"); blockDim = 32 * p.team * sets.
+template<uint32_t TABLE, int U, class CT, int MODE = MODE_FULL, bool TEAM = false>
 __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const place_params p)
 {
     constexpr bool PARTIAL = MODE == MODE_PARTIAL;
     constexpr bool GATHER_ONLY = MODE == MODE_GATHER_ONLY;
+    static_assert(!TEAM || MODE == MODE_FULL, "teams only exist where there is a sweep");
     extern __shared__ __align__(16) unsigned char smem[];
     if (p.class_reads && p.class_reads[p.cls] == 0) { return; } // no query of this class in the batch
     const uint32_t lane = threadIdx.x & 31u;
-    const uint32_t warp = threadIdx.x >> 5;
+    const uint32_t team = TEAM ? p.team : 1u;
+    const uint32_t warp = (threadIdx.x >> 5) / team;   // accumulator set
+    const uint32_t member = (threadIdx.x >> 5) % team; // 0: the leader
     const device_db& db = p.db;
     const uint32_t N = db.n_nodes;
     const uint32_t np = padded_nodes(N);
@@ -969,8 +1073,9 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
     uint32_t* letters = reinterpret_cast<uint32_t*>(smem);
     for (uint32_t i = threadIdx.x; i < 256; i += blockDim.x) { letters[i] = p.letters[i]; }
 
-    // per warp: float S[np] | CT C[np] | seen bitmap np/8 bytes | segment descriptors | letter codes
-    unsigned char* base = smem + CTA_SMEM_FIXED + warp * warp_smem_bytes(N, sizeof(CT));
+    // per set: float S[np] | CT C[np] | seen bitmap np/8 bytes | segment descriptors | letter codes | team area
+    unsigned char* base = smem + CTA_SMEM_FIXED + warp * (warp_smem_bytes(N, sizeof(CT)) + team_smem_bytes(team));
+    unsigned char* team_area = base + warp_smem_bytes(N, sizeof(CT));
     float* S = reinterpret_cast<float*>(base);
     CT* C = reinterpret_cast<CT*>(base + static_cast<size_t>(np) * 4);
     uint32_t* seen = reinterpret_cast<uint32_t*>(base + static_cast<size_t>(np) * (4 + sizeof(CT)));
@@ -981,13 +1086,21 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
     uint32_t* cand_base = reinterpret_cast<uint32_t*>(segs); // the segment buffer is idle during the sweep
     uint8_t* codes = reinterpret_cast<uint8_t*>(segs + SEG_CAP + SEG_PAD);
 
-    for (uint32_t b = lane; b < np; b += 32)
+    if (member == 0)
     {
-        S[b] = 0.0f;
-        C[b] = 0;
+        for (uint32_t b = lane; b < np; b += 32)
+        {
+            S[b] = 0.0f;
+            C[b] = 0;
+        }
+        for (uint32_t i = lane; i < seen_words; i += 32) { seen[i] = 0; }
     }
-    for (uint32_t i = lane; i < seen_words; i += 32) { seen[i] = 0; }
     __syncthreads();
+    if (TEAM && member != 0)
+    {
+        team_helper_loop<CT>(p, S, C, np, lane, team_area, warp, member, team);
+        return;
+    }
 
     const float kf = static_cast<float>(k);
     const uint32_t key_mask = db.key_mask;
@@ -998,7 +1111,16 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
         uint32_t q = 0;
         if (lane == 0) { q = static_cast<uint32_t>(atomicAdd(p.counters + CTR_CURSOR, 1ull)); }
         q = __shfl_sync(FULL, q, 0);
-        if (q >= p.n) { break; }
+        if (q >= p.n)
+        {
+            if (TEAM)
+            {
+                if (lane == 0) { reinterpret_cast<team_mailbox*>(team_area)->q = NO_BRANCH; }
+                __syncwarp();
+                team_sync(warp, team); // A: tells the members to leave
+            }
+            break;
+        }
 
         const uint64_t s0 = p.seq_off[q];
         const uint64_t len = p.seq_off[q + 1] - s0;
@@ -1262,7 +1384,8 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
 
         // ---- correction, likelihood mass, top-k, weight ratios (place.cpp:417-422, 164-184, 134-159, 241-267) ----
         const uint32_t gathered = __reduce_add_sync(FULL, static_cast<uint32_t>(min(static_cast<unsigned long long>(ctr_entries - entries_before), 0xFFFFFFull)));
-        finish_query(p, shared_acc<CT>{ S, C }, np, n_windows, gathered, q, lane, cand_base);
+        if (TEAM) { finish_query_leader<CT>(p, S, C, np, static_cast<uint32_t>(n_windows), gathered, q, lane, team_area, warp, team); }
+        else { finish_query(p, shared_acc<CT>{ S, C }, np, n_windows, gathered, q, lane, cand_base); }
     }
 
 #pragma unroll

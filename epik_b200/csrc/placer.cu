@@ -117,6 +117,9 @@ struct epk_placer
     uint32_t warps_per_cta[N_CLASSES] = { 0, 0, 0 }; // 0: the accumulators of this class do not fit shared memory
     size_t smem_bytes[N_CLASSES] = { 0, 0, 0 };
     uint32_t unsupported_mask = 0;
+    uint32_t team[N_CLASSES] = { 1, 1, 1 };           // warps per accumulator set of the fused launch
+    uint32_t sets_fused[N_CLASSES] = { 0, 0, 0 };     // accumulator sets per CTA of the fused launch
+    size_t smem_fused[N_CLASSES] = { 0, 0, 0 };
     device_buffer<uint32_t> fake_order;
     device_buffer<unsigned long long> totals;          // folded work counters
     device_buffer<unsigned long long> device_counters; // per-launch counters of epk_place_device
@@ -150,6 +153,15 @@ namespace
 
     kernel_fn pick_kernel(const epk_placer& pl, int cls)
     {
+        if (pl.team[cls] > 1)
+        {
+            // large tree, few accumulator sets per SM: several warps per set (place_kernel.cuh, "teams")
+            if (pl.db->table_kind == TABLE_DIRECT)
+            {
+                return cls == 0 ? place_kernel<TABLE_DIRECT, 8, uint8_t, MODE_FULL, true> : place_kernel<TABLE_DIRECT, 8, uint16_t, MODE_FULL, true>;
+            }
+            return cls == 0 ? place_kernel<TABLE_HASH, 8, uint8_t, MODE_FULL, true> : place_kernel<TABLE_HASH, 8, uint16_t, MODE_FULL, true>;
+        }
         if (pl.db->table_kind == TABLE_DIRECT)
         {
             return cls == 0 ? place_kernel<TABLE_DIRECT, 8, uint8_t> : cls == 1 ? place_kernel<TABLE_DIRECT, 8, uint16_t>
@@ -199,8 +211,9 @@ namespace
                 p.cls = static_cast<uint32_t>(c);
                 p.counters = counters + c * CTR_COUNT;
                 const unsigned grid = static_cast<unsigned>(
-                    std::min<uint64_t>(pl.n_sms, (static_cast<uint64_t>(n) + pl.warps_per_cta[c] - 1) / pl.warps_per_cta[c]));
-                pick_kernel(pl, c)<<<grid, pl.warps_per_cta[c] * 32, pl.smem_bytes[c], stream>>>(p);
+                    std::min<uint64_t>(pl.n_sms, (static_cast<uint64_t>(n) + pl.sets_fused[c] - 1) / pl.sets_fused[c]));
+                p.team = pl.team[c];
+                pick_kernel(pl, c)<<<grid, pl.sets_fused[c] * pl.team[c] * 32, pl.smem_fused[c], stream>>>(p);
                 EPK_CUDA(cudaGetLastError());
                 ++pl.n_launches;
             }
@@ -336,6 +349,22 @@ extern "C" epk_status epk_placer_create(const epk_db* db, uint64_t keep_at_most,
             pl->warps_per_cta[c] = static_cast<uint32_t>(
                 std::min<size_t>(MAX_WARPS_PER_CTA, (static_cast<size_t>(max_smem) - CTA_SMEM_FIXED) / per_warp));
             pl->smem_bytes[c] = CTA_SMEM_FIXED + pl->warps_per_cta[c] * per_warp;
+            // teams: when at most four sets fit, every set gets 8 / sets warps (a power of two) for its sweep
+            pl->sets_fused[c] = pl->warps_per_cta[c];
+            pl->smem_fused[c] = pl->smem_bytes[c];
+            if (pl->warps_per_cta[c] <= 4 && c < 2 && pl->variant != 1)
+            {
+                uint32_t team = pl->warps_per_cta[c] == 1 ? 8 : pl->warps_per_cta[c] == 2 ? 4 : 2;
+                const size_t per_set = per_warp + team_smem_bytes(team);
+                const uint32_t sets = static_cast<uint32_t>(
+                    std::min<size_t>(pl->warps_per_cta[c], (static_cast<size_t>(max_smem) - CTA_SMEM_FIXED) / per_set));
+                if (sets >= 1)
+                {
+                    pl->team[c] = team;
+                    pl->sets_fused[c] = sets;
+                    pl->smem_fused[c] = CTA_SMEM_FIXED + sets * per_set;
+                }
+            }
             // the attribute belongs to the function, not to this placer: always the device's limit, so that
             // placers for trees of different sizes can live side by side
             EPK_CUDA(cudaFuncSetAttribute(pick_kernel(*pl, c), cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));

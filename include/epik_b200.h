@@ -93,7 +93,8 @@ typedef struct epk_placer epk_placer;
 /* Options of a placer beyond the reference's constructor arguments. Zero-initialise for defaults. */
 typedef struct epk_placer_opts
 {
-    uint32_t variant;        /* 0 = default; 1 = register-staged gathers; 2 = TMA bulk-copy ring  */
+    uint32_t variant;        /* 0 = default; 1 = always one warp per query (no sweep teams on     */
+                             /* large trees)                                                      */
     uint32_t chunk_reads;    /* reads per pipelined H2D/kernel/D2H chunk of epk_place; 0 = auto   */
     uint32_t reserved[6];
 } epk_placer_opts;

@@ -333,3 +333,29 @@ def test_gather_ceiling_launch_moves_the_same_postings():
     c = p.counters()
     assert (c["n_windows"], c["n_hits"], c["n_entries"]) == (full["n_windows"], full["n_hits"], full["n_entries"])
     assert torch.equal(sums[0], sums[1]) and int((sums[0] != 0).sum()) > 1900
+
+
+@pytest.mark.parametrize("n_leaves,read_len,variant", [
+    (6500, 150, 0),    # N = 12 999: three accumulator sets per SM, teams of 2 warps
+    (10000, 150, 0),   # N = 19 999 (C5's tree): two sets, teams of 4
+    (10000, 150, 1),   # the same with one warp per query
+    (20000, 150, 0),   # N = 39 999: one set, a team of 8
+    (10000, 400, 0),   # 16-bit hit counts: one set, a team of 8
+])
+def test_large_trees_sweep_in_teams(n_leaves, read_len, variant):
+    """Several warps sweep one query's accumulators (place_kernel.cuh "teams"): same bits as the reference,
+    including ambiguous windows and queries without hits."""
+    flat = synth.make_db(0, 8, n_leaves, 0.6, 40.0, seed=2000 + n_leaves)
+    n = 1500 if read_len <= 200 else 400
+    data, off = synth.make_reads(0, n, read_len, seed=78, amb_rate=0.002)
+    p = Placer(Database(flat), variant=variant)
+    got = p.place_packed(data, off)
+    oracle, kind = best_oracle(flat)
+    want = oracle.place_packed(data, off, threads=4)
+    helpers.assert_same_placements(got, want, what="%s N=%d" % (kind, 2 * n_leaves - 1))
+    valid = np.arange(7)[None, :] < want["n_place"][:, None]
+    assert np.array_equal(got["score"][valid], want["score"][valid])
+    # a second call reuses the accumulators the teams left behind
+    again = p.place_packed(data, off)
+    for name in ("n_place", "branch", "score", "lwr", "count"):
+        assert np.array_equal(again[name], got[name]), name
