@@ -210,3 +210,19 @@ def test_two_gpus_exchange(built, tmp_path, transport):
         assert_close_placements({k: part[k] for k in dbshard.RESULT_FIELDS}, piece, what="rank %d" % rank)
         for k in dbshard.RESULT_FIELDS:  # the transport does not change a bit: same sums in the same shard order
             assert np.array_equal(part[k], local[k][first:last]), k
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n", [0, 1, 2, 5])
+def test_tiny_and_empty_batches(built, n):
+    """fewer queries than shards / owners, and no queries at all"""
+    flat = synth.make_db(0, 8, 300, 0.6, 12.0, seed=21)
+    data, off = synth.make_reads(0, max(n, 1), 150, seed=5)
+    if n == 0:
+        data, off = data[:0], off[:1]
+    sp = dbshard.LocalShardedPlacer(flat, 3)
+    got = sp.place_packed(data, off)
+    assert got["n_place"].shape == (n,) and sp.unsupported == 0
+    if n:
+        want = _oracle(flat).place_packed(data, off)
+        assert_close_placements(got, want, what="n=%d" % n)
