@@ -187,6 +187,9 @@ static void build_db(const epk_db_desc& d, const epk_load_filter* filter, int de
     upload(entries.get(), d.entries, n_total * 8, stream);
 
     const unsigned T = 256;
+    // large tree (at most four accumulator sets of the placement kernel fit an SM): lists sorted by branch
+    // behind range headers, for the range teams of place_kernel.cuh
+    const bool with_ranges = 5 * epk::warp_smem_bytes(d.n_nodes, 1) + epk::CTA_SMEM_FIXED > 232448;
     device_buffer<uint64_t> new_len(n_keys), padded_len(n_keys), new_off(n_keys);
     uint64_t n_padded = 0;
     if (n_keys)
@@ -229,8 +232,13 @@ static void build_db(const epk_db_desc& d, const epk_load_filter* filter, int de
         }
         // ---- per-entry omega threshold, packed layout ----
         surviving_lengths_kernel<<<blocks_for(n_keys * 32, T), T, 0, stream>>>(
-            offsets.get(), entries.get(), keep.get(), n_keys, min_score, use_min_score, new_len.get(), padded_len.get());
+            offsets.get(), entries.get(), keep.get(), n_keys, min_score, use_min_score, new_len.get(), padded_len.get(),
+            with_ranges ? RANGE_HEADER_ENTRIES : 0u);
         n_padded = exclusive_scan(padded_len.get(), new_off.get(), n_keys, stream);
+        if (with_ranges)
+        {
+            add_header_room_kernel<<<blocks_for(n_keys, T), T, 0, stream>>>(new_off.get(), new_len.get(), n_keys);
+        }
     }
     db.postings.resize(std::max<uint64_t>(n_padded, 2));
     EPK_CUDA(cudaMemsetAsync(db.postings.get(), 0, 16, stream));
@@ -249,6 +257,22 @@ static void build_db(const epk_db_desc& d, const epk_load_filter* filter, int de
     EPK_CUDA(cudaStreamSynchronize(stream));
     EPK_CUDA(cudaGetLastError());
     entries.release();
+    if (with_ranges && n_keys)
+    {
+        const uint32_t np = epk::padded_nodes(d.n_nodes);
+        device_buffer<uint2> sorted(db.postings.size());
+        EPK_CUDA(cudaMemsetAsync(sorted.get(), 0, 16, stream));
+        unsigned warps = 8;
+        while (warps > 1 && static_cast<size_t>(warps) * 2 * (np / 32) * 4 > 96 * 1024) { warps >>= 1; }
+        const size_t smem = static_cast<size_t>(warps) * 2 * (np / 32) * 4;
+        if (smem > 200 * 1024) { throw error(EPK_E_UNSUPPORTED, "tree too large"); }
+        EPK_CUDA(cudaFuncSetAttribute(sort_lists_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+        sort_lists_kernel<<<1184, warps * 32, smem, stream>>>(db.postings.get(), sorted.get(), new_len.get(), new_off.get(),
+                                                             n_keys, d.n_nodes, np);
+        EPK_CUDA(cudaStreamSynchronize(stream));
+        EPK_CUDA(cudaGetLastError());
+        db.postings = std::move(sorted);
+    }
 
     // ---- key table ----
     device_db& dd = db.d;
@@ -333,6 +357,7 @@ static void build_db(const epk_db_desc& d, const epk_load_filter* filter, int de
     dd.bits = bits;
     dd.key_mask = key_bits >= 32 ? 0xFFFFFFFFu : ((1u << key_bits) - 1u);
     dd.n_nodes = d.n_nodes;
+    dd.range_headers = with_ranges ? 1u : 0u;
     dd.alphabet = d.alphabet;
     dd.threshold = score_threshold(d.alphabet, omega, d.kmer_size);
     dd.log_threshold = std::log10(dd.threshold); // place.cpp:88, float log10

@@ -66,7 +66,7 @@ __global__ void shard_keep_kernel(const uint32_t* keys, uint64_t n_keys, uint32_
 // One warp per list: surviving entry count (and its even-padded size).
 __global__ void surviving_lengths_kernel(const uint64_t* offsets, const uint2* entries, const uint8_t* keep,
                                          uint64_t n_keys, float min_score, bool use_min_score,
-                                         uint64_t* new_len, uint64_t* padded_len)
+                                         uint64_t* new_len, uint64_t* padded_len, uint32_t header_entries)
 {
     const uint64_t i = (blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x) >> 5;
     const uint32_t lane = threadIdx.x & 31u;
@@ -90,7 +90,7 @@ __global__ void surviving_lengths_kernel(const uint64_t* offsets, const uint2* e
     if (lane == 0)
     {
         new_len[i] = n;
-        padded_len[i] = (n + 1) & ~1ull;
+        padded_len[i] = n ? ((n + 1) & ~1ull) + header_entries : 0;
     }
 }
 
@@ -225,6 +225,91 @@ __global__ void validate_lists_kernel(const uint2* postings, const uint64_t* new
         {
             const uint32_t b = list[j].x;
             if (b < n_nodes) { bitmap[b >> 5] = 0; }
+        }
+        __syncwarp();
+    }
+}
+
+// ---- branch-sorted lists with range headers (large trees) -----------------------------------------
+//
+// For trees so large that few accumulator sets fit an SM, the placement kernel splits a query over the
+// warps of a team by BRANCH RANGE (place_kernel.cuh, "range teams"): member m of T applies, of every
+// posting list the query hits, only the postings whose branch lies in [m * Np / T, (m + 1) * Np / T).
+// For that a list is stored sorted by branch (a list names a branch once, so the order inside a list
+// does not change any sum) behind a 32-byte header h[0..7]: h[r] = number of postings with branch
+// < (r + 1) * Np / 8 (h[7] = the length), i.e. the split positions for T = 2, 4 or 8.
+constexpr uint32_t RANGE_HEADER_ENTRIES = 4; // 32 bytes, in units of postings; the header ends where the list begins
+constexpr uint32_t RANGE_PARTS = 8;
+
+__global__ void add_header_room_kernel(uint64_t* new_off, const uint64_t* new_len, uint64_t n_keys)
+{
+    const uint64_t i = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x;
+    if (i < n_keys && new_len[i] != 0) { new_off[i] += RANGE_HEADER_ENTRIES; }
+}
+
+// One warp per list: counting sort by branch through a bitmap of np bits (shared memory, per warp) and the
+// header. `in` and `out` have the same layout; np = n_nodes rounded up to 128. Lists with an invalid or
+// repeated branch are copied as they are (validate_lists_kernel reports them).
+__global__ void sort_lists_kernel(const uint2* in, uint2* out, const uint64_t* new_len, const uint64_t* new_off,
+                                  uint64_t n_keys, uint32_t n_nodes, uint32_t np)
+{
+    extern __shared__ uint32_t sort_smem[];
+    const uint32_t words = np / 32;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t warp = threadIdx.x >> 5;
+    const uint32_t warps_per_block = blockDim.x >> 5;
+    uint32_t* bitmap = sort_smem + static_cast<size_t>(warp) * 2 * words; // bits | exclusive prefix of the word popcounts
+    uint32_t* before = bitmap + words;
+    for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * warps_per_block + warp; i < n_keys;
+         i += static_cast<uint64_t>(gridDim.x) * warps_per_block)
+    {
+        const uint64_t n = new_len[i];
+        if (n == 0) { continue; }
+        const uint2* list = in + new_off[i];
+        uint2* dst = out + new_off[i];
+        for (uint32_t w = lane; w < words; w += 32) { bitmap[w] = 0; }
+        __syncwarp();
+        bool bad = false;
+        for (uint64_t j = lane; j < n; j += 32)
+        {
+            const uint32_t b = list[j].x;
+            if (b >= n_nodes) { bad = true; continue; }
+            const uint32_t bit = 1u << (b & 31u);
+            if (atomicOr(bitmap + (b >> 5), bit) & bit) { bad = true; }
+        }
+        bad = __any_sync(0xFFFFFFFFu, bad);
+        __syncwarp();
+        uint32_t running = 0;
+        for (uint32_t w0 = 0; w0 < words; w0 += 32)
+        {
+            const uint32_t w = w0 + lane;
+            const uint32_t c = w < words ? __popc(bitmap[w]) : 0u;
+            uint32_t incl = c;
+            for (int d = 1; d < 32; d <<= 1)
+            {
+                const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+                if (lane >= static_cast<uint32_t>(d)) { incl += o; }
+            }
+            if (w < words) { before[w] = running + incl - c; }
+            running += __shfl_sync(0xFFFFFFFFu, incl, 31);
+        }
+        __syncwarp();
+        for (uint64_t j = lane; j < ((n + 1) & ~1ull); j += 32)
+        {
+            const uint2 v = list[j]; // the pad entry of an odd list travels with it
+            uint64_t at = j;
+            if (!bad && j < n) { at = before[v.x >> 5] + __popc(bitmap[v.x >> 5] & ((1u << (v.x & 31u)) - 1u)); }
+            dst[at] = v;
+        }
+        if (lane < RANGE_PARTS)
+        {
+            uint32_t h = static_cast<uint32_t>(n);
+            if (lane + 1 < RANGE_PARTS && !bad)
+            {
+                const uint32_t bound = (lane + 1) * (np / RANGE_PARTS); // a multiple of 16
+                h = before[bound >> 5] + __popc(bitmap[bound >> 5] & ((1u << (bound & 31u)) - 1u));
+            }
+            reinterpret_cast<uint32_t*>(dst - RANGE_HEADER_ENTRIES)[lane] = h;
         }
         __syncwarp();
     }

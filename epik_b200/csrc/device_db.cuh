@@ -43,6 +43,8 @@ struct device_db
     float log_threshold;     // std::log10 of it, place.cpp:88
     float score_lo;          // smallest / largest score of the loaded postings (0 when there are none)
     float score_hi;
+    uint32_t range_headers;  // 1: lists are sorted by branch and preceded by a 32-byte header of split positions
+                             // (db_build.cuh "branch-sorted lists with range headers"); large trees only
     uint32_t fast_ok;        // 1 when every score is finite, <= 0, and 0 or >= 1e-20 in magnitude:
                              // the short arithmetic forms of the sweep then hold (place_kernel.cuh)
 };
@@ -95,6 +97,28 @@ __device__ __forceinline__ uint64_t db_search_from(const device_db& db, uint32_t
         s = __ldg(db.hashed + h);
     }
 }
+
+// ---- shapes of the placement kernel that the database build also needs ---------------------------------
+constexpr int WPL = 8;                 // consecutive windows per lane per chunk
+constexpr int CHUNK = 32 * WPL;        // windows staged per pass
+constexpr int CODE_BYTES = CHUNK + 32; // letter codes of one pass (k - 1 <= 31 extra letters)
+constexpr int SEG_CAP = 256;           // segment descriptors buffered per warp
+constexpr int SEG_LEN = 64;            // postings per segment: one 128-bit load per lane
+constexpr int SEG_PAD = 8;             // zero descriptors after the last one (= segments in flight)
+constexpr int SWEEP_STEP = 128;        // branches per warp and run of the sweep (4 consecutive ones per lane)
+
+__host__ __device__ inline uint32_t padded_nodes(uint32_t n_nodes)
+{
+    return (n_nodes + SWEEP_STEP - 1) / SWEEP_STEP * SWEEP_STEP;
+}
+
+// bytes of shared memory one warp needs for a tree of n_nodes and counts of count_bytes
+__host__ __device__ inline size_t warp_smem_bytes(uint32_t n_nodes, uint32_t count_bytes)
+{
+    const size_t np = padded_nodes(n_nodes);
+    return np * 4 + np * count_bytes + np / 8 + (SEG_CAP + SEG_PAD) * 8 + CODE_BYTES;
+}
+constexpr size_t CTA_SMEM_FIXED = 1024; // letter table
 
 // Letter tables: the 2-bit / 5-bit codes of i2l (absent submodule; SURVEY.md Appendix B, the same
 // tables the oracle shim states with switch statements). Filled by make_letter_table on the host.

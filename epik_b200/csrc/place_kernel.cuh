@@ -34,15 +34,8 @@
 
 namespace epk
 {
-constexpr int WPL = 8;                 // consecutive windows per lane per chunk
-constexpr int CHUNK = 32 * WPL;        // windows staged per pass
-constexpr int CODE_BYTES = CHUNK + 32; // letter codes of one pass (k - 1 <= 31 extra letters)
-constexpr int SEG_CAP = 256;           // segment descriptors buffered per warp
-constexpr int SEG_LEN = 64;            // postings per segment: one 128-bit load per lane
-constexpr int SEG_PAD = 8;             // zero descriptors after the last one (= segments in flight)
 constexpr int CAND_CAP = 128;          // top-k candidates buffered per warp (aliases the segments)
 constexpr int MAX_WARPS_PER_CTA = 8;
-constexpr int SWEEP_STEP = 128;        // branches per warp and run of the sweep (4 consecutive ones per lane)
 constexpr int MAX_OWNERS = 8;          // ranks of a database-sharded group (one NVSwitch domain)
 constexpr uint32_t NO_BRANCH = 0xFFFFFFFFu;
 constexpr uint32_t FULL = 0xFFFFFFFFu;
@@ -89,18 +82,6 @@ struct place_params
     uint32_t team;                       // warps per accumulator set (TEAM launches)
 };
 
-__host__ __device__ inline uint32_t padded_nodes(uint32_t n_nodes)
-{
-    return (n_nodes + SWEEP_STEP - 1) / SWEEP_STEP * SWEEP_STEP;
-}
-
-// bytes of shared memory one warp needs for a tree of n_nodes and counts of count_bytes
-__host__ __device__ inline size_t warp_smem_bytes(uint32_t n_nodes, uint32_t count_bytes)
-{
-    const size_t np = padded_nodes(n_nodes);
-    return np * 4 + np * count_bytes + np / 8 + (SEG_CAP + SEG_PAD) * 8 + CODE_BYTES;
-}
-constexpr size_t CTA_SMEM_FIXED = 1024; // letter table
 
 // Number of queries of each class (sequences shorter than k - 1 letters count for class 0, which
 // reports them). Classes in unsupported_mask have no launch: their rows get n_place = 0 here.
