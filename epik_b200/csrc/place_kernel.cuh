@@ -220,7 +220,8 @@ __device__ __forceinline__ uint32_t warp_inclusive_sum(uint32_t v, uint32_t lane
 struct seg_regs
 {
     uint32_t b0, s0, b1, s1; // two postings: (branch, score bits) x 2
-    uint32_t cnt;
+    uint32_t cnt;            // postings of the segment, counted from the (even) posting the descriptor names
+    uint32_t start;          // 1: the first of them belongs to the neighbouring branch range and is skipped
 };
 
 __device__ __forceinline__ void load_segment(const unsigned char* lane_base, uint32_t segs_shared, uint32_t idx,
@@ -230,8 +231,9 @@ __device__ __forceinline__ void load_segment(const unsigned char* lane_base, uin
     extern __shared__ __align__(16) unsigned char smem_base[];
     const uint32_t smem0 = static_cast<uint32_t>(__cvta_generic_to_shared(smem_base));
     const uint2 d = *reinterpret_cast<const uint2*>(smem_base + (segs_shared + idx * 8u - smem0));
-    r.cnt = d.y;
-    if (lane2 < d.y)
+    r.cnt = d.y & 0x7FFFFFFFu;
+    r.start = d.y >> 31;
+    if (lane2 < r.cnt)
     {
         const uint4 v = __ldg(reinterpret_cast<const uint4*>(lane_base + 16ull * d.x));
         r.b0 = v.x; r.s0 = v.y; r.b1 = v.z; r.s1 = v.w;
@@ -241,14 +243,16 @@ __device__ __forceinline__ void load_segment(const unsigned char* lane_base, uin
     asm volatile(
         "{\n\t"
         ".reg .pred p;\n\t"
-        ".reg .b32 pair;\n\t"
+        ".reg .b32 pair, y;\n\t"
         ".reg .b64 addr;\n\t"
-        "ld.shared.v2.b32 {pair, %4}, [%5];\n\t"
-        "setp.lt.u32 p, %7, %4;\n\t"
-        "mad.wide.u32 addr, pair, 16, %6;\n\t"
+        "ld.shared.v2.b32 {pair, y}, [%6];\n\t"
+        "and.b32 %4, y, 0x7FFFFFFF;\n\t"
+        "shr.u32 %5, y, 31;\n\t"
+        "setp.lt.u32 p, %8, %4;\n\t"
+        "mad.wide.u32 addr, pair, 16, %7;\n\t"
         "@p ld.global.nc.v4.b32 {%0, %1, %2, %3}, [addr];\n\t"
         "}"
-        : "+r"(r.b0), "+r"(r.s0), "+r"(r.b1), "+r"(r.s1), "=&r"(r.cnt)
+        : "+r"(r.b0), "+r"(r.s0), "+r"(r.b1), "+r"(r.s1), "=&r"(r.cnt), "=&r"(r.start)
         : "r"(segs_shared + idx * 8u), "l"(lane_base), "r"(lane2)
         : "memory");
 }
@@ -273,7 +277,8 @@ struct acc_ref
             ".reg .pred p0, p1;\n\t"                                                                       \
             ".reg .b32 a0, a1, d0, d1, c0, c1;\n\t"                                                        \
             ".reg .f32 f0, f1;\n\t"                                                                        \
-            "setp.lt.u32 p0, %5, %4;\n\t"                                                                  \
+            "setp.ge.u32 p0, %5, %10;\n\t"                                                                 \
+            "setp.lt.and.u32 p0, %5, %4, p0;\n\t"                                                          \
             "setp.lt.u32 p1, %6, %4;\n\t"                                                                  \
             "mad.lo.u32 a0, %0, 4, %7;\n\t"                                                                \
             "mad.lo.u32 a1, %2, 4, %7;\n\t"                                                                \
@@ -295,7 +300,7 @@ struct acc_ref
             :                                                                                              \
             : "r"(r.b0), "f"(__uint_as_float(r.s0)), "r"(r.b1), "f"(__uint_as_float(r.s1)), "r"(r.cnt),    \
               "r"(lane2), "r"(lane2 + 1u), "r"(acc.s_shared), "r"(acc.c_shared),                           \
-              "n"(static_cast<int>(sizeof(CT)))                                                            \
+              "n"(static_cast<int>(sizeof(CT))), "r"(r.start)                                              \
             : "memory");                                                                                   \
         __syncwarp(); /* the next segment may name the same branches from other lanes */                  \
     }
@@ -313,6 +318,7 @@ EPK_APPLY_SEGMENT(uint32_t, "u32", "u32")
 __device__ __forceinline__ void sink_segment(uint32_t& sink, uint32_t lane2, const seg_regs& r)
 {
     if (lane2 < r.cnt) { sink ^= r.b0 ^ r.s0 ^ r.b1 ^ r.s1; }
+    (void)r.start;
 }
 
 template<int U, class CT, bool SINK = false>
@@ -326,8 +332,8 @@ __device__ EPK_GATHER_INLINE void gather_segments(const uint2* __restrict__ post
 #pragma unroll
     for (int u = 0; u < U; ++u)
     {
-        a[u] = seg_regs{ 0, 0, 0, 0, 0 };
-        b[u] = seg_regs{ 0, 0, 0, 0, 0 };
+        a[u] = seg_regs{ 0, 0, 0, 0, 0, 0 };
+        b[u] = seg_regs{ 0, 0, 0, 0, 0, 0 };
     }
 #pragma unroll
     for (int u = 0; u < U; ++u) { load_segment(lane_base, segs_shared, u, lane2, a[u]); }
@@ -369,7 +375,7 @@ __device__ __noinline__ void apply_list(const uint2* __restrict__ postings, acc_
     const uint32_t lane2 = 2u * lane;
     for (uint32_t pos = 0; pos < len; pos += SEG_LEN)
     {
-        seg_regs r{ 0, 0, 0, 0, min(len - pos, static_cast<uint32_t>(SEG_LEN)) };
+        seg_regs r{ 0, 0, 0, 0, min(len - pos, static_cast<uint32_t>(SEG_LEN)), 0 };
         if (lane2 < r.cnt)
         {
             const uint4 v = __ldg(reinterpret_cast<const uint4*>(postings + off + pos) + lane);
@@ -916,10 +922,18 @@ __device__ __noinline__ sweep_result team_sweep(const device_db& db, float* S, C
                                                     member * SWEEP_STEP, team * SWEEP_STEP);
 }
 
-template<class CT>
+constexpr uint32_t TEAM_CMD_GATHER = 0x80000000u; // mailbox.pad: gather the low bits' worth of published hits, else sweep
+
+template<int U, class CT>
+__device__ __noinline__ void range_gather(const device_db& db, acc_ref acc, const uint64_t* hits, uint32_t n_hits, uint2* my_segs,
+                                          uint32_t member, uint32_t team, uint32_t lane);
+
+template<int U, class CT>
 __device__ __forceinline__ void team_helper_loop(const place_params& p, float* S, CT* C, uint32_t np, uint32_t lane,
-                                                 unsigned char* team_area, uint32_t set, uint32_t member, uint32_t team)
+                                                 unsigned char* team_area, const uint64_t* hits, uint32_t set,
+                                                 uint32_t member, uint32_t team)
 {
+    const acc_ref acc{ static_cast<uint32_t>(__cvta_generic_to_shared(S)), static_cast<uint32_t>(__cvta_generic_to_shared(C)) };
     const team_mailbox* box = reinterpret_cast<const team_mailbox*>(team_area);
     team_result* results = reinterpret_cast<team_result*>(team_area + sizeof(team_mailbox));
     uint32_t* member_base = reinterpret_cast<uint32_t*>(team_area + sizeof(team_mailbox) + team * sizeof(team_result))
@@ -927,8 +941,14 @@ __device__ __forceinline__ void team_helper_loop(const place_params& p, float* S
     while (true)
     {
         team_sync(set, team); // A
-        const uint32_t q = box->q, nw32 = box->nw32, gathered = box->gathered;
+        const uint32_t q = box->q, nw32 = box->nw32, gathered = box->gathered, cmd = box->pad;
         if (q == NO_BRANCH) { break; }
+        if (cmd & TEAM_CMD_GATHER)
+        {
+            range_gather<U, CT>(p.db, acc, hits, cmd & ~TEAM_CMD_GATHER, reinterpret_cast<uint2*>(member_base), member, team, lane);
+            team_sync(set, team); // G: this chunk's postings are in the accumulators
+            continue;
+        }
         const sweep_result sw = team_sweep<CT>(p.db, S, C, np, nw32, gathered, p.keep_at_most, lane, member_base, member, team);
         if (lane == 0)
         {
@@ -973,6 +993,82 @@ __device__ __forceinline__ void finish_query_leader(const place_params& p, float
         sw.n_keep = select_best(mine.key, mine.branch, mine.count, sw.n_keep + r.n_keep, K, lane, sw.key, sw.branch, sw.count);
     }
     emit_query(p, sw, nw32, q, lane);
+}
+
+// ---- range teams: every member gathers its own branch range ------------------------------------------
+//
+// With branch-sorted lists behind range headers (db_build.cuh) the gather splits too: the leader
+// publishes the packed slots of a chunk's hit windows, in window order, and member m of T turns every hit
+// into descriptors of ITS sub-list - the postings with branch in [m * np / T, (m + 1) * np / T), found
+// through the list's header - and applies them to the shared accumulators. The ranges are disjoint, so
+// members never touch the same S[b], and each member walks the hits in window order: every S[b] still
+// receives the additions of place.cpp:358-367 in the reference's order. A sub-list may start on an odd
+// posting: its first descriptor then carries the skip flag (bit 31 of the count word).
+constexpr uint32_t RANGE_DESC_CAP = TEAM_MEMBER_WORDS / 2 - SEG_PAD; // descriptors a member buffers (aliases its candidates)
+constexpr uint32_t RANGE_HEADER_POSTINGS = 4;                        // = RANGE_HEADER_ENTRIES of db_build.cuh
+
+template<int U, class CT>
+__device__ __noinline__ void range_gather(const device_db& db, acc_ref acc, const uint64_t* hits, uint32_t n_hits,
+                                          uint2* my_segs, uint32_t member, uint32_t team, uint32_t lane)
+{
+    const uint32_t segs_shared = static_cast<uint32_t>(__cvta_generic_to_shared(my_segs));
+    const uint32_t part_lo = member * (8u / team); // header entries are eighths of the padded branch range
+    const uint32_t part_hi = (member + 1u) * (8u / team);
+    uint32_t n_desc = 0;
+    for (uint32_t h0 = 0; h0 < n_hits; h0 += 32)
+    {
+        uint32_t pair0 = 0, count = 0, first_skip = 0;
+        if (h0 + lane < n_hits)
+        {
+            const uint64_t slot = hits[h0 + lane];
+            const uint64_t off = slot >> LEN_BITS;
+            const uint32_t* header = reinterpret_cast<const uint32_t*>(db.postings + (off - RANGE_HEADER_POSTINGS));
+            const uint32_t lo = part_lo == 0 ? 0u : __ldg(header + part_lo - 1);
+            const uint32_t hi = __ldg(header + part_hi - 1);
+            if (hi > lo)
+            {
+                first_skip = lo & 1u;
+                pair0 = static_cast<uint32_t>((off + (lo - first_skip)) >> 1);
+                count = hi - (lo - first_skip);
+            }
+        }
+        const uint32_t my_total = (count + SEG_LEN - 1) / SEG_LEN;
+        uint32_t emitted = 0; // of my_total
+        while (true)
+        {
+            const uint32_t remaining = my_total - emitted;
+            const uint32_t incl = warp_inclusive_sum(remaining, lane);
+            const uint32_t total = __shfl_sync(FULL, incl, 31);
+            if (total == 0) { break; }
+            const uint32_t space = RANGE_DESC_CAP - n_desc;
+            const uint32_t excl = incl - remaining;
+            const uint32_t can = excl >= space ? 0u : min(remaining, space - excl);
+            for (uint32_t i = 0; i < can; ++i)
+            {
+                const uint32_t sidx = emitted + i;
+                const uint32_t pos = sidx * SEG_LEN;
+                my_segs[n_desc + excl + i] = make_uint2(pair0 + pos / 2, min(count - pos, static_cast<uint32_t>(SEG_LEN))
+                                                                             | ((sidx == 0 && first_skip) ? 0x80000000u : 0u));
+            }
+            emitted += can;
+            n_desc += min(total, space);
+            if (total >= space)
+            {
+                if (lane < SEG_PAD) { my_segs[n_desc + lane] = make_uint2(0, 0); }
+                __syncwarp();
+                gather_segments<U, CT>(db.postings, acc, segs_shared, n_desc, lane);
+                n_desc = 0;
+                __syncwarp();
+            }
+        }
+    }
+    if (n_desc)
+    {
+        if (lane < SEG_PAD) { my_segs[n_desc + lane] = make_uint2(0, 0); }
+        __syncwarp();
+        gather_segments<U, CT>(db.postings, acc, segs_shared, n_desc, lane);
+    }
+    __syncwarp();
 }
 
 // ---- partial rows (database-sharded mode) ---------------------------------------------------------
@@ -1079,7 +1175,7 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
     __syncthreads();
     if (TEAM && member != 0)
     {
-        team_helper_loop<CT>(p, S, C, np, lane, team_area, warp, member, team);
+        team_helper_loop<U, CT>(p, S, C, np, lane, team_area, reinterpret_cast<const uint64_t*>(segs), warp, member, team);
         return;
     }
 
@@ -1221,6 +1317,31 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
                 my_segs += (l + SEG_LEN - 1) / SEG_LEN;
                 ctr_hits += l != 0;
                 ctr_entries += l;
+            }
+            if (TEAM && db.range_headers)
+            {
+                // range teams: publish the hits in window order, every member gathers its branch range of them
+                uint32_t my_hits = 0;
+#pragma unroll
+                for (int r = 0; r < WPL; ++r) { my_hits += (slot[r] & LEN_MASK) != 0; }
+                const uint32_t hits_incl = warp_inclusive_sum(my_hits, lane);
+                const uint32_t n_hits = __shfl_sync(FULL, hits_incl, 31);
+                if (n_hits == 0) { continue; }
+                uint64_t* hits = reinterpret_cast<uint64_t*>(segs);
+                uint32_t at = hits_incl - my_hits;
+#pragma unroll
+                for (int r = 0; r < WPL; ++r)
+                {
+                    if (slot[r] & LEN_MASK) { hits[at++] = slot[r]; }
+                }
+                team_mailbox* box = reinterpret_cast<team_mailbox*>(team_area);
+                if (lane == 0) { *box = team_mailbox{ q, 0u, 0u, TEAM_CMD_GATHER | n_hits }; }
+                __syncwarp();
+                team_sync(warp, team); // command: gather
+                uint2* my_desc = reinterpret_cast<uint2*>(team_area + sizeof(team_mailbox) + team * sizeof(team_result));
+                range_gather<U, CT>(db, acc, hits, n_hits, my_desc, 0u, team, lane);
+                team_sync(warp, team); // G
+                continue;
             }
             const uint32_t incl = warp_inclusive_sum(my_segs, lane);
             const uint32_t total = __shfl_sync(FULL, incl, 31);
