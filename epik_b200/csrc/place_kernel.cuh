@@ -922,7 +922,15 @@ __device__ __noinline__ sweep_result team_sweep(const device_db& db, float* S, C
                                                     member * SWEEP_STEP, team * SWEEP_STEP);
 }
 
-constexpr uint32_t TEAM_CMD_GATHER = 0x80000000u; // mailbox.pad: gather the low bits' worth of published hits, else sweep
+// mailbox.pad: 0 = sweep; GATHER | n_hits = gather the published hits (range teams); DUMP = write this member's part of
+// the query's partial row (database-sharded mode; nw32 carries the row flags)
+constexpr uint32_t TEAM_CMD_GATHER = 0x80000000u;
+constexpr uint32_t TEAM_CMD_DUMP = 0x40000000u;
+
+template<class CT>
+__device__ __forceinline__ void dump_partial_row(const place_params& p, float* S, CT* C, uint32_t np, uint32_t q,
+                                                 uint32_t flags, uint32_t gathered, uint32_t lane, uint32_t part = 0,
+                                                 uint32_t parts = 1);
 
 template<int U, class CT>
 __device__ __noinline__ void range_gather(const device_db& db, acc_ref acc, const uint64_t* hits, uint32_t n_hits, uint2* my_segs,
@@ -947,6 +955,12 @@ __device__ __forceinline__ void team_helper_loop(const place_params& p, float* S
         {
             range_gather<U, CT>(p.db, acc, hits, cmd & ~TEAM_CMD_GATHER, reinterpret_cast<uint2*>(member_base), member, team, lane);
             team_sync(set, team); // G: this chunk's postings are in the accumulators
+            continue;
+        }
+        if (cmd & TEAM_CMD_DUMP)
+        {
+            dump_partial_row<CT>(p, S, C, np, q, nw32, gathered, lane, member, team);
+            team_sync(set, team); // the row is out, the accumulators are clear
             continue;
         }
         const sweep_result sw = team_sweep<CT>(p.db, S, C, np, nw32, gathered, p.keep_at_most, lane, member_base, member, team);
@@ -1095,17 +1109,19 @@ __device__ __forceinline__ void store_counts4_u16(unsigned char* at, const uint3
 }
 
 // S, C of query q -> its row at the owner; leaves both arrays zeroed
+// (a team dumps a row together: member `part` of `parts` takes every parts-th 128-branch step)
 template<class CT>
 __device__ __forceinline__ void dump_partial_row(const place_params& p, float* S, CT* C, uint32_t np, uint32_t q,
-                                                 uint32_t flags, uint32_t gathered, uint32_t lane)
+                                                 uint32_t flags, uint32_t gathered, uint32_t lane, uint32_t part,
+                                                 uint32_t parts)
 {
     uint32_t g = 0;
     while (g + 1 < p.n_owners && q >= p.owner_first[g + 1]) { ++g; }
     unsigned char* row = p.rows_out[g] + static_cast<uint64_t>(q - p.owner_first[g]) * partial_row_bytes(p.db.n_nodes);
-    if (lane == 0) { *reinterpret_cast<uint4*>(row) = make_uint4(flags, gathered, 0u, 0u); }
+    if (lane == 0 && part == 0) { *reinterpret_cast<uint4*>(row) = make_uint4(flags, gathered, 0u, 0u); }
     unsigned char* s_out = row + ROW_HEADER_BYTES;
     unsigned char* c_out = s_out + 4ull * np;
-    for (uint32_t j = 4u * lane; j < np; j += SWEEP_STEP)
+    for (uint32_t j = 4u * lane + part * SWEEP_STEP; j < np; j += parts * SWEEP_STEP)
     {
         const float4 s4 = *reinterpret_cast<const float4*>(S + j);
         uint32_t c[4];
@@ -1133,7 +1149,7 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
 {
     constexpr bool PARTIAL = MODE == MODE_PARTIAL;
     constexpr bool GATHER_ONLY = MODE == MODE_GATHER_ONLY;
-    static_assert(!TEAM || MODE == MODE_FULL, "teams only exist where there is a sweep");
+    static_assert(!TEAM || MODE != MODE_GATHER_ONLY, "the ceiling kernel is the one-warp gather");
     extern __shared__ __align__(16) unsigned char smem[];
     if (p.class_reads && p.class_reads[p.cls] == 0) { return; } // no query of this class in the batch
     const uint32_t lane = threadIdx.x & 31u;
@@ -1416,7 +1432,16 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
         if (PARTIAL)
         {
             const uint32_t gathered_here = __reduce_add_sync(FULL, static_cast<uint32_t>(min(static_cast<unsigned long long>(ctr_entries - entries_before), 0xFFFFFFull)));
-            dump_partial_row<CT>(p, S, C, np, q, has_ambiguous ? ROW_FLAG_AMBIGUOUS : 0u, gathered_here, lane);
+            const uint32_t row_flags = has_ambiguous ? ROW_FLAG_AMBIGUOUS : 0u;
+            if (TEAM)
+            {
+                if (lane == 0) { *reinterpret_cast<team_mailbox*>(team_area) = team_mailbox{ q, row_flags, gathered_here, TEAM_CMD_DUMP }; }
+                __syncwarp();
+                team_sync(warp, team); // command: dump
+                dump_partial_row<CT>(p, S, C, np, q, row_flags, gathered_here, lane, 0u, team);
+                team_sync(warp, team);
+            }
+            else { dump_partial_row<CT>(p, S, C, np, q, row_flags, gathered_here, lane); }
             continue;
         }
         if (has_ambiguous)

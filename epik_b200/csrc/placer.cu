@@ -137,6 +137,14 @@ namespace
     // the launch of database-sharded mode that leaves partial rows (classes 0 and 1 only)
     kernel_fn pick_partial_kernel(const epk_placer& pl, int cls)
     {
+        if (pl.team[cls] > 1)
+        {
+            if (pl.db->table_kind == TABLE_DIRECT)
+            {
+                return cls == 0 ? place_kernel<TABLE_DIRECT, 8, uint8_t, MODE_PARTIAL, true> : place_kernel<TABLE_DIRECT, 8, uint16_t, MODE_PARTIAL, true>;
+            }
+            return cls == 0 ? place_kernel<TABLE_HASH, 8, uint8_t, MODE_PARTIAL, true> : place_kernel<TABLE_HASH, 8, uint16_t, MODE_PARTIAL, true>;
+        }
         if (pl.db->table_kind == TABLE_DIRECT)
         {
             return cls == 0 ? place_kernel<TABLE_DIRECT, 8, uint8_t, MODE_PARTIAL> : place_kernel<TABLE_DIRECT, 8, uint16_t, MODE_PARTIAL>;
@@ -657,8 +665,9 @@ extern "C" epk_status epk_place_partial_device(epk_placer* pl, const char* d_seq
                 p.cls = static_cast<uint32_t>(c);
                 p.counters = counters + c * CTR_COUNT;
                 const unsigned grid = static_cast<unsigned>(
-                    std::min<uint64_t>(pl->n_sms, (static_cast<uint64_t>(n) + pl->warps_per_cta[c] - 1) / pl->warps_per_cta[c]));
-                pick_partial_kernel(*pl, c)<<<grid, pl->warps_per_cta[c] * 32, pl->smem_bytes[c], s>>>(p);
+                    std::min<uint64_t>(pl->n_sms, (static_cast<uint64_t>(n) + pl->sets_fused[c] - 1) / pl->sets_fused[c]));
+                p.team = pl->team[c];
+                pick_partial_kernel(*pl, c)<<<grid, pl->sets_fused[c] * pl->team[c] * 32, pl->smem_fused[c], s>>>(p);
                 EPK_CUDA(cudaGetLastError());
                 ++pl->n_launches;
             }

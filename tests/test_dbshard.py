@@ -138,7 +138,9 @@ def test_one_shard_equals_the_fused_kernel_bit_for_bit(built):
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("alphabet,k,leaves,p_occ,m,length,shards", [(0, 8, 300, 0.6, 12.0, 150, 3), (0, 10, 2500, 0.6, 32.0, 150, 2),
-                                                                  (1, 6, 200, 0.05, 8.0, 100, 4), (0, 8, 100, 0.5, 6.0, 700, 2)])
+                                                                  (1, 6, 200, 0.05, 8.0, 100, 4), (0, 8, 100, 0.5, 6.0, 700, 2),
+                                                                  (0, 8, 10000, 0.6, 40.0, 150, 2),   # N = 19 999: the partial launch runs in range teams
+                                                                  (0, 8, 10000, 0.6, 40.0, 400, 3)])  # ... with 16-bit counts, a team of 8
 def test_sharded_database_matches_the_oracle(built, alphabet, k, leaves, p_occ, m, length, shards):
     flat = synth.make_db(alphabet, k, leaves, p_occ, m, seed=31)
     data, off = synth.make_reads(alphabet, 2000, length, seed=32)
