@@ -224,35 +224,41 @@ struct seg_regs
     uint32_t start;          // 1: the first of them belongs to the neighbouring branch range and is skipped
 };
 
+template<bool RANGE>
 __device__ __forceinline__ void load_segment(const unsigned char* lane_base, uint32_t segs_shared, uint32_t idx,
                                              uint32_t lane2, seg_regs& r)
 {
-#ifdef EPK_CXX_LOAD
-    extern __shared__ __align__(16) unsigned char smem_base[];
-    const uint32_t smem0 = static_cast<uint32_t>(__cvta_generic_to_shared(smem_base));
-    const uint2 d = *reinterpret_cast<const uint2*>(smem_base + (segs_shared + idx * 8u - smem0));
-    r.cnt = d.y & 0x7FFFFFFFu;
-    r.start = d.y >> 31;
-    if (lane2 < r.cnt)
+    if (RANGE)
     {
-        const uint4 v = __ldg(reinterpret_cast<const uint4*>(lane_base + 16ull * d.x));
-        r.b0 = v.x; r.s0 = v.y; r.b1 = v.z; r.s1 = v.w;
+        // descriptors of a range team: bit 31 of the count word = skip the first posting
+        asm volatile(
+            "{\n\t"
+            ".reg .pred p;\n\t"
+            ".reg .b32 pair, y;\n\t"
+            ".reg .b64 addr;\n\t"
+            "ld.shared.v2.b32 {pair, y}, [%6];\n\t"
+            "and.b32 %4, y, 0x7FFFFFFF;\n\t"
+            "shr.u32 %5, y, 31;\n\t"
+            "setp.lt.u32 p, %8, %4;\n\t"
+            "mad.wide.u32 addr, pair, 16, %7;\n\t"
+            "@p ld.global.nc.v4.b32 {%0, %1, %2, %3}, [addr];\n\t"
+            "}"
+            : "+r"(r.b0), "+r"(r.s0), "+r"(r.b1), "+r"(r.s1), "=&r"(r.cnt), "=&r"(r.start)
+            : "r"(segs_shared + idx * 8u), "l"(lane_base), "r"(lane2)
+            : "memory");
+        return;
     }
-    return;
-#endif
     asm volatile(
         "{\n\t"
         ".reg .pred p;\n\t"
-        ".reg .b32 pair, y;\n\t"
+        ".reg .b32 pair;\n\t"
         ".reg .b64 addr;\n\t"
-        "ld.shared.v2.b32 {pair, y}, [%6];\n\t"
-        "and.b32 %4, y, 0x7FFFFFFF;\n\t"
-        "shr.u32 %5, y, 31;\n\t"
-        "setp.lt.u32 p, %8, %4;\n\t"
-        "mad.wide.u32 addr, pair, 16, %7;\n\t"
+        "ld.shared.v2.b32 {pair, %4}, [%5];\n\t"
+        "setp.lt.u32 p, %7, %4;\n\t"
+        "mad.wide.u32 addr, pair, 16, %6;\n\t"
         "@p ld.global.nc.v4.b32 {%0, %1, %2, %3}, [addr];\n\t"
         "}"
-        : "+r"(r.b0), "+r"(r.s0), "+r"(r.b1), "+r"(r.s1), "=&r"(r.cnt), "=&r"(r.start)
+        : "+r"(r.b0), "+r"(r.s0), "+r"(r.b1), "+r"(r.s1), "=&r"(r.cnt)
         : "r"(segs_shared + idx * 8u), "l"(lane_base), "r"(lane2)
         : "memory");
 }
@@ -269,16 +275,15 @@ struct acc_ref
 // list are distinct, so the two read-modify-writes of a lane and those of different lanes are
 // independent. Lanes past the end of the segment hold 0 or an older, valid branch: they read it
 // and store nothing.
-#define EPK_APPLY_SEGMENT(CT, LD, ST)                                                                      \
-    __device__ __forceinline__ void apply_segment(const acc_ref& acc, uint32_t lane2, const seg_regs& r, CT) \
+#define EPK_APPLY_SEGMENT(NAME, CT, LD, ST, P0, EXTRA)                                                     \
+    __device__ __forceinline__ void NAME(const acc_ref& acc, uint32_t lane2, const seg_regs& r, CT)          \
     {                                                                                                      \
         asm volatile(                                                                                      \
             "{\n\t"                                                                                        \
             ".reg .pred p0, p1;\n\t"                                                                       \
             ".reg .b32 a0, a1, d0, d1, c0, c1;\n\t"                                                        \
             ".reg .f32 f0, f1;\n\t"                                                                        \
-            "setp.ge.u32 p0, %5, %10;\n\t"                                                                 \
-            "setp.lt.and.u32 p0, %5, %4, p0;\n\t"                                                          \
+            P0                                                                                             \
             "setp.lt.u32 p1, %6, %4;\n\t"                                                                  \
             "mad.lo.u32 a0, %0, 4, %7;\n\t"                                                                \
             "mad.lo.u32 a1, %2, 4, %7;\n\t"                                                                \
@@ -300,13 +305,20 @@ struct acc_ref
             :                                                                                              \
             : "r"(r.b0), "f"(__uint_as_float(r.s0)), "r"(r.b1), "f"(__uint_as_float(r.s1)), "r"(r.cnt),    \
               "r"(lane2), "r"(lane2 + 1u), "r"(acc.s_shared), "r"(acc.c_shared),                           \
-              "n"(static_cast<int>(sizeof(CT))), "r"(r.start)                                              \
+              "n"(static_cast<int>(sizeof(CT))) EXTRA                                                      \
             : "memory");                                                                                   \
         __syncwarp(); /* the next segment may name the same branches from other lanes */                  \
     }
-EPK_APPLY_SEGMENT(uint8_t, "u8", "u8")
-EPK_APPLY_SEGMENT(uint16_t, "u16", "u16")
-EPK_APPLY_SEGMENT(uint32_t, "u32", "u32")
+#define EPK_P0_PLAIN "setp.lt.u32 p0, %5, %4;\n\t"
+#define EPK_P0_RANGE "setp.ge.u32 p0, %5, %10;\n\tsetp.lt.and.u32 p0, %5, %4, p0;\n\t" /* lane2 in [start, cnt) */
+#define EPK_NO_EXTRA
+#define EPK_START_EXTRA , "r"(r.start)
+EPK_APPLY_SEGMENT(apply_segment, uint8_t, "u8", "u8", EPK_P0_PLAIN, EPK_NO_EXTRA)
+EPK_APPLY_SEGMENT(apply_segment, uint16_t, "u16", "u16", EPK_P0_PLAIN, EPK_NO_EXTRA)
+EPK_APPLY_SEGMENT(apply_segment, uint32_t, "u32", "u32", EPK_P0_PLAIN, EPK_NO_EXTRA)
+EPK_APPLY_SEGMENT(apply_segment_range, uint8_t, "u8", "u8", EPK_P0_RANGE, EPK_START_EXTRA)
+EPK_APPLY_SEGMENT(apply_segment_range, uint16_t, "u16", "u16", EPK_P0_RANGE, EPK_START_EXTRA)
+EPK_APPLY_SEGMENT(apply_segment_range, uint32_t, "u32", "u32", EPK_P0_RANGE, EPK_START_EXTRA)
 #undef EPK_APPLY_SEGMENT
 
 // Applies segs[0, n) in order; U segments are in flight while the previous U are applied.
@@ -321,7 +333,7 @@ __device__ __forceinline__ void sink_segment(uint32_t& sink, uint32_t lane2, con
     (void)r.start;
 }
 
-template<int U, class CT, bool SINK = false>
+template<int U, class CT, bool SINK = false, bool RANGE = false>
 __device__ EPK_GATHER_INLINE void gather_segments(const uint2* __restrict__ postings, acc_ref acc, uint32_t segs_shared,
                                              uint32_t n, uint32_t lane, uint32_t* sink_out = nullptr)
 {
@@ -336,31 +348,33 @@ __device__ EPK_GATHER_INLINE void gather_segments(const uint2* __restrict__ post
         b[u] = seg_regs{ 0, 0, 0, 0, 0, 0 };
     }
 #pragma unroll
-    for (int u = 0; u < U; ++u) { load_segment(lane_base, segs_shared, u, lane2, a[u]); }
+    for (int u = 0; u < U; ++u) { load_segment<RANGE>(lane_base, segs_shared, u, lane2, a[u]); }
     for (uint32_t first = 0; first < n; first += 2 * U)
     {
         const bool more_b = first + U < n;
         if (more_b)
         {
 #pragma unroll
-            for (int u = 0; u < U; ++u) { load_segment(lane_base, segs_shared, first + U + u, lane2, b[u]); }
+            for (int u = 0; u < U; ++u) { load_segment<RANGE>(lane_base, segs_shared, first + U + u, lane2, b[u]); }
         }
 #pragma unroll
         for (int u = 0; u < U; ++u)
         {
             if (SINK) { sink_segment(sink, lane2, a[u]); }
+            else if (RANGE) { apply_segment_range(acc, lane2, a[u], CT{}); }
             else { apply_segment(acc, lane2, a[u], CT{}); }
         }
         if (!more_b) { break; }
         if (first + 2 * U < n)
         {
 #pragma unroll
-            for (int u = 0; u < U; ++u) { load_segment(lane_base, segs_shared, first + 2 * U + u, lane2, a[u]); }
+            for (int u = 0; u < U; ++u) { load_segment<RANGE>(lane_base, segs_shared, first + 2 * U + u, lane2, a[u]); }
         }
 #pragma unroll
         for (int u = 0; u < U; ++u)
         {
             if (SINK) { sink_segment(sink, lane2, b[u]); }
+            else if (RANGE) { apply_segment_range(acc, lane2, b[u], CT{}); }
             else { apply_segment(acc, lane2, b[u], CT{}); }
         }
     }
@@ -1070,7 +1084,7 @@ __device__ __noinline__ void range_gather(const device_db& db, acc_ref acc, cons
             {
                 if (lane < SEG_PAD) { my_segs[n_desc + lane] = make_uint2(0, 0); }
                 __syncwarp();
-                gather_segments<U, CT>(db.postings, acc, segs_shared, n_desc, lane);
+                gather_segments<U, CT, false, true>(db.postings, acc, segs_shared, n_desc, lane);
                 n_desc = 0;
                 __syncwarp();
             }
@@ -1080,7 +1094,7 @@ __device__ __noinline__ void range_gather(const device_db& db, acc_ref acc, cons
     {
         if (lane < SEG_PAD) { my_segs[n_desc + lane] = make_uint2(0, 0); }
         __syncwarp();
-        gather_segments<U, CT>(db.postings, acc, segs_shared, n_desc, lane);
+        gather_segments<U, CT, false, true>(db.postings, acc, segs_shared, n_desc, lane);
     }
     __syncwarp();
 }
