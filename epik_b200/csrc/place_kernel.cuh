@@ -717,10 +717,8 @@ __device__ __forceinline__ sweep_result sweep(const ACC acc, uint32_t np, uint32
         }
         ++step;
         // ---- likelihood mass (place.cpp:164-184) ----
-        bool in_any = false;
-#pragma unroll
-        for (int u = 0; u < 4; ++u) { in_any |= key[u] >= cut_key; }
-        if (__any_sync(FULL, in_any))
+        const uint32_t best4 = max(max(key[0], key[1]), max(key[2], key[3])); // best key of the quad
+        if (__any_sync(FULL, best4 >= cut_key))
         {
             double e[4];
 #pragma unroll
@@ -732,10 +730,9 @@ __device__ __forceinline__ sweep_result sweep(const ACC acc, uint32_t np, uint32
             }
         }
         // ---- top-k candidates (place.cpp:134-159) ----
-        bool cand_any = false;
-#pragma unroll
-        for (int u = 0; u < 4; ++u) { cand_any |= (key[u] > bar_key) | ((key[u] == bar_key) & (j + u < bar_branch)); }
-        if (__any_sync(FULL, cand_any))
+        // (a candidate has key >= bar_key: one compare of the quad's best key keeps the four exact tests, ties
+        // and all, out of the common path)
+        if (__any_sync(FULL, best4 >= max(bar_key, 1u)))
         {
 #pragma unroll
             for (int u = 0; u < 4; ++u)
