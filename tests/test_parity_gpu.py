@@ -335,18 +335,21 @@ def test_gather_ceiling_launch_moves_the_same_postings():
     assert torch.equal(sums[0], sums[1]) and int((sums[0] != 0).sum()) > 1900
 
 
-@pytest.mark.parametrize("n_leaves,read_len,variant", [
-    (6500, 150, 0),    # N = 12 999: three accumulator sets per SM, teams of 2 warps
-    (10000, 150, 0),   # N = 19 999 (C5's tree): two sets, teams of 4
-    (10000, 150, 1),   # the same with one warp per query
-    (20000, 150, 0),   # N = 39 999: one set, a team of 8
-    (10000, 400, 0),   # 16-bit hit counts: one set, a team of 8
+@pytest.mark.parametrize("n_leaves,read_len,variant,k,m", [
+    (6500, 150, 0, 8, 40.0),    # N = 12 999: three accumulator sets per SM, teams of 2 warps
+    (10000, 150, 0, 8, 40.0),   # N = 19 999 (C5's tree): two sets, teams of 4
+    (10000, 150, 1, 8, 40.0),   # the same with one warp per query
+    (20000, 150, 0, 8, 40.0),   # N = 39 999: one set, a team of 8
+    (10000, 400, 0, 8, 40.0),   # 16-bit hit counts: one set, a team of 8
+    (10000, 150, 0, 5, 6000.0), # lists of thousands of postings: a member's sub-lists of one round of hits overflow its
+                                # 120-descriptor buffer many times over
+    (4300, 150, 0, 8, 300.0),   # N = 8599, just above the range-team threshold: four sets, teams of 2, long lists
 ])
-def test_large_trees_sweep_in_teams(n_leaves, read_len, variant):
-    """Several warps sweep one query's accumulators (place_kernel.cuh "teams"): same bits as the reference,
-    including ambiguous windows and queries without hits."""
-    flat = synth.make_db(0, 8, n_leaves, 0.6, 40.0, seed=2000 + n_leaves)
-    n = 1500 if read_len <= 200 else 400
+def test_large_trees_sweep_in_teams(n_leaves, read_len, variant, k, m):
+    """Several warps per query on large trees (place_kernel.cuh "teams" and "range teams"): same bits as the
+    reference, including ambiguous windows and queries without hits."""
+    flat = synth.make_db(0, k, n_leaves, 0.6 if k == 8 else 0.9, m, seed=2000 + n_leaves)
+    n = 150 if m > 1000 else 1500 if read_len <= 200 else 400
     data, off = synth.make_reads(0, n, read_len, seed=78, amb_rate=0.002)
     p = Placer(Database(flat), variant=variant)
     got = p.place_packed(data, off)
