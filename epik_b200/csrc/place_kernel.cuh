@@ -943,11 +943,11 @@ __device__ __forceinline__ void dump_partial_row(const place_params& p, float* S
                                                  uint32_t flags, uint32_t gathered, uint32_t lane, uint32_t part = 0,
                                                  uint32_t parts = 1);
 
-template<int U, class CT>
+template<int U, class CT, bool SINK>
 __device__ __noinline__ void range_gather(const device_db& db, acc_ref acc, const uint64_t* hits, uint32_t n_hits, uint2* my_segs,
-                                          uint32_t member, uint32_t team, uint32_t lane);
+                                          uint32_t member, uint32_t team, uint32_t lane, uint32_t* sink_out);
 
-template<int U, class CT>
+template<int U, class CT, bool SINK>
 __device__ __forceinline__ void team_helper_loop(const place_params& p, float* S, CT* C, uint32_t np, uint32_t lane,
                                                  unsigned char* team_area, const uint64_t* hits, uint32_t set,
                                                  uint32_t member, uint32_t team)
@@ -964,7 +964,14 @@ __device__ __forceinline__ void team_helper_loop(const place_params& p, float* S
         if (q == NO_BRANCH) { break; }
         if (cmd & TEAM_CMD_GATHER)
         {
-            range_gather<U, CT>(p.db, acc, hits, cmd & ~TEAM_CMD_GATHER, reinterpret_cast<uint2*>(member_base), member, team, lane);
+            uint32_t sink = 0;
+            range_gather<U, CT, SINK>(p.db, acc, hits, cmd & ~TEAM_CMD_GATHER, reinterpret_cast<uint2*>(member_base), member, team,
+                                      lane, &sink);
+            if (SINK)
+            {
+                sink = __reduce_xor_sync(FULL, sink);
+                if (lane == 0) { atomicXor(p.n_place + q, sink); } // the ceiling launch: one checksum word per query
+            }
             team_sync(set, team); // G: this chunk's postings are in the accumulators
             continue;
         }
@@ -1032,9 +1039,9 @@ __device__ __forceinline__ void finish_query_leader(const place_params& p, float
 constexpr uint32_t RANGE_DESC_CAP = TEAM_MEMBER_WORDS / 2 - SEG_PAD; // descriptors a member buffers (aliases its candidates)
 constexpr uint32_t RANGE_HEADER_POSTINGS = 4;                        // = RANGE_HEADER_ENTRIES of db_build.cuh
 
-template<int U, class CT>
+template<int U, class CT, bool SINK>
 __device__ __noinline__ void range_gather(const device_db& db, acc_ref acc, const uint64_t* hits, uint32_t n_hits,
-                                          uint2* my_segs, uint32_t member, uint32_t team, uint32_t lane)
+                                          uint2* my_segs, uint32_t member, uint32_t team, uint32_t lane, uint32_t* sink_out)
 {
     const uint32_t segs_shared = static_cast<uint32_t>(__cvta_generic_to_shared(my_segs));
     const uint32_t part_lo = member * (8u / team); // header entries are eighths of the padded branch range
@@ -1081,7 +1088,7 @@ __device__ __noinline__ void range_gather(const device_db& db, acc_ref acc, cons
             {
                 if (lane < SEG_PAD) { my_segs[n_desc + lane] = make_uint2(0, 0); }
                 __syncwarp();
-                gather_segments<U, CT, false, true>(db.postings, acc, segs_shared, n_desc, lane);
+                gather_segments<U, CT, SINK, true>(db.postings, acc, segs_shared, n_desc, lane, sink_out);
                 n_desc = 0;
                 __syncwarp();
             }
@@ -1091,7 +1098,7 @@ __device__ __noinline__ void range_gather(const device_db& db, acc_ref acc, cons
     {
         if (lane < SEG_PAD) { my_segs[n_desc + lane] = make_uint2(0, 0); }
         __syncwarp();
-        gather_segments<U, CT, false, true>(db.postings, acc, segs_shared, n_desc, lane);
+        gather_segments<U, CT, SINK, true>(db.postings, acc, segs_shared, n_desc, lane, sink_out);
     }
     __syncwarp();
 }
@@ -1160,7 +1167,6 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
 {
     constexpr bool PARTIAL = MODE == MODE_PARTIAL;
     constexpr bool GATHER_ONLY = MODE == MODE_GATHER_ONLY;
-    static_assert(!TEAM || MODE != MODE_GATHER_ONLY, "the ceiling kernel is the one-warp gather");
     extern __shared__ __align__(16) unsigned char smem[];
     if (p.class_reads && p.class_reads[p.cls] == 0) { return; } // no query of this class in the batch
     const uint32_t lane = threadIdx.x & 31u;
@@ -1202,7 +1208,7 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
     __syncthreads();
     if (TEAM && member != 0)
     {
-        team_helper_loop<U, CT>(p, S, C, np, lane, team_area, reinterpret_cast<const uint64_t*>(segs), warp, member, team);
+        team_helper_loop<U, CT, GATHER_ONLY>(p, S, C, np, lane, team_area, reinterpret_cast<const uint64_t*>(segs), warp, member, team);
         return;
     }
 
@@ -1253,6 +1259,7 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
         const char* seq = p.seq + s0;
         bool has_ambiguous = false;
         uint32_t nseg = 0, sink = 0;
+        if (GATHER_ONLY && TEAM && lane == 0) { p.n_place[q] = 0; } // every member XORs its part in (after a team barrier)
         if (lane == 0) { ctr_windows += n_windows; }
 
         // ---- exact k-mers, window order (place.cpp:294-304, 349-371) ----
@@ -1366,7 +1373,7 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
                 __syncwarp();
                 team_sync(warp, team); // command: gather
                 uint2* my_desc = reinterpret_cast<uint2*>(team_area + sizeof(team_mailbox) + team * sizeof(team_result));
-                range_gather<U, CT>(db, acc, hits, n_hits, my_desc, 0u, team, lane);
+                range_gather<U, CT, GATHER_ONLY>(db, acc, hits, n_hits, my_desc, 0u, team, lane, &sink);
                 team_sync(warp, team); // G
                 continue;
             }
@@ -1434,7 +1441,11 @@ __global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const 
         if (GATHER_ONLY)
         {
             sink = __reduce_xor_sync(FULL, sink);
-            if (lane == 0) { p.n_place[q] = sink; }
+            if (lane == 0)
+            {
+                if (TEAM) { atomicXor(p.n_place + q, sink); } // the members have added theirs
+                else { p.n_place[q] = sink; }
+            }
             continue;
         }
 

@@ -155,6 +155,11 @@ namespace
     // the load-only form of the class-0 launch (roofline ceiling, epk_gather_ceiling_device)
     kernel_fn pick_gather_only_kernel(const epk_placer& pl)
     {
+        if (pl.team[0] > 1)
+        {
+            return pl.db->table_kind == TABLE_DIRECT ? place_kernel<TABLE_DIRECT, 8, uint8_t, MODE_GATHER_ONLY, true>
+                                                     : place_kernel<TABLE_HASH, 8, uint8_t, MODE_GATHER_ONLY, true>;
+        }
         return pl.db->table_kind == TABLE_DIRECT ? place_kernel<TABLE_DIRECT, 8, uint8_t, MODE_GATHER_ONLY>
                                                  : place_kernel<TABLE_HASH, 8, uint8_t, MODE_GATHER_ONLY>;
     }
@@ -594,8 +599,9 @@ extern "C" epk_status epk_gather_ceiling_device(epk_placer* pl, const char* d_se
         if (n)
         {
             const unsigned grid = static_cast<unsigned>(
-                std::min<uint64_t>(pl->n_sms, (static_cast<uint64_t>(n) + pl->warps_per_cta[0] - 1) / pl->warps_per_cta[0]));
-            pick_gather_only_kernel(*pl)<<<grid, pl->warps_per_cta[0] * 32, pl->smem_bytes[0], s>>>(p);
+                std::min<uint64_t>(pl->n_sms, (static_cast<uint64_t>(n) + pl->sets_fused[0] - 1) / pl->sets_fused[0]));
+            p.team = pl->team[0];
+            pick_gather_only_kernel(*pl)<<<grid, pl->sets_fused[0] * pl->team[0] * 32, pl->smem_fused[0], s>>>(p);
             EPK_CUDA(cudaGetLastError());
             fold_counters_kernel<<<1, 1, 0, s>>>(p.counters, pl->device_class_reads.get(), 0u, pl->totals.get());
             EPK_CUDA(cudaGetLastError());

@@ -314,11 +314,12 @@ def test_load_filter_matches_its_restatement(mu, omega, max_entries):
             assert np.array_equal(x, y)
 
 
-def test_gather_ceiling_launch_moves_the_same_postings():
+@pytest.mark.parametrize("n_leaves", [300, 10000], ids=["one-warp", "range-teams"])
+def test_gather_ceiling_launch_moves_the_same_postings(n_leaves):
     """epk_gather_ceiling_device (the roofline's measuring stick) walks the same probes and posting lists as the
     placement launch: same windows / hits / entries counters, one checksum word per query, deterministic."""
     import torch
-    flat = synth.make_db(0, 8, 300, 0.6, 12.0, seed=11)
+    flat = synth.make_db(0, 8, n_leaves, 0.6, 12.0 if n_leaves == 300 else 40.0, seed=11)
     data, off = synth.make_reads(0, 2000, 150, seed=12)
     p = Placer(Database(flat))
     p.place_packed(data, off)
