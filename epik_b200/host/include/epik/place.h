@@ -8,10 +8,13 @@
 #include <algorithm>
 #include <cstdint>
 #include <cstring>
+#include <exception>
 #include <limits>
+#include <mutex>
 #include <stdexcept>
 #include <string>
 #include <string_view>
+#include <thread>
 #include <unordered_map>
 #include <vector>
 
@@ -56,6 +59,38 @@ namespace epik::impl
         sequence_map_t sequence_map;
         std::vector<placed_sequence> placed_seqs;
     };
+
+    /// fn(i) for i in [0, n) on up to `threads` host threads (the -j / --jobs of the driver, main.cpp:212): the
+    /// host side of a batch - grouping, result objects, jplace text - is independent per reference-sized batch
+    template<class F>
+    void parallel_for(size_t n, size_t threads, F&& fn)
+    {
+        threads = std::max<size_t>(1, std::min<size_t>(std::min(threads, n), 256));
+        if (threads == 1)
+        {
+            for (size_t i = 0; i < n; ++i) { fn(i); }
+            return;
+        }
+        std::vector<std::thread> pool;
+        std::exception_ptr error;
+        std::mutex error_lock;
+        for (size_t t = 0; t < threads; ++t)
+        {
+            pool.emplace_back([&, t] {
+                try
+                {
+                    for (size_t i = t; i < n; i += threads) { fn(i); }
+                }
+                catch (...)
+                {
+                    const std::lock_guard<std::mutex> hold(error_lock);
+                    if (!error) { error = std::current_exception(); }
+                }
+            });
+        }
+        for (auto& th : pool) { th.join(); }
+        if (error) { std::rethrow_exception(error); }
+    }
 
     /// Pinned host memory (epk_host_alloc) that only ever grows.
     template<class T>
@@ -195,15 +230,16 @@ namespace epik
         /// place() calls on slices of `batch_size` records would (main.cpp:332-344: identical sequences
         /// merge only within one --batch-size batch).
         template<class Record>
-        std::vector<placed_collection> place_batched(const std::vector<Record>& seq_records, size_t batch_size)
+        std::vector<placed_collection> place_batched(const std::vector<Record>& seq_records, size_t batch_size,
+                                                     size_t num_threads = 1)
         {
             const epk_result out = run(seq_records);
-            std::vector<placed_collection> batches;
-            if (batch_size == 0) { batch_size = seq_records.size(); }
-            for (size_t first = 0; first < seq_records.size(); first += batch_size)
-            {
-                batches.push_back(collect(seq_records, out, first, std::min(seq_records.size(), first + batch_size)));
-            }
+            if (batch_size == 0) { batch_size = std::max<size_t>(1, seq_records.size()); }
+            const size_t n_batches = (seq_records.size() + batch_size - 1) / batch_size;
+            std::vector<placed_collection> batches(n_batches);
+            impl::parallel_for(n_batches, num_threads, [&](size_t b) {
+                batches[b] = collect(seq_records, out, b * batch_size, std::min(seq_records.size(), (b + 1) * batch_size));
+            });
             return batches;
         }
 
@@ -254,8 +290,8 @@ namespace epik
         placed_collection collect(const std::vector<Record>& seq_records, const epk_result& out, size_t first, size_t last)
         {
             const size_t K = _keep_at_most, n = last - first;
-            uint32_t* rep = _rep.reserve(n + 1);
-            impl::check(epk_group_batch(_letters.data(), _offsets.data() + first, static_cast<uint32_t>(n), rep));
+            std::vector<uint32_t> rep(n + 1); // (called concurrently for different batches)
+            impl::check(epk_group_batch(_letters.data(), _offsets.data() + first, static_cast<uint32_t>(n), rep.data()));
             placed_collection result;
             result.sequence_map.reserve(n);
             for (size_t i = first; i < last; ++i)
@@ -291,7 +327,7 @@ namespace epik
 
         impl::pinned_array<char> _letters;
         impl::pinned_array<uint64_t> _offsets;
-        impl::pinned_array<uint32_t> _n_place, _branch, _count, _rep;
+        impl::pinned_array<uint32_t> _n_place, _branch, _count;
         impl::pinned_array<float> _score;
         impl::pinned_array<double> _lwr, _distal, _pendant;
     };

@@ -5,9 +5,12 @@
 //   * the database is an `.epkdb` file (epik/flat_db.h): the `.ipk` format lives in the absent i2l submodule;
 //   * FASTA records are read `--batch-size` at a time as the reference does, but many such batches are placed
 //     in one device pass (--device-batches, default 128); dedupe and "nm" grouping stay per --batch-size batch;
-//   * -j/--jobs is accepted and ignored (there are no host placement threads);
+//   * -j/--jobs sizes the host side: grouping, result objects and jplace text of the --batch-size batches of a
+//     device pass are produced on that many threads (the placement itself has no host threads);
 //   * --device N picks the CUDA device.
 #include <chrono>
+#include <future>
+#include <memory>
 #include <cmath>
 #include <cstdlib>
 #include <iomanip>
@@ -197,6 +200,7 @@ int main(int argc, char** argv)
         const std::string output_dir = opts.get("output-dir");
         const int device = std::stoi(opts.get("device", "0"));
         const size_t device_batches = std::max<size_t>(1, std::stoull(opts.get("device-batches", "128")));
+        const size_t num_threads = std::max<size_t>(1, std::stoull(opts.get("jobs", "1")));
 
         if (user_mu < 0.0f || user_mu > 1.0f) { throw std::runtime_error("Mu has to a value in [0, 1]"); } // main.cpp:196-202
 
@@ -241,24 +245,41 @@ int main(int argc, char** argv)
         double average_speed = 0.0;
 
         epik::io::batch_fasta reader(query_file, batch_size * device_batches);
+        // Two passes are in flight: while the jplace text of one device pass is produced (on the -j threads) and
+        // appended, the next pass is read and placed. A pass owns its records: the results hold views into them.
+        using records_t = decltype(reader.next_batch());
+        struct pass_t
+        {
+            records_t records;
+            std::vector<epik::impl::placed_collection> placed;
+        };
+        std::future<void> writing;
         while (true)
         {
-            const auto records = reader.next_batch();
-            if (records.empty()) { break; }
+            auto pass = std::make_shared<pass_t>();
+            pass->records = reader.next_batch();
+            if (pass->records.empty()) { break; }
 
             const auto begin_batch = std::chrono::steady_clock::now();
-            const auto placed_batches = placer.place_batched(records, batch_size);
+            pass->placed = placer.place_batched(pass->records, batch_size, num_threads);
             const auto end_batch = std::chrono::steady_clock::now();
 
             // the reference's figure, main.cpp:348-353: nominal batch size over the time spent in place()
-            double ms = std::chrono::duration<double, std::milli>(end_batch - begin_batch).count() / static_cast<double>(placed_batches.size());
+            double ms = std::chrono::duration<double, std::milli>(end_batch - begin_batch).count() / static_cast<double>(pass->placed.size());
             if (ms <= 0.0) { ms = 1e-3; }
-            average_speed += 1000.0 * static_cast<double>(batch_size) / ms * static_cast<double>(placed_batches.size());
-            num_iterations += placed_batches.size();
+            average_speed += 1000.0 * static_cast<double>(batch_size) / ms * static_cast<double>(pass->placed.size());
+            num_iterations += pass->placed.size();
+            num_seq_placed += pass->records.size();
 
-            for (const auto& placed : placed_batches) { jplace << placed; }
-            num_seq_placed += records.size();
+            if (writing.valid()) { writing.get(); } // passes are appended in order
+            writing = std::async(std::launch::async, [pass, &jplace, num_threads] {
+                std::vector<std::string> text(pass->placed.size());
+                epik::impl::parallel_for(pass->placed.size(), num_threads,
+                                         [&](size_t b) { text[b] = epik::io::jplace_writer::format(pass->placed[b]); });
+                for (size_t b = 0; b < pass->placed.size(); ++b) { jplace.append(text[b], pass->placed[b].placed_seqs.size()); }
+            });
         }
+        if (writing.valid()) { writing.get(); }
         jplace.end();
         if (num_iterations) { average_speed /= static_cast<double>(num_iterations); }
 
