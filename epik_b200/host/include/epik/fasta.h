@@ -46,7 +46,7 @@ namespace epik::io
         {
             std::vector<seq_record> batch;
             batch.reserve(_batch_size);
-            std::string line;
+            std::string_view line;
             while (batch.size() < _batch_size)
             {
                 if (!_have_header)
@@ -58,7 +58,7 @@ namespace epik::io
                         if (!line.empty() && line[0] == '>') { found = true; break; }
                     }
                     if (!found) { break; }
-                    _header.assign(line, 1, std::string::npos);
+                    _header.assign(line.data() + 1, line.size() - 1);
                     _have_header = true;
                 }
                 std::string sequence;
@@ -66,6 +66,11 @@ namespace epik::io
                 while (read_line(line))
                 {
                     if (!line.empty() && line[0] == '>') { next_header = true; break; }
+                    if (std::memchr(line.data(), ' ', line.size()) == nullptr && std::memchr(line.data(), '\t', line.size()) == nullptr)
+                    {
+                        sequence.append(line.data(), line.size()); // the usual line: letters only
+                        continue;
+                    }
                     for (const char c : line)
                     {
                         if (c != ' ' && c != '\t') { sequence.push_back(c); }
@@ -74,7 +79,7 @@ namespace epik::io
                 batch.emplace_back(std::move(_header), std::move(sequence));
                 _header.clear();
                 _have_header = next_header;
-                if (next_header) { _header.assign(line, 1, std::string::npos); }
+                if (next_header) { _header.assign(line.data() + 1, line.size() - 1); }
                 else { break; } // end of file
             }
             return batch;
@@ -83,11 +88,15 @@ namespace epik::io
         size_t bytes_read() const noexcept { return _bytes_consumed; }
 
     private:
-        /// One line without its terminator (LF or CRLF); false at end of file.
-        bool read_line(std::string& line)
+        /// One line without its terminator (LF or CRLF) and without trailing blanks; false at end of file. The view
+        /// points into the read buffer (a line that straddles two buffer fills is assembled in _straddle) and is
+        /// valid until the next call.
+        bool read_line(std::string_view& line)
         {
-            line.clear();
-            bool any = false;
+            _straddle.clear();
+            bool any = false, whole = false;
+            const char* start = nullptr;
+            size_t length = 0;
             while (true)
             {
                 if (_pos == _len)
@@ -97,20 +106,23 @@ namespace epik::io
                     if (_len == 0) { break; }
                 }
                 any = true;
-                const char* start = _buffer.data() + _pos;
+                start = _buffer.data() + _pos;
                 const char* nl = static_cast<const char*>(std::memchr(start, '\n', _len - _pos));
                 if (nl)
                 {
-                    line.append(start, nl);
-                    _bytes_consumed += static_cast<size_t>(nl - start) + 1;
-                    _pos += static_cast<size_t>(nl - start) + 1;
+                    length = static_cast<size_t>(nl - start);
+                    _bytes_consumed += length + 1;
+                    _pos += length + 1;
+                    whole = _straddle.empty();
+                    if (!whole) { _straddle.append(start, length); }
                     break;
                 }
-                line.append(start, _len - _pos);
+                _straddle.append(start, _len - _pos); // no terminator in what is left of the buffer
                 _bytes_consumed += _len - _pos;
                 _pos = _len;
             }
-            while (!line.empty() && (line.back() == '\r' || line.back() == ' ' || line.back() == '\t')) { line.pop_back(); }
+            line = whole ? std::string_view(start, length) : std::string_view(_straddle);
+            while (!line.empty() && (line.back() == '\r' || line.back() == ' ' || line.back() == '\t')) { line.remove_suffix(1); }
             return any;
         }
 
@@ -118,7 +130,7 @@ namespace epik::io
         size_t _batch_size;
         std::vector<char> _buffer;
         size_t _pos = 0, _len = 0, _bytes_consumed = 0;
-        std::string _header;
+        std::string _header, _straddle;
         bool _have_header = false;
     };
 }

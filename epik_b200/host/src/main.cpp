@@ -254,11 +254,13 @@ int main(int argc, char** argv)
             std::vector<epik::impl::placed_collection> placed;
         };
         std::future<void> writing;
+        std::future<records_t> reading = std::async(std::launch::async, [&reader] { return reader.next_batch(); });
         while (true)
         {
             auto pass = std::make_shared<pass_t>();
-            pass->records = reader.next_batch();
+            pass->records = reading.get();
             if (pass->records.empty()) { break; }
+            reading = std::async(std::launch::async, [&reader] { return reader.next_batch(); }); // parsed while this pass is placed
 
             const auto begin_batch = std::chrono::steady_clock::now();
             pass->placed = placer.place_batched(pass->records, batch_size, num_threads);
