@@ -20,6 +20,9 @@
 #include <string_view>
 #include <vector>
 
+#include <fcntl.h>
+#include <unistd.h>
+
 #include <epik/place.h>
 
 namespace epik::io
@@ -301,6 +304,46 @@ namespace epik::io
             flush();
         }
 
+        /// append() for the batches of one device pass at once: the pieces go to their places in the file with
+        /// concurrent pwrite()s (one thread moves ~1.2 GB/s into the page cache; the text of a pass is ~230 MB).
+        void append_many(std::vector<std::string>& texts, const std::vector<size_t>& n_records, size_t threads)
+        {
+            flush(); // what is buffered (the file's opening) goes first
+            std::vector<size_t> offset(texts.size() + 1, 0);
+            size_t total_records = 0;
+            for (size_t b = 0; b < texts.size(); ++b)
+            {
+                if (n_records[b] && _n_records + total_records == 0) { texts[b].erase(0, 1); } // no comma before the first record
+                total_records += n_records[b];
+                offset[b + 1] = offset[b] + texts[b].size();
+            }
+            const int fd = ::open(_filename.c_str(), O_WRONLY);
+            if (fd < 0) { throw std::runtime_error("Could not open file " + _filename); }
+            const size_t base = _file_bytes;
+            try
+            {
+                impl::parallel_for(texts.size(), threads, [&](size_t b) {
+                    size_t done = 0;
+                    while (done < texts[b].size())
+                    {
+                        const ssize_t w = ::pwrite(fd, texts[b].data() + done, texts[b].size() - done,
+                                                   static_cast<off_t>(base + offset[b] + done));
+                        if (w <= 0) { throw std::runtime_error("Could not write to " + _filename); }
+                        done += static_cast<size_t>(w);
+                    }
+                });
+            }
+            catch (...)
+            {
+                ::close(fd);
+                throw;
+            }
+            ::close(fd);
+            _file_bytes += offset.back();
+            _n_records += total_records;
+            if (total_records) { _writer.add_elements(total_records); }
+        }
+
         void end()
         {
             _writer.end_array();
@@ -313,6 +356,7 @@ namespace epik::io
         {
             if (!_out.is_open()) { _out.open(_filename, std::ios_base::app); }
             _out << _buffer;
+            _file_bytes += _buffer.size();
             _buffer.clear();
             _out.close();
         }
@@ -323,7 +367,7 @@ namespace epik::io
         json_pretty_writer _writer;
         std::string _invocation;
         std::string _tree;
-        size_t _n_records = 0;
+        size_t _n_records = 0, _file_bytes = 0;
     };
 }
 

@@ -278,7 +278,9 @@ int main(int argc, char** argv)
                 std::vector<std::string> text(pass->placed.size());
                 epik::impl::parallel_for(pass->placed.size(), num_threads,
                                          [&](size_t b) { text[b] = epik::io::jplace_writer::format(pass->placed[b]); });
-                for (size_t b = 0; b < pass->placed.size(); ++b) { jplace.append(text[b], pass->placed[b].placed_seqs.size()); }
+                std::vector<size_t> n_records(pass->placed.size());
+                for (size_t b = 0; b < pass->placed.size(); ++b) { n_records[b] = pass->placed[b].placed_seqs.size(); }
+                jplace.append_many(text, n_records, num_threads);
             });
         }
         if (writing.valid()) { writing.get(); }
