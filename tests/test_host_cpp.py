@@ -17,7 +17,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CPP = os.path.join(ROOT, "tests", "cpp")
 CXX = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
 OURS = ["-I" + os.path.join(ROOT, "epik_b200", "host", "include"), "-I" + os.path.join(ROOT, "include")]
-LINK = ["-L" + os.path.join(ROOT, "epik_b200"), "-lepik_b200", "-Wl,-rpath," + os.path.join(ROOT, "epik_b200")]
+LINK = ["-pthread", "-L" + os.path.join(ROOT, "epik_b200"), "-lepik_b200", "-Wl,-rpath," + os.path.join(ROOT, "epik_b200")]
 
 
 def compile_cpp(tmp_path, name, flags, sources, link=()):
@@ -32,6 +32,10 @@ def test_jplace_writer_is_byte_identical_to_the_reference_writer(built, tmp_path
     subprocess.run([exe, out], check=True)
     golden = open(os.path.join(helpers.GOLDEN, "jplace_reference.jplace"), "rb").read()
     assert open(out, "rb").read() == golden
+    # the driver's way of writing - batches formatted on threads, a pass written with concurrent pwrites - gives the same bytes
+    out2 = str(tmp_path / "ours_parallel.jplace")
+    subprocess.run([exe, out2, "parallel"], check=True)
+    assert open(out2, "rb").read() == golden
     # (the case data holds one float(1.8e308) = inf score: RapidJSON writes the separator and no value for it,
     # and so does this writer — the file is deliberately not valid JSON at that spot)
     # keep the golden file honest when the reference and a RapidJSON are available
