@@ -1162,8 +1162,10 @@ __device__ __forceinline__ void dump_partial_row(const place_params& p, float* S
 enum kernel_mode { MODE_FULL = 0, MODE_PARTIAL = 1, MODE_GATHER_ONLY = 2 };
 
 // TEAM: p.team warps per accumulator set (see "teams"); blockDim = 32 * p.team * sets.
-template<uint32_t TABLE, int U, class CT, int MODE = MODE_FULL, bool TEAM = false>
-__global__ void __launch_bounds__(MAX_WARPS_PER_CTA * 32, 1) place_kernel(const place_params p)
+// MAXW: warps per CTA the launch may use (small trees: 16 accumulator sets fit an SM, and 16 warps at 128 registers
+// hide the latency of the key-table probes better than 8 at 255).
+template<uint32_t TABLE, int U, class CT, int MODE = MODE_FULL, bool TEAM = false, int MAXW = MAX_WARPS_PER_CTA>
+__global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params p)
 {
     constexpr bool PARTIAL = MODE == MODE_PARTIAL;
     constexpr bool GATHER_ONLY = MODE == MODE_GATHER_ONLY;

@@ -118,6 +118,7 @@ struct epk_placer
     size_t smem_bytes[N_CLASSES] = { 0, 0, 0 };
     uint32_t unsupported_mask = 0;
     uint32_t team[N_CLASSES] = { 1, 1, 1 };           // warps per accumulator set of the fused launch
+    bool wide[N_CLASSES] = { false, false, false };   // 16 one-warp sets per CTA (small trees)
     uint32_t sets_fused[N_CLASSES] = { 0, 0, 0 };     // accumulator sets per CTA of the fused launch
     size_t smem_fused[N_CLASSES] = { 0, 0, 0 };
     device_buffer<uint32_t> fake_order;
@@ -166,6 +167,15 @@ namespace
 
     kernel_fn pick_kernel(const epk_placer& pl, int cls)
     {
+        if (pl.wide[cls])
+        {
+            // small tree: 16 accumulator sets and 16 warps per SM
+            if (pl.db->table_kind == TABLE_DIRECT)
+            {
+                return cls == 0 ? place_kernel<TABLE_DIRECT, 4, uint8_t, MODE_FULL, false, 16> : place_kernel<TABLE_DIRECT, 4, uint16_t, MODE_FULL, false, 16>;
+            }
+            return cls == 0 ? place_kernel<TABLE_HASH, 4, uint8_t, MODE_FULL, false, 16> : place_kernel<TABLE_HASH, 4, uint16_t, MODE_FULL, false, 16>;
+        }
         if (pl.team[cls] > 1)
         {
             // large tree, few accumulator sets per SM: several warps per set (place_kernel.cuh, "teams")
@@ -377,6 +387,12 @@ extern "C" epk_status epk_placer_create(const epk_db* db, uint64_t keep_at_most,
                     pl->sets_fused[c] = sets;
                     pl->smem_fused[c] = CTA_SMEM_FIXED + sets * per_set;
                 }
+            }
+            if (c < 2 && pl->variant != 1 && CTA_SMEM_FIXED + 16 * per_warp <= static_cast<size_t>(max_smem))
+            {
+                pl->wide[c] = true;
+                pl->sets_fused[c] = 16;
+                pl->smem_fused[c] = CTA_SMEM_FIXED + 16 * per_warp;
             }
             // the attribute belongs to the function, not to this placer: always the device's limit, so that
             // placers for trees of different sizes can live side by side
@@ -598,10 +614,11 @@ extern "C" epk_status epk_gather_ceiling_device(epk_placer* pl, const char* d_se
         pl->n_reads = n;
         if (n)
         {
-            const unsigned grid = static_cast<unsigned>(
-                std::min<uint64_t>(pl->n_sms, (static_cast<uint64_t>(n) + pl->sets_fused[0] - 1) / pl->sets_fused[0]));
+            const bool teams = pl->team[0] > 1; // (the 16-set form of small trees exists for the fused launch only)
+            const uint32_t sets = teams ? pl->sets_fused[0] : pl->warps_per_cta[0];
+            const unsigned grid = static_cast<unsigned>(std::min<uint64_t>(pl->n_sms, (static_cast<uint64_t>(n) + sets - 1) / sets));
             p.team = pl->team[0];
-            pick_gather_only_kernel(*pl)<<<grid, pl->sets_fused[0] * pl->team[0] * 32, pl->smem_fused[0], s>>>(p);
+            pick_gather_only_kernel(*pl)<<<grid, sets * pl->team[0] * 32, teams ? pl->smem_fused[0] : pl->smem_bytes[0], s>>>(p);
             EPK_CUDA(cudaGetLastError());
             fold_counters_kernel<<<1, 1, 0, s>>>(p.counters, pl->device_class_reads.get(), 0u, pl->totals.get());
             EPK_CUDA(cudaGetLastError());
@@ -670,10 +687,11 @@ extern "C" epk_status epk_place_partial_device(epk_placer* pl, const char* d_seq
             {
                 p.cls = static_cast<uint32_t>(c);
                 p.counters = counters + c * CTR_COUNT;
-                const unsigned grid = static_cast<unsigned>(
-                    std::min<uint64_t>(pl->n_sms, (static_cast<uint64_t>(n) + pl->sets_fused[c] - 1) / pl->sets_fused[c]));
+                const bool teams = pl->team[c] > 1;
+                const uint32_t sets = teams ? pl->sets_fused[c] : pl->warps_per_cta[c];
+                const unsigned grid = static_cast<unsigned>(std::min<uint64_t>(pl->n_sms, (static_cast<uint64_t>(n) + sets - 1) / sets));
                 p.team = pl->team[c];
-                pick_partial_kernel(*pl, c)<<<grid, pl->sets_fused[c] * pl->team[c] * 32, pl->smem_fused[c], s>>>(p);
+                pick_partial_kernel(*pl, c)<<<grid, sets * pl->team[c] * 32, teams ? pl->smem_fused[c] : pl->smem_bytes[c], s>>>(p);
                 EPK_CUDA(cudaGetLastError());
                 ++pl->n_launches;
             }

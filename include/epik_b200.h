@@ -93,8 +93,9 @@ typedef struct epk_placer epk_placer;
 /* Options of a placer beyond the reference's constructor arguments. Zero-initialise for defaults. */
 typedef struct epk_placer_opts
 {
-    uint32_t variant;        /* 0 = default; 1 = always one warp per query (no sweep teams on     */
-                             /* large trees)                                                      */
+    uint32_t variant;        /* 0 = default: 16 warps per SM on small trees, one warp per query   */
+                             /* at C2's size, teams of warps per query on large trees;            */
+                             /* 1 = always one warp per query, 8 per SM                           */
     uint32_t chunk_reads;    /* reads per pipelined H2D/kernel/D2H chunk of epk_place; 0 = auto   */
     uint32_t reserved[6];
 } epk_placer_opts;
