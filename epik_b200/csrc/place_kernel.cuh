@@ -70,6 +70,7 @@ struct place_params
     const uint32_t* letters;     // [256] letter table
     const uint32_t* fake_order;  // [keep_at_most] order of the zero-hit placements
     unsigned long long* counters; // [CTR_COUNT] of this launch
+    unsigned long long* totals;   // [CTR_COUNT] running totals of the placer, bumped with the counters (NULL: none)
     const uint32_t* class_reads; // [N_CLASSES] queries per class (classify_kernel); NULL = unknown
     uint32_t cls;                // class this launch handles
     // ---- database-sharded mode (partial rows out / partial rows in), see "partial rows" below ----
@@ -86,7 +87,7 @@ struct place_params
 // Number of queries of each class (sequences shorter than k - 1 letters count for class 0, which
 // reports them). Classes in unsupported_mask have no launch: their rows get n_place = 0 here.
 __global__ void classify_kernel(const uint64_t* __restrict__ seq_off, uint32_t n, uint32_t k, uint32_t* class_reads,
-                                uint32_t unsupported_mask, uint32_t* n_place)
+                                uint32_t unsupported_mask, uint32_t* n_place, unsigned long long* totals)
 {
     uint32_t mine[N_CLASSES] = { 0, 0, 0 };
     for (uint64_t i = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x; i < n;
@@ -103,8 +104,21 @@ __global__ void classify_kernel(const uint64_t* __restrict__ seq_off, uint32_t n
     for (int c = 0; c < N_CLASSES; ++c)
     {
         const uint32_t total = __reduce_add_sync(FULL, mine[c]);
-        if ((threadIdx.x & 31u) == 0 && total) { atomicAdd(class_reads + c, total); }
+        if ((threadIdx.x & 31u) == 0 && total)
+        {
+            atomicAdd(class_reads + c, total);
+            if (totals && ((unsupported_mask >> c) & 1u)) { atomicAdd(totals + CTR_UNSUPPORTED, static_cast<unsigned long long>(total)); }
+        }
     }
+}
+
+// A work counter of the launch and, with it, the running total of the placer. (The totals used to be folded by a
+// one-thread launch after the placement launch; with every SM's register file taken by the next placement launch
+// of another stream, that little launch - and the copies out queued behind it - waited for a whole launch.)
+__device__ __forceinline__ void bump(const place_params& p, int slot, unsigned long long v)
+{
+    atomicAdd(p.counters + slot, v);
+    if (p.totals) { atomicAdd(p.totals + slot, v); }
 }
 
 struct window_class
@@ -1241,7 +1255,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
             // the reference dies here (size_t wrap at place.cpp:291); reported as EPK_E_SHORT_SEQ
             if (lane == 0 && p.cls == 0 && !PARTIAL) // (sharded mode: the finalising launch reports it)
             {
-                atomicAdd(p.counters + CTR_SHORT, 1ull);
+                bump(p, CTR_SHORT, 1ull);
                 p.n_place[q] = 0;
             }
             continue;
@@ -1253,7 +1267,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
         {
             if (lane == 0 && !PARTIAL)
             {
-                atomicAdd(p.counters + CTR_TOO_LONG, 1ull);
+                bump(p, CTR_TOO_LONG, 1ull);
                 p.n_place[q] = 0;
             }
             continue;
@@ -1548,9 +1562,9 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
     }
     if (lane == 0)
     {
-        atomicAdd(p.counters + CTR_WINDOWS, static_cast<unsigned long long>(ctr_windows));
-        atomicAdd(p.counters + CTR_HITS, static_cast<unsigned long long>(ctr_hits));
-        atomicAdd(p.counters + CTR_ENTRIES, static_cast<unsigned long long>(ctr_entries));
+        bump(p, CTR_WINDOWS, static_cast<unsigned long long>(ctr_windows));
+        bump(p, CTR_HITS, static_cast<unsigned long long>(ctr_hits));
+        bump(p, CTR_ENTRIES, static_cast<unsigned long long>(ctr_entries));
     }
 }
 // Database-sharded mode, the owner's side: the sweep of finish_query runs straight over the partial rows

@@ -18,18 +18,6 @@ namespace
 {
     constexpr int N_SLOTS = 3; // chunks in flight in epk_place: copy in / compute / copy out
 
-    // adds the work counters of the (up to N_CLASSES) launches of one batch to the running totals;
-    // queries of a class this placer cannot run (accumulators larger than shared memory) are reported
-    __global__ void fold_counters_kernel(const unsigned long long* launch, const uint32_t* class_reads,
-                                         uint32_t unsupported_mask, unsigned long long* totals)
-    {
-        for (int c = 0; c < N_CLASSES; ++c)
-        {
-            for (int i = 1; i < CTR_COUNT; ++i) { atomicAdd(totals + i, launch[c * CTR_COUNT + i]); }
-            if ((unsupported_mask >> c) & 1u) { atomicAdd(totals + CTR_UNSUPPORTED, static_cast<unsigned long long>(class_reads[c])); }
-        }
-    }
-
     // letter codes straight from the sequence bytes (the placement kernel stages them in shared memory)
     struct letter_codes
     {
@@ -216,6 +204,7 @@ namespace
         p.letters = pl.db->letters.get();
         p.fake_order = pl.fake_order.get();
         p.class_reads = class_reads;
+        p.totals = pl.totals.get();
         EPK_CUDA(cudaMemsetAsync(counters, 0, N_CLASSES * CTR_COUNT * sizeof(unsigned long long), stream));
         EPK_CUDA(cudaMemsetAsync(class_reads, 0, N_CLASSES * sizeof(uint32_t), stream));
         {
@@ -225,7 +214,7 @@ namespace
         if (n)
         {
             const unsigned cgrid = static_cast<unsigned>(std::min<uint64_t>(4ull * pl.n_sms, (static_cast<uint64_t>(n) + 255) / 256));
-            classify_kernel<<<cgrid, 256, 0, stream>>>(d_off, n, pl.db->d.k, class_reads, pl.unsupported_mask, d_out.n_place);
+            classify_kernel<<<cgrid, 256, 0, stream>>>(d_off, n, pl.db->d.k, class_reads, pl.unsupported_mask, d_out.n_place, pl.totals.get());
             EPK_CUDA(cudaGetLastError());
             ++pl.n_launches;
             for (int c = 0; c < N_CLASSES; ++c)
@@ -240,9 +229,6 @@ namespace
                 EPK_CUDA(cudaGetLastError());
                 ++pl.n_launches;
             }
-            fold_counters_kernel<<<1, 1, 0, stream>>>(counters, class_reads, pl.unsupported_mask, pl.totals.get());
-            EPK_CUDA(cudaGetLastError());
-            ++pl.n_launches;
         }
         pl.n_reads += n;
         pl.totals_dirty = true;
@@ -607,6 +593,7 @@ extern "C" epk_status epk_gather_ceiling_device(epk_placer* pl, const char* d_se
         p.letters = pl->db->letters.get();
         p.cls = 0;
         p.counters = pl->device_counters.get();
+        p.totals = pl->totals.get();
         EPK_CUDA(cudaMemsetAsync(pl->totals.get(), 0, pl->totals.bytes(), s));
         EPK_CUDA(cudaMemsetAsync(p.counters, 0, N_CLASSES * CTR_COUNT * sizeof(unsigned long long), s));
         EPK_CUDA(cudaMemsetAsync(pl->device_class_reads.get(), 0, N_CLASSES * sizeof(uint32_t), s));
@@ -620,9 +607,7 @@ extern "C" epk_status epk_gather_ceiling_device(epk_placer* pl, const char* d_se
             p.team = pl->team[0];
             pick_gather_only_kernel(*pl)<<<grid, sets * pl->team[0] * 32, teams ? pl->smem_fused[0] : pl->smem_bytes[0], s>>>(p);
             EPK_CUDA(cudaGetLastError());
-            fold_counters_kernel<<<1, 1, 0, s>>>(p.counters, pl->device_class_reads.get(), 0u, pl->totals.get());
-            EPK_CUDA(cudaGetLastError());
-            pl->n_launches = 2;
+            pl->n_launches = 1;
         }
         pl->totals_dirty = true;
         pl->last_stream = s;
@@ -679,10 +664,11 @@ extern "C" epk_status epk_place_partial_device(epk_placer* pl, const char* d_seq
         if (n)
         {
             const unsigned cgrid = static_cast<unsigned>(std::min<uint64_t>(4ull * pl->n_sms, (static_cast<uint64_t>(n) + 255) / 256));
-            classify_kernel<<<cgrid, 256, 0, s>>>(d_seq_off, n, pl->db->d.k, class_reads, 0u, nullptr);
+            classify_kernel<<<cgrid, 256, 0, s>>>(d_seq_off, n, pl->db->d.k, class_reads, 0u, nullptr, nullptr);
             EPK_CUDA(cudaGetLastError());
             ++pl->n_launches;
             p.class_reads = class_reads;
+            p.totals = pl->totals.get();
             for (int c = 0; c < 2; ++c)
             {
                 p.cls = static_cast<uint32_t>(c);
@@ -695,9 +681,6 @@ extern "C" epk_status epk_place_partial_device(epk_placer* pl, const char* d_seq
                 EPK_CUDA(cudaGetLastError());
                 ++pl->n_launches;
             }
-            fold_counters_kernel<<<1, 1, 0, s>>>(counters, class_reads, 0u, pl->totals.get());
-            EPK_CUDA(cudaGetLastError());
-            ++pl->n_launches;
         }
         pl->totals_dirty = true;
         pl->last_stream = s;
