@@ -110,7 +110,7 @@ struct epk_placer
     uint32_t sets_fused[N_CLASSES] = { 0, 0, 0 };     // accumulator sets per CTA of the fused launch
     size_t smem_fused[N_CLASSES] = { 0, 0, 0 };
     device_buffer<uint32_t> fake_order;
-    device_buffer<unsigned long long> totals;          // folded work counters
+    device_buffer<unsigned long long> totals;          // running work counters (bumped by the launches)
     device_buffer<unsigned long long> device_counters; // per-launch counters of epk_place_device
     device_buffer<uint32_t> device_class_reads;
     chunk_slot slots[N_SLOTS];
@@ -184,8 +184,9 @@ namespace
 
     // One batch of n sequences already on the device: a count of the queries per class, then one
     // launch of the placement kernel per class (uint8 / uint16 / uint32 hit counts; a launch whose
-    // class is empty returns at once), then the counters. `class_mask` names the classes the caller
-    // knows to be present (all of them when it does not know).
+    // class is empty returns at once). The launches add their work counters to pl.totals themselves:
+    // nothing small follows a placement launch on its stream. `class_mask` names
+    // the classes the caller knows to be present (all of them when it does not know).
     void launch(epk_placer& pl, const char* d_seq, const uint64_t* d_off, uint32_t n, const epk_result& d_out,
                 unsigned long long* counters, uint32_t* class_reads, uint32_t class_mask, cudaStream_t stream)
     {
