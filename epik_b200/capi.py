@@ -23,6 +23,7 @@ SYMBOLS = [
     "epk_db_create_shard", "epk_shard_of_key", "epk_partial_row_bytes", "epk_place_partial_device",
     "epk_place_finalize_device", "epk_gather_ceiling_device",
     "epk_device_alloc", "epk_device_free", "epk_ipc_export", "epk_ipc_import", "epk_ipc_close",
+    "epk_gather_microbench", "epk_placer_set_trace", "epk_trace_term",
 ]
 
 
@@ -68,6 +69,11 @@ class Result(C.Structure):
 class Counters(C.Structure):
     _fields_ = [("n_reads", C.c_uint64), ("n_windows", C.c_uint64), ("n_hits", C.c_uint64), ("n_entries", C.c_uint64),
                 ("n_launches", C.c_uint64), ("n_short", C.c_uint64), ("n_unsupported", C.c_uint64)]
+
+
+class Microbench(C.Structure):
+    _fields_ = [("ms_per_launch", C.c_double), ("n_probes", C.c_uint64), ("n_hits", C.c_uint64),
+                ("n_entries", C.c_uint64), ("bytes", C.c_uint64), ("checksum", C.c_uint64)]
 
 
 _lib = None
@@ -132,6 +138,12 @@ def lib():
     l.epk_ipc_import.argtypes = [C.c_int, C.c_char_p, C.POINTER(C.c_void_p)]
     l.epk_ipc_close.restype = None
     l.epk_ipc_close.argtypes = [C.c_int, C.c_void_p]
+    l.epk_placer_set_trace.restype = C.c_int
+    l.epk_placer_set_trace.argtypes = [C.c_void_p, C.c_void_p]
+    l.epk_trace_term.restype = C.c_uint32
+    l.epk_trace_term.argtypes = [C.c_uint32] * 4
+    l.epk_gather_microbench.restype = C.c_int
+    l.epk_gather_microbench.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32, C.POINTER(Microbench)]
     l.epk_host_alloc.restype = C.c_void_p
     l.epk_host_alloc.argtypes = [C.c_size_t]
     l.epk_host_free.argtypes = [C.c_void_p]

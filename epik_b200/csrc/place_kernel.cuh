@@ -81,6 +81,8 @@ struct place_params
     uint64_t shard_stride;               // bytes from a row of shard g to the same row of shard g + 1
     uint32_t n_shards;
     uint32_t team;                       // warps per accumulator set (TEAM launches)
+    uint32_t prefetch;                   // L2 prefetch of a descriptor buffer's postings before it is gathered (PREFETCH_*)
+    uint32_t* trace;                     // [4 n] per query: keys looked up, keys found, postings, checksum of the k-mer stream (NULL: none)
 };
 
 
@@ -119,6 +121,17 @@ __device__ __forceinline__ void bump(const place_params& p, int slot, unsigned l
 {
     atomicAdd(p.counters + slot, v);
     if (p.totals) { atomicAdd(p.totals + slot, v); }
+}
+
+// One term of the per-query checksum of the k-mer stream (epk_placer_set_trace): position of the window, code,
+// number of keys of the window (1 = exact k-mer), length of the posting list found (0 = absent). The terms are
+// summed modulo 2^32, so the order in which lanes meet the windows does not matter. Mirrored by tests/helpers.py.
+__host__ __device__ inline uint32_t trace_term(uint32_t pos, uint32_t key, uint32_t group, uint32_t len)
+{
+    uint32_t h = pos * 0x9E3779B1u ^ key * 0x85EBCA6Bu ^ group * 0xC2B2AE35u ^ len * 0x27D4EB2Fu;
+    h ^= h >> 15; h *= 0x2C1B3C6Du;
+    h ^= h >> 12; h *= 0x297A2D39u;
+    return h ^ (h >> 15);
 }
 
 struct window_class
@@ -335,6 +348,39 @@ EPK_APPLY_SEGMENT(apply_segment_range, uint16_t, "u16", "u16", EPK_P0_RANGE, EPK
 EPK_APPLY_SEGMENT(apply_segment_range, uint32_t, "u32", "u32", EPK_P0_RANGE, EPK_START_EXTRA)
 #undef EPK_APPLY_SEGMENT
 
+// ---- L2 prefetch of the postings a descriptor buffer names ------------------------------------------
+//
+// gather_segments keeps U segments (U * 512 bytes) of a warp in flight; with 8 warps per SM that is far too
+// little to cover the latency of HBM. Before a buffer of descriptors is gathered, the warp therefore asks L2
+// for every 128-byte line (PREFETCH_LINES) or 32-byte sector (PREFETCH_SECTORS) of all its segments at once -
+// prefetch.global.L2 takes no register, no shared memory and no scoreboard, the two resources this kernel
+// has none left of - and the in-order gather that follows finds its postings in L2.
+enum prefetch_mode { PREFETCH_NONE = 0, PREFETCH_LINES = 1, PREFETCH_SECTORS = 2 };
+
+template<uint32_t GRANULE, uint32_t LANES_PER_SEG>
+__device__ __forceinline__ void prefetch_segments_as(const unsigned char* postings, uint32_t segs_shared, uint32_t n, uint32_t lane)
+{
+    constexpr uint32_t PER = 32u / LANES_PER_SEG; // segments per instruction
+    static_assert(PER <= SEG_PAD, "descriptors read past the end are the zero padding");
+    const uint32_t sub = lane % LANES_PER_SEG, which = lane / LANES_PER_SEG;
+    for (uint32_t s0 = 0; s0 < n; s0 += PER)
+    {
+        uint32_t pair, cnt;
+        asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(pair), "=r"(cnt) : "r"(segs_shared + (s0 + which) * 8u));
+        cnt &= 0x7FFFFFFFu; // (bit 31: skip flag of a range team's descriptor)
+        const uint64_t base = static_cast<uint64_t>(pair) * 16u;
+        const uint32_t head = static_cast<uint32_t>(base) & (GRANULE - 1u); // the postings array itself is 256-byte aligned
+        const uint32_t granules = (head + cnt * 8u + GRANULE - 1u) / GRANULE;
+        if (sub < granules) { asm volatile("prefetch.global.L2 [%0];" ::"l"(postings + (base - head) + sub * GRANULE)); }
+    }
+}
+__device__ __forceinline__ void prefetch_segments(uint32_t mode, const uint2* postings, uint32_t segs_shared, uint32_t n, uint32_t lane)
+{
+    const unsigned char* base = reinterpret_cast<const unsigned char*>(postings);
+    if (mode == PREFETCH_LINES) { prefetch_segments_as<128, 8>(base, segs_shared, n, lane); }       // 512 unaligned bytes: up to 5 lines
+    else if (mode == PREFETCH_SECTORS) { prefetch_segments_as<32, 32>(base, segs_shared, n, lane); } // up to 17 sectors
+}
+
 // Applies segs[0, n) in order; U segments are in flight while the previous U are applied.
 // segs[n, n + U) must hold zero descriptors.
 #ifndef EPK_GATHER_INLINE
@@ -349,9 +395,10 @@ __device__ __forceinline__ void sink_segment(uint32_t& sink, uint32_t lane2, con
 
 template<int U, class CT, bool SINK = false, bool RANGE = false>
 __device__ EPK_GATHER_INLINE void gather_segments(const uint2* __restrict__ postings, acc_ref acc, uint32_t segs_shared,
-                                             uint32_t n, uint32_t lane, uint32_t* sink_out = nullptr)
+                                             uint32_t n, uint32_t lane, uint32_t pf, uint32_t* sink_out = nullptr)
 {
     uint32_t sink = 0;
+    if (pf) { prefetch_segments(pf, postings, segs_shared, n, lane); }
     const unsigned char* lane_base = reinterpret_cast<const unsigned char*>(postings) + 16u * lane;
     const uint32_t lane2 = 2u * lane;
     seg_regs a[U], b[U];
@@ -543,18 +590,41 @@ __device__ __forceinline__ void clear_counts4(uint32_t* C, uint32_t j) { *reinte
 // (taking a quad clears it for the next query). rows_acc (database-sharded mode, the owner's side): the
 // partial rows of the shards in global memory, added in shard order as they are read - the sum never
 // exists anywhere but in registers.
+// take-and-clear of four consecutive counts through a shared-window address (the generic-pointer form made
+// nvcc recompute the window base - S2UR SR_CgaCtaId + ULEA, ~35 cycles - in every step of the sweep)
+__device__ __forceinline__ void take_counts4(uint32_t c_sh, uint32_t j, uint32_t (&c)[4], uint8_t)
+{
+    uint32_t w;
+    asm volatile("ld.shared.b32 %0, [%1];\n\tst.shared.b32 [%1], %2;" : "=r"(w) : "r"(c_sh + j), "r"(0u));
+    c[0] = w & 0xFFu; c[1] = (w >> 8) & 0xFFu; c[2] = (w >> 16) & 0xFFu; c[3] = w >> 24;
+}
+__device__ __forceinline__ void take_counts4(uint32_t c_sh, uint32_t j, uint32_t (&c)[4], uint16_t)
+{
+    uint32_t x, y;
+    asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];\n\tst.shared.v2.b32 [%2], {%3, %3};" : "=r"(x), "=r"(y) : "r"(c_sh + 2u * j), "r"(0u));
+    c[0] = x & 0xFFFFu; c[1] = x >> 16; c[2] = y & 0xFFFFu; c[3] = y >> 16;
+}
+__device__ __forceinline__ void take_counts4(uint32_t c_sh, uint32_t j, uint32_t (&c)[4], uint32_t)
+{
+    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];\n\tst.shared.v4.b32 [%4], {%5, %5, %5, %5};"
+                 : "=r"(c[0]), "=r"(c[1]), "=r"(c[2]), "=r"(c[3]) : "r"(c_sh + 4u * j), "r"(0u));
+}
+
 template<class CT>
 struct shared_acc
 {
     float* S;
     CT* C;
+    uint32_t s_sh, c_sh; // the same two arrays as shared-window addresses
+    __device__ __forceinline__ shared_acc(float* s, CT* c)
+        : S(s), C(c), s_sh(static_cast<uint32_t>(__cvta_generic_to_shared(s))), c_sh(static_cast<uint32_t>(__cvta_generic_to_shared(c))) {}
     __device__ __forceinline__ bool any(uint32_t j) const { return any_count4(C, j); }
     __device__ __forceinline__ float4 take(uint32_t j, uint32_t (&c)[4]) const
     {
-        const float4 s4 = *reinterpret_cast<const float4*>(S + j);
-        load_counts4(C, j, c);
-        *reinterpret_cast<float4*>(S + j) = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-        clear_counts4(C, j);
+        float4 s4;
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];\n\tst.shared.v4.b32 [%4], {%5, %5, %5, %5};"
+                     : "=f"(s4.x), "=f"(s4.y), "=f"(s4.z), "=f"(s4.w) : "r"(s_sh + 4u * j), "r"(0u));
+        take_counts4(c_sh, j, c, CT{});
         return s4;
     }
 };
@@ -712,15 +782,16 @@ __device__ __forceinline__ sweep_result sweep(const ACC acc, uint32_t np, uint32
         }
         if ((step & (step + 1)) == 0)
         {
-            // K-th largest of the lanes' maxima (0 while fewer than K lanes have a touched branch)
-            uint32_t mine = lane_max, kth = 0;
-            const uint32_t top = __reduce_max_sync(FULL, mine);
+            // K-th largest of the lanes' maxima (0 while fewer than K lanes have a touched branch). A round takes
+            // the maximum and strikes every lane that holds it: lanes that tie are struck together, which can only
+            // lower the result - still a lower bound of the K-th best score. (Striking one lane per round through
+            // ballot + ffs cost 130 cycles a round, 7 % of a 150-bp query.)
+            uint32_t mine = lane_max, kth = 0, top = 0;
             for (uint32_t i = 0; i < K; ++i)
             {
                 kth = __reduce_max_sync(FULL, mine);
-                if (kth == 0) { break; }
-                const uint32_t first = __ffs(__ballot_sync(FULL, mine == kth)) - 1u;
-                if (lane == first) { mine = 0; }
+                top = i == 0 ? kth : top;
+                mine = mine == kth ? 0u : mine;
             }
             if (kth > bar_key)
             {
@@ -738,10 +809,8 @@ __device__ __forceinline__ sweep_result sweep(const ACC acc, uint32_t np, uint32
 #pragma unroll
             for (int u = 0; u < 4; ++u) { e[u] = FAST ? exp10_small(s[u]) : exp10(static_cast<double>(s[u])); }
 #pragma unroll
-            for (int u = 0; u < 4; ++u)
-            {
-                if (key[u] >= cut_key) { mass += e[u]; }
-            }
+            for (int u = 0; u < 4; ++u) { e[u] = key[u] >= cut_key ? e[u] : 0.0; }
+            mass += (e[0] + e[1]) + (e[2] + e[3]); // a tree: four chained additions waited 8 cycles each
         }
         // ---- top-k candidates (place.cpp:134-159) ----
         // (a candidate has key >= bar_key: one compare of the quad's best key keeps the four exact tests, ties
@@ -943,7 +1012,7 @@ __device__ __noinline__ sweep_result team_sweep(const device_db& db, float* S, C
                                                 uint32_t member, uint32_t team)
 {
     const cand_buffers<TEAM_CAND_CAP> cb(member_base);
-    return run_sweep<shared_acc<CT>, TEAM_CAND_CAP>(db, shared_acc<CT>{ S, C }, np, nw32, gathered, K, lane, cb,
+    return run_sweep<shared_acc<CT>, TEAM_CAND_CAP>(db, shared_acc<CT>(S, C), np, nw32, gathered, K, lane, cb,
                                                     member * SWEEP_STEP, team * SWEEP_STEP);
 }
 
@@ -959,7 +1028,7 @@ __device__ __forceinline__ void dump_partial_row(const place_params& p, float* S
 
 template<int U, class CT, bool SINK>
 __device__ __noinline__ void range_gather(const device_db& db, acc_ref acc, const uint64_t* hits, uint32_t n_hits, uint2* my_segs,
-                                          uint32_t member, uint32_t team, uint32_t lane, uint32_t* sink_out);
+                                          uint32_t member, uint32_t team, uint32_t lane, uint32_t pf, uint32_t* sink_out);
 
 template<int U, class CT, bool SINK>
 __device__ __forceinline__ void team_helper_loop(const place_params& p, float* S, CT* C, uint32_t np, uint32_t lane,
@@ -980,7 +1049,7 @@ __device__ __forceinline__ void team_helper_loop(const place_params& p, float* S
         {
             uint32_t sink = 0;
             range_gather<U, CT, SINK>(p.db, acc, hits, cmd & ~TEAM_CMD_GATHER, reinterpret_cast<uint2*>(member_base), member, team,
-                                      lane, &sink);
+                                      lane, p.prefetch, &sink);
             if (SINK)
             {
                 sink = __reduce_xor_sync(FULL, sink);
@@ -1055,7 +1124,7 @@ constexpr uint32_t RANGE_HEADER_POSTINGS = 4;                        // = RANGE_
 
 template<int U, class CT, bool SINK>
 __device__ __noinline__ void range_gather(const device_db& db, acc_ref acc, const uint64_t* hits, uint32_t n_hits,
-                                          uint2* my_segs, uint32_t member, uint32_t team, uint32_t lane, uint32_t* sink_out)
+                                          uint2* my_segs, uint32_t member, uint32_t team, uint32_t lane, uint32_t pf, uint32_t* sink_out)
 {
     const uint32_t segs_shared = static_cast<uint32_t>(__cvta_generic_to_shared(my_segs));
     const uint32_t part_lo = member * (8u / team); // header entries are eighths of the padded branch range
@@ -1102,7 +1171,7 @@ __device__ __noinline__ void range_gather(const device_db& db, acc_ref acc, cons
             {
                 if (lane < SEG_PAD) { my_segs[n_desc + lane] = make_uint2(0, 0); }
                 __syncwarp();
-                gather_segments<U, CT, SINK, true>(db.postings, acc, segs_shared, n_desc, lane, sink_out);
+                gather_segments<U, CT, SINK, true>(db.postings, acc, segs_shared, n_desc, lane, pf, sink_out);
                 n_desc = 0;
                 __syncwarp();
             }
@@ -1112,7 +1181,7 @@ __device__ __noinline__ void range_gather(const device_db& db, acc_ref acc, cons
     {
         if (lane < SEG_PAD) { my_segs[n_desc + lane] = make_uint2(0, 0); }
         __syncwarp();
-        gather_segments<U, CT, SINK, true>(db.postings, acc, segs_shared, n_desc, lane, sink_out);
+        gather_segments<U, CT, SINK, true>(db.postings, acc, segs_shared, n_desc, lane, pf, sink_out);
     }
     __syncwarp();
 }
@@ -1164,6 +1233,18 @@ __device__ __forceinline__ void dump_partial_row(const place_params& p, float* S
         store_counts4_u16(c_out + 2ull * j, c);
     }
     __syncwarp();
+}
+
+// the segment descriptors of one lane's hit windows, in window order, from `at` on
+__device__ __forceinline__ void emit_lane_descriptors(uint2* at, const uint64_t (&slot)[WPL])
+{
+#pragma unroll
+    for (int r = 0; r < WPL; ++r)
+    {
+        const uint32_t l = static_cast<uint32_t>(slot[r] & LEN_MASK);
+        const uint32_t pair = static_cast<uint32_t>(slot[r] >> (LEN_BITS + 1));
+        for (uint32_t pos = 0; pos < l; pos += SEG_LEN) { *at++ = make_uint2(pair + pos / 2, min(l - pos, static_cast<uint32_t>(SEG_LEN))); }
+    }
 }
 
 // ---- the kernel ----------------------------------------------------------------------------------
@@ -1275,6 +1356,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
         const char* seq = p.seq + s0;
         bool has_ambiguous = false;
         uint32_t nseg = 0, sink = 0;
+        uint32_t tr_keys = 0, tr_hits = 0, tr_entries = 0, tr_sum = 0; // this lane's share of the query's trace record
         if (GATHER_ONLY && TEAM && lane == 0) { p.n_place[q] = 0; } // every member XORs its part in (after a team barrier)
         if (lane == 0) { ctr_windows += n_windows; }
 
@@ -1368,6 +1450,19 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
                 ctr_hits += l != 0;
                 ctr_entries += l;
             }
+            if (p.trace)
+            {
+#pragma unroll
+                for (int r = 0; r < WPL; ++r)
+                {
+                    if (!((look >> r) & 1u)) { continue; }
+                    const uint32_t l = static_cast<uint32_t>(slot[r] & LEN_MASK);
+                    ++tr_keys;
+                    tr_hits += l != 0;
+                    tr_entries += l;
+                    tr_sum += trace_term(static_cast<uint32_t>(c0) + w0 + r, keys[r], 1u, l);
+                }
+            }
             if (TEAM && db.range_headers)
             {
                 // range teams: publish the hits in window order, every member gathers its branch range of them
@@ -1389,7 +1484,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
                 __syncwarp();
                 team_sync(warp, team); // command: gather
                 uint2* my_desc = reinterpret_cast<uint2*>(team_area + sizeof(team_mailbox) + team * sizeof(team_result));
-                range_gather<U, CT, GATHER_ONLY>(db, acc, hits, n_hits, my_desc, 0u, team, lane, &sink);
+                range_gather<U, CT, GATHER_ONLY>(db, acc, hits, n_hits, my_desc, 0u, team, lane, p.prefetch, &sink);
                 team_sync(warp, team); // G
                 continue;
             }
@@ -1414,7 +1509,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
                     {
                         if (lane < SEG_PAD) { segs[nseg + lane] = make_uint2(0, 0); }
                         __syncwarp();
-                        gather_segments<U, CT, GATHER_ONLY>(db.postings, acc, segs_shared, nseg, lane, &sink);
+                        gather_segments<U, CT, GATHER_ONLY>(db.postings, acc, segs_shared, nseg, lane, p.prefetch, &sink);
                         nseg = 0;
                         __syncwarp();
                         continue;
@@ -1429,20 +1524,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
                     ++done;
                     continue;
                 }
-                if (fit)
-                {
-                    uint32_t at = nseg + excl - start;
-#pragma unroll
-                    for (int r = 0; r < WPL; ++r)
-                    {
-                        const uint32_t l = static_cast<uint32_t>(slot[r] & LEN_MASK);
-                        const uint32_t pair = static_cast<uint32_t>(slot[r] >> (LEN_BITS + 1));
-                        for (uint32_t pos = 0; pos < l; pos += SEG_LEN)
-                        {
-                            segs[at++] = make_uint2(pair + pos / 2, min(l - pos, static_cast<uint32_t>(SEG_LEN)));
-                        }
-                    }
-                }
+                if (fit) { emit_lane_descriptors(segs + (nseg + excl - start), slot); }
                 nseg += __shfl_sync(FULL, incl, done + n_fit - 1) - start;
                 done += n_fit;
             }
@@ -1451,7 +1533,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
         {
             if (lane < SEG_PAD) { segs[nseg + lane] = make_uint2(0, 0); }
             __syncwarp();
-            gather_segments<U, CT, GATHER_ONLY>(db.postings, acc, segs_shared, nseg, lane, &sink);
+            gather_segments<U, CT, GATHER_ONLY>(db.postings, acc, segs_shared, nseg, lane, p.prefetch, &sink);
         }
         __syncwarp();
         if (GATHER_ONLY)
@@ -1522,6 +1604,14 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
                             {
                                 ctr_hits += flen != 0;
                                 ctr_entries += flen;
+                                if (p.trace)
+                                {
+                                    ++tr_keys;
+                                    tr_hits += flen != 0;
+                                    tr_entries += flen;
+                                    tr_sum += trace_term(static_cast<uint32_t>(c0) + r * 32u + src, base_key | (code << shift),
+                                                         __popc(letter >> 8), flen);
+                                }
                             }
                             for (uint32_t e = lane; e < flen; e += 32)
                             {
@@ -1547,10 +1637,18 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
             __syncwarp();
         }
 
+        if (p.trace)
+        {
+            tr_keys = __reduce_add_sync(FULL, tr_keys);
+            tr_hits = __reduce_add_sync(FULL, tr_hits);
+            tr_entries = __reduce_add_sync(FULL, tr_entries);
+            tr_sum = __reduce_add_sync(FULL, tr_sum);
+            if (lane == 0) { *reinterpret_cast<uint4*>(p.trace + 4ull * q) = make_uint4(tr_keys, tr_hits, tr_entries, tr_sum); }
+        }
         // ---- correction, likelihood mass, top-k, weight ratios (place.cpp:417-422, 164-184, 134-159, 241-267) ----
         const uint32_t gathered = __reduce_add_sync(FULL, static_cast<uint32_t>(min(static_cast<unsigned long long>(ctr_entries - entries_before), 0xFFFFFFull)));
         if (TEAM) { finish_query_leader<CT>(p, S, C, np, static_cast<uint32_t>(n_windows), gathered, q, lane, team_area, warp, team); }
-        else { finish_query(p, shared_acc<CT>{ S, C }, np, n_windows, gathered, q, lane, cand_base); }
+        else { finish_query(p, shared_acc<CT>(S, C), np, n_windows, gathered, q, lane, cand_base); }
     }
 
 #pragma unroll

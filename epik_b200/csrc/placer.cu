@@ -100,6 +100,8 @@ struct epk_placer
     uint32_t keep_at_most = 0;
     double keep_factor = 0.0;
     uint32_t variant = 0;
+    uint32_t prefetch = 0;   // prefetch_mode of the gathers
+    uint32_t* trace = nullptr; // epk_placer_set_trace: DEVICE array of the caller, [4 n] of the next epk_place_device calls
     uint32_t chunk_reads = 0;
     int n_sms = 0;
     uint32_t warps_per_cta[N_CLASSES] = { 0, 0, 0 }; // 0: the accumulators of this class do not fit shared memory
@@ -188,7 +190,8 @@ namespace
     // nothing small follows a placement launch on its stream. `class_mask` names
     // the classes the caller knows to be present (all of them when it does not know).
     void launch(epk_placer& pl, const char* d_seq, const uint64_t* d_off, uint32_t n, const epk_result& d_out,
-                unsigned long long* counters, uint32_t* class_reads, uint32_t class_mask, cudaStream_t stream)
+                unsigned long long* counters, uint32_t* class_reads, uint32_t class_mask, cudaStream_t stream,
+                uint32_t* trace = nullptr)
     {
         place_params p{};
         p.db = pl.db->d;
@@ -196,6 +199,7 @@ namespace
         p.seq_off = d_off;
         p.n = n;
         p.keep_at_most = pl.keep_at_most;
+        p.prefetch = pl.prefetch;
         p.keep_factor = pl.keep_factor;
         p.n_place = d_out.n_place;
         p.branch = d_out.branch;
@@ -206,6 +210,8 @@ namespace
         p.fake_order = pl.fake_order.get();
         p.class_reads = class_reads;
         p.totals = pl.totals.get();
+        p.trace = trace;
+        if (trace && n) { EPK_CUDA(cudaMemsetAsync(trace, 0, 16ull * n, stream)); } // queries that are not placed keep zeros
         EPK_CUDA(cudaMemsetAsync(counters, 0, N_CLASSES * CTR_COUNT * sizeof(unsigned long long), stream));
         EPK_CUDA(cudaMemsetAsync(class_reads, 0, N_CLASSES * sizeof(uint32_t), stream));
         {
@@ -340,7 +346,9 @@ extern "C" epk_status epk_placer_create(const epk_db* db, uint64_t keep_at_most,
         pl->device = db->device;
         pl->keep_at_most = static_cast<uint32_t>(keep_at_most);
         pl->keep_factor = keep_factor;
-        pl->variant = opts ? opts->variant : 0;
+        pl->variant = opts ? opts->variant & 0xFu : 0;
+        // bits 4-7 of the variant word: 0 = this build's default, otherwise prefetch_mode + 1 (kernel experiments)
+        pl->prefetch = opts && (opts->variant >> 4) ? ((opts->variant >> 4) & 0xFu) - 1u : PREFETCH_LINES;
         pl->chunk_reads = opts && opts->chunk_reads ? opts->chunk_reads : (1u << 18);
 
         int max_smem = 0;
@@ -453,7 +461,20 @@ extern "C" epk_status epk_place_device(epk_placer* pl, const char* d_seq, const 
         pl->n_launches = 0;
         pl->n_reads = 0;
         launch(*pl, d_seq, d_seq_off, n, *d_out, pl->device_counters.get(), pl->device_class_reads.get(),
-               (1u << N_CLASSES) - 1u, s);
+               (1u << N_CLASSES) - 1u, s, pl->trace);
+    });
+}
+
+extern "C" uint32_t epk_trace_term(uint32_t pos, uint32_t key, uint32_t group, uint32_t len)
+{
+    return trace_term(pos, key, group, len);
+}
+
+extern "C" epk_status epk_placer_set_trace(epk_placer* pl, uint32_t* d_trace)
+{
+    return guarded([&] {
+        if (!pl) { throw error(EPK_E_INVALID, "null argument"); }
+        pl->trace = d_trace;
     });
 }
 
@@ -590,6 +611,7 @@ extern "C" epk_status epk_gather_ceiling_device(epk_placer* pl, const char* d_se
         p.seq_off = d_seq_off;
         p.n = n;
         p.keep_at_most = pl->keep_at_most;
+        p.prefetch = pl->prefetch;
         p.n_place = d_checksum;
         p.letters = pl->db->letters.get();
         p.cls = 0;
@@ -641,6 +663,7 @@ extern "C" epk_status epk_place_partial_device(epk_placer* pl, const char* d_seq
         p.seq_off = d_seq_off;
         p.n = n;
         p.keep_at_most = pl->keep_at_most;
+        p.prefetch = pl->prefetch;
         p.keep_factor = pl->keep_factor;
         p.letters = pl->db->letters.get();
         p.fake_order = pl->fake_order.get();
@@ -707,6 +730,7 @@ extern "C" epk_status epk_place_finalize_device(epk_placer* pl, const void* d_ro
         p.seq_off = d_seq_off;
         p.n = n;
         p.keep_at_most = pl->keep_at_most;
+        p.prefetch = pl->prefetch;
         p.keep_factor = pl->keep_factor;
         p.n_place = d_out->n_place;
         p.branch = d_out->branch;

@@ -204,6 +204,29 @@ class Placer:
         s = None if stream is None else C.c_void_p(stream.cuda_stream)
         capi.check(capi.lib().epk_place_device(self.handle, d_seq.data_ptr(), d_off.data_ptr(), int(n), C.byref(res), s))
 
+    def trace_packed(self, data, offsets):
+        """The placement kernel's own k-mer stream evidence (epk_placer_set_trace) for a packed batch: places the
+        batch with everything resident in HBM and returns (trace [n, 4] uint32, results dict of numpy arrays)."""
+        import torch
+        n, K = len(offsets) - 1, self.keep_at_most
+        dev = torch.device("cuda", self.db.device)
+        d_seq = torch.from_numpy(np.ascontiguousarray(data, np.uint8)).to(dev) if len(data) else torch.zeros(1, dtype=torch.uint8, device=dev)
+        d_off = torch.from_numpy(np.ascontiguousarray(offsets, np.uint64).view(np.int64)).to(dev)
+        d_trace = torch.full((max(n, 1), 4), -1, dtype=torch.int32, device=dev)
+        d_out = {"n_place": torch.zeros(max(n, 1), dtype=torch.int32, device=dev),
+                 "branch": torch.zeros(max(n, 1) * K, dtype=torch.int32, device=dev),
+                 "score": torch.zeros(max(n, 1) * K, dtype=torch.float32, device=dev),
+                 "lwr": torch.zeros(max(n, 1) * K, dtype=torch.float64, device=dev),
+                 "count": torch.zeros(max(n, 1) * K, dtype=torch.int32, device=dev)}
+        capi.check(capi.lib().epk_placer_set_trace(self.handle, C.c_void_p(d_trace.data_ptr())))
+        try:
+            self.place_device(d_seq, d_off, n, d_out)
+            torch.cuda.synchronize(dev)
+        finally:
+            capi.check(capi.lib().epk_placer_set_trace(self.handle, None))
+        res = {k: v.cpu().numpy() for k, v in d_out.items()}
+        return d_trace.cpu().numpy().view(np.uint32)[:n], res
+
     # ------------------------------------------------------------- database-sharded mode -----
     def partial_row_bytes(self) -> int:
         return int(capi.lib().epk_partial_row_bytes(self.handle))

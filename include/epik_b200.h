@@ -162,10 +162,23 @@ epk_status epk_group_batch(const char* seq, const uint64_t* seq_off, uint32_t n,
 /* The k-mer stream of one sequence in the order query_kmers (place.cpp:278-316) consumes it, one
  * record per (window, resolved key): pos = window start, key = code, group = number of keys of
  * the window (1 = unambiguous), hit_len = posting-list length or -1 when the key is absent.
- * Computed ON THE DEVICE by the same encode + probe code the placement kernel runs. Returns the
+ * Computed ON THE DEVICE by a one-thread kernel through classify_window / db_search (the placement kernel's
+ * ambiguous-window path uses the same two; its exact k-mers come from a rolling per-lane encoder, whose
+ * output is exposed by epk_placer_set_trace below). Returns the
  * number of records through *n_out (only `cap` are written). HOST buffers. */
 epk_status epk_kmers(const epk_db* db, const char* seq, uint64_t len, uint64_t cap,
                      uint32_t* pos, uint32_t* key, uint32_t* group, int64_t* hit_len, uint64_t* n_out);
+
+/* The same evidence from the placement kernel itself: while d_trace (DEVICE memory, 4 uint32 per query of the
+ * largest batch to come; NULL switches it off) is set, every epk_place_device call leaves per query
+ *   { keys looked up, keys found, postings of the keys found, checksum }
+ * where the keys are those of query_kmers (place.cpp:294-313): one per exact k-mer, one per resolution of a
+ * window with a single ambiguous letter; checksum = sum modulo 2^32 over them of epk_trace_term(window
+ * position, code, keys of the window, list length or 0). These are the rolling encoder and the probes of the
+ * hot kernel, not a second implementation: a dropped, duplicated or miscoded window changes the record.
+ * Queries that are not placed (too short, unsupported) leave zeros. */
+epk_status epk_placer_set_trace(epk_placer* placer, uint32_t* d_trace);
+uint32_t epk_trace_term(uint32_t pos, uint32_t key, uint32_t group, uint32_t len);
 
 /* Work counters of the last epk_place / epk_place_device call on this placer (for roofline
  * arithmetic): windows looked up, hits, posting entries gathered, kernels launched. */
@@ -235,6 +248,20 @@ void epk_ipc_close(int device, void* p);
  * receives one word per query; epk_placer_counters reports the postings gathered. */
 epk_status epk_gather_ceiling_device(epk_placer* placer, const char* d_seq, const uint64_t* d_seq_off, uint32_t n,
                                      uint32_t* d_checksum, void* stream);
+
+/* A second, independent measuring stick: n_probes uniformly random k-mer codes looked up in this database's
+ * key table, every hit's posting list gathered, by a kernel with no accumulators, no shared-memory budget and
+ * full occupancy (method 0 / 1: 128-bit loads, 4 / 8 lists in flight per warp, 32 warps per SM; method 2: bulk
+ * asynchronous copies of whole lists into shared memory, completion on an mbarrier). What the memory system
+ * gives the path's access pattern, rather than what the placement kernel's design asks of it. Synchronous;
+ * `reps` timed launches after one warm-up. bytes = 16 * n_probes + 8 * n_entries (SURVEY.md 8d's accounting). */
+typedef struct epk_microbench
+{
+    double ms_per_launch;
+    uint64_t n_probes, n_hits, n_entries, bytes, checksum;
+} epk_microbench;
+epk_status epk_gather_microbench(const epk_db* db, uint64_t n_probes, uint64_t seed, uint32_t method,
+                                 uint32_t reps, epk_microbench* out);
 
 /* Pinned host memory for the buffers of epk_place. */
 void* epk_host_alloc(size_t bytes);

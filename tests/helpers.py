@@ -116,3 +116,29 @@ def assert_close_placements(got: dict, want: dict, score_rtol: float = 1e-5, lwr
             near = [jj for jj in (j - 1, j + 1) if 0 <= jj < wn[i] and abs(ws[i, jj] - ws[i, j]) <= score_rtol * abs(ws[i, j])]
             assert near or j == K - 1, "%s row %d: branches differ beyond near ties" % (what, i)
     assert swapped <= max(1, int(max_reordered * len(wn))), "%s: %d rows reordered" % (what, swapped)
+
+
+def trace_terms(pos, key, group, length):
+    """epk_trace_term (place_kernel.cuh::trace_term) over numpy arrays, modulo 2^32."""
+    u = lambda a: np.asarray(a).astype(np.uint64)
+    M = np.uint64(0xFFFFFFFF)
+    h = ((u(pos) * np.uint64(0x9E3779B1)) ^ (u(key) * np.uint64(0x85EBCA6B)) ^ (u(group) * np.uint64(0xC2B2AE35))
+         ^ (u(length) * np.uint64(0x27D4EB2F))) & M
+    h ^= h >> np.uint64(15)
+    h = (h * np.uint64(0x2C1B3C6D)) & M
+    h ^= h >> np.uint64(12)
+    h = (h * np.uint64(0x297A2D39)) & M
+    return (h ^ (h >> np.uint64(15))).astype(np.uint32)
+
+
+def expected_trace(oracle, data, off):
+    """Per query {keys looked up, keys found, postings, checksum} from the oracle's k-mer stream (orc_kmers)."""
+    n = len(off) - 1
+    out = np.zeros((n, 4), np.uint32)
+    for i in range(n):
+        seq = bytes(data[int(off[i]):int(off[i + 1])])
+        pos, key, group, hit = oracle.kmers(seq)
+        found = np.maximum(np.asarray(hit, np.int64), 0)
+        out[i] = (len(pos), int((np.asarray(hit) >= 0).sum()), int(found.sum() & 0xFFFFFFFF),
+                  int(trace_terms(pos, key, group, found).sum(dtype=np.uint64) & np.uint64(0xFFFFFFFF)))
+    return out

@@ -404,3 +404,51 @@ def test_large_trees_sweep_in_teams(n_leaves, read_len, variant, k, m):
     again = p.place_packed(data, off)
     for name in ("n_place", "branch", "score", "lwr", "count"):
         assert np.array_equal(again[name], got[name]), name
+
+
+def _ragged_reads(alphabet, lengths, seed, spoil=0.01):
+    """Random reads of the given lengths with gaps, N / X and two-way ambiguity letters sprinkled in."""
+    rng = np.random.default_rng(seed)
+    plain = np.frombuffer(b"ACGT" if alphabet == 0 else b"RHKDESTNQCGPAILMFWYV", np.uint8)
+    odd = np.frombuffer(b"-NRY" if alphabet == 0 else b"-XBZ", np.uint8)
+    total = int(np.sum(lengths))
+    data = plain[rng.integers(0, len(plain), total)].copy()
+    hit = rng.random(total) < spoil
+    data[hit] = odd[rng.integers(0, len(odd), int(hit.sum()))]
+    off = np.concatenate([[0], np.cumsum(lengths)]).astype(np.uint64)
+    return data, off
+
+
+@pytest.mark.parametrize("shape", ["dna-direct", "aa-hashed", "dna-range-teams", "dna-k12"])
+def test_hot_kernel_kmer_stream_matches_the_oracle(shape):
+    """K-mer codes and database hits of the PLACEMENT kernel itself (its per-lane rolling encoder and its probes,
+    epk_placer_set_trace), per read, against the oracle's k-mer stream (place.cpp:294-313): number of keys looked
+    up, keys found, postings, and a checksum over (window position, code, keys of the window, list length).
+    Lengths cover 1..8 windows per lane, the 256-window chunk boundary and multi-chunk reads; gaps and
+    ambiguous letters fall on and around lane boundaries."""
+    if shape == "aa-hashed":
+        alphabet, k, flat = 1, 6, synth.make_db(1, 6, 150, 0.02, 6.0, seed=21, key_space_limit=1 << 22)
+    elif shape == "dna-range-teams":
+        alphabet, k, flat = 0, 8, synth.make_db(0, 8, 10000, 0.6, 24.0, seed=22)
+    elif shape == "dna-k12":
+        alphabet, k, flat = 0, 12, synth.make_db(0, 12, 300, 0.05, 8.0, seed=23)
+    else:
+        alphabet, k, flat = 0, 10, synth.make_db(0, 10, 600, 0.6, 12.0, seed=20)
+    windows = [1, 2, 31, 32, 33, 63, 64, 65, 96, 97, 128, 141, 160, 161, 192, 224, 225, 255, 256, 257, 300, 511, 512, 513, 700]
+    lengths = np.array([w + k - 1 for w in windows] * 8 + [150] * 200 + [k - 1], np.int64)
+    data, off = _ragged_reads(alphabet, lengths, seed=31)
+    db = Database(flat)
+    p = Placer(db)
+    trace, got = p.trace_packed(data, off)
+    oracle, kind = best_oracle(flat)
+    want = helpers.expected_trace(oracle, data, off)
+    bad = np.nonzero((trace != want).any(axis=1))[0]
+    assert len(bad) == 0, "reads %s: kernel %s, oracle %s" % (bad[:5], trace[bad[:5]], want[bad[:5]])
+    assert want[:, 0].sum() > 0 and want[:, 1].sum() > 0 and (want[:, 0] != np.array(list(lengths - k + 1))).any()
+    # and the placements of the same launch are the reference's
+    ref = oracle.place_packed(data, off, threads=4)
+    K = 7
+    shaped = {"n_place": got["n_place"].view(np.uint32), "branch": got["branch"].view(np.uint32).reshape(-1, K),
+              "score": got["score"].reshape(-1, K), "lwr": got["lwr"].reshape(-1, K),
+              "count": got["count"].view(np.uint32).reshape(-1, K)}
+    helpers.assert_same_placements(shaped, ref, what="trace launch " + kind, lengths=False)
