@@ -140,6 +140,12 @@ static void build_db(const epk_db_desc& d, const epk_load_filter* filter, int de
     {
         throw error(EPK_E_INVALID, "null array in the database description");
     }
+    if (d.n_keys && d.offsets[0] != 0) { throw error(EPK_E_INVALID, "offsets[0] must be 0"); }
+    // every kernel below trusts e - b of neighbouring offsets: a decreasing pair would wrap into a list of 2^64 postings
+    for (uint64_t i = 0; i < d.n_keys; ++i)
+    {
+        if (d.offsets[i + 1] < d.offsets[i]) { throw error(EPK_E_INVALID, "offsets must be non-decreasing"); }
+    }
     int n_devices = 0;
     if (cudaGetDeviceCount(&n_devices) != cudaSuccess || n_devices == 0)
     {
@@ -152,7 +158,6 @@ static void build_db(const epk_db_desc& d, const epk_load_filter* filter, int de
 
     const uint64_t n_keys = d.n_keys;
     const uint64_t n_total = n_keys ? d.offsets[n_keys] : 0;
-    if (n_keys && d.offsets[0] != 0) { throw error(EPK_E_INVALID, "offsets[0] must be 0"); }
     if (n_total && !d.entries) { throw error(EPK_E_INVALID, "null entries"); }
 
     float omega = d.omega;

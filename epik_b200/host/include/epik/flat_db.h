@@ -8,6 +8,7 @@
 #ifndef EPIK_B200_HOST_FLAT_DB_H
 #define EPIK_B200_HOST_FLAT_DB_H
 
+#include <algorithm>
 #include <cstdint>
 #include <cstring>
 #include <fstream>
@@ -141,8 +142,25 @@ namespace epik
             in.read(reinterpret_cast<char*>(&has_filter), 8);
             in.read(reinterpret_cast<char*>(&newick_bytes), 8);
             if (!in) { throw std::runtime_error("Truncated database file"); }
+            // the header is not trusted: the counts must fit the file before anything is allocated for them
+            {
+                const auto here = in.tellg();
+                in.seekg(0, std::ios::end);
+                const uint64_t left = static_cast<uint64_t>(in.tellg() - here);
+                in.seekg(here);
+                if (n_keys > left / 12 || n_entries > left / 8 || n_nodes > left / 24 || newick_bytes > left)
+                {
+                    throw std::runtime_error("Corrupt database file: the header counts exceed the file size");
+                }
+            }
             detail::read_array(in, db.keys, n_keys, true);
             detail::read_array(in, db.offsets, n_keys + 1, false);
+            // offsets describe the entries array: 0 first, non-decreasing, n_entries last (epk_db_create checks the
+            // same again; here the message can name the file)
+            if (db.offsets.front() != 0 || db.offsets.back() != n_entries || !std::is_sorted(db.offsets.begin(), db.offsets.end()))
+            {
+                throw std::runtime_error("Corrupt database file: posting-list offsets of " + filename + " are inconsistent");
+            }
             detail::read_array(in, db.entries, n_entries, false);
             if (has_filter) { detail::read_array(in, db.filter_value, n_keys, true); }
             detail::read_array(in, db.branch_length, n_nodes, false);

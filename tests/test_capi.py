@@ -79,6 +79,23 @@ def test_group_batch_is_first_occurrence():
     assert list(rep) == [0, 1, 0, 3, 4, 1, 3]
 
 
+def test_malformed_offsets_are_refused_before_anything_runs():
+    """A CSR description whose offsets decrease (corrupt or hand-made database) is EPK_E_INVALID - checked on the host,
+    before any kernel computes a list length from it (and before a device is even looked for)."""
+    from epik_b200.placer import ENTRY_DTYPE
+    keys = np.array([1, 2, 3], np.uint32)
+    entries = np.zeros(4, ENTRY_DTYPE)
+    one = np.ones(3, np.float64)
+    num = np.ones(3, np.uint64)
+    p = lambda a: a.ctypes.data_as(C.c_void_p)
+    for offsets, message in (([0, 3, 2, 4], "non-decreasing"), ([1, 2, 3, 4], "offsets[0]")):
+        off = np.array(offsets, np.uint64)
+        desc = capi.DbDesc(0, 4, 1.5, 3, p(keys), p(off), p(entries), None, 3, p(one), p(num), p(one))
+        handle = C.c_void_p()
+        status = capi.lib().epk_db_create(C.byref(desc), None, 0, C.byref(handle))
+        assert status == capi.EPK_E_INVALID and message in capi.lib().epk_last_error().decode(), (offsets, status)
+
+
 def test_no_cpu_fallback():
     """Without a CUDA device the product path must fail loudly, not compute on the host."""
     if capi.lib().epk_device_count() > 0:

@@ -80,6 +80,35 @@ def test_epkdb_round_trip(tmp_path):
         assert np.array_equal(getattr(back, name), getattr(db, name)), name
 
 
+def test_corrupt_epkdb_is_refused_by_the_loader(built, tmp_path):
+    """The .epkdb header and offsets are not trusted: inconsistent offsets or counts larger than the file are an
+    "Error: ..." exit like any other bad input (main.cpp:384-388), before anything is uploaded."""
+    from epik_b200 import flatdb, synth
+    subprocess.run(["make", "-s", "-C", os.path.join(ROOT, "epik_b200", "host")], check=True)
+    flat = synth.make_db(0, 6, 20, 0.5, 4.0, seed=5)
+    good = str(tmp_path / "good.epkdb")
+    flatdb.save_epkdb(flat, good, synth.tree_newick(flat.branch_length, flat.meta["parent"]))
+    q_path = str(tmp_path / "q.fasta")
+    open(q_path, "w").write(">a\nACGTACGTACGT\n")
+    raw = bytearray(open(good, "rb").read())
+    n_keys = int(np.frombuffer(raw[24:32], np.uint64)[0])
+    keys_bytes = (4 * n_keys + 7) // 8 * 8
+    exe = os.path.join(ROOT, "bin", "epik", "epik-dna")
+    cases = {}
+    bad = bytearray(raw)
+    at = 56 + keys_bytes + 8 * 2                       # offsets[2] := a huge value -> decreasing at offsets[3]
+    bad[at:at + 8] = np.uint64(1 << 40).tobytes()
+    cases["offsets"] = (bad, "offsets")
+    bad = bytearray(raw)
+    bad[32:40] = np.uint64(1 << 50).tobytes()          # n_entries far beyond the file
+    cases["counts"] = (bad, "exceed the file size")
+    for name, (blob, message) in cases.items():
+        path = str(tmp_path / (name + ".epkdb"))
+        open(path, "wb").write(bytes(blob))
+        r = subprocess.run([exe, "-d", path, "-q", q_path, "-o", str(tmp_path)], capture_output=True, text=True)
+        assert r.returncode == 255 and "Error:" in r.stderr and message in r.stderr, (name, r.returncode, r.stderr)
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("states", ["nucl", "amino"])
 def test_driver_end_to_end(built, tmp_path, states):
