@@ -134,6 +134,26 @@ __host__ __device__ inline uint32_t trace_term(uint32_t pos, uint32_t key, uint3
     return h ^ (h >> 15);
 }
 
+// ---- phase clocks (kernel experiments only: -DEPK_PHASE_CLOCKS) ------------------------------------------
+// Cycles the leader warps spent per phase of a query, summed over the launch: 0 claim + offsets, 1 letters + encode +
+// probe (until the slots are in), 2 descriptors, 3 gather + accumulate, 4 ambiguous windows, 5 sweep, 6 weight ratios
+// + rows out, 7 queries. Read and cleared by epk_debug_phase_clocks.
+#ifndef EPK_ABLATE
+#define EPK_ABLATE 0 // kernel experiments: 1 = no likelihood mass, 2 = no candidates, 4 = postings loaded but not accumulated
+#endif
+#ifdef EPK_PHASE_CLOCKS
+__device__ unsigned long long g_phase_clocks[8];
+#define EPK_PHASE_DECL uint32_t ph_acc[8] = { 0, 0, 0, 0, 0, 0, 0, 0 }; uint32_t ph_t = clock();
+#define EPK_PHASE(i) { const uint32_t ph_now = clock(); ph_acc[i] += ph_now - ph_t; ph_t = ph_now; }
+#define EPK_PHASE_COUNT(i) { ++ph_acc[i]; }
+#define EPK_PHASE_FLUSH if (lane == 0) { for (int i = 0; i < 8; ++i) { atomicAdd(g_phase_clocks + i, static_cast<unsigned long long>(ph_acc[i])); } }
+#else
+#define EPK_PHASE_DECL
+#define EPK_PHASE(i)
+#define EPK_PHASE_COUNT(i)
+#define EPK_PHASE_FLUSH
+#endif
+
 struct window_class
 {
     uint32_t key;      // code with 0 in the place of an ambiguous letter
@@ -421,7 +441,7 @@ __device__ EPK_GATHER_INLINE void gather_segments(const uint2* __restrict__ post
 #pragma unroll
         for (int u = 0; u < U; ++u)
         {
-            if (SINK) { sink_segment(sink, lane2, a[u]); }
+            if (SINK || (EPK_ABLATE & 4)) { sink_segment(sink, lane2, a[u]); }
             else if (RANGE) { apply_segment_range(acc, lane2, a[u], CT{}); }
             else { apply_segment(acc, lane2, a[u], CT{}); }
         }
@@ -434,12 +454,12 @@ __device__ EPK_GATHER_INLINE void gather_segments(const uint2* __restrict__ post
 #pragma unroll
         for (int u = 0; u < U; ++u)
         {
-            if (SINK) { sink_segment(sink, lane2, b[u]); }
+            if (SINK || (EPK_ABLATE & 4)) { sink_segment(sink, lane2, b[u]); }
             else if (RANGE) { apply_segment_range(acc, lane2, b[u], CT{}); }
             else { apply_segment(acc, lane2, b[u], CT{}); }
         }
     }
-    if (SINK) { *sink_out ^= sink; }
+    if (SINK || (EPK_ABLATE & 4)) { if (sink_out) { *sink_out ^= sink; } }
 }
 
 // One long list on its own (only when a single chunk's lists overflow the segment buffer).
@@ -803,7 +823,7 @@ __device__ __forceinline__ sweep_result sweep(const ACC acc, uint32_t np, uint32
         ++step;
         // ---- likelihood mass (place.cpp:164-184) ----
         const uint32_t best4 = max(max(key[0], key[1]), max(key[2], key[3])); // best key of the quad
-        if (__any_sync(FULL, best4 >= cut_key))
+        if (!(EPK_ABLATE & 1) && __any_sync(FULL, best4 >= cut_key))
         {
             double e[4];
 #pragma unroll
@@ -815,12 +835,195 @@ __device__ __forceinline__ sweep_result sweep(const ACC acc, uint32_t np, uint32
         // ---- top-k candidates (place.cpp:134-159) ----
         // (a candidate has key >= bar_key: one compare of the quad's best key keeps the four exact tests, ties
         // and all, out of the common path)
-        if (__any_sync(FULL, best4 >= max(bar_key, 1u)))
+        if (!(EPK_ABLATE & 2) && __any_sync(FULL, best4 >= max(bar_key, 1u)))
         {
 #pragma unroll
             for (int u = 0; u < 4; ++u)
             {
                 const bool cand = (key[u] > bar_key) | ((key[u] == bar_key) & (j + u < bar_branch));
+                const uint32_t ballot = __ballot_sync(FULL, cand);
+                if (ballot == 0) { continue; }
+                if (cand)
+                {
+                    const uint32_t at = n_cand + __popc(ballot & ((1u << lane) - 1u));
+                    cand_key[at] = key[u];
+                    cand_branch[at] = j + u;
+                    cand_count[at] = c[u];
+                }
+                n_cand += __popc(ballot);
+                __syncwarp();
+                if (n_cand > CAP - 32)
+                {
+                    // keep the best K, raise the bar to the K-th of them
+                    n_cand = select_best(cand_key, cand_branch, cand_count, n_cand, K, lane, out.key, out.branch, out.count);
+                    if (n_cand == K)
+                    {
+                        bar_key = __shfl_sync(FULL, out.key, K - 1);
+                        bar_branch = __shfl_sync(FULL, out.branch, K - 1);
+                    }
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1)
+    {
+        mass += __shfl_xor_sync(FULL, mass, d);
+        touched += __shfl_xor_sync(FULL, touched, d);
+    }
+    __syncwarp();
+    out.n_keep = select_best(cand_key, cand_branch, cand_count, n_cand, K, lane, out.key, out.branch, out.count);
+    out.mass = mass;
+    out.touched = touched;
+    return out;
+}
+
+// ---- the dense sweep over shared-memory accumulators: two passes ---------------------------------------
+//
+// Phase clocks of the one-pass sweep on C2 (150-bp reads, 4999 branches; gpurun r3b): 36 k cycles per query, of
+// which 12 k the likelihood mass - four dependent DFMA chains per lane against ~20 cycles of FP64 latency - and
+// 13 k the candidate bookkeeping against a bar that is refreshed six times per query: votes, ballots and branches
+// in 15 of the 40 steps. Here
+//   pass 1 corrects NQ quads (4 * NQ branches) per lane and iteration - 4 * NQ independent 10^s chains -, adds the
+//          mass, tracks the lane's best key and leaves the KEYS in place of the sums (counts stay);
+//   then   the bar is the K-th largest of the lanes' best keys over the WHOLE query - at most K - 1 lanes, hence
+//          typically a dozen branches, beat it;
+//   pass 2 re-reads the keys (LDS.128 per quad), clears sums and counts, and hands the few quads that reach the
+//          bar to the same tie-aware candidate code as the one-pass sweep.
+// Same results as sweep<..., FAST = true, DENSE = true>: scores, counts, ties; the mass differs in the order of
+// its FP64 additions only.
+#ifndef EPK_SWEEP_NQ
+#define EPK_SWEEP_NQ 2
+#endif
+__device__ __forceinline__ void load_counts4_sh(uint32_t c_sh, uint32_t j, uint32_t (&c)[4], uint8_t)
+{
+    uint32_t w;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w) : "r"(c_sh + j));
+    c[0] = w & 0xFFu; c[1] = (w >> 8) & 0xFFu; c[2] = (w >> 16) & 0xFFu; c[3] = w >> 24;
+}
+__device__ __forceinline__ void load_counts4_sh(uint32_t c_sh, uint32_t j, uint32_t (&c)[4], uint16_t)
+{
+    uint32_t x, y;
+    asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(x), "=r"(y) : "r"(c_sh + 2u * j));
+    c[0] = x & 0xFFFFu; c[1] = x >> 16; c[2] = y & 0xFFFFu; c[3] = y >> 16;
+}
+__device__ __forceinline__ void load_counts4_sh(uint32_t c_sh, uint32_t j, uint32_t (&c)[4], uint32_t)
+{
+    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(c[0]), "=r"(c[1]), "=r"(c[2]), "=r"(c[3]) : "r"(c_sh + 4u * j));
+}
+
+template<class CT, int CAP, int NQ>
+__device__ __forceinline__ sweep_result sweep_dense_two_pass(const shared_acc<CT> acc, uint32_t np, uint32_t nw32, float logthr,
+                                                             float kf, float rcp_k, uint32_t K, uint32_t lane,
+                                                             const cand_buffers<CAP>& cb, uint32_t scan0, uint32_t stride)
+{
+    uint32_t* const cand_key = cb.key;
+    uint32_t* const cand_branch = cb.branch;
+    uint32_t* const cand_count = cb.count;
+    sweep_result out{ 0.0, 0u, 0u, 0u, NO_BRANCH, 0u };
+    double mass = 0.0;
+    uint32_t touched = 0, lane_max = 0, cut_key = 1, step = 0;
+    const uint32_t lane4 = 4u * lane;
+
+    // ---- pass 1: correction (place.cpp:417-422), likelihood mass (place.cpp:164-184), keys in place of the sums ----
+    for (uint32_t scan = scan0; scan < np; scan += NQ * stride)
+    {
+        float sc[NQ][4];
+        uint32_t key[NQ][4];
+        uint32_t best = 0;
+#pragma unroll
+        for (int q = 0; q < NQ; ++q)
+        {
+            const uint32_t j = scan + q * stride + lane4;
+            float4 s4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            uint32_t c[4] = { 0u, 0u, 0u, 0u };
+            if (q == 0 || scan + q * stride < np) // (warp-uniform)
+            {
+                asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(s4.x), "=f"(s4.y), "=f"(s4.z), "=f"(s4.w) : "r"(acc.s_sh + 4u * j));
+                load_counts4_sh(acc.c_sh, j, c, CT{});
+            }
+            const float sum[4] = { s4.x, s4.y, s4.z, s4.w };
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+            {
+                // the reference converts the size_t difference to float (place.cpp:420)
+                const float x = __fadd_rn(sum[u], __fmul_rn(static_cast<float>(nw32 - c[u]), logthr));
+                sc[q][u] = div_by_k_plain(x, kf, rcp_k);
+                key[q][u] = c[u] != 0 ? score_key_raw(sc[q][u]) : 0u; // (no -0 can come out of the division)
+                touched += c[u] != 0;
+            }
+            best = max(best, max(max(key[q][0], key[q][1]), max(key[q][2], key[q][3])));
+        }
+        lane_max = max(lane_max, best);
+        if ((step & (step + 1)) == 0)
+        {
+            // mass terms 20 decades under the best score seen so far are negligible
+            const uint32_t top = __reduce_max_sync(FULL, lane_max);
+            if (top != 0) { cut_key = max(cut_key, score_key_raw(key_score(top) - MASS_CUTOFF_DECADES)); }
+        }
+        ++step;
+        if (!(EPK_ABLATE & 1) && __any_sync(FULL, best >= cut_key))
+        {
+            double e[NQ][4];
+#pragma unroll
+            for (int q = 0; q < NQ; ++q)
+            {
+#pragma unroll
+                for (int u = 0; u < 4; ++u) { e[q][u] = exp10_small(sc[q][u]); }
+            }
+#pragma unroll
+            for (int q = 0; q < NQ; ++q)
+            {
+#pragma unroll
+                for (int u = 0; u < 4; ++u) { e[q][u] = key[q][u] >= cut_key ? e[q][u] : 0.0; }
+            }
+            double part = 0.0;
+#pragma unroll
+            for (int q = 0; q < NQ; ++q) { part += (e[q][0] + e[q][1]) + (e[q][2] + e[q][3]); }
+            mass += part;
+        }
+#pragma unroll
+        for (int q = 0; q < NQ; ++q)
+        {
+            if (q == 0 || scan + q * stride < np)
+            {
+                const uint32_t j = scan + q * stride + lane4;
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(acc.s_sh + 4u * j), "r"(key[q][0]), "r"(key[q][1]),
+                             "r"(key[q][2]), "r"(key[q][3]));
+            }
+        }
+    }
+
+    // ---- the bar: K-th largest of the lanes' best keys (0 while fewer than K lanes have a touched branch). A round
+    // takes the maximum and strikes every lane that holds it; lanes that tie are struck together, which can only
+    // lower the result - still a lower bound of the K-th best key of the query. ----
+    uint32_t bar_key = 0, bar_branch = NO_BRANCH;
+    {
+        uint32_t mine = lane_max, kth = 0;
+        for (uint32_t i = 0; i < K; ++i)
+        {
+            kth = __reduce_max_sync(FULL, mine);
+            mine = mine == kth ? 0u : mine;
+        }
+        bar_key = kth;
+    }
+
+    // ---- pass 2: the candidates (place.cpp:134-159); sums and counts cleared for the next query ----
+    uint32_t n_cand = 0;
+    for (uint32_t scan = scan0; scan < np; scan += stride)
+    {
+        const uint32_t j = scan + lane4;
+        uint32_t key[4], c[4];
+        asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];\n\tst.shared.v4.b32 [%4], {%5, %5, %5, %5};"
+                     : "=r"(key[0]), "=r"(key[1]), "=r"(key[2]), "=r"(key[3]) : "r"(acc.s_sh + 4u * j), "r"(0u));
+        take_counts4(acc.c_sh, j, c, CT{});
+        const uint32_t best4 = max(max(key[0], key[1]), max(key[2], key[3]));
+        if (!(EPK_ABLATE & 2) && __any_sync(FULL, best4 >= max(bar_key, 1u)))
+        {
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+            {
+                const bool cand = (key[u] > bar_key) | ((key[u] == bar_key) & (j + u < bar_branch) & (key[u] != 0u));
                 const uint32_t ballot = __ballot_sync(FULL, cand);
                 if (ballot == 0) { continue; }
                 if (cand)
@@ -892,6 +1095,22 @@ __device__ __forceinline__ bool fast_sweep_ok(const device_db& db, float nwf, fl
 // correction + likelihood mass + top-k (the sweep), weight ratios, keep_factor, the rows of query q.
 // `gathered` = postings the query gathered (warp-uniform; only steers dense / scan-and-queue).
 
+// the dense form by kind of accumulators: two passes over shared memory, one pass over the partial rows in HBM
+template<int CAP, class CT>
+__device__ __forceinline__ sweep_result sweep_dense_form(const shared_acc<CT> acc, uint32_t np, uint32_t nw32, float logthr, float kf,
+                                                         float rcp_k, uint32_t K, uint32_t lane, const cand_buffers<CAP>& cb,
+                                                         uint32_t scan0, uint32_t stride)
+{
+    return sweep_dense_two_pass<CT, CAP, EPK_SWEEP_NQ>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride);
+}
+template<int CAP>
+__device__ __forceinline__ sweep_result sweep_dense_form(const rows_acc acc, uint32_t np, uint32_t nw32, float logthr, float kf,
+                                                         float rcp_k, uint32_t K, uint32_t lane, const cand_buffers<CAP>& cb,
+                                                         uint32_t scan0, uint32_t stride)
+{
+    return sweep<rows_acc, true, true, CAP>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride);
+}
+
 // the sweep form that fits the query
 template<class ACC, int CAP>
 __device__ __forceinline__ sweep_result run_sweep(const device_db& db, const ACC acc, uint32_t np, uint32_t nw32,
@@ -904,7 +1123,7 @@ __device__ __forceinline__ sweep_result run_sweep(const device_db& db, const ACC
     const float nwf = static_cast<float>(nw32);
     const bool dense = 6ull * gathered >= np;
     return !fast_sweep_ok(db, nwf, kf) ? sweep_ieee<ACC, CAP>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride)
-           : dense                     ? sweep<ACC, true, true, CAP>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride)
+           : dense                     ? sweep_dense_form<CAP>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride)
                                        : sweep_sparse<ACC, CAP>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride);
 }
 
@@ -1312,6 +1531,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
     const float kf = static_cast<float>(k);
     const uint32_t key_mask = db.key_mask;
     uint64_t ctr_windows = 0, ctr_hits = 0, ctr_entries = 0; // per lane, folded once at the end
+    EPK_PHASE_DECL
 
     while (true)
     {
@@ -1354,6 +1574,8 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
             continue;
         }
         const char* seq = p.seq + s0;
+        EPK_PHASE(0)
+        EPK_PHASE_COUNT(7)
         bool has_ambiguous = false;
         uint32_t nseg = 0, sink = 0;
         uint32_t tr_keys = 0, tr_hits = 0, tr_entries = 0, tr_sum = 0; // this lane's share of the query's trace record
@@ -1450,6 +1672,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
                 ctr_hits += l != 0;
                 ctr_entries += l;
             }
+            EPK_PHASE(1)
             if (p.trace)
             {
 #pragma unroll
@@ -1509,7 +1732,9 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
                     {
                         if (lane < SEG_PAD) { segs[nseg + lane] = make_uint2(0, 0); }
                         __syncwarp();
+                        EPK_PHASE(2)
                         gather_segments<U, CT, GATHER_ONLY>(db.postings, acc, segs_shared, nseg, lane, p.prefetch, &sink);
+                        EPK_PHASE(3)
                         nseg = 0;
                         __syncwarp();
                         continue;
@@ -1533,7 +1758,9 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
         {
             if (lane < SEG_PAD) { segs[nseg + lane] = make_uint2(0, 0); }
             __syncwarp();
+            EPK_PHASE(2)
             gather_segments<U, CT, GATHER_ONLY>(db.postings, acc, segs_shared, nseg, lane, p.prefetch, &sink);
+            EPK_PHASE(3)
         }
         __syncwarp();
         if (GATHER_ONLY)
@@ -1637,6 +1864,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
             __syncwarp();
         }
 
+        EPK_PHASE(4)
         if (p.trace)
         {
             tr_keys = __reduce_add_sync(FULL, tr_keys);
@@ -1648,8 +1876,20 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
         // ---- correction, likelihood mass, top-k, weight ratios (place.cpp:417-422, 164-184, 134-159, 241-267) ----
         const uint32_t gathered = __reduce_add_sync(FULL, static_cast<uint32_t>(min(static_cast<unsigned long long>(ctr_entries - entries_before), 0xFFFFFFull)));
         if (TEAM) { finish_query_leader<CT>(p, S, C, np, static_cast<uint32_t>(n_windows), gathered, q, lane, team_area, warp, team); }
-        else { finish_query(p, shared_acc<CT>(S, C), np, n_windows, gathered, q, lane, cand_base); }
+        else
+        {
+#ifdef EPK_PHASE_CLOCKS
+            const cand_buffers<CAND_CAP> cb(cand_base);
+            const sweep_result sw = run_sweep<shared_acc<CT>, CAND_CAP>(p.db, shared_acc<CT>(S, C), np, static_cast<uint32_t>(n_windows), gathered, p.keep_at_most, lane, cb);
+            EPK_PHASE(5)
+            emit_query(p, sw, static_cast<uint32_t>(n_windows), q, lane);
+            EPK_PHASE(6)
+#else
+            finish_query(p, shared_acc<CT>(S, C), np, n_windows, gathered, q, lane, cand_base);
+#endif
+        }
     }
+    EPK_PHASE_FLUSH
 
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1)

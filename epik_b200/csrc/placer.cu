@@ -880,3 +880,14 @@ extern "C" epk_status epk_kmers(const epk_db* db, const char* seq, uint64_t len,
         *n_out = n;
     });
 }
+
+#ifdef EPK_PHASE_CLOCKS
+// kernel experiments only (not part of the ABI): cycles per phase summed over the launches since the last call
+extern "C" int epk_debug_phase_clocks(unsigned long long* out8)
+{
+    if (cudaDeviceSynchronize() != cudaSuccess) { return 1; }
+    if (cudaMemcpyFromSymbol(out8, epk::g_phase_clocks, sizeof(unsigned long long) * 8) != cudaSuccess) { return 1; }
+    unsigned long long zero[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
+    return cudaMemcpyToSymbol(epk::g_phase_clocks, zero, sizeof(zero)) != cudaSuccess;
+}
+#endif

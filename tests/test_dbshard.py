@@ -133,7 +133,12 @@ def test_one_shard_equals_the_fused_kernel_bit_for_bit(built):
     got = sp.place_packed(data, off, max_rows=1024)
     assert sp.unsupported == 0 and sp.short == 0
     for name in dbshard.RESULT_FIELDS:
-        assert np.array_equal(got[name], want[name]), name
+        if name == "lwr":
+            # the fused kernel's two-pass sweep and the finalising launch's one-pass sweep add the FP64 terms of the
+            # likelihood mass in different orders: equal to a few ulps, not to the bit
+            np.testing.assert_allclose(got[name], want[name], rtol=1e-13, atol=0)
+        else:
+            assert np.array_equal(got[name], want[name]), name
 
 
 @pytest.mark.gpu
