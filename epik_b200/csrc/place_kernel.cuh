@@ -137,18 +137,25 @@ __host__ __device__ inline uint32_t trace_term(uint32_t pos, uint32_t key, uint3
 // ---- phase clocks (kernel experiments only: -DEPK_PHASE_CLOCKS) ------------------------------------------
 // Cycles the leader warps spent per phase of a query, summed over the launch: 0 claim + offsets, 1 letters + encode +
 // probe (until the slots are in), 2 descriptors, 3 gather + accumulate, 4 ambiguous windows, 5 sweep, 6 weight ratios
-// + rows out, 7 queries. Read and cleared by epk_debug_phase_clocks.
+// + rows out, 7 queries; inside the two-pass sweep: 5 first pass, 8 bar, 9 second pass, 10 final selection. Read and
+// cleared by epk_debug_phase_clocks.
 #ifndef EPK_ABLATE
 #define EPK_ABLATE 0 // kernel experiments: 1 = no likelihood mass, 2 = no candidates, 4 = postings loaded but not accumulated
 #endif
 #ifdef EPK_PHASE_CLOCKS
-__device__ unsigned long long g_phase_clocks[8];
-#define EPK_PHASE_DECL uint32_t ph_acc[8] = { 0, 0, 0, 0, 0, 0, 0, 0 }; uint32_t ph_t = clock();
+__device__ unsigned long long g_phase_clocks[12];
+#define EPK_PHASE_DECL uint32_t ph_acc[12] = { 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0 }; uint32_t ph_t = clock();
+#define EPK_PHASE_PARAMS , uint32_t (&ph_acc)[12], uint32_t& ph_t
+#define EPK_PHASE_ARGS , ph_acc, ph_t
+#define EPK_PHASE_DUMMY uint32_t ph_acc[12] = { 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0 }; uint32_t ph_t = 0;
 #define EPK_PHASE(i) { const uint32_t ph_now = clock(); ph_acc[i] += ph_now - ph_t; ph_t = ph_now; }
 #define EPK_PHASE_COUNT(i) { ++ph_acc[i]; }
-#define EPK_PHASE_FLUSH if (lane == 0) { for (int i = 0; i < 8; ++i) { atomicAdd(g_phase_clocks + i, static_cast<unsigned long long>(ph_acc[i])); } }
+#define EPK_PHASE_FLUSH if (lane == 0) { for (int i = 0; i < 12; ++i) { atomicAdd(g_phase_clocks + i, static_cast<unsigned long long>(ph_acc[i])); } }
 #else
 #define EPK_PHASE_DECL
+#define EPK_PHASE_PARAMS
+#define EPK_PHASE_ARGS
+#define EPK_PHASE_DUMMY
 #define EPK_PHASE(i)
 #define EPK_PHASE_COUNT(i)
 #define EPK_PHASE_FLUSH
@@ -550,12 +557,45 @@ __device__ __forceinline__ uint32_t select_best_n(uint32_t* cand_key, uint32_t* 
     return n_sel;
 }
 
+// m <= 32 candidates, one per lane: every lane ranks its own against all the others - m independent pairs of
+// shuffles instead of `want` dependent arg-max rounds (each a chain of two reductions, a vote and a shuffle).
+__device__ __forceinline__ uint32_t select_best_ranked(uint32_t* cand_key, uint32_t* cand_branch, uint32_t* cand_count, uint32_t m,
+                                                       uint32_t want, uint32_t lane, uint32_t& my_key, uint32_t& my_branch,
+                                                       uint32_t& my_count)
+{
+    const bool have = lane < m;
+    const uint32_t hi = have ? cand_key[lane] : 0u;
+    const uint32_t lo = have ? ~cand_branch[lane] : 0u;
+    const uint32_t cn = have ? cand_count[lane] : 0u;
+    __syncwarp();
+    uint32_t rank = 0; // candidates that come before mine: higher key, or the same key and a lower branch id
+    for (uint32_t i = 0; i < m; ++i)
+    {
+        const uint32_t oh = __shfl_sync(FULL, hi, i);
+        const uint32_t ol = __shfl_sync(FULL, lo, i);
+        rank += (oh > hi) | ((oh == hi) & (ol > lo));
+    }
+    const uint32_t n_sel = min(want, m);
+    if (have && rank < n_sel) // branches are distinct: so are the ranks
+    {
+        cand_key[rank] = hi;
+        cand_branch[rank] = ~lo;
+        cand_count[rank] = cn;
+    }
+    __syncwarp();
+    my_key = lane < n_sel ? cand_key[lane] : 0u;
+    my_branch = lane < n_sel ? cand_branch[lane] : NO_BRANCH;
+    my_count = lane < n_sel ? cand_count[lane] : 0u;
+    __syncwarp();
+    return n_sel;
+}
+
 // m <= CAND_CAP candidates: the fewer there are, the fewer each lane has to look at per round
 __device__ __noinline__ uint32_t select_best(uint32_t* cand_key, uint32_t* cand_branch, uint32_t* cand_count, uint32_t m,
                                              uint32_t want, uint32_t lane, uint32_t& my_key, uint32_t& my_branch,
                                              uint32_t& my_count)
 {
-    if (m <= 32) { return select_best_n<1>(cand_key, cand_branch, cand_count, m, want, lane, my_key, my_branch, my_count); }
+    if (m <= 32) { return select_best_ranked(cand_key, cand_branch, cand_count, m, want, lane, my_key, my_branch, my_count); }
     if (m <= 64) { return select_best_n<2>(cand_key, cand_branch, cand_count, m, want, lane, my_key, my_branch, my_count); }
     return select_best_n<CAND_CAP / 32>(cand_key, cand_branch, cand_count, m, want, lane, my_key, my_branch, my_count);
 }
@@ -895,6 +935,9 @@ __device__ __forceinline__ sweep_result sweep(const ACC acc, uint32_t np, uint32
 #ifndef EPK_SWEEP_NQ
 #define EPK_SWEEP_NQ 2
 #endif
+#ifndef EPK_SWEEP_P2
+#define EPK_SWEEP_P2 4
+#endif
 __device__ __forceinline__ void load_counts4_sh(uint32_t c_sh, uint32_t j, uint32_t (&c)[4], uint8_t)
 {
     uint32_t w;
@@ -912,10 +955,36 @@ __device__ __forceinline__ void load_counts4_sh(uint32_t c_sh, uint32_t j, uint3
     asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(c[0]), "=r"(c[1]), "=r"(c[2]), "=r"(c[3]) : "r"(c_sh + 4u * j));
 }
 
+// single words through the shared window, as volatile asm like every other access of the two-pass sweep (the
+// compiler keeps volatile asm statements in program order; it knows nothing about the memory they touch)
+__device__ __forceinline__ uint32_t lds_b32(uint32_t addr)
+{
+    uint32_t v;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ uint32_t load_count_sh(uint32_t c_sh, uint32_t b, uint8_t)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(c_sh + b));
+    return v;
+}
+__device__ __forceinline__ uint32_t load_count_sh(uint32_t c_sh, uint32_t b, uint16_t)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(c_sh + 2u * b));
+    return v;
+}
+__device__ __forceinline__ uint32_t load_count_sh(uint32_t c_sh, uint32_t b, uint32_t) { return lds_b32(c_sh + 4u * b); }
+__device__ __forceinline__ void clear_counts4_sh(uint32_t c_sh, uint32_t j, uint8_t) { asm volatile("st.shared.b32 [%0], %1;" ::"r"(c_sh + j), "r"(0u)); }
+__device__ __forceinline__ void clear_counts4_sh(uint32_t c_sh, uint32_t j, uint16_t) { asm volatile("st.shared.v2.b32 [%0], {%1, %1};" ::"r"(c_sh + 2u * j), "r"(0u)); }
+__device__ __forceinline__ void clear_counts4_sh(uint32_t c_sh, uint32_t j, uint32_t) { asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};" ::"r"(c_sh + 4u * j), "r"(0u)); }
+
 template<class CT, int CAP, int NQ>
 __device__ __forceinline__ sweep_result sweep_dense_two_pass(const shared_acc<CT> acc, uint32_t np, uint32_t nw32, float logthr,
                                                              float kf, float rcp_k, uint32_t K, uint32_t lane,
-                                                             const cand_buffers<CAP>& cb, uint32_t scan0, uint32_t stride)
+                                                             const cand_buffers<CAP>& cb, uint32_t scan0, uint32_t stride
+                                                             EPK_PHASE_PARAMS)
 {
     uint32_t* const cand_key = cb.key;
     uint32_t* const cand_branch = cb.branch;
@@ -994,6 +1063,7 @@ __device__ __forceinline__ sweep_result sweep_dense_two_pass(const shared_acc<CT
         }
     }
 
+    EPK_PHASE(5)
     // ---- the bar: K-th largest of the lanes' best keys (0 while fewer than K lanes have a touched branch). A round
     // takes the maximum and strikes every lane that holds it; lanes that tie are struck together, which can only
     // lower the result - still a lower bound of the K-th best key of the query. ----
@@ -1008,36 +1078,86 @@ __device__ __forceinline__ sweep_result sweep_dense_two_pass(const shared_acc<CT
         bar_key = kth;
     }
 
-    // ---- pass 2: the candidates (place.cpp:134-159); sums and counts cleared for the next query ----
-    uint32_t n_cand = 0;
-    for (uint32_t scan = scan0; scan < np; scan += stride)
+    EPK_PHASE(8)
+    // ---- pass 2: the candidates (place.cpp:134-159) ----
+    // Every key that reaches the bar is a candidate; there are few (K - 1 lanes at most have a best key above the
+    // bar). The lanes append theirs on their own - a counter in shared memory hands out the slots, no vote, no
+    // prefix sum: the collective version of this loop cost 6 k cycles per C2 query (gpurun r3e), ten times its
+    // loads. Only when more candidates turn up than the buffer holds (masses of exact ties) is the scan repeated
+    // with the collective append-and-squeeze of the one-pass sweep. The accumulators are cleared afterwards.
+    constexpr int P2 = EPK_SWEEP_P2;
+    uint32_t* const counter = cb.pending; // (the quad queue of the scan-and-queue sweep: idle here)
+    const uint32_t floor_key = max(bar_key, 1u);
+    if (lane == 0) { *counter = 0u; }
+    __syncwarp();
+    if (!(EPK_ABLATE & 2))
     {
-        const uint32_t j = scan + lane4;
-        uint32_t key[4], c[4];
-        asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];\n\tst.shared.v4.b32 [%4], {%5, %5, %5, %5};"
-                     : "=r"(key[0]), "=r"(key[1]), "=r"(key[2]), "=r"(key[3]) : "r"(acc.s_sh + 4u * j), "r"(0u));
-        take_counts4(acc.c_sh, j, c, CT{});
-        const uint32_t best4 = max(max(key[0], key[1]), max(key[2], key[3]));
-        if (!(EPK_ABLATE & 2) && __any_sync(FULL, best4 >= max(bar_key, 1u)))
+        for (uint32_t scan = scan0; scan < np; scan += P2 * stride)
         {
+            uint32_t key[P2][4];
+            uint32_t best = 0;
 #pragma unroll
-            for (int u = 0; u < 4; ++u)
+            for (int i = 0; i < P2; ++i)
             {
-                const bool cand = (key[u] > bar_key) | ((key[u] == bar_key) & (j + u < bar_branch) & (key[u] != 0u));
+                key[i][0] = key[i][1] = key[i][2] = key[i][3] = 0u;
+                if (i == 0 || scan + i * stride < np) // (warp-uniform)
+                {
+                    const uint32_t j = scan + i * stride + lane4;
+                    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(key[i][0]), "=r"(key[i][1]), "=r"(key[i][2]), "=r"(key[i][3]) : "r"(acc.s_sh + 4u * j));
+                }
+                best = max(best, max(max(key[i][0], key[i][1]), max(key[i][2], key[i][3])));
+            }
+            if (best >= floor_key)
+            {
+                uint32_t mask = 0; // bit 4 i + u: branch u of the lane's quad in step i
+#pragma unroll
+                for (int i = 0; i < P2; ++i)
+                {
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) { mask |= key[i][u] >= floor_key ? 1u << (4 * i + u) : 0u; }
+                }
+                uint32_t at = atomicAdd(counter, static_cast<uint32_t>(__popc(mask)));
+                while (mask && at < static_cast<uint32_t>(CAP))
+                {
+                    const uint32_t b = __ffs(mask) - 1u;
+                    mask &= mask - 1u;
+                    const uint32_t branch = scan + (b >> 2) * stride + lane4 + (b & 3u);
+                    cand_key[at] = lds_b32(acc.s_sh + 4u * branch); // (the key pass 1 left there)
+                    cand_branch[at] = branch;
+                    cand_count[at] = load_count_sh(acc.c_sh, branch, CT{});
+                    ++at;
+                }
+            }
+        }
+    }
+    __syncwarp();
+    uint32_t n_cand = *counter;
+    __syncwarp();
+    if (n_cand > static_cast<uint32_t>(CAP))
+    {
+        // too many for the buffer: position by position with votes, squeezing to the best K (and raising the bar to
+        // the K-th of them, ties by branch id) whenever the buffer fills up
+        n_cand = 0;
+        for (uint32_t scan = scan0; scan < np; scan += stride)
+        {
+            for (uint32_t u = 0; u < 4; ++u)
+            {
+                const uint32_t branch = scan + lane4 + u;
+                const uint32_t key = lds_b32(acc.s_sh + 4u * branch);
+                const bool cand = (key > bar_key) | ((key == bar_key) & (branch < bar_branch) & (key != 0u));
                 const uint32_t ballot = __ballot_sync(FULL, cand);
                 if (ballot == 0) { continue; }
                 if (cand)
                 {
                     const uint32_t at = n_cand + __popc(ballot & ((1u << lane) - 1u));
-                    cand_key[at] = key[u];
-                    cand_branch[at] = j + u;
-                    cand_count[at] = c[u];
+                    cand_key[at] = key;
+                    cand_branch[at] = branch;
+                    cand_count[at] = load_count_sh(acc.c_sh, branch, CT{});
                 }
                 n_cand += __popc(ballot);
                 __syncwarp();
                 if (n_cand > CAP - 32)
                 {
-                    // keep the best K, raise the bar to the K-th of them
                     n_cand = select_best(cand_key, cand_branch, cand_count, n_cand, K, lane, out.key, out.branch, out.count);
                     if (n_cand == K)
                     {
@@ -1048,6 +1168,14 @@ __device__ __forceinline__ sweep_result sweep_dense_two_pass(const shared_acc<CT
             }
         }
     }
+    // ---- sums and counts cleared for the next query ----
+    for (uint32_t scan = scan0; scan < np; scan += stride)
+    {
+        const uint32_t j = scan + lane4;
+        asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};" ::"r"(acc.s_sh + 4u * j), "r"(0u));
+        clear_counts4_sh(acc.c_sh, j, CT{});
+    }
+    EPK_PHASE(9)
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1)
     {
@@ -1056,6 +1184,7 @@ __device__ __forceinline__ sweep_result sweep_dense_two_pass(const shared_acc<CT
     }
     __syncwarp();
     out.n_keep = select_best(cand_key, cand_branch, cand_count, n_cand, K, lane, out.key, out.branch, out.count);
+    EPK_PHASE(10)
     out.mass = mass;
     out.touched = touched;
     return out;
@@ -1099,14 +1228,14 @@ __device__ __forceinline__ bool fast_sweep_ok(const device_db& db, float nwf, fl
 template<int CAP, class CT>
 __device__ __forceinline__ sweep_result sweep_dense_form(const shared_acc<CT> acc, uint32_t np, uint32_t nw32, float logthr, float kf,
                                                          float rcp_k, uint32_t K, uint32_t lane, const cand_buffers<CAP>& cb,
-                                                         uint32_t scan0, uint32_t stride)
+                                                         uint32_t scan0, uint32_t stride EPK_PHASE_PARAMS)
 {
-    return sweep_dense_two_pass<CT, CAP, EPK_SWEEP_NQ>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride);
+    return sweep_dense_two_pass<CT, CAP, EPK_SWEEP_NQ>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride EPK_PHASE_ARGS);
 }
 template<int CAP>
 __device__ __forceinline__ sweep_result sweep_dense_form(const rows_acc acc, uint32_t np, uint32_t nw32, float logthr, float kf,
                                                          float rcp_k, uint32_t K, uint32_t lane, const cand_buffers<CAP>& cb,
-                                                         uint32_t scan0, uint32_t stride)
+                                                         uint32_t scan0, uint32_t stride EPK_PHASE_PARAMS)
 {
     return sweep<rows_acc, true, true, CAP>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride);
 }
@@ -1115,7 +1244,7 @@ __device__ __forceinline__ sweep_result sweep_dense_form(const rows_acc acc, uin
 template<class ACC, int CAP>
 __device__ __forceinline__ sweep_result run_sweep(const device_db& db, const ACC acc, uint32_t np, uint32_t nw32,
                                                   uint32_t gathered, uint32_t K, uint32_t lane, const cand_buffers<CAP>& cb,
-                                                  uint32_t scan0 = 0, uint32_t stride = SWEEP_STEP)
+                                                  uint32_t scan0, uint32_t stride EPK_PHASE_PARAMS)
 {
     const float kf = static_cast<float>(db.k);
     const float rcp_k = __frcp_rn(kf);
@@ -1123,7 +1252,7 @@ __device__ __forceinline__ sweep_result run_sweep(const device_db& db, const ACC
     const float nwf = static_cast<float>(nw32);
     const bool dense = 6ull * gathered >= np;
     return !fast_sweep_ok(db, nwf, kf) ? sweep_ieee<ACC, CAP>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride)
-           : dense                     ? sweep_dense_form<CAP>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride)
+           : dense                     ? sweep_dense_form<CAP>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride EPK_PHASE_ARGS)
                                        : sweep_sparse<ACC, CAP>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride);
 }
 
@@ -1196,7 +1325,8 @@ __device__ __forceinline__ void finish_query(const place_params& p, const ACC ac
 {
     const cand_buffers<CAND_CAP> cb(cand_base);
     const uint32_t nw32 = static_cast<uint32_t>(n_windows);
-    const sweep_result sw = run_sweep<ACC, CAND_CAP>(p.db, acc, np, nw32, gathered, p.keep_at_most, lane, cb);
+    EPK_PHASE_DUMMY
+    const sweep_result sw = run_sweep<ACC, CAND_CAP>(p.db, acc, np, nw32, gathered, p.keep_at_most, lane, cb, 0u, SWEEP_STEP EPK_PHASE_ARGS);
     emit_query(p, sw, nw32, q, lane);
 }
 
@@ -1231,8 +1361,9 @@ __device__ __noinline__ sweep_result team_sweep(const device_db& db, float* S, C
                                                 uint32_t member, uint32_t team)
 {
     const cand_buffers<TEAM_CAND_CAP> cb(member_base);
+    EPK_PHASE_DUMMY
     return run_sweep<shared_acc<CT>, TEAM_CAND_CAP>(db, shared_acc<CT>(S, C), np, nw32, gathered, K, lane, cb,
-                                                    member * SWEEP_STEP, team * SWEEP_STEP);
+                                                    member * SWEEP_STEP, team * SWEEP_STEP EPK_PHASE_ARGS);
 }
 
 // mailbox.pad: 0 = sweep; GATHER | n_hits = gather the published hits (range teams); DUMP = write this member's part of
@@ -1533,11 +1664,21 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
     uint64_t ctr_windows = 0, ctr_hits = 0, ctr_entries = 0; // per lane, folded once at the end
     EPK_PHASE_DECL
 
+    // Looking one query ahead: a query used to start with two dependent round trips to memory - the cursor, then its
+    // two offsets - before a single letter could be asked for (1.7 k of the 65 k cycles of a C2 query; phase clocks,
+    // gpurun r3e). Now the cursor is bumped for the NEXT query at the top of this one (A), and the next query's offsets
+    // are asked for before this one's last gather (B): both are there when the sweep is over.
+    // (Carrying more than that across the sweep - the next query's letters, its key-table slots for an L2 prefetch
+    // of its lists - cost more in spilled registers than the latencies it hid: 28 instead of 38 M reads/s, gpurun r3g.)
+    uint32_t q_next = 0;
+    if (lane == 0) { q_next = static_cast<uint32_t>(atomicAdd(p.counters + CTR_CURSOR, 1ull)); }
+    q_next = __shfl_sync(FULL, q_next, 0);
+    uint64_t next_s0 = 0, next_len = 0; // offsets of query q_next ...
+    bool next_known = false;            // ... when they have been asked for
+
     while (true)
     {
-        uint32_t q = 0;
-        if (lane == 0) { q = static_cast<uint32_t>(atomicAdd(p.counters + CTR_CURSOR, 1ull)); }
-        q = __shfl_sync(FULL, q, 0);
+        const uint32_t q = q_next;
         if (q >= p.n)
         {
             if (TEAM)
@@ -1548,9 +1689,11 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
             }
             break;
         }
-
-        const uint64_t s0 = p.seq_off[q];
-        const uint64_t len = p.seq_off[q + 1] - s0;
+        uint32_t claim = 0; // A (read at B, or where this query is left early)
+        if (lane == 0) { claim = static_cast<uint32_t>(atomicAdd(p.counters + CTR_CURSOR, 1ull)); }
+        const uint64_t s0 = next_known ? next_s0 : p.seq_off[q];
+        const uint64_t len = next_known ? next_len : p.seq_off[q + 1] - s0;
+        next_known = false;
         if (len + 1 < k)
         {
             // the reference dies here (size_t wrap at place.cpp:291); reported as EPK_E_SHORT_SEQ
@@ -1559,11 +1702,16 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
                 bump(p, CTR_SHORT, 1ull);
                 p.n_place[q] = 0;
             }
+            q_next = __shfl_sync(FULL, claim, 0);
             continue;
         }
         const uint64_t entries_before = ctr_entries;
         const uint64_t n_windows = len + 1 - k; // place.cpp:322, counts skipped windows too
-        if (class_of_windows(n_windows) != static_cast<int>(p.cls)) { continue; } // another launch's query
+        if (class_of_windows(n_windows) != static_cast<int>(p.cls)) // another launch's query
+        {
+            q_next = __shfl_sync(FULL, claim, 0);
+            continue;
+        }
         if (n_windows > class_max_windows(N_CLASSES - 1))
         {
             if (lane == 0 && !PARTIAL)
@@ -1571,6 +1719,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
                 bump(p, CTR_TOO_LONG, 1ull);
                 p.n_place[q] = 0;
             }
+            q_next = __shfl_sync(FULL, claim, 0);
             continue;
         }
         const char* seq = p.seq + s0;
@@ -1754,6 +1903,14 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
                 done += n_fit;
             }
         }
+        // B: the next query's index is there; its offsets are asked for
+        q_next = __shfl_sync(FULL, claim, 0);
+        uint64_t off0 = 0, off1 = 0;
+        if (q_next < p.n)
+        {
+            off0 = __ldg(p.seq_off + q_next);
+            off1 = __ldg(p.seq_off + q_next + 1);
+        }
         if (nseg)
         {
             if (lane < SEG_PAD) { segs[nseg + lane] = make_uint2(0, 0); }
@@ -1763,6 +1920,12 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
             EPK_PHASE(3)
         }
         __syncwarp();
+        if (q_next < p.n)
+        {
+            next_s0 = off0;
+            next_len = off1 - off0;
+            next_known = true;
+        }
         if (GATHER_ONLY)
         {
             sink = __reduce_xor_sync(FULL, sink);
@@ -1880,8 +2043,8 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
         {
 #ifdef EPK_PHASE_CLOCKS
             const cand_buffers<CAND_CAP> cb(cand_base);
-            const sweep_result sw = run_sweep<shared_acc<CT>, CAND_CAP>(p.db, shared_acc<CT>(S, C), np, static_cast<uint32_t>(n_windows), gathered, p.keep_at_most, lane, cb);
-            EPK_PHASE(5)
+            const sweep_result sw = run_sweep<shared_acc<CT>, CAND_CAP>(p.db, shared_acc<CT>(S, C), np, static_cast<uint32_t>(n_windows), gathered, p.keep_at_most, lane, cb, 0u, SWEEP_STEP EPK_PHASE_ARGS);
+            EPK_PHASE(10)
             emit_query(p, sw, static_cast<uint32_t>(n_windows), q, lane);
             EPK_PHASE(6)
 #else

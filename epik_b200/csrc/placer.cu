@@ -488,6 +488,22 @@ extern "C" epk_status epk_place(epk_placer* pl, const char* seq, const uint64_t*
         EPK_CUDA(cudaSetDevice(pl->db->device));
         const size_t K = pl->keep_at_most;
         const uint32_t k = pl->db->d.k;
+        // a call that failed half way (an allocation in reserve_slot, say) may have left results staged for ITS caller's
+        // arrays: nothing of them is ever copied into this caller's
+        struct pending_guard
+        {
+            epk_placer& pl;
+            void clear()
+            {
+                for (auto& s : pl.slots)
+                {
+                    if (s.pending) { cudaStreamSynchronize(s.stream); }
+                    s.pending = false;
+                }
+            }
+            ~pending_guard() { clear(); }
+        } guard{ *pl };
+        guard.clear();
         EPK_CUDA(cudaMemset(pl->totals.get(), 0, pl->totals.bytes()));
         pl->n_launches = 0;
         pl->n_reads = 0;
@@ -567,17 +583,6 @@ extern "C" epk_status epk_place(epk_placer* pl, const char* seq, const uint64_t*
         }
         unsigned long long totals[CTR_COUNT];
         EPK_CUDA(cudaMemcpy(totals, pl->totals.get(), sizeof(totals), cudaMemcpyDeviceToHost));
-        if (totals[CTR_SHORT] != 0)
-        {
-            throw error(EPK_E_SHORT_SEQ, std::to_string(totals[CTR_SHORT]) + " sequence(s) shorter than k - 1 = "
-                                             + std::to_string(k - 1) + " letters");
-        }
-        if (totals[CTR_UNSUPPORTED] + totals[CTR_TOO_LONG] != 0)
-        {
-            throw error(EPK_E_UNSUPPORTED, std::to_string(totals[CTR_UNSUPPORTED] + totals[CTR_TOO_LONG])
-                                               + " sequence(s) too long for the shared-memory accumulators of a tree of "
-                                               + std::to_string(pl->db->d.n_nodes) + " nodes");
-        }
         // distal / pendant are look-ups by branch (place.cpp:434-437); zero for the zero-hit placements
         if (out->distal || out->pendant)
         {
@@ -592,6 +597,18 @@ extern "C" epk_status epk_place(epk_placer* pl, const char* seq, const uint64_t*
                     if (out->pendant) { out->pendant[at] = real ? db.pendant[out->branch[at]] : 0.0; }
                 }
             }
+        }
+        // every other row of the pass is complete (lengths included) before the rows left with n_place = 0 are reported
+        if (totals[CTR_SHORT] != 0)
+        {
+            throw error(EPK_E_SHORT_SEQ, std::to_string(totals[CTR_SHORT]) + " sequence(s) shorter than k - 1 = "
+                                             + std::to_string(k - 1) + " letters");
+        }
+        if (totals[CTR_UNSUPPORTED] + totals[CTR_TOO_LONG] != 0)
+        {
+            throw error(EPK_E_UNSUPPORTED, std::to_string(totals[CTR_UNSUPPORTED] + totals[CTR_TOO_LONG])
+                                               + " sequence(s) too long for the shared-memory accumulators of a tree of "
+                                               + std::to_string(pl->db->d.n_nodes) + " nodes");
         }
     });
 }
@@ -883,11 +900,11 @@ extern "C" epk_status epk_kmers(const epk_db* db, const char* seq, uint64_t len,
 
 #ifdef EPK_PHASE_CLOCKS
 // kernel experiments only (not part of the ABI): cycles per phase summed over the launches since the last call
-extern "C" int epk_debug_phase_clocks(unsigned long long* out8)
+extern "C" int epk_debug_phase_clocks(unsigned long long* out12)
 {
     if (cudaDeviceSynchronize() != cudaSuccess) { return 1; }
-    if (cudaMemcpyFromSymbol(out8, epk::g_phase_clocks, sizeof(unsigned long long) * 8) != cudaSuccess) { return 1; }
-    unsigned long long zero[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
+    if (cudaMemcpyFromSymbol(out12, epk::g_phase_clocks, sizeof(unsigned long long) * 12) != cudaSuccess) { return 1; }
+    unsigned long long zero[12] = { 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0 };
     return cudaMemcpyToSymbol(epk::g_phase_clocks, zero, sizeof(zero)) != cudaSuccess;
 }
 #endif

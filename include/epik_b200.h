@@ -151,7 +151,10 @@ epk_status epk_place(epk_placer* placer, const char* seq, const uint64_t* seq_of
                      const epk_result* out);
 
 /* Same work with everything already resident in HBM: DEVICE pointers, asynchronous on `stream`
- * (a cudaStream_t, NULL = the legacy default stream). */
+ * (a cudaStream_t, NULL = the legacy default stream). A placer is a single-stream object: its work cursor
+ * and counters are shared by all its launches, so calls on one placer (this one, the partial / finalize /
+ * ceiling calls below, epk_place) must be ordered - the same stream, or a synchronisation in between;
+ * use one placer per concurrent stream (placers share the database). */
 epk_status epk_place_device(epk_placer* placer, const char* d_seq, const uint64_t* d_seq_off, uint32_t n,
                             const epk_result* d_out, void* stream);
 

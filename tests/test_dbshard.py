@@ -134,9 +134,10 @@ def test_one_shard_equals_the_fused_kernel_bit_for_bit(built):
     assert sp.unsupported == 0 and sp.short == 0
     for name in dbshard.RESULT_FIELDS:
         if name == "lwr":
-            # the fused kernel's two-pass sweep and the finalising launch's one-pass sweep add the FP64 terms of the
-            # likelihood mass in different orders: equal to a few ulps, not to the bit
-            np.testing.assert_allclose(got[name], want[name], rtol=1e-13, atol=0)
+            # the fused kernel's two-pass sweep and the finalising launch's one-pass sweep evaluate 10^s with different
+            # polynomials (relative error 6e-12 / 2e-12) and add the FP64 terms of the likelihood mass in different
+            # orders: equal far below the 1e-9 asked of the weight ratios, not to the bit
+            np.testing.assert_allclose(got[name], want[name], rtol=1e-10, atol=0)
         else:
             assert np.array_equal(got[name], want[name]), name
 

@@ -6,7 +6,7 @@ a different order + CUDA's exp10 vs glibc's pow)."""
 import numpy as np
 import pytest
 
-from epik_b200 import capi, synth
+from epik_b200 import capi, flatdb, synth
 from epik_b200.placer import Database, Placer, pack_sequences
 from oracle import oracle as O
 from tests import helpers
@@ -317,6 +317,33 @@ def test_databases_outside_the_short_arithmetic_forms(tweak):
     helpers.assert_same_placements(got, want, what=tweak + " " + kind)
     valid = np.arange(7)[None, :] < want["n_place"][:, None]
     assert np.array_equal(got["score"][valid], want["score"][valid])
+
+
+@pytest.mark.parametrize("n_nodes", [1500, 5001, 9001], ids=["16-warps", "8-warps", "range-teams"])
+def test_masses_of_exact_ties_overflow_the_candidate_buffer(n_nodes):
+    """Hundreds of branches with bit-equal scores at the top: more candidates reach the bar than the candidate buffer
+    holds, so the second pass of the sweep has to squeeze; the kept set follows the documented tie rule (lower branch id
+    first), the scores / counts / weight ratios are the reference's."""
+    rng = np.random.default_rng(n_nodes)
+    tied = sorted(int(b) for b in rng.choice(n_nodes, size=700, replace=False))
+    better = [tied[5], tied[300], tied[650]]
+    kmers = {"ACGT": [(b, -1.0) for b in tied], "CGTA": [(b, -0.5) for b in better], "TTTT": [(tied[10], -2.0)]}
+    flat = flatdb.from_dict(flatdb.DNA, 4, 1.5, kmers, [0.01 * (i % 7 + 1) for i in range(n_nodes)], [1] * n_nodes,
+                            [0.0] * n_nodes, encode=helpers.encode_dna)
+    seqs = [b"ACGT", b"ACGTA", b"GGACGTGG", b"ACGTTTT", b"CGTA", b"GGGGGG"]
+    data = np.frombuffer(b"".join(seqs), np.uint8).copy()
+    off = np.zeros(len(seqs) + 1, np.uint64)
+    off[1:] = np.cumsum([len(x) for x in seqs])
+    for K in (7, 32):
+        oracle, kind = best_oracle(flat, keep_at_most=K, keep_factor=0.0, threads=1)
+        got = Placer(Database(flat), K, 0.0).place_packed(data, off)
+        want = oracle.place_packed(data, off, threads=1)
+        helpers.assert_same_placements(got, want, what="ties K=%d %s" % (K, kind))
+        valid = np.arange(K)[None, :] < want["n_place"][:, None]
+        assert np.array_equal(got["score"][valid], want["score"][valid])
+        assert list(got["branch"][0]) == tied[:K]                                      # all tied: the K lowest ids
+        assert list(got["branch"][1][:3]) == better and list(got["branch"][1][3:]) == [b for b in tied if b not in better][:K - 3]
+        assert list(got["branch"][4][:3]) == better
 
 
 @pytest.mark.parametrize("mu,omega,max_entries", [
