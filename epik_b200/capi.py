@@ -24,6 +24,7 @@ SYMBOLS = [
     "epk_place_finalize_device", "epk_gather_ceiling_device",
     "epk_device_alloc", "epk_device_free", "epk_ipc_export", "epk_ipc_import", "epk_ipc_close",
     "epk_gather_microbench", "epk_placer_set_trace", "epk_trace_term",
+    "epk_db_get_view", "epk_placer_set_shard_views", "epk_place_finalize_seq_device",
 ]
 
 
@@ -53,6 +54,11 @@ class DbInfo(C.Structure):
         ("n_keys_loaded", C.c_uint64), ("n_entries_loaded", C.c_uint64), ("n_entries_total", C.c_uint64),
         ("table_slots", C.c_uint64), ("device_bytes", C.c_uint64),
     ]
+
+
+class DbView(C.Structure):
+    _fields_ = [("table", C.c_uint64), ("postings", C.c_uint64), ("hash_mask", C.c_uint64), ("hash_shift", C.c_uint32),
+                ("table_kind", C.c_uint32)]
 
 
 class PlacerOpts(C.Structure):
@@ -144,6 +150,13 @@ def lib():
     l.epk_trace_term.argtypes = [C.c_uint32] * 4
     l.epk_gather_microbench.restype = C.c_int
     l.epk_gather_microbench.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32, C.POINTER(Microbench)]
+    l.epk_db_get_view.restype = C.c_int
+    l.epk_db_get_view.argtypes = [C.c_void_p, C.POINTER(DbView)]
+    l.epk_placer_set_shard_views.restype = C.c_int
+    l.epk_placer_set_shard_views.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p]
+    l.epk_place_finalize_seq_device.restype = C.c_int
+    l.epk_place_finalize_seq_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint64, C.c_void_p, C.c_void_p,
+                                                C.c_uint32, C.POINTER(Result), C.c_void_p]
     l.epk_host_alloc.restype = C.c_void_p
     l.epk_host_alloc.argtypes = [C.c_size_t]
     l.epk_host_free.argtypes = [C.c_void_p]

@@ -48,12 +48,6 @@ __global__ void prefix_cut_kernel(const uint64_t* before, const uint32_t* order,
     if (j < n_keys) { keep[order ? order[j] : j] = before[j] < budget ? 1 : 0; }
 }
 
-// Database-sharded mode: the shard a key belongs to is a range of a 16-bit multiplicative hash of the
-// key (shard g of G owns hashes [g * 65536 / G, (g + 1) * 65536 / G)).
-__host__ __device__ inline uint32_t shard_of_key(uint32_t key, uint32_t n_shards)
-{
-    return (((key * 0x9E3779B1u) >> 16) * n_shards) >> 16;
-}
 
 // keep[i] &= key i belongs to shard `index` (keep_in == nullptr: every key was kept so far)
 __global__ void shard_keep_kernel(const uint32_t* keys, uint64_t n_keys, uint32_t index, uint32_t n_shards,

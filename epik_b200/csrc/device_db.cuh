@@ -54,6 +54,13 @@ __host__ __device__ inline uint32_t hash_slot(uint32_t key, uint32_t shift)
     return (key * 0x9E3779B1u) >> shift;
 }
 
+// Database-sharded mode: the shard a key belongs to is a range of a 16-bit multiplicative hash of the
+// key (shard g of G owns hashes [g * 65536 / G, (g + 1) * 65536 / G)).
+__host__ __device__ inline uint32_t shard_of_key(uint32_t key, uint32_t n_shards)
+{
+    return (((key * 0x9E3779B1u) >> 16) * n_shards) >> 16;
+}
+
 // phylo_kmer_db::search (place.cpp:300,311): returns the packed (offset << LEN_BITS | length)
 // of the key's posting list, 0 when the key is absent (or its list is empty).
 template<uint32_t TABLE>

@@ -83,6 +83,9 @@ struct place_params
     uint32_t team;                       // warps per accumulator set (TEAM launches)
     uint32_t prefetch;                   // L2 prefetch of a descriptor buffer's postings before it is gathered (PREFETCH_*)
     uint32_t* trace;                     // [4 n] per query: keys looked up, keys found, postings, checksum of the k-mer stream (NULL: none)
+    // ---- finalize launch: ambiguous windows of database-sharded mode, replayed by the owner ----
+    const device_db* shard_views;        // [n_shards] the shards' tables and postings as seen from this device (NULL: none)
+    uint32_t* seen_scratch;              // np / 32 words per warp of the finalize grid, zero between queries
 };
 
 
@@ -695,24 +698,34 @@ struct rows_acc
     const unsigned char* c_rows; // C (uint16) of shard 0
     uint64_t stride;
     uint32_t n_shards;
+    bool modified;               // this launch has written to the rows (ambiguous windows replayed by the owner): read
+                                 // them through L2 (ld.global.cg), not through the read-only path
+    __device__ __forceinline__ float4 load_s(const unsigned char* at) const
+    {
+        return modified ? __ldcg(reinterpret_cast<const float4*>(at)) : __ldg(reinterpret_cast<const float4*>(at));
+    }
+    __device__ __forceinline__ uint2 load_c(const unsigned char* at) const
+    {
+        return modified ? __ldcg(reinterpret_cast<const uint2*>(at)) : __ldg(reinterpret_cast<const uint2*>(at));
+    }
     __device__ __forceinline__ bool any(uint32_t j) const
     {
         uint32_t seen = 0;
         for (uint32_t g = 0; g < n_shards; ++g)
         {
-            const uint2 u = __ldg(reinterpret_cast<const uint2*>(c_rows + g * stride + 2ull * j));
+            const uint2 u = load_c(c_rows + g * stride + 2ull * j);
             seen |= u.x | u.y;
         }
         return seen != 0u;
     }
     __device__ __forceinline__ float4 take(uint32_t j, uint32_t (&c)[4]) const
     {
-        float4 s4 = __ldg(reinterpret_cast<const float4*>(s_rows + 4ull * j));
-        uint2 c2 = __ldg(reinterpret_cast<const uint2*>(c_rows + 2ull * j));
+        float4 s4 = load_s(s_rows + 4ull * j);
+        uint2 c2 = load_c(c_rows + 2ull * j);
         for (uint32_t g = 1; g < n_shards; ++g)
         {
-            const float4 t = __ldg(reinterpret_cast<const float4*>(s_rows + g * stride + 4ull * j));
-            const uint2 u = __ldg(reinterpret_cast<const uint2*>(c_rows + g * stride + 2ull * j));
+            const float4 t = load_s(s_rows + g * stride + 4ull * j);
+            const uint2 u = load_c(c_rows + g * stride + 2ull * j);
             s4.x = __fadd_rn(s4.x, t.x); s4.y = __fadd_rn(s4.y, t.y);
             s4.z = __fadd_rn(s4.z, t.z); s4.w = __fadd_rn(s4.w, t.w);
             c2.x += u.x; c2.y += u.y; // 16-bit halves cannot carry: a branch is hit at most n_windows <= 65535 times
@@ -2072,8 +2085,87 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
 // of the n_shards shards (rows_acc adds them in shard order as it reads: a fixed association, the same
 // on every run). One warp per query; shared memory only holds the candidate buffers, so the launch is
 // not limited by the size of the tree.
-constexpr size_t FINALIZE_WARP_SMEM = cand_buffers<CAND_CAP>::WORDS * 4;
+constexpr size_t FINALIZE_WARP_SMEM = cand_buffers<CAND_CAP>::WORDS * 4 + CODE_BYTES; // candidates, letter codes of a chunk
+constexpr size_t FINALIZE_CTA_SMEM = 1024;                                               // letter table
 constexpr int FINALIZE_WARPS = 8;
+
+// phylo_kmer_db::search in a shard seen through its view (the table kind is the view's: a run-time branch)
+__device__ __forceinline__ uint64_t view_search(const device_db& view, uint32_t key)
+{
+    return view.table_kind == TABLE_DIRECT ? db_search<TABLE_DIRECT>(view, key) : db_search<TABLE_HASH>(view, key);
+}
+
+// place.cpp:373-415 for one query of database-sharded mode, by the warp that finalises it: every key an ambiguous window
+// resolves to lives in exactly one shard, so walking the windows in order and looking each key up in its shard keeps
+// the reference's global "first ambiguous key to name a branch" order. The contributions go to the query's row of
+// shard 0 (S float, C uint16, in this GPU's memory), which the sweep then adds to the other shards' rows.
+__device__ __noinline__ void replay_ambiguous_into_row(const place_params& p, const char* seq, uint64_t n_windows, unsigned char* row0,
+                                                       uint32_t np, uint32_t* seen, uint8_t* codes, const uint32_t* letters,
+                                                       uint32_t lane, uint64_t& hits, uint64_t& entries)
+{
+    const device_db& db = p.db;
+    const uint32_t k = db.k, bits = db.bits;
+    const float kf = static_cast<float>(k);
+    const float thr_rest = __fmul_rn(static_cast<float>(k - 1), db.threshold);
+    float* S = reinterpret_cast<float*>(row0 + ROW_HEADER_BYTES);
+    uint16_t* C = reinterpret_cast<uint16_t*>(row0 + ROW_HEADER_BYTES + 4ull * np);
+    for (uint64_t c0 = 0; c0 < n_windows; c0 += CHUNK)
+    {
+        const uint32_t nw = static_cast<uint32_t>(min(n_windows - c0, static_cast<uint64_t>(CHUNK)));
+        const uint32_t ncode = nw + k - 1;
+        __syncwarp();
+        for (uint32_t i = lane; i < ncode; i += 32) { codes[i] = static_cast<uint8_t>(letters[static_cast<uint8_t>(seq[c0 + i])]); }
+        __syncwarp();
+        for (uint32_t r = 0; r * 32 < nw; ++r)
+        {
+            const uint32_t w = r * 32 + lane;
+            window_class c{ 0, 1, 0, 0 };
+            if (w < nw) { c = classify_window(codes, w, k, bits); }
+            uint32_t todo = __ballot_sync(FULL, c.gaps == 0 && c.ambs == 1);
+            while (todo)
+            {
+                const int src = __ffs(todo) - 1;
+                todo &= todo - 1;
+                const uint32_t base_key = __shfl_sync(FULL, c.key, src);
+                const uint32_t amb_at = __shfl_sync(FULL, c.amb_at, src);
+                const uint32_t letter = letters[static_cast<uint8_t>(seq[c0 + r * 32 + src + amb_at])];
+                uint32_t resolutions = letter >> 8;
+                const uint32_t shift = bits * (k - 1 - amb_at);
+                while (resolutions) // one key per resolution, each on its own (place.cpp:308-312)
+                {
+                    const uint32_t code = __ffs(resolutions) - 1;
+                    resolutions &= resolutions - 1;
+                    const uint32_t key = base_key | (code << shift);
+                    const device_db& view = p.shard_views[shard_of_key(key, p.n_shards)];
+                    const uint64_t found = view_search(view, key);
+                    const uint32_t flen = static_cast<uint32_t>(found & LEN_MASK);
+                    const uint2* list = view.postings + (found >> LEN_BITS);
+                    hits += flen != 0;
+                    entries += flen;
+                    for (uint32_t e = lane; e < flen; e += 32)
+                    {
+                        const uint2 entry = __ldg(list + e);
+                        const uint32_t bit = 1u << (entry.x & 31u);
+                        const uint32_t old = atomicOr(seen + (entry.x >> 5), bit);
+                        if (!(old & bit))
+                        {
+                            // first ambiguous key that names this branch: (10^s + (k-1)·thr)/k is added to the LOG
+                            // score (place.cpp:391,400-410)
+                            const float prob = static_cast<float>(pow(10.0, static_cast<double>(__uint_as_float(entry.y))));
+                            const float mean = __fdiv_rn(__fadd_rn(prob, thr_rest), kf);
+                            S[entry.x] = __fadd_rn(S[entry.x], mean);
+                            C[entry.x] = static_cast<uint16_t>(C[entry.x] + 1u);
+                        }
+                    }
+                    __syncwarp(); // (a list names a branch once; the next key may name the same branches from other lanes)
+                }
+            }
+        }
+    }
+    for (uint32_t i = lane; i < np / 32; i += 32) { seen[i] = 0; }
+    __threadfence_block();
+    __syncwarp();
+}
 
 __global__ void __launch_bounds__(FINALIZE_WARPS * 32, 2) finalize_kernel(const place_params p)
 {
@@ -2084,7 +2176,16 @@ __global__ void __launch_bounds__(FINALIZE_WARPS * 32, 2) finalize_kernel(const 
     const uint32_t N = db.n_nodes;
     const uint32_t np = padded_nodes(N);
     const uint32_t k = db.k;
-    uint32_t* cand_base = reinterpret_cast<uint32_t*>(smem + warp * FINALIZE_WARP_SMEM);
+    uint32_t* letters = reinterpret_cast<uint32_t*>(smem);
+    const bool can_replay = p.shard_views != nullptr && p.seq != nullptr;
+    if (can_replay)
+    {
+        for (uint32_t i = threadIdx.x; i < 256; i += blockDim.x) { letters[i] = p.letters[i]; }
+        __syncthreads();
+    }
+    uint32_t* cand_base = reinterpret_cast<uint32_t*>(smem + FINALIZE_CTA_SMEM + warp * FINALIZE_WARP_SMEM);
+    uint8_t* codes = reinterpret_cast<uint8_t*>(cand_base + cand_buffers<CAND_CAP>::WORDS);
+    uint32_t* seen = p.seen_scratch ? p.seen_scratch + (static_cast<size_t>(blockIdx.x) * FINALIZE_WARPS + warp) * (np / 32) : nullptr;
     const uint64_t row_bytes = partial_row_bytes(N);
 
     while (true)
@@ -2093,7 +2194,8 @@ __global__ void __launch_bounds__(FINALIZE_WARPS * 32, 2) finalize_kernel(const 
         if (lane == 0) { q = static_cast<uint32_t>(atomicAdd(p.counters + CTR_CURSOR, 1ull)); }
         q = __shfl_sync(FULL, q, 0);
         if (q >= p.n) { break; }
-        const uint64_t len = p.seq_off[q + 1] - p.seq_off[q];
+        const uint64_t s0 = p.seq_off[q];
+        const uint64_t len = p.seq_off[q + 1] - s0;
         const unsigned char* row0 = p.rows_in + static_cast<uint64_t>(q) * row_bytes;
         uint32_t flags = 0, gathered = 0;
         if (lane < p.n_shards)
@@ -2106,7 +2208,8 @@ __global__ void __launch_bounds__(FINALIZE_WARPS * 32, 2) finalize_kernel(const 
         gathered = __reduce_add_sync(FULL, gathered);
         const bool too_short = len + 1 < k;
         const uint64_t n_windows = too_short ? 0 : len + 1 - k;
-        if (too_short || n_windows > class_max_windows(1) || (flags & ROW_FLAG_AMBIGUOUS))
+        const bool ambiguous = (flags & ROW_FLAG_AMBIGUOUS) != 0;
+        if (too_short || n_windows > class_max_windows(1) || (ambiguous && !can_replay))
         {
             if (lane == 0)
             {
@@ -2115,12 +2218,20 @@ __global__ void __launch_bounds__(FINALIZE_WARPS * 32, 2) finalize_kernel(const 
             }
             continue;
         }
+        uint64_t amb_hits = 0, amb_entries = 0;
+        if (ambiguous)
+        {
+            replay_ambiguous_into_row(p, p.seq + s0, n_windows, const_cast<unsigned char*>(row0), np, seen, codes, letters, lane,
+                                      amb_hits, amb_entries);
+            gathered = static_cast<uint32_t>(min(static_cast<unsigned long long>(gathered) + amb_entries, 0xFFFFFFull));
+        }
         if (lane == 0)
         {
             atomicAdd(p.counters + CTR_WINDOWS, static_cast<unsigned long long>(n_windows));
             atomicAdd(p.counters + CTR_ENTRIES, static_cast<unsigned long long>(gathered));
+            if (amb_hits) { atomicAdd(p.counters + CTR_HITS, static_cast<unsigned long long>(amb_hits)); }
         }
-        const rows_acc acc{ row0 + ROW_HEADER_BYTES, row0 + ROW_HEADER_BYTES + 4ull * np, p.shard_stride, p.n_shards };
+        const rows_acc acc{ row0 + ROW_HEADER_BYTES, row0 + ROW_HEADER_BYTES + 4ull * np, p.shard_stride, p.n_shards, ambiguous };
         finish_query(p, acc, np, n_windows, gathered, q, lane, cand_base);
     }
 }

@@ -115,6 +115,9 @@ struct epk_placer
     device_buffer<unsigned long long> totals;          // running work counters (bumped by the launches)
     device_buffer<unsigned long long> device_counters; // per-launch counters of epk_place_device
     device_buffer<uint32_t> device_class_reads;
+    device_buffer<device_db> shard_views;   // epk_placer_set_shard_views: the shards of a database-sharded group, from this device
+    uint32_t n_shard_views = 0;
+    device_buffer<uint32_t> seen_scratch;   // bitmaps of the finalising launch's ambiguous-window replay (one per warp)
     chunk_slot slots[N_SLOTS];
     uint64_t n_launches = 0, n_reads = 0;
     cudaStream_t last_stream = nullptr;
@@ -728,9 +731,56 @@ extern "C" epk_status epk_place_partial_device(epk_placer* pl, const char* d_seq
     });
 }
 
-extern "C" epk_status epk_place_finalize_device(epk_placer* pl, const void* d_rows, uint32_t n_shards,
-                                                uint64_t shard_stride_bytes, const uint64_t* d_seq_off, uint32_t n,
-                                                const epk_result* d_out, void* stream)
+extern "C" epk_status epk_db_get_view(const epk_db* db, epk_db_view* out)
+{
+    return guarded([&] {
+        if (!db || !out) { throw error(EPK_E_INVALID, "null argument"); }
+        out->table = reinterpret_cast<uint64_t>(db->table_kind == TABLE_DIRECT ? static_cast<const void*>(db->direct.get())
+                                                                               : static_cast<const void*>(db->hashed.get()));
+        out->postings = reinterpret_cast<uint64_t>(db->postings.get());
+        out->hash_mask = db->d.hash_mask;
+        out->hash_shift = db->d.hash_shift;
+        out->table_kind = db->table_kind;
+    });
+}
+
+extern "C" epk_status epk_placer_set_shard_views(epk_placer* pl, uint32_t n_shards, const epk_db_view* views)
+{
+    return guarded([&] {
+        if (!pl || (n_shards && !views)) { throw error(EPK_E_INVALID, "null argument"); }
+        if (n_shards > 32) { throw error(EPK_E_INVALID, "n_shards must be in [0, 32]"); }
+        EPK_CUDA(cudaSetDevice(pl->db->device));
+        EPK_CUDA(cudaDeviceSynchronize()); // no launch may still be reading the old views
+        pl->n_shard_views = 0;
+        pl->shard_views.release();
+        if (n_shards == 0) { return; }
+        std::vector<device_db> host(n_shards, pl->db->d); // k, alphabet, thresholds are the group's; the tables are each shard's
+        for (uint32_t g = 0; g < n_shards; ++g)
+        {
+            if (!views[g].table || !views[g].postings) { throw error(EPK_E_INVALID, "null address in a shard view"); }
+            if (views[g].table_kind != pl->db->table_kind) { throw error(EPK_E_INVALID, "the shards of a group share one table kind"); }
+            host[g].direct = views[g].table_kind == TABLE_DIRECT ? reinterpret_cast<const uint64_t*>(views[g].table) : nullptr;
+            host[g].hashed = views[g].table_kind == TABLE_HASH ? reinterpret_cast<const uint4*>(views[g].table) : nullptr;
+            host[g].postings = reinterpret_cast<const uint2*>(views[g].postings);
+            host[g].hash_mask = views[g].hash_mask;
+            host[g].hash_shift = views[g].hash_shift;
+            host[g].table_kind = views[g].table_kind;
+        }
+        pl->shard_views.resize(n_shards);
+        EPK_CUDA(cudaMemcpy(pl->shard_views.get(), host.data(), n_shards * sizeof(device_db), cudaMemcpyHostToDevice));
+        const size_t words = static_cast<size_t>(2) * pl->n_sms * FINALIZE_WARPS * (padded_nodes(pl->db->d.n_nodes) / 32);
+        if (pl->seen_scratch.size() < words)
+        {
+            pl->seen_scratch.resize(words);
+            EPK_CUDA(cudaMemset(pl->seen_scratch.get(), 0, words * 4));
+        }
+        pl->n_shard_views = n_shards;
+    });
+}
+
+extern "C" epk_status epk_place_finalize_seq_device(epk_placer* pl, void* d_rows, uint32_t n_shards, uint64_t shard_stride_bytes,
+                                                    const char* d_seq, const uint64_t* d_seq_off, uint32_t n,
+                                                    const epk_result* d_out, void* stream)
 {
     return guarded([&] {
         if (!pl || !d_out || (n && (!d_rows || !d_seq_off || !d_out->n_place || !d_out->branch || !d_out->score || !d_out->lwr || !d_out->count)))
@@ -758,6 +808,14 @@ extern "C" epk_status epk_place_finalize_device(epk_placer* pl, const void* d_ro
         p.rows_in = static_cast<const unsigned char*>(d_rows);
         p.n_shards = n_shards;
         p.shard_stride = shard_stride_bytes;
+        // ambiguous windows are replayed here when the owner can see every shard and has the letters
+        if (d_seq && pl->n_shard_views == n_shards)
+        {
+            p.seq = d_seq;
+            p.letters = pl->db->letters.get();
+            p.shard_views = pl->shard_views.get();
+            p.seen_scratch = pl->seen_scratch.get();
+        }
         // the counters of this call replace those of the partial launch: they now describe whole queries
         EPK_CUDA(cudaMemsetAsync(pl->totals.get(), 0, pl->totals.bytes(), s));
         p.counters = pl->totals.get();
@@ -767,13 +825,20 @@ extern "C" epk_status epk_place_finalize_device(epk_placer* pl, const void* d_ro
         {
             const unsigned grid = static_cast<unsigned>(
                 std::min<uint64_t>(2ull * pl->n_sms, (static_cast<uint64_t>(n) + FINALIZE_WARPS - 1) / FINALIZE_WARPS));
-            finalize_kernel<<<grid, FINALIZE_WARPS * 32, FINALIZE_WARPS * FINALIZE_WARP_SMEM, s>>>(p);
+            finalize_kernel<<<grid, FINALIZE_WARPS * 32, FINALIZE_CTA_SMEM + FINALIZE_WARPS * FINALIZE_WARP_SMEM, s>>>(p);
             EPK_CUDA(cudaGetLastError());
             ++pl->n_launches;
         }
         pl->totals_dirty = true;
         pl->last_stream = s;
     });
+}
+
+extern "C" epk_status epk_place_finalize_device(epk_placer* pl, const void* d_rows, uint32_t n_shards,
+                                                uint64_t shard_stride_bytes, const uint64_t* d_seq_off, uint32_t n,
+                                                const epk_result* d_out, void* stream)
+{
+    return epk_place_finalize_seq_device(pl, const_cast<void*>(d_rows), n_shards, shard_stride_bytes, nullptr, d_seq_off, n, d_out, stream);
 }
 
 // ---- peer memory for the fused exchange of database-sharded mode -------------------------------------

@@ -68,6 +68,8 @@ class LocalShardedPlacer:
     def __init__(self, flat, n_shards: int, device: int = 0, keep_at_most: int = 7, keep_factor: float = 0.01, **load):
         self.dbs = [Database(flat, device=device, shard=(g, n_shards), **load) for g in range(n_shards)]
         self.placers = [Placer(db, keep_at_most, keep_factor) for db in self.dbs]
+        # the finalising placer sees every shard: windows with one ambiguous letter are replayed there (place.cpp:373-415)
+        self.placers[0].set_shard_views([db.view() for db in self.dbs])
         self.n_shards = n_shards
         self.device = device
         self.keep_at_most = keep_at_most
@@ -91,7 +93,8 @@ class LocalShardedPlacer:
                 # absolute offsets: the sequence base stays, the offsets pointer moves
                 pl.place_partial_device(d_seq, _Ptr(off_ptr), m, [0, m], [slab[g].data_ptr()])
             piece = {k: v[first:first + m] for k, v in out.items()}
-            self.placers[0].place_finalize_device(slab.data_ptr(), self.n_shards, step * row_bytes, off_ptr, m, piece)
+            self.placers[0].place_finalize_device(slab.data_ptr(), self.n_shards, step * row_bytes, off_ptr, m, piece,
+                                                  d_seq_ptr=d_seq.data_ptr())
             c = self.placers[0].counters()
             self.unsupported += c["n_unsupported"]
             self.short += c["n_short"]
@@ -114,7 +117,8 @@ class ShardedPlacer:
     SAME batch; rank r gets back the placements of its slice [first, last) of the batch."""
 
     def __init__(self, flat, rank: int, world: int, group=None, device: int = 0, keep_at_most: int = 7,
-                 keep_factor: float = 0.01, transport: str = "a2a", max_rows: int = 1 << 15, **load):
+                 keep_factor: float = 0.01, transport: str = "a2a", max_rows: int = 1 << 15, peer_databases: bool = True,
+                 **load):
         if transport not in ("a2a", "p2p"):
             raise ValueError("transport must be 'a2a' or 'p2p'")
         self.db = Database(flat, device=device, shard=(rank, world), **load)
@@ -128,9 +132,11 @@ class ShardedPlacer:
         self.unsupported = 0
         self.short = 0
         self._slabs, self._peer = [], []
+        self._peer_db = []
         self._turn = 0
         if transport == "p2p":
             self._open_peer_slabs()
+        self.replays_ambiguous = self._open_peer_databases() if peer_databases else False
 
     # ------------------------------------------------------------------ fused exchange -----
     def _slab_rows(self) -> int:
@@ -165,11 +171,56 @@ class ShardedPlacer:
                 mapped.append(q.value)
             self._peer.append(mapped)
 
+    def _open_peer_databases(self) -> bool:
+        """Maps every peer shard's key table and postings here (CUDA IPC over NVLink) and hands the views to the placer:
+        the finalising launch then replays the ambiguous windows of its queries against the shard that holds each key.
+        With either transport (the rows may still travel through NCCL). False if the peers cannot be mapped."""
+        import ctypes as C
+        import torch.distributed as dist
+        from . import capi
+        l = capi.lib()
+        mine = self.db.view()
+        handles = []
+        for addr in (mine.table, mine.postings):
+            h = C.create_string_buffer(64)
+            capi.check(l.epk_ipc_export(C.c_void_p(addr), h))
+            handles.append(h.raw)
+        everyone = [None] * self.world
+        dist.all_gather_object(everyone, (handles, int(mine.hash_mask), int(mine.hash_shift), int(mine.table_kind)), group=self.group)
+        views, ok = [], True
+        for r in range(self.world):
+            if r == self.rank:
+                views.append(mine)
+                continue
+            (h_table, h_post), mask, shift, kind = everyone[r]
+            addrs = []
+            for h in (h_table, h_post):
+                q = C.c_void_p()
+                if l.epk_ipc_import(self.device, h, C.byref(q)) != capi.EPK_OK:
+                    ok = False
+                    break
+                addrs.append(q.value)
+                self._peer_db.append(q.value)
+            if not ok:
+                break
+            views.append(capi.DbView(addrs[0], addrs[1], mask, shift, kind))
+        flags = [None] * self.world
+        dist.all_gather_object(flags, ok, group=self.group)
+        if not all(flags):
+            return False
+        self.placer.set_shard_views(views)
+        return True
+
     def close(self):
-        if not self._slabs and not self._peer:
+        if not self._slabs and not self._peer and not self._peer_db:
             return
         from . import capi
         l = capi.lib()
+        if self._peer_db:
+            self.placer.set_shard_views([])
+            for p in self._peer_db:
+                l.epk_ipc_close(self.device, p)
+            self._peer_db = []
         for turn, mapped in enumerate(self._peer):
             for r, p in enumerate(mapped):
                 if r != self.rank:
@@ -204,7 +255,8 @@ class ShardedPlacer:
         m = last - first
         if out is None:
             out = _alloc_out(torch, m, self.keep_at_most, d_off.device)
-        self.placer.place_finalize_device(self._slabs[turn], self.world, stride, d_off.data_ptr() + 8 * first, m, out)
+        self.placer.place_finalize_device(self._slabs[turn], self.world, stride, d_off.data_ptr() + 8 * first, m, out,
+                                          d_seq_ptr=d_seq.data_ptr())
         return out, first, last
 
     _flag = None
@@ -227,7 +279,8 @@ class ShardedPlacer:
         m = last - first
         if out is None:
             out = _alloc_out(torch, m, self.keep_at_most, dev)
-        self.placer.place_finalize_device(slabs.data_ptr(), self.world, m * self.row_bytes, d_off.data_ptr() + 8 * first, m, out)
+        self.placer.place_finalize_device(slabs.data_ptr(), self.world, m * self.row_bytes, d_off.data_ptr() + 8 * first, m, out,
+                                          d_seq_ptr=d_seq.data_ptr())
         return out, first, last
 
     def place_packed(self, data, offsets):

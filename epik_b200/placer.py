@@ -145,6 +145,16 @@ class PlacedCollection:
     placed_seqs: list = field(default_factory=list)
 
 
+def _db_view(self) -> "capi.DbView":
+    """epk_db_get_view: the device addresses of this database's key table and postings."""
+    v = capi.DbView()
+    capi.check(capi.lib().epk_db_get_view(self.handle, C.byref(v)))
+    return v
+
+
+Database.view = _db_view
+
+
 class Placer:
     """epik::placer (place.h:81-140)."""
 
@@ -241,14 +251,21 @@ class Placer:
                                                        len(row_ptrs), _ptr(first), ptrs, s))
 
     def place_finalize_device(self, rows_ptr: int, n_shards: int, shard_stride: int, d_off_ptr: int, n: int, d_out: dict,
-                              stream=None):
-        """epk_place_finalize_device over n queries whose rows of shard g start at rows_ptr + g * shard_stride."""
+                              stream=None, d_seq_ptr: int | None = None):
+        """epk_place_finalize_seq_device over n queries whose rows of shard g start at rows_ptr + g * shard_stride.
+        With d_seq_ptr (the base the offsets refer to) and shard views set, ambiguous windows are replayed here."""
         res = capi.Result(d_out["n_place"].data_ptr(), d_out["branch"].data_ptr(), d_out["score"].data_ptr(),
                           d_out["lwr"].data_ptr(), d_out["count"].data_ptr(), None, None)
         s = None if stream is None else C.c_void_p(stream.cuda_stream)
-        capi.check(capi.lib().epk_place_finalize_device(self.handle, C.c_void_p(int(rows_ptr)), int(n_shards),
-                                                        int(shard_stride), C.c_void_p(int(d_off_ptr)), int(n),
-                                                        C.byref(res), s))
+        seq = None if d_seq_ptr is None else C.c_void_p(int(d_seq_ptr))
+        capi.check(capi.lib().epk_place_finalize_seq_device(self.handle, C.c_void_p(int(rows_ptr)), int(n_shards),
+                                                            int(shard_stride), seq, C.c_void_p(int(d_off_ptr)), int(n),
+                                                            C.byref(res), s))
+
+    def set_shard_views(self, views) -> None:
+        """epk_placer_set_shard_views: views[g] = capi.DbView of shard g with addresses valid on this placer's device."""
+        arr = (capi.DbView * len(views))(*views)
+        capi.check(capi.lib().epk_placer_set_shard_views(self.handle, len(views), C.cast(arr, C.c_void_p) if len(views) else None))
 
     def gather_ceiling_device(self, d_seq, d_off, n: int, d_checksum, stream=None):
         """epk_gather_ceiling_device: the load-only form of the placement launch (roofline measuring stick)."""

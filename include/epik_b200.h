@@ -205,8 +205,9 @@ epk_status epk_placer_counters(epk_placer* placer, epk_counters* out);
  * is the caller's: an NCCL all-to-all of the row buffers, or row buffers that ARE the owners' memory
  * (CUDA IPC / peer pointers over NVLink), in which case the partial launch is the exchange.
  * Scores agree with the reference within float rounding of a re-associated sum (1e-5 relative), not
- * bit for bit. Queries with ambiguous windows (place.cpp:373-415 needs the global key order) and
- * queries with more than 65535 windows are reported through epk_counters.n_unsupported, n_place = 0. */
+ * bit for bit. Queries with more than 65535 windows are reported through epk_counters.n_unsupported,
+ * n_place = 0; so are queries with ambiguous windows (place.cpp:373-415 needs the global key order) unless
+ * the owner has been given the views of all the shards - see "windows with one ambiguous letter" below. */
 
 /* epk_db_create keeping only the keys of shard `shard_index` of `shard_count`; the load filter's
  * informative prefix (mu / max_entries) is still taken over the whole description. */
@@ -232,6 +233,39 @@ epk_status epk_place_partial_device(epk_placer* placer, const char* d_seq, const
 epk_status epk_place_finalize_device(epk_placer* placer, const void* d_rows, uint32_t n_shards,
                                      uint64_t shard_stride_bytes, const uint64_t* d_seq_off, uint32_t n,
                                      const epk_result* d_out, void* stream);
+
+/* ---- windows with one ambiguous letter in database-sharded mode -----------------------------------------
+ *
+ * place.cpp:373-415 lets the FIRST ambiguous key (window order, then resolution order) that names a branch
+ * decide that branch's contribution - an order over all keys, which no shard has. The owner of a query has
+ * it: with the views of all the shards set (epk_placer_set_shard_views) and the letters passed along
+ * (epk_place_finalize_seq_device), the finalising launch replays the ambiguous windows of its flagged queries
+ * itself, looking every resolved key up in the one shard that holds it (its own HBM, or a peer's key table
+ * and postings mapped over NVLink with epk_ipc_export / epk_ipc_import on the addresses of the view), and adds
+ * the contributions to the query's row of shard 0 before the rows are summed and swept. Without views such
+ * queries stay unplaced (n_place = 0, counted in n_unsupported) as before. */
+typedef struct epk_db_view
+{
+    uint64_t table;       /* device address of the key table (base of its allocation)              */
+    uint64_t postings;    /* device address of the postings  (base of its allocation)              */
+    uint64_t hash_mask;   /* open addressing: slots - 1                                            */
+    uint32_t hash_shift;
+    uint32_t table_kind;  /* 0 direct-address, 1 open addressing                                   */
+} epk_db_view;
+
+/* The addresses of this database on its own device. */
+epk_status epk_db_get_view(const epk_db* db, epk_db_view* out);
+
+/* views[g] = shard g of the group (this placer's own shard included), with addresses valid on THIS placer's
+ * device; n_shards as passed to epk_place_finalize_*; n_shards = 0 forgets them. The views are copied. */
+epk_status epk_placer_set_shard_views(epk_placer* placer, uint32_t n_shards, const epk_db_view* views);
+
+/* epk_place_finalize_device with the letters of the n queries: d_seq + d_seq_off[i] is query i (the same
+ * absolute offsets and base the partial launches were given). d_seq = NULL behaves like
+ * epk_place_finalize_device. The rows of flagged queries are modified in place. */
+epk_status epk_place_finalize_seq_device(epk_placer* placer, void* d_rows, uint32_t n_shards,
+                                         uint64_t shard_stride_bytes, const char* d_seq, const uint64_t* d_seq_off,
+                                         uint32_t n, const epk_result* d_out, void* stream);
 
 /* Peer memory for the fused exchange: with one process per GPU, each owner allocates its slab with
  * epk_device_alloc, exports it (64-byte CUDA IPC handle, sent to the peers by any means), the peers
