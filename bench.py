@@ -58,7 +58,7 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="C2", choices=["C2", "C3", "C4", "C1p", "C5r"])
+    ap.add_argument("--workload", default="C2", choices=["C2", "C3", "C4", "C1p", "C5r", "C5"])
     ap.add_argument("--mode", default="replicated", choices=["replicated", "dbshard"],
                     help="replicated: queries sharded over the ranks, database in every HBM (default); "
                          "dbshard: database sharded by key over the ranks, every rank sees every query, partial rows "
@@ -70,11 +70,14 @@ def parse_args():
     ap.add_argument("--reads", type=int, default=0, help="reads per GPU per step (default: the workload's)")
     ap.add_argument("--variant", type=int, default=0)
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-dbshard", action="store_true", help="N > 1: skip the database-sharded leg (the `dbshard` key)")
+    ap.add_argument("--dbshard-reads", type=int, default=262144, help="reads per step of the database-sharded leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
 
 
-WORKLOAD_READS = {"C2": 10_000_000, "C3": 10_000_000, "C4": 1_000_000, "C1p": 100_000, "C5r": 1_000_000}
+WORKLOAD_READS = {"C2": 10_000_000, "C3": 10_000_000, "C4": 1_000_000, "C1p": 100_000, "C5r": 1_000_000, "C5": 2_000_000}
+DEVICE_GENERATED = ("C5",)  # databases that exist only as the on-device generator makes them (epk_db_create_synthetic)
 
 
 def workload_config(name, n_reads, world):
@@ -167,6 +170,24 @@ def cpu_reference(db, alphabet, read_len, seconds_target, steps=1, warmup=0, loa
     from oracle import oracle as O
     kind = "reference" if O.available("reference", alphabet) else "port"
     cores = host_threads()
+    gen = db if isinstance(db, synth.Gen2) else None
+    if gen is not None:
+        # a device-generated database: the reference is given the lists of the keys its sample of reads looks up and
+        # nothing else (same look-ups, same hits, same postings; a smaller hash map than the real one - which flatters
+        # the CPU a little: fewer cache misses per look-up)
+        n = 4000  # (130 M postings of lists for these reads: what numpy restates in a few seconds)
+        data, off = synth.make_reads(alphabet, n, read_len, first=0)
+        sub = gen.lists(synth.keys_of_reads(alphabet, gen.k, data, off))
+        o = O.Oracle(sub, 7, 0.01, cores, kind=kind)
+        times = []
+        for i in range(warmup + steps + 1):
+            r = o.place_packed(data, off, threads=cores, batch_size=2000)
+            if i >= warmup + 1:
+                times.append(r["seconds"])
+        value = n * len(times) / sum(times)
+        sample = "%d reads of the workload (the first %d) against the %d lists they look up, batches of 2000 (main.cpp:214), " \
+                 "timer around placer::place only (main.cpp:343-345), %d OpenMP threads" % (n, n, sub.n_keys, cores)
+        return value, ("reference" if kind == "reference" else "port"), cores, sample, sum(times) / len(times)
     if load_filter is not None:
         # what i2l::load would hand the placer (main.cpp:277): the filter applied before the timed region
         from oracle import load_filter as LF
@@ -202,7 +223,7 @@ def run_reference(args):
     from epik_b200 import synth
     alphabet, k, n_leaves, p_occ, m, read_len = synth.CONFIGS[args.workload]
     n_reads = args.reads or WORKLOAD_READS[args.workload]
-    db = synth.make_config_db(args.workload)
+    db = synth.make_config_gen2(args.workload) if args.workload in DEVICE_GENERATED else synth.make_config_db(args.workload)
     total = max(args.steps + args.warmup, 1)
     value, kind, cores, sample, step_s = cpu_reference(db, alphabet, read_len, seconds_target=min(20.0, 150.0 / total),
                                                        steps=args.steps, warmup=args.warmup,
@@ -263,9 +284,15 @@ def run_ours(args):
     n = args.reads or WORKLOAD_READS[args.workload]
     K = 7
     log("world %d, device %d: generating database %s" % (world, local, args.workload))
-    flat = synth.make_config_db(args.workload)
     flt = synth.LOAD_FILTERS.get(args.workload)
-    db = Database(flat, device=local) if flt is None else Database(flat, mu=flt[0], omega=flt[1], max_entries=flt[2], device=local)
+    if args.workload in DEVICE_GENERATED:
+        flat = synth.make_config_gen2(args.workload)
+        t_build = time.perf_counter()
+        db = Database.synthetic(flat, device=local)
+        log("generated and built on the device in %.1f s" % (time.perf_counter() - t_build))
+    else:
+        flat = synth.make_config_db(args.workload)
+        db = Database(flat, device=local) if flt is None else Database(flat, mu=flt[0], omega=flt[1], max_entries=flt[2], device=local)
     placer = Placer(db, K, 0.01, variant=args.variant)
 
     log("database on the device: %d entries; generating %d reads" % (db.info["n_entries_loaded"], n))
@@ -383,14 +410,33 @@ def run_ours(args):
     # ---- e2e: pinned host buffers through epk_place, copies inside the timed region ----
     e2e = None
     if not args.no_e2e:
-        out = placer.alloc_result(n, pinned=True, lengths=False)
+        # what placer::place does between taking a batch and handing back its placed_collection (place.cpp:201-275):
+        # the grouping of identical sequences per --batch-size batch (place.cpp:207) - here on the host threads,
+        # concurrently with the device pass, as the C++ facade does - the placement itself, and the distal / pendant
+        # lengths of the kept placements (place.cpp:424-439, filled by epk_place after the copy out)
+        import ctypes
+        from epik_b200 import capi
+        out = placer.alloc_result(n, pinned=True, lengths=True)
+        group_rep = np.zeros(n, np.uint32)
+        threads = max(1, host_threads() // max(1, world))
+
+        def group():
+            capi.check(capi.lib().epk_group_batches(h_seq.array.ctypes.data_as(ctypes.c_void_p), h_off.array.ctypes.data_as(ctypes.c_void_p),
+                                                    n, 2000, threads, group_rep.ctypes.data_as(ctypes.c_void_p)))
+
+        def one_pass():
+            worker = threading.Thread(target=group)
+            worker.start()
+            placer.place_packed(h_seq.array, h_off.array, out=out)
+            worker.join()
+
         e2e_warm = min(args.warmup, 1)
         for _ in range(e2e_warm):
-            placer.place_packed(h_seq.array, h_off.array, out=out)
+            one_pass()
         barrier()
         t0 = time.perf_counter()
         for _ in range(args.steps):
-            placer.place_packed(h_seq.array, h_off.array, out=out)
+            one_pass()
         torch.cuda.synchronize()
         t1 = time.perf_counter()
         e2e_s = max_over_ranks(t1 - t0)
@@ -400,13 +446,24 @@ def run_ours(args):
                "h2d_bytes_per_step": int(n * read_len + (n + 1) * 8),
                "d2h_bytes_per_step": int(n * (4 + K * 20)),
                "ms_per_step": e2e_s / args.steps * 1e3,
-               "api": "epk_place (C ABI), pinned host buffers, %d-read chunks on 3 streams" % (1 << 18)}
+               "api": "epk_place (C ABI), pinned host buffers, %d-read chunks on 3 streams, distal / pendant filled; "
+                      "epk_group_batches (batches of 2000, place.cpp:207) on %d host threads alongside" % (1 << 18, threads)}
 
+    db_info = {k2: int(v2) if isinstance(v2, (int, np.integer)) else float(v2) for k2, v2 in db.info.items()}
     # ---- CPU baseline: rank 0, N = 1 only ----
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         v, kind, cores, sample, _ = cpu_reference(flat, alphabet, read_len, seconds_target=15.0, load_filter=flt)
         cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample}
+
+    # ---- N > 1: the one path with an exchange - BASELINE config 5 with the database SHARDED over the ranks ----
+    dbshard_leg = None
+    if world > 1 and not args.no_dbshard:
+        del placer, db, d_seq, d_off, d_out
+        h_seq.free() if hasattr(h_seq, "free") else None
+        torch.cuda.empty_cache()
+        dbshard_leg = time_dbshard(args, "C5", rank, world, local, dev, reads=args.dbshard_reads, steps=max(2, min(args.steps, 3)),
+                                   warmup=1, transport=args.transport)
 
     total_reads = sum_over_ranks(float(n))
     if rank == 0:
@@ -417,11 +474,67 @@ def run_ours(args):
             "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
             "kmer_lookups_per_sec": value * (read_len - k + 1), "reads_per_step_all_gpus": int(total_reads),
             "dtype_note": "scores accumulate in f32 (bit-identical to the reference), likelihood weight ratios in f64",
-            "db": {k2: int(v2) if isinstance(v2, (int, np.integer)) else float(v2) for k2, v2 in db.info.items()},
+            "db": db_info,
         }
+        if dbshard_leg is not None:
+            line["dbshard"] = dbshard_leg
         emit(line)
     if world > 1:
         dist.destroy_process_group()
+
+
+def time_dbshard(args, workload, rank, world, local, dev, reads, steps, warmup, transport):
+    """One measurement of database-sharded mode inside an initialised process group: rank r holds shard r of
+    `workload`'s keys, every rank sees the same `reads` queries per step and finalises its slice of them. Returns the
+    record of the `dbshard` key (rank 0) - reads of a step / max-over-ranks time."""
+    import torch
+    import torch.distributed as dist
+    from epik_b200 import dbshard, synth
+    alphabet, k, n_leaves, p_occ, m, read_len = synth.CONFIGS[workload]
+    K = 7
+    flat = synth.make_config_gen2(workload) if workload in DEVICE_GENERATED else synth.make_config_db(workload)
+    rows = args.dbshard_rows
+    sp = dbshard.ShardedPlacer(flat, rank, world, device=local, keep_at_most=K, transport=transport, max_rows=rows)
+    h_seq = np.zeros(reads * read_len, np.uint8)
+    make_reads_chunked(alphabet, reads, read_len, 0, h_seq)  # the SAME reads on every rank
+    d_seq = torch.from_numpy(h_seq).to(dev)
+    d_off = torch.from_numpy((np.arange(reads + 1, dtype=np.uint64) * np.uint64(read_len)).view(np.int64)).to(dev)
+
+    def step():
+        out = None
+        for first in range(0, reads, rows):
+            mrows = min(rows, reads - first)
+            out, _, _ = sp.place_device(d_seq, d_off[first:first + mrows + 1], mrows)
+        return out
+
+    for _ in range(warmup):
+        step()
+    torch.cuda.synchronize()
+    dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        out = step()
+    e1.record()
+    torch.cuda.synchronize()
+    dist.barrier()
+    t = torch.tensor([e0.elapsed_time(e1) / 1e3], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    secs = float(t.item())
+    placed = torch.tensor([float(out["n_place"].sum().item())], dtype=torch.float64, device=dev)
+    dist.all_reduce(placed, op=dist.ReduceOp.SUM)
+    row_bytes = sp.row_bytes
+    info = sp.db.info
+    sp.close()
+    return {"metric": METRIC, "value": reads * steps / secs, "unit": UNIT, "n_gpus": world, "scaling": "strong",
+            "workload": "%s: k=%d, %d branches, database sharded by key hash over %d GPUs (%.1f GB of postings per shard), "
+                        "%d x %d-letter reads per step, every rank sees every read" % (
+                            workload, k, 2 * n_leaves - 1, world, info["n_entries_loaded"] * 8 / 1e9, reads, read_len),
+            "transport": transport, "ms_per_step": secs / steps * 1e3, "steps": steps, "queries_per_exchange": rows,
+            "row_bytes": int(row_bytes), "exchange_bytes_per_query": row_bytes * (world - 1) / world,
+            "ambiguous_reads": "replayed by the owner over the peers' tables" if sp.replays_ambiguous else "unsupported",
+            "placed_last_pass": int(placed.item())}
 
 
 def run_dbshard(args):
@@ -443,7 +556,7 @@ def run_dbshard(args):
     n = args.reads or WORKLOAD_READS[args.workload]
     K = 7
     log("dbshard: world %d, generating database %s" % (world, args.workload))
-    flat = synth.make_config_db(args.workload)
+    flat = synth.make_config_gen2(args.workload) if args.workload in DEVICE_GENERATED else synth.make_config_db(args.workload)
     if world > 1:
         sp = dbshard.ShardedPlacer(flat, rank, world, device=local, keep_at_most=K, transport=args.transport,
                                    max_rows=args.dbshard_rows)

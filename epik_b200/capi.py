@@ -24,7 +24,7 @@ SYMBOLS = [
     "epk_place_finalize_device", "epk_gather_ceiling_device",
     "epk_device_alloc", "epk_device_free", "epk_ipc_export", "epk_ipc_import", "epk_ipc_close",
     "epk_gather_microbench", "epk_placer_set_trace", "epk_trace_term",
-    "epk_db_get_view", "epk_placer_set_shard_views", "epk_place_finalize_seq_device",
+    "epk_db_get_view", "epk_placer_set_shard_views", "epk_place_finalize_seq_device", "epk_db_create_synthetic", "epk_place_many", "epk_group_batches",
 ]
 
 
@@ -59,6 +59,13 @@ class DbInfo(C.Structure):
 class DbView(C.Structure):
     _fields_ = [("table", C.c_uint64), ("postings", C.c_uint64), ("hash_mask", C.c_uint64), ("hash_shift", C.c_uint32),
                 ("table_kind", C.c_uint32)]
+
+
+class SynthDesc(C.Structure):
+    _fields_ = [("alphabet", C.c_uint32), ("kmer_size", C.c_uint32), ("omega", C.c_float), ("n_nodes", C.c_uint32),
+                ("branch_length", C.c_void_p), ("subtree_num_nodes", C.c_void_p), ("subtree_total_length", C.c_void_p),
+                ("seed", C.c_uint64), ("presence_threshold", C.c_uint64), ("length_table", C.c_void_p),
+                ("length_table_bits", C.c_uint32), ("score_lo", C.c_double), ("key_space_limit", C.c_uint64)]
 
 
 class PlacerOpts(C.Structure):
@@ -110,10 +117,14 @@ def lib():
     l.epk_placer_destroy.restype = None
     l.epk_place.restype = C.c_int
     l.epk_place.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.POINTER(Result)]
+    l.epk_place_many.restype = C.c_int
+    l.epk_place_many.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32, C.POINTER(Result)]
     l.epk_place_device.restype = C.c_int
     l.epk_place_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.POINTER(Result), C.c_void_p]
     l.epk_group_batch.restype = C.c_int
     l.epk_group_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
+    l.epk_group_batches.restype = C.c_int
+    l.epk_group_batches.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p]
     l.epk_kmers.restype = C.c_int
     l.epk_kmers.argtypes = [C.c_void_p, C.c_char_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p,
                             C.c_void_p, C.POINTER(C.c_uint64)]
@@ -150,6 +161,9 @@ def lib():
     l.epk_trace_term.argtypes = [C.c_uint32] * 4
     l.epk_gather_microbench.restype = C.c_int
     l.epk_gather_microbench.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32, C.POINTER(Microbench)]
+    l.epk_db_create_synthetic.restype = C.c_int
+    l.epk_db_create_synthetic.argtypes = [C.POINTER(SynthDesc), C.POINTER(LoadFilter), C.c_int, C.c_uint32, C.c_uint32,
+                                          C.POINTER(C.c_void_p)]
     l.epk_db_get_view.restype = C.c_int
     l.epk_db_get_view.argtypes = [C.c_void_p, C.POINTER(DbView)]
     l.epk_placer_set_shard_views.restype = C.c_int

@@ -3,8 +3,11 @@
 // sm_100a placement kernel (place_kernel.cuh).
 #include <algorithm>
 #include <cstring>
+#include <future>
 #include <memory>
+#include <string>
 #include <string_view>
+#include <thread>
 #include <unordered_map>
 #include <vector>
 
@@ -87,6 +90,9 @@ namespace
         // pending copy-out of the previous chunk that used this slot (pageable destination)
         bool pending = false;
         uint32_t pending_first = 0, pending_n = 0;
+        // rows of the caller's arrays this slot's work in flight will have filled once its stream is idle
+        bool rows_in_flight = false;
+        uint32_t rows_first = 0, rows_n = 0;
     };
 } // namespace
 } // namespace epk
@@ -500,8 +506,9 @@ extern "C" epk_status epk_place(epk_placer* pl, const char* seq, const uint64_t*
             {
                 for (auto& s : pl.slots)
                 {
-                    if (s.pending) { cudaStreamSynchronize(s.stream); }
+                    if (s.pending || s.rows_in_flight) { cudaStreamSynchronize(s.stream); }
                     s.pending = false;
+                    s.rows_in_flight = false;
                 }
             }
             ~pending_guard() { clear(); }
@@ -517,6 +524,37 @@ extern "C" epk_status epk_place(epk_placer* pl, const char* seq, const uint64_t*
                                 && is_pinned(out->lwr) && is_pinned(out->count);
         const size_t max_chunk_bytes = 256u << 20;
 
+        // distal / pendant are look-ups by branch (place.cpp:434-437; zero for the zero-hit placements): 2 x 8 bytes per
+        // placement row - 1.1 GB for 10 M reads, 0.2 s on one thread. The rows of a chunk are filled on a thread of their
+        // own as soon as the chunk has landed in the caller's arrays, while the GPU works on the chunks behind it.
+        const bool want_lengths = out->distal || out->pendant;
+        std::vector<std::future<void>> filling;
+        auto fill_lengths = [pl, out, K](size_t row0, size_t rows) {
+            const auto& db = *pl->db;
+            for (size_t i = row0; i < row0 + rows; ++i)
+            {
+                for (size_t j = 0; j < K; ++j)
+                {
+                    const size_t at = i * K + j;
+                    const bool real = j < out->n_place[i] && out->count[at] != 0;
+                    if (out->distal) { out->distal[at] = real ? db.distal[out->branch[at]] : 0.0; }
+                    if (out->pendant) { out->pendant[at] = real ? db.pendant[out->branch[at]] : 0.0; }
+                }
+            }
+        };
+        auto landed = [&](chunk_slot& s) { // the slot's stream is idle and its rows are in the caller's arrays
+            if (s.rows_in_flight && want_lengths)
+            {
+                filling.push_back(std::async(std::launch::async, fill_lengths, static_cast<size_t>(s.rows_first), static_cast<size_t>(s.rows_n)));
+            }
+            s.rows_in_flight = false;
+        };
+        struct fill_guard // (an exception on the way out must not leave threads writing into the caller's arrays)
+        {
+            std::vector<std::future<void>>& f;
+            ~fill_guard() { for (auto& x : f) { if (x.valid()) { x.wait(); } } }
+        } wait_for_fills{ filling };
+
         uint32_t first = 0;
         int turn = 0;
         while (first < n)
@@ -531,6 +569,12 @@ extern "C" epk_status epk_place(epk_placer* pl, const char* seq, const uint64_t*
             const size_t bytes = seq_off[last] - seq_off[first];
             chunk_slot& s = pl->slots[turn % N_SLOTS];
             ++turn;
+            if (s.rows_in_flight)
+            {
+                EPK_CUDA(cudaStreamSynchronize(s.stream)); // (two younger chunks are in flight behind it)
+                finish_slot(*pl, s, *out);
+                landed(s);
+            }
             finish_slot(*pl, s, *out);
             reserve_slot(*pl, s, m, bytes, !in_pinned, !out_pinned);
 
@@ -577,30 +621,20 @@ extern "C" epk_status epk_place(epk_placer* pl, const char* seq, const uint64_t*
                 s.pending_first = first;
                 s.pending_n = m;
             }
+            s.rows_in_flight = true;
+            s.rows_first = first;
+            s.rows_n = m;
             first = last;
         }
         for (auto& s : pl->slots)
         {
             finish_slot(*pl, s, *out);
             EPK_CUDA(cudaStreamSynchronize(s.stream));
+            landed(s);
         }
+        for (auto& f : filling) { f.get(); }
         unsigned long long totals[CTR_COUNT];
         EPK_CUDA(cudaMemcpy(totals, pl->totals.get(), sizeof(totals), cudaMemcpyDeviceToHost));
-        // distal / pendant are look-ups by branch (place.cpp:434-437); zero for the zero-hit placements
-        if (out->distal || out->pendant)
-        {
-            const auto& db = *pl->db;
-            for (size_t i = 0; i < n; ++i)
-            {
-                for (size_t j = 0; j < K; ++j)
-                {
-                    const size_t at = i * K + j;
-                    const bool real = j < out->n_place[i] && out->count[at] != 0;
-                    if (out->distal) { out->distal[at] = real ? db.distal[out->branch[at]] : 0.0; }
-                    if (out->pendant) { out->pendant[at] = real ? db.pendant[out->branch[at]] : 0.0; }
-                }
-            }
-        }
         // every other row of the pass is complete (lengths included) before the rows left with n_place = 0 are reported
         if (totals[CTR_SHORT] != 0)
         {
@@ -614,6 +648,84 @@ extern "C" epk_status epk_place(epk_placer* pl, const char* seq, const uint64_t*
                                                + std::to_string(pl->db->d.n_nodes) + " nodes");
         }
     });
+}
+
+// ---- one host process, several GPUs ---------------------------------------------------------------
+
+static epk_status check_many_args(epk_placer* const* placers, uint32_t n_placers, const uint64_t* seq_off, uint32_t n,
+                                  const epk_result* out)
+{
+    return guarded([&] {
+        if (!placers || n_placers == 0 || !out) { throw error(EPK_E_INVALID, "null argument"); }
+        for (uint32_t g = 0; g < n_placers; ++g)
+        {
+            if (!placers[g]) { throw error(EPK_E_INVALID, "null placer"); }
+            if (placers[g]->keep_at_most != placers[0]->keep_at_most) { throw error(EPK_E_INVALID, "the placers must share keep_at_most"); }
+            for (uint32_t h = 0; h < g; ++h)
+            {
+                if (placers[h] == placers[g]) { throw error(EPK_E_INVALID, "the same placer twice"); }
+            }
+        }
+        if (n_placers == 1) { return; }
+        if (n && (!seq_off || !out->n_place || !out->branch || !out->score || !out->lwr || !out->count)) { throw error(EPK_E_INVALID, "null argument"); }
+    });
+}
+
+namespace
+{
+    // rows [first, ...) of the caller's result arrays
+    epk_result result_slice(const epk_result& out, size_t first, size_t K)
+    {
+        epk_result r{};
+        r.n_place = out.n_place + first;
+        r.branch = out.branch + first * K;
+        r.score = out.score + first * K;
+        r.lwr = out.lwr + first * K;
+        r.count = out.count + first * K;
+        r.distal = out.distal ? out.distal + first * K : nullptr;
+        r.pendant = out.pendant ? out.pendant + first * K : nullptr;
+        return r;
+    }
+}
+
+// The records of a pass are independent (the reference's only parallelism is an OpenMP loop over them,
+// place.cpp:218-230): contiguous slices of the pass go to the placers - one per GPU, each over its own replica of the
+// database - on one host thread each, and land in the caller's arrays in input order.
+extern "C" epk_status epk_place_many(epk_placer* const* placers, uint32_t n_placers, const char* seq, const uint64_t* seq_off,
+                                     uint32_t n, const epk_result* out)
+{
+    const epk_status args = check_many_args(placers, n_placers, seq_off, n, out);
+    if (args != EPK_OK) { return args; }
+    if (n_placers == 1) { return epk_place(placers[0], seq, seq_off, n, out); }
+    const size_t K = placers[0]->keep_at_most;
+    std::vector<epk_status> status(n_placers, EPK_OK);
+    std::vector<std::string> message(n_placers);
+    std::vector<std::thread> workers;
+    for (uint32_t g = 0; g < n_placers; ++g)
+    {
+        workers.emplace_back([&, g] {
+            const uint32_t first = static_cast<uint32_t>(static_cast<uint64_t>(n) * g / n_placers);
+            const uint32_t last = static_cast<uint32_t>(static_cast<uint64_t>(n) * (g + 1) / n_placers);
+            const epk_result part = result_slice(*out, first, K);
+            // (offsets stay absolute: sequence i of the slice is seq[seq_off[first + i] ..))
+            status[g] = epk_place(placers[g], seq, seq_off + first, last - first, &part);
+            if (status[g] != EPK_OK) { message[g] = epk_last_error(); }
+        });
+    }
+    for (auto& w : workers) { w.join(); }
+    // the most serious condition wins; EPK_E_SHORT_SEQ / EPK_E_UNSUPPORTED leave every other row complete
+    epk_status worst = EPK_OK;
+    for (uint32_t g = 0; g < n_placers; ++g)
+    {
+        const bool soft = status[g] == EPK_E_SHORT_SEQ || status[g] == EPK_E_UNSUPPORTED;
+        const bool worst_soft = worst == EPK_E_SHORT_SEQ || worst == EPK_E_UNSUPPORTED;
+        if (status[g] != EPK_OK && (worst == EPK_OK || (worst_soft && !soft)))
+        {
+            worst = status[g];
+            set_last_error("device " + std::to_string(placers[g]->device) + ": " + message[g]);
+        }
+    }
+    return worst;
 }
 
 // ---- the random-gather ceiling of the roofline -----------------------------------------------------
@@ -924,6 +1036,37 @@ extern "C" epk_status epk_group_batch(const char* seq, const uint64_t* seq_off, 
             const std::string_view s(seq + seq_off[i], seq_off[i + 1] - seq_off[i]);
             group_rep[i] = first_of.try_emplace(s, i).first->second;
         }
+    });
+}
+
+// The grouping of a whole pass, --batch-size records at a time (main.cpp:332-344: identical sequences merge only
+// within one batch), the batches spread over host threads.
+extern "C" epk_status epk_group_batches(const char* seq, const uint64_t* seq_off, uint32_t n, uint32_t batch_size,
+                                        uint32_t n_threads, uint32_t* group_rep)
+{
+    return guarded([&] {
+        if (n && (!seq_off || !group_rep)) { throw error(EPK_E_INVALID, "null argument"); }
+        if (batch_size == 0) { batch_size = std::max<uint32_t>(n, 1); }
+        const uint32_t n_batches = (n + batch_size - 1) / batch_size;
+        const uint32_t threads = std::max<uint32_t>(1, std::min<uint32_t>(std::min<uint32_t>(n_threads, n_batches), 256));
+        auto work = [&](uint32_t t) {
+            std::unordered_map<std::string_view, uint32_t> first_of;
+            for (uint32_t b = t; b < n_batches; b += threads)
+            {
+                const uint32_t first = b * batch_size, last = std::min<uint64_t>(n, static_cast<uint64_t>(first) + batch_size);
+                first_of.clear();
+                first_of.reserve(last - first);
+                for (uint32_t i = first; i < last; ++i)
+                {
+                    const std::string_view sv(seq + seq_off[i], seq_off[i + 1] - seq_off[i]);
+                    group_rep[i] = first_of.try_emplace(sv, i - first).first->second; // index within the batch
+                }
+            }
+        };
+        if (threads == 1) { work(0); return; }
+        std::vector<std::thread> pool;
+        for (uint32_t t = 0; t < threads; ++t) { pool.emplace_back(work, t); }
+        for (auto& th : pool) { th.join(); }
     });
 }
 

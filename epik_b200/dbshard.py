@@ -62,11 +62,19 @@ def _to_host(out: dict) -> dict:
     return res
 
 
+def _shard_database(flat, device: int, shard, load: dict):
+    """One shard of `flat`: a FlatDB (host arrays) or a synth.Gen2 (generated on the device, shard by shard)."""
+    from .synth import Gen2
+    if isinstance(flat, Gen2):
+        return Database.synthetic(flat, device=device, shard=shard, **load)
+    return Database(flat, device=device, shard=shard, **load)
+
+
 class LocalShardedPlacer:
     """All n_shards shards on one device: partial launches write into the slab the finalising launch reads."""
 
     def __init__(self, flat, n_shards: int, device: int = 0, keep_at_most: int = 7, keep_factor: float = 0.01, **load):
-        self.dbs = [Database(flat, device=device, shard=(g, n_shards), **load) for g in range(n_shards)]
+        self.dbs = [_shard_database(flat, device, (g, n_shards), load) for g in range(n_shards)]
         self.placers = [Placer(db, keep_at_most, keep_factor) for db in self.dbs]
         # the finalising placer sees every shard: windows with one ambiguous letter are replayed there (place.cpp:373-415)
         self.placers[0].set_shard_views([db.view() for db in self.dbs])
@@ -121,7 +129,7 @@ class ShardedPlacer:
                  **load):
         if transport not in ("a2a", "p2p"):
             raise ValueError("transport must be 'a2a' or 'p2p'")
-        self.db = Database(flat, device=device, shard=(rank, world), **load)
+        self.db = _shard_database(flat, device, (rank, world), load)
         self.placer = Placer(self.db, keep_at_most, keep_factor)
         self.rank, self.world, self.group, self.device = rank, world, group, device
         self.keep_at_most = keep_at_most

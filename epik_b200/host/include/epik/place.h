@@ -186,20 +186,36 @@ namespace epik
         placer(const Db& db, const Tree& original_tree, size_t keep_at_most, double keep_factor, size_t max_threads,
                uint32_t alphabet = EPK_DNA)
             : _owned_flat(new flat_db(flatten(db, original_tree, alphabet))),
-              _owned_db(new device_database(*_owned_flat)), _db(_owned_db)
+              _owned_db(new device_database(*_owned_flat)), _db(_owned_db), _host_threads(std::max<size_t>(1, max_threads))
         {
-            (void)max_threads;
             _owned_flat->entries.clear(); // the device holds them now
             _owned_flat->entries.shrink_to_fit();
             create(keep_at_most, keep_factor);
         }
 
         /// Over a database that is already on the device (it must outlive the placer, as in place.h:91-93).
+        /// `max_threads` (the reference sized per-thread scratch with it) sizes the host side here: the records of a
+        /// pass are packed on that many threads.
         placer(const device_database& db, size_t keep_at_most, double keep_factor, size_t max_threads = 1)
-            : _db(&db)
+            : _db(&db), _host_threads(std::max<size_t>(1, max_threads))
         {
-            (void)max_threads;
             create(keep_at_most, keep_factor);
+        }
+
+        /// Over replicas of one database on several GPUs: a pass is cut into one contiguous slice per replica
+        /// (epk_place_many), the results come back in input order. One process, one FASTA stream, one jplace, as in
+        /// main.cpp:332-366 - with every GPU of the node behind it.
+        placer(const std::vector<const device_database*>& replicas, size_t keep_at_most, double keep_factor, size_t max_threads = 1)
+            : _db(replicas.empty() ? nullptr : replicas.front()), _host_threads(std::max<size_t>(1, max_threads))
+        {
+            if (replicas.empty()) { throw std::runtime_error("No database replica given"); }
+            create(keep_at_most, keep_factor);
+            for (size_t g = 1; g < replicas.size(); ++g)
+            {
+                epk_placer* more = nullptr;
+                impl::check(epk_placer_create(replicas[g]->handle(), keep_at_most, keep_factor, nullptr, &more));
+                _replicas.push_back(more);
+            }
         }
 
         placer(const placer&) = delete;
@@ -208,6 +224,7 @@ namespace epik
         placer& operator=(placer&&) = delete;
         ~placer() noexcept
         {
+            for (epk_placer* more : _replicas) { epk_placer_destroy(more); }
             epk_placer_destroy(_handle);
             delete _owned_db;
             delete _owned_flat;
@@ -259,19 +276,24 @@ namespace epik
             const size_t n = seq_records.size();
             if (n > std::numeric_limits<uint32_t>::max()) { throw std::runtime_error("Batch too large"); }
             const size_t K = _keep_at_most;
-            size_t total = 0;
-            for (const auto& r : seq_records) { total += std::string_view(r.sequence()).size(); }
-            char* letters = _letters.reserve(total + 1);
             uint64_t* offsets = _offsets.reserve(n + 1);
-            size_t at = 0;
+            size_t total = 0;
             for (size_t i = 0; i < n; ++i)
             {
-                const std::string_view s(seq_records[i].sequence());
-                offsets[i] = at;
-                std::memcpy(letters + at, s.data(), s.size());
-                at += s.size();
+                offsets[i] = total;
+                total += std::string_view(seq_records[i].sequence()).size();
             }
-            offsets[n] = at;
+            offsets[n] = total;
+            char* letters = _letters.reserve(total + 1);
+            // (a pass is hundreds of MB of letters: one thread copies them at a few GB/s, the GPUs eat 5 GB/s each)
+            const size_t pieces = std::min<size_t>(_host_threads, std::max<size_t>(1, n / 4096));
+            impl::parallel_for(pieces, pieces, [&](size_t t) {
+                for (size_t i = n * t / pieces; i < n * (t + 1) / pieces; ++i)
+                {
+                    const std::string_view s(seq_records[i].sequence());
+                    std::memcpy(letters + offsets[i], s.data(), s.size());
+                }
+            });
 
             epk_result out{};
             out.n_place = _n_place.reserve(n + 1);
@@ -281,7 +303,13 @@ namespace epik
             out.count = _count.reserve(n * K + 1);
             out.distal = _distal.reserve(n * K + 1);
             out.pendant = _pendant.reserve(n * K + 1);
-            impl::check(epk_place(_handle, letters, offsets, static_cast<uint32_t>(n), &out));
+            if (_replicas.empty()) { impl::check(epk_place(_handle, letters, offsets, static_cast<uint32_t>(n), &out)); }
+            else
+            {
+                std::vector<epk_placer*> all{ _handle };
+                all.insert(all.end(), _replicas.begin(), _replicas.end());
+                impl::check(epk_place_many(all.data(), static_cast<uint32_t>(all.size()), letters, offsets, static_cast<uint32_t>(n), &out));
+            }
             return out;
         }
 
@@ -323,7 +351,9 @@ namespace epik
         device_database* _owned_db = nullptr;
         const device_database* _db = nullptr;
         epk_placer* _handle = nullptr;
+        std::vector<epk_placer*> _replicas; // placers on the other GPUs (database replicated), epk_place_many
         size_t _keep_at_most = 0;
+        size_t _host_threads = 1;
 
         impl::pinned_array<char> _letters;
         impl::pinned_array<uint64_t> _offsets;

@@ -7,7 +7,8 @@
 //     in one device pass (--device-batches, default 128); dedupe and "nm" grouping stay per --batch-size batch;
 //   * -j/--jobs sizes the host side: grouping, result objects and jplace text of the --batch-size batches of a
 //     device pass are produced on that many threads (the placement itself has no host threads);
-//   * --device N picks the CUDA device.
+//   * --device N picks the CUDA device; --devices N replicates the database on devices 0 .. N-1 ("all": every visible
+//     one) and cuts every device pass into N slices (epk_place_many): one process, one FASTA, one jplace, N GPUs.
 #include <chrono>
 #include <future>
 #include <memory>
@@ -163,6 +164,7 @@ namespace
         "      --keep-at-most arg  Number of branches to report (default: 7)\n"
         "      --keep-factor arg   Minimum LWR to report (default: 0.01)\n"
         "      --device arg        CUDA device (default: 0)\n"
+        "      --devices arg       Number of CUDA devices to place on, or 'all' (default: 1)\n"
         "      --device-batches arg  Batches placed per device pass (default: 128)\n"
         "  -h, --help              Print usage\n";
 }
@@ -222,7 +224,15 @@ int main(int argc, char** argv)
                                                               : "This is epik-dna: the database holds amino-acid k-mers");
         }
         const epik::load_filter filter{ user_mu, user_omega, max_entries };
-        const epik::device_database db(flat, &filter, device);
+        const std::string devices_arg = opts.get("devices", "1");
+        const size_t n_devices = devices_arg == "all" ? static_cast<size_t>(std::max(1, epk_device_count()))
+                                                      : std::max<size_t>(1, std::stoull(devices_arg));
+        // the database is replicated: every GPU gets the filtered, flattened copy (uploaded concurrently)
+        std::vector<std::unique_ptr<epik::device_database>> replicas(n_devices);
+        epik::impl::parallel_for(n_devices, n_devices, [&](size_t g) {
+            replicas[g] = std::make_unique<epik::device_database>(flat, &filter, n_devices == 1 ? device : static_cast<int>(g));
+        });
+        const epik::device_database& db = *replicas[0];
 
         std::cout << "Database parameters:" << std::endl
                   << "\tSequence type: " << db.sequence_type() << std::endl
@@ -232,7 +242,10 @@ int main(int argc, char** argv)
         std::cout << "Loaded " << to_human_readable(static_cast<double>(db.get_num_entries_loaded())) << " of "
                   << to_human_readable(static_cast<double>(db.get_num_entries_total())) << " phylo-k-mers. " << std::endl << std::endl;
 
-        epik::placer placer(db, keep_at_most, keep_factor);
+        std::vector<const epik::device_database*> replica_ptrs;
+        for (const auto& r : replicas) { replica_ptrs.push_back(r.get()); }
+        epik::placer placer(replica_ptrs, keep_at_most, keep_factor, num_threads);
+        if (n_devices > 1) { std::cout << "Placing on " << n_devices << " CUDA devices." << std::endl; }
         const std::string jplace_filename = make_output_filename(query_file, output_dir);
         epik::io::jplace_writer jplace(jplace_filename, make_invocation(argc, argv), flat.newick);
         jplace.start();

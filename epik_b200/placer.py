@@ -145,6 +145,40 @@ class PlacedCollection:
     placed_seqs: list = field(default_factory=list)
 
 
+def _db_synthetic(cls, gen, mu: float | None = None, omega: float | None = None, max_entries: int | None = None,
+                  device: int = 0, shard: tuple[int, int] | None = None):
+    """epk_db_create_synthetic: the gen2 database of synth.Gen2 `gen`, generated on the device (never held raw)."""
+    self = cls.__new__(cls)
+    self.flat = None
+    self.gen = gen
+    bl = np.ascontiguousarray(gen.length, np.float64)
+    sn = np.ascontiguousarray(gen.num, np.uint64)
+    st = np.ascontiguousarray(gen.tot, np.float64)
+    table = np.ascontiguousarray(gen.length_table, np.uint32)
+    bits = int(len(table)).bit_length() - 1
+    desc = capi.SynthDesc(int(gen.alphabet), int(gen.k), float(gen.omega), len(bl), _ptr(bl), _ptr(sn), _ptr(st),
+                          int(gen.seed), int(gen.presence_threshold), _ptr(table), bits, float(gen.score_lo),
+                          int(gen.key_space_limit))
+    flt = None
+    if mu is not None or omega is not None or max_entries is not None:
+        flt = capi.LoadFilter(1.0 if mu is None else float(mu), float(gen.omega if omega is None else omega),
+                              capi.UINT64_MAX if max_entries is None else int(max_entries))
+    handle = C.c_void_p()
+    idx, cnt = shard if shard is not None else (0, 1)
+    capi.check(capi.lib().epk_db_create_synthetic(C.byref(desc), C.byref(flt) if flt is not None else None, int(device),
+                                                  int(idx), int(cnt), C.byref(handle)))
+    self.handle = handle
+    info = capi.DbInfo()
+    capi.check(capi.lib().epk_db_get_info(self.handle, C.byref(info)))
+    self.info = {name: getattr(info, name) for name, _ in capi.DbInfo._fields_}
+    self.device = int(device)
+    self.shard = shard
+    return self
+
+
+Database.synthetic = classmethod(_db_synthetic)
+
+
 def _db_view(self) -> "capi.DbView":
     """epk_db_get_view: the device addresses of this database's key table and postings."""
     v = capi.DbView()
@@ -204,6 +238,22 @@ class Placer:
                           _ptr(out["count"]), _ptr(out.get("distal")), _ptr(out.get("pendant")))
         dptr = _ptr(data) if data.size else None
         capi.check(capi.lib().epk_place(self.handle, dptr, _ptr(offsets), n, C.byref(res)))
+        return out
+
+    @staticmethod
+    def place_packed_many(placers, data, offsets, out=None):
+        """epk_place_many: one pass over several GPUs from this one process (one placer per device, database replicated);
+        rows come back in input order, as from place_packed on one device."""
+        data = np.ascontiguousarray(data, np.uint8)
+        offsets = np.ascontiguousarray(offsets, np.uint64)
+        n = len(offsets) - 1
+        if out is None:
+            out = placers[0].alloc_result(n)
+        res = capi.Result(_ptr(out["n_place"]), _ptr(out["branch"]), _ptr(out["score"]), _ptr(out["lwr"]),
+                          _ptr(out["count"]), _ptr(out.get("distal")), _ptr(out.get("pendant")))
+        handles = (C.c_void_p * len(placers))(*[p.handle for p in placers])
+        capi.check(capi.lib().epk_place_many(C.cast(handles, C.c_void_p), len(placers), _ptr(data) if data.size else None,
+                                             _ptr(offsets), n, C.byref(res)))
         return out
 
     def place_device(self, d_seq, d_off, n: int, d_out: dict, stream=None):

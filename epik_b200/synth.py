@@ -170,6 +170,113 @@ def make_reads(alphabet: int, n: int, length: int, seed: int = SEED_READS, first
     return np.ascontiguousarray(data, np.uint8), off
 
 
+# ------------------------------------------------------- gen2: the generator the device shares -----
+# A database as a pure function of (seed, key, position in the list), every step integer arithmetic or one correctly
+# rounded IEEE operation, so that epik_b200/csrc/synth_gen.cuh builds the same database on the device - BASELINE
+# config 5 (32 GB) exists only there - and this module restates any subset of its lists for the reference.
+GEN2_TABLE_BITS = 10
+
+
+class Gen2:
+    """Parameters of a gen2 database (what epk_synth_desc carries)."""
+
+    def __init__(self, alphabet: int, k: int, n_leaves: int, p_occ: float, m: float, omega: float = 1.5, seed: int = SEED_DB,
+                 key_space_limit: int = 0):
+        self.alphabet, self.k, self.omega, self.seed, self.key_space_limit = alphabet, k, omega, seed, key_space_limit
+        self.length, self.num, self.tot, self.parent = make_tree(n_leaves, seed ^ 0x7EE)
+        self.n_nodes = len(self.length)
+        self.presence_threshold = min((1 << 64) - 1, int(p_occ * float(1 << 64)))
+        # list lengths: 2^GEN2_TABLE_BITS quantiles of log-normal(ln m, 1), clamped to [1, N / 8] (distinct branches)
+        from scipy.special import ndtri
+        q = (np.arange(1 << GEN2_TABLE_BITS, dtype=np.float64) + 0.5) / float(1 << GEN2_TABLE_BITS)
+        cap = max(1, self.n_nodes // 8)
+        self.length_table = np.clip(np.rint(np.exp(np.log(m) + ndtri(q))), 1, cap).astype(np.uint32)
+        thr = np.float32(omega / (20.0 if alphabet == AA else 4.0)) ** np.float32(k)
+        self.score_lo = float(np.log10(thr))
+        self.n_space = (20 if alphabet == AA else 4) ** k
+        if key_space_limit:
+            self.n_space = min(self.n_space, key_space_limit)
+        self.meta = dict(p_occ=p_occ, m=m, n_leaves=n_leaves, seed=seed, parent=self.parent, generator="gen2")
+
+    def candidate_of(self, keys: np.ndarray) -> np.ndarray:
+        """Index of a code in the device's enumeration of the key space (inverse of all_keys)."""
+        kk = np.asarray(keys).astype(np.uint64)
+        if self.alphabet == DNA:
+            return kk
+        cand, scale = np.zeros(len(kk), np.uint64), _U64(1)
+        for i in range(self.k):
+            cand += ((kk >> _U64(5 * i)) & _U64(31)) * scale
+            scale *= _U64(20)
+        return cand
+
+    def present(self, keys: np.ndarray) -> np.ndarray:
+        """Whether the database holds a list for these codes (inside the key space and drawn as present)."""
+        inside = self.candidate_of(keys) < _U64(self.n_space)
+        return inside & (_stream(self.seed, 3, np.asarray(keys).astype(_U64)) < _U64(self.presence_threshold))
+
+    def all_keys(self) -> np.ndarray:
+        """Codes of the whole key space, in the order the device enumerates them."""
+        cand = np.arange(self.n_space, dtype=np.uint64)
+        if self.alphabet == DNA:
+            return cand.astype(np.uint32)
+        idx, key = cand.copy(), np.zeros(len(cand), np.uint64)
+        for i in range(self.k):
+            key |= (idx % _U64(20)) << _U64(5 * i)
+            idx //= _U64(20)
+        return key.astype(np.uint32)
+
+    def lists(self, keys: np.ndarray) -> FlatDB:
+        """The database restricted to `keys` (absent ones are dropped; order kept): what the reference needs to
+        place reads that look up only these keys."""
+        keys = np.asarray(keys, np.uint32)
+        keys = keys[self.present(keys)]
+        kk = keys.astype(np.uint64)
+        ell = self.length_table[(_stream(self.seed, 4, kk) >> _U64(64 - GEN2_TABLE_BITS)).astype(np.int64)].astype(np.uint64)
+        offsets = np.zeros(len(keys) + 1, np.uint64)
+        np.cumsum(ell, out=offsets[1:])
+        n_entries = int(offsets[-1])
+        owner = np.repeat(np.arange(len(keys), dtype=np.uint64), ell.astype(np.int64))
+        j = np.arange(n_entries, dtype=np.uint64) - offsets[:-1][owner]
+        eid = (kk[owner] << _U64(24)) ^ j
+        stride = (_stream(self.seed, 6, eid) % _U64(7)) + _U64(1)
+        run = np.cumsum(stride, dtype=np.uint64)
+        if n_entries:
+            first = offsets[:-1].astype(np.int64)
+            run -= np.repeat(run[first] - stride[first], ell.astype(np.int64))
+        start = _stream(self.seed, 7, kk) % _U64(self.n_nodes)
+        branch = ((start[owner] + run) % _U64(self.n_nodes)).astype(np.uint32)
+        u = ((_stream(self.seed, 8, eid) >> _U64(11)).astype(np.float64) + 0.5) * (1.0 / 9007199254740992.0)
+        score = np.minimum((self.score_lo + (-0.3 - self.score_lo) * u).astype(np.float32), np.float32(-0.3))
+        entries = np.empty(n_entries, ENTRY_DTYPE)
+        entries["branch"], entries["score"] = branch, score
+        return FlatDB(self.alphabet, self.k, self.omega, keys, offsets, entries, self.length, self.num, self.tot, None,
+                      meta=dict(self.meta))
+
+    def whole(self) -> FlatDB:
+        """Every list (small shapes only: this is what the device generates without ever holding it raw)."""
+        return self.lists(self.all_keys())
+
+
+def keys_of_reads(alphabet: int, k: int, data: np.ndarray, off: np.ndarray) -> np.ndarray:
+    """The distinct exact k-mer codes of unambiguous fixed-alphabet reads (what place_seq looks up for them)."""
+    order = _AA_ORDER if alphabet == AA else _DNA_ORDER
+    bits = 5 if alphabet == AA else 2
+    lut = np.full(256, 255, np.uint8)
+    for i, c in enumerate(order):
+        lut[c] = i
+    out = []
+    for i in range(len(off) - 1):
+        codes = lut[data[int(off[i]):int(off[i + 1])]].astype(np.uint64)
+        assert (codes != 255).all(), "unambiguous letters only"
+        if len(codes) < k:
+            continue
+        key = np.zeros(len(codes) - k + 1, np.uint64)
+        for j in range(k):
+            key = (key << _U64(bits)) | codes[j:len(codes) - k + 1 + j]
+        out.append(key)
+    return np.unique(np.concatenate(out)).astype(np.uint32) if out else np.zeros(0, np.uint32)
+
+
 # ---------------------------------------------------------------- the BASELINE.json configs -----
 CONFIGS = {
     # name: (alphabet, k, n_leaves, p_occ, m, read_len)
@@ -186,6 +293,14 @@ CONFIGS = {
 # (mu, omega, max_entries) of i2l::load for the configs that filter at load time; --max-ram 4G is
 # 4 * 2^30 / sizeof(pkdb_value) entries (main.cpp:252-265)
 LOAD_FILTERS = {"C3": (0.5, 1.5, (4 << 30) // 8)}
+
+
+def make_config_gen2(name: str) -> Gen2:
+    """The device-generated form of a config (C5: the only form it has)."""
+    alphabet, k, n_leaves, p_occ, m, _ = CONFIGS[name]
+    g = Gen2(alphabet, k, n_leaves, p_occ, m)
+    g.meta["config"] = name
+    return g
 
 
 def make_config_db(name: str, **kw) -> FlatDB:

@@ -150,6 +150,14 @@ void epk_placer_destroy(epk_placer* placer);
 epk_status epk_place(epk_placer* placer, const char* seq, const uint64_t* seq_off, uint32_t n,
                      const epk_result* out);
 
+/* epk_place over several GPUs from ONE host process (the reference is one process, one FASTA stream, one jplace:
+ * main.cpp:332-366): placers[g] sits on its own device over its own replica of the database; the pass is cut into
+ * n_placers contiguous slices, each placed by one placer on one host thread, and the rows land in `out` in input
+ * order - exactly what epk_place on one device leaves there. The placers must share keep_at_most / keep_factor.
+ * Returns the most serious status of the slices (EPK_E_SHORT_SEQ / EPK_E_UNSUPPORTED leave every other row complete). */
+epk_status epk_place_many(epk_placer* const* placers, uint32_t n_placers, const char* seq, const uint64_t* seq_off,
+                          uint32_t n, const epk_result* out);
+
 /* Same work with everything already resident in HBM: DEVICE pointers, asynchronous on `stream`
  * (a cudaStream_t, NULL = the legacy default stream). A placer is a single-stream object: its work cursor
  * and counters are shared by all its launches, so calls on one placer (this one, the partial / finalize /
@@ -161,6 +169,12 @@ epk_status epk_place_device(epk_placer* placer, const char* d_seq, const uint64_
 /* group_by_sequence_content (place.cpp:73-81) for one batch: group_rep[i] = index of the first
  * record of [0, n) with the same sequence. HOST buffers. */
 epk_status epk_group_batch(const char* seq, const uint64_t* seq_off, uint32_t n, uint32_t* group_rep);
+
+/* The same for a whole pass of n records cut into batches of batch_size (main.cpp:332-344: sequences merge only
+ * within one --batch-size batch): group_rep[i] = index WITHIN ITS BATCH of the first record of that batch with the same
+ * sequence; the batches are spread over n_threads host threads. */
+epk_status epk_group_batches(const char* seq, const uint64_t* seq_off, uint32_t n, uint32_t batch_size, uint32_t n_threads,
+                             uint32_t* group_rep);
 
 /* The k-mer stream of one sequence in the order query_kmers (place.cpp:278-316) consumes it, one
  * record per (window, resolved key): pos = window start, key = code, group = number of keys of
@@ -299,6 +313,34 @@ typedef struct epk_microbench
 } epk_microbench;
 epk_status epk_gather_microbench(const epk_db* db, uint64_t n_probes, uint64_t seed, uint32_t method,
                                  uint32_t reps, epk_microbench* out);
+
+/* Test / bench infrastructure: a synthetic database generated ON THE DEVICE, a pure function of (seed, key, position
+ * in the list) that epik_b200/synth.py restates in numpy for any subset of keys (the reference is fed exactly the
+ * lists a set of reads looks up). BASELINE config 5 - k = 12, ~20 k branches, ~4 G postings = 32 GB - exists only
+ * this way: numpy would need minutes and > 100 GB of host memory for it. The entries are generated one key range
+ * at a time into the chunk buffer the build streams every database through (raw and packed never coexist in HBM).
+ *   key present    iff  stream(3, key) < presence_threshold
+ *   list length     =   length_table[stream(4, key) >> (64 - length_table_bits)]   (each in [1, n_nodes / 8])
+ *   branches        =   (stream(7, key) % n_nodes + running sum of strides stream(6, key << 24 ^ j) % 7 + 1) % n_nodes
+ *   scores          =   min(float(score_lo + (-0.3 - score_lo) * unit(stream(8, key << 24 ^ j))), -0.3f)
+ * (stream / unit: epik_b200/csrc/synth_gen.cuh). Keys are the codes 0 .. |alphabet|^k (or key_space_limit). */
+typedef struct epk_synth_desc
+{
+    uint32_t alphabet, kmer_size;
+    float omega;
+    uint32_t n_nodes;
+    const double* branch_length;        /* [n_nodes] HOST, as in epk_db_desc */
+    const uint64_t* subtree_num_nodes;
+    const double* subtree_total_length;
+    uint64_t seed;
+    uint64_t presence_threshold;
+    const uint32_t* length_table;       /* [1 << length_table_bits] HOST */
+    uint32_t length_table_bits;
+    double score_lo;
+    uint64_t key_space_limit;           /* 0 = the whole code space */
+} epk_synth_desc;
+epk_status epk_db_create_synthetic(const epk_synth_desc* desc, const epk_load_filter* filter, int device,
+                                   uint32_t shard_index, uint32_t shard_count, epk_db** out);
 
 /* Pinned host memory for the buffers of epk_place. */
 void* epk_host_alloc(size_t bytes);

@@ -79,6 +79,25 @@ def test_group_batch_is_first_occurrence():
     assert list(rep) == [0, 1, 0, 3, 4, 1, 3]
 
 
+def test_group_batches_groups_within_each_batch_on_threads():
+    """epk_group_batches = epk_group_batch on every --batch-size slice (main.cpp:332-344), whatever the thread count."""
+    rng = np.random.default_rng(3)
+    pool = [bytes(rng.choice(np.frombuffer(b"ACGT", np.uint8), size=int(rng.integers(0, 12)))) for _ in range(40)]
+    seqs = [pool[int(i)] for i in rng.integers(0, len(pool), size=1000)]
+    data = np.frombuffer(b"".join(seqs), np.uint8).copy()
+    off = np.zeros(len(seqs) + 1, np.uint64)
+    off[1:] = np.cumsum([len(s) for s in seqs])
+    p = lambda a: a.ctypes.data_as(C.c_void_p)
+    for batch, threads in ((64, 1), (64, 7), (1000, 4), (0, 3), (1, 2)):
+        rep = np.full(len(seqs), 0xFFFFFFFF, np.uint32)
+        capi.check(capi.lib().epk_group_batches(p(data), p(off), len(seqs), batch, threads, p(rep)))
+        size = batch or len(seqs)
+        for first in range(0, len(seqs), size):
+            want = np.zeros(min(size, len(seqs) - first), np.uint32)
+            capi.check(capi.lib().epk_group_batch(p(data), p(off[first:]), len(want), p(want)))
+            assert np.array_equal(rep[first:first + len(want)], want), (batch, threads, first)
+
+
 def test_malformed_offsets_are_refused_before_anything_runs():
     """A CSR description whose offsets decrease (corrupt or hand-made database) is EPK_E_INVALID - checked on the host,
     before any kernel computes a list length from it (and before a device is even looked for)."""

@@ -479,3 +479,110 @@ def test_hot_kernel_kmer_stream_matches_the_oracle(shape):
               "score": got["score"].reshape(-1, K), "lwr": got["lwr"].reshape(-1, K),
               "count": got["count"].view(np.uint32).reshape(-1, K)}
     helpers.assert_same_placements(shaped, ref, what="trace launch " + kind, lengths=False)
+
+
+@pytest.mark.parametrize("shape", ["dna", "dna-range-teams", "aa-hashed", "dna-filtered"])
+def test_database_generated_on_the_device_is_its_host_restatement(shape, monkeypatch):
+    """epk_db_create_synthetic (gen2, epik_b200/csrc/synth_gen.cuh) against synth.Gen2 in numpy: same key count, same
+    entry count, and bit-identical placements whichever way the database got into HBM - streamed through many small key
+    ranges or one, generated or uploaded; and the oracle agrees when it is fed only the lists the reads look up."""
+    flt = {}
+    if shape == "dna":
+        gen, length = synth.Gen2(0, 8, 300, 0.6, 12.0, seed=5), 150
+    elif shape == "dna-range-teams":
+        gen, length = synth.Gen2(0, 8, 5000, 0.7, 40.0, seed=6), 200
+    elif shape == "aa-hashed":
+        gen, length = synth.Gen2(1, 6, 150, 0.02, 6.0, seed=7, key_space_limit=1 << 21), 60
+    else:
+        gen, length, flt = synth.Gen2(0, 8, 300, 0.6, 12.0, seed=8), 150, dict(mu=0.6, omega=1.2)
+    data, off = synth.make_reads(gen.alphabet, 3000, length, seed=9)
+    monkeypatch.setenv("EPK_BUILD_CHUNK_ENTRIES", "20000")
+    device_db = Database.synthetic(gen, **flt)
+    flat = gen.whole()
+    if flt:
+        flat.filter_value = None  # (the device generator has no filter values: file order)
+    host_db = Database(flat, **flt)
+    monkeypatch.delenv("EPK_BUILD_CHUNK_ENTRIES")
+    one_range_db = Database(flat, **flt)
+    for name in ("n_keys_loaded", "n_entries_loaded", "n_entries_total", "table_kind"):
+        assert device_db.info[name] == host_db.info[name] == one_range_db.info[name], name
+    assert device_db.info["n_entries_total"] == flat.n_entries
+    got = Placer(device_db).place_packed(data, off)
+    for other in (host_db, one_range_db):
+        again = Placer(other).place_packed(data, off)
+        for name in ("n_place", "branch", "score", "lwr", "count"):
+            assert np.array_equal(got[name], again[name]), name
+    if not flt:
+        # the reference, fed the lists of the keys these reads contain and nothing else
+        some = gen.lists(synth.keys_of_reads(gen.alphabet, gen.k, data, off))
+        assert some.n_keys < flat.n_keys or shape == "dna"
+        oracle, kind = best_oracle(some)
+        want = oracle.place_packed(data, off, threads=4)
+        helpers.assert_same_placements(got, want, what=shape + " " + kind, lengths=False)
+        valid = np.arange(7)[None, :] < want["n_place"][:, None]
+        assert np.array_equal(got["score"][valid], want["score"][valid])
+
+
+def test_config5_proper_generated_on_the_device():
+    """BASELINE config 5 itself: k = 12, 19 999 branches, ~3.9 G postings = 31 GB generated and built on the device
+    (key table of 128 MB, posting offsets far beyond 2^32 bytes, lists sorted behind range headers), a sample of reads
+    placed, and the reference run on the lists those reads look up. Takes a minute and 40 GB of HBM: only with
+    EPK_TEST_C5=1 (tools/gpu_c5.sh runs it; log under profiles/)."""
+    import os
+    if os.environ.get("EPK_TEST_C5") != "1":
+        pytest.skip("set EPK_TEST_C5=1 (needs ~40 GB of HBM and a minute)")
+    gen = synth.make_config_gen2("C5")
+    db = Database.synthetic(gen)
+    assert db.info["n_entries_loaded"] == db.info["n_entries_total"] > 3_500_000_000 and db.info["table_slots"] == 4 ** 12
+    assert db.info["device_bytes"] > 28 * (1 << 30)
+    n = 2000
+    data, off = synth.make_reads(0, n, 150, seed=77)
+    p = Placer(db)
+    got = p.place_packed(data, off)
+    c = p.counters()
+    some = gen.lists(synth.keys_of_reads(0, 12, data, off))
+    # the kernel's own work counters against the restated lists: every window's key, each list as often as it is hit
+    codes = np.searchsorted(np.frombuffer(b"ACGT", np.uint8), data).astype(np.uint64).reshape(n, 150)
+    keys = np.zeros((n, 139), np.uint64)
+    for j in range(12):
+        keys = (keys << np.uint64(2)) | codes[:, j:j + 139]
+    at = np.searchsorted(some.keys, keys.ravel())
+    hit = (at < some.n_keys) & (some.keys[np.minimum(at, some.n_keys - 1)] == keys.ravel())
+    lens = np.diff(some.offsets.astype(np.int64))
+    assert c["n_hits"] == int(hit.sum()) > 0.85 * n * 139 and c["n_entries"] == int(lens[at[hit]].sum())
+    oracle, kind = best_oracle(some, threads=8)
+    want = oracle.place_packed(data, off, threads=8)
+    helpers.assert_same_placements(got, want, what="C5 " + kind, lengths=False)
+    valid = np.arange(7)[None, :] < want["n_place"][:, None]
+    assert np.array_equal(got["score"][valid], want["score"][valid])
+    # the same database in two shards (database-sharded mode): what the mode is for
+    from epik_b200 import dbshard
+    del p, db
+    sp = dbshard.LocalShardedPlacer(gen, 2)
+    assert sum(d.info["n_entries_loaded"] for d in sp.dbs) == sp.dbs[0].info["n_entries_total"]
+    got2 = sp.place_packed(data, off, max_rows=1024)
+    assert sp.unsupported == 0
+    helpers.assert_close_placements(got2, want, what="C5 in two shards")
+
+
+def test_one_process_several_placers_fill_one_result_in_input_order():
+    """epk_place_many: the pass is cut into contiguous slices, one per placer (one per GPU when there are several; two
+    placers on one device otherwise), and the caller's arrays come back exactly as epk_place on one device leaves them -
+    including the rows a slice leaves unplaced (a too-short read) and the status that reports them."""
+    import torch
+    flat = synth.make_db(0, 8, 300, 0.6, 12.0, seed=11)
+    data, off = synth.make_reads(0, 5001, 150, seed=12, amb_rate=0.01)
+    n_dev = min(torch.cuda.device_count(), 4)
+    devices = list(range(n_dev)) if n_dev > 1 else [0, 0, 0]
+    dbs = {d: Database(flat, device=d) for d in set(devices)}
+    placers = [Placer(dbs[d]) for d in devices]
+    want = placers[0].place_packed(data, off)
+    got = Placer.place_packed_many(placers, data, off)
+    for name in ("n_place", "branch", "score", "lwr", "count", "distal", "pendant"):
+        assert np.array_equal(got[name], want[name]), name
+    seqs = [bytes(data[int(off[i]):int(off[i + 1])]) for i in range(40)]
+    seqs[33] = b"ACG"
+    d2, o2 = pack_sequences(seqs)
+    with pytest.raises(capi.EpkError) as e:
+        Placer.place_packed_many(placers, d2, o2)
+    assert e.value.status == capi.EPK_E_SHORT_SEQ and "device" in str(e.value)
