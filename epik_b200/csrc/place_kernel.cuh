@@ -83,6 +83,8 @@ struct place_params
     uint32_t team;                       // warps per accumulator set (TEAM launches)
     uint32_t prefetch;                   // L2 prefetch of a descriptor buffer's postings before it is gathered (PREFETCH_*)
     uint32_t* trace;                     // [4 n] per query: keys looked up, keys found, postings, checksum of the k-mer stream (NULL: none)
+    // ---- accumulators in global memory (trees / reads too large for shared memory), see "accumulators in HBM" ----
+    unsigned char* acc_scratch;          // per warp of the grid: float S[np] | uint32 C[np] | seen bitmap np / 8 bytes, all zero
     // ---- finalize launch: ambiguous windows of database-sharded mode, replayed by the owner ----
     const device_db* shard_views;        // [n_shards] the shards' tables and postings as seen from this device (NULL: none)
     uint32_t* seen_scratch;              // np / 32 words per warp of the finalize grid, zero between queries
@@ -489,6 +491,94 @@ __device__ __noinline__ void apply_list(const uint2* __restrict__ postings, acc_
         apply_segment(acc, lane2, r, CT{});
     }
 }
+
+// ---- accumulators in HBM ------------------------------------------------------------------------------
+//
+// The shared-memory accumulators bound the tree: 5.125 bytes per node for 150-bp reads, 8.125 for reads of more than
+// 65535 windows - 44 k / 28 k nodes at most per SM. The reference has no such limit (its scratch is max_threads x
+// node_count in host memory, place.cpp:92-96). Beyond it the same kernel runs with every warp's S / C / seen bitmap
+// in a row of its own in global memory (L2-resident: a few hundred KB per warp): the same additions in the same
+// order - results stay bit-identical to the reference's - through plain loads and stores, a __syncwarp() between
+// segments as in shared memory. A fallback for shapes outside the design point, several times slower per posting.
+__host__ __device__ inline size_t global_acc_bytes(uint32_t n_nodes)
+{
+    const size_t np = padded_nodes(n_nodes);
+    return np * 8 + np / 8;
+}
+// what a warp of this form keeps in shared memory: segment descriptors and letter codes
+constexpr size_t GLOBAL_WARP_SMEM = (SEG_CAP + SEG_PAD) * 8 + CODE_BYTES;
+
+__device__ __forceinline__ void apply_segment_global(float* S, uint32_t* C, uint32_t lane2, const seg_regs& r)
+{
+    if (lane2 < r.cnt)
+    {
+        __stcg(S + r.b0, __fadd_rn(__ldcg(S + r.b0), __uint_as_float(r.s0)));
+        __stcg(C + r.b0, __ldcg(C + r.b0) + 1u);
+    }
+    if (lane2 + 1u < r.cnt)
+    {
+        __stcg(S + r.b1, __fadd_rn(__ldcg(S + r.b1), __uint_as_float(r.s1)));
+        __stcg(C + r.b1, __ldcg(C + r.b1) + 1u);
+    }
+    __syncwarp(); // the next segment may name the same branches from other lanes
+}
+
+template<int U>
+__device__ __noinline__ void gather_segments_global(const uint2* __restrict__ postings, float* S, uint32_t* C, uint32_t segs_shared,
+                                                    uint32_t n, uint32_t lane)
+{
+    const unsigned char* lane_base = reinterpret_cast<const unsigned char*>(postings) + 16u * lane;
+    const uint32_t lane2 = 2u * lane;
+    for (uint32_t first = 0; first < n; first += U)
+    {
+        seg_regs a[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+        {
+            a[u] = seg_regs{ 0, 0, 0, 0, 0, 0 };
+            load_segment<false>(lane_base, segs_shared, first + u, lane2, a[u]); // (descriptors past n are the zero padding)
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) { apply_segment_global(S, C, lane2, a[u]); }
+    }
+}
+
+__device__ __noinline__ void apply_list_global(const uint2* __restrict__ postings, float* S, uint32_t* C, uint64_t off, uint32_t len,
+                                               uint32_t lane)
+{
+    const uint32_t lane2 = 2u * lane;
+    for (uint32_t pos = 0; pos < len; pos += SEG_LEN)
+    {
+        seg_regs r{ 0, 0, 0, 0, min(len - pos, static_cast<uint32_t>(SEG_LEN)), 0 };
+        if (lane2 < r.cnt)
+        {
+            const uint4 v = __ldg(reinterpret_cast<const uint4*>(postings + off + pos) + lane);
+            r.b0 = v.x; r.s0 = v.y; r.b1 = v.z; r.s1 = v.w;
+        }
+        apply_segment_global(S, C, lane2, r);
+    }
+}
+
+// the sweep's view of such a row: four consecutive branches are taken (and cleared) at a time
+struct global_acc
+{
+    float* S;
+    uint32_t* C;
+    __device__ __forceinline__ bool any(uint32_t j) const
+    {
+        const uint4 w = __ldcg(reinterpret_cast<const uint4*>(C + j));
+        return (w.x | w.y | w.z | w.w) != 0u;
+    }
+    __device__ __forceinline__ float4 take(uint32_t j, uint32_t (&c)[4]) const
+    {
+        const float4 s4 = __ldcg(reinterpret_cast<const float4*>(S + j));
+        const uint4 w = __ldcg(reinterpret_cast<const uint4*>(C + j));
+        __stcg(reinterpret_cast<float4*>(S + j), make_float4(0.0f, 0.0f, 0.0f, 0.0f));
+        __stcg(reinterpret_cast<uint4*>(C + j), make_uint4(0u, 0u, 0u, 0u));
+        c[0] = w.x; c[1] = w.y; c[2] = w.z; c[3] = w.w;
+        return s4;
+    }
+};
 
 // ---- top-k selection --------------------------------------------------------------------------
 
@@ -1245,12 +1335,12 @@ __device__ __forceinline__ sweep_result sweep_dense_form(const shared_acc<CT> ac
 {
     return sweep_dense_two_pass<CT, CAP, EPK_SWEEP_NQ>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride EPK_PHASE_ARGS);
 }
-template<int CAP>
-__device__ __forceinline__ sweep_result sweep_dense_form(const rows_acc acc, uint32_t np, uint32_t nw32, float logthr, float kf,
+template<int CAP, class ACC>
+__device__ __forceinline__ sweep_result sweep_dense_form(const ACC acc, uint32_t np, uint32_t nw32, float logthr, float kf,
                                                          float rcp_k, uint32_t K, uint32_t lane, const cand_buffers<CAP>& cb,
                                                          uint32_t scan0, uint32_t stride EPK_PHASE_PARAMS)
 {
-    return sweep<rows_acc, true, true, CAP>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride);
+    return sweep<ACC, true, true, CAP>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride);
 }
 
 // the sweep form that fits the query
@@ -1622,9 +1712,11 @@ enum kernel_mode { MODE_FULL = 0, MODE_PARTIAL = 1, MODE_GATHER_ONLY = 2 };
 // TEAM: p.team warps per accumulator set (see "teams"); blockDim = 32 * p.team * sets.
 // MAXW: warps per CTA the launch may use (small trees: 16 accumulator sets fit an SM, and 16 warps at 128 registers
 // hide the latency of the key-table probes better than 8 at 255).
-template<uint32_t TABLE, int U, class CT, int MODE = MODE_FULL, bool TEAM = false, int MAXW = MAX_WARPS_PER_CTA>
+// GLOBAL: the accumulators live in p.acc_scratch ("accumulators in HBM"; CT = uint32_t, one warp per query).
+template<uint32_t TABLE, int U, class CT, int MODE = MODE_FULL, bool TEAM = false, int MAXW = MAX_WARPS_PER_CTA, bool GLOBAL = false>
 __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params p)
 {
+    static_assert(!GLOBAL || (!TEAM && MODE == MODE_FULL && sizeof(CT) == 4), "accumulators in HBM: the plain fused launch, 32-bit counts");
     constexpr bool PARTIAL = MODE == MODE_PARTIAL;
     constexpr bool GATHER_ONLY = MODE == MODE_GATHER_ONLY;
     extern __shared__ __align__(16) unsigned char smem[];
@@ -1644,19 +1736,22 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
     for (uint32_t i = threadIdx.x; i < 256; i += blockDim.x) { letters[i] = p.letters[i]; }
 
     // per set: float S[np] | CT C[np] | seen bitmap np/8 bytes | segment descriptors | letter codes | team area
-    unsigned char* base = smem + CTA_SMEM_FIXED + warp * (warp_smem_bytes(N, sizeof(CT)) + team_smem_bytes(team));
+    // (GLOBAL: the first three in this warp's row of p.acc_scratch, zero from the start and after every query)
+    unsigned char* base = GLOBAL ? p.acc_scratch + (static_cast<size_t>(blockIdx.x) * (blockDim.x >> 5) + warp) * global_acc_bytes(N)
+                                 : smem + CTA_SMEM_FIXED + warp * (warp_smem_bytes(N, sizeof(CT)) + team_smem_bytes(team));
     unsigned char* team_area = base + warp_smem_bytes(N, sizeof(CT));
     float* S = reinterpret_cast<float*>(base);
     CT* C = reinterpret_cast<CT*>(base + static_cast<size_t>(np) * 4);
     uint32_t* seen = reinterpret_cast<uint32_t*>(base + static_cast<size_t>(np) * (4 + sizeof(CT)));
     const uint32_t seen_words = np / 32;
-    uint2* segs = reinterpret_cast<uint2*>(reinterpret_cast<unsigned char*>(seen) + np / 8);
+    uint2* segs = GLOBAL ? reinterpret_cast<uint2*>(smem + CTA_SMEM_FIXED + warp * GLOBAL_WARP_SMEM)
+                         : reinterpret_cast<uint2*>(reinterpret_cast<unsigned char*>(seen) + np / 8);
     const uint32_t segs_shared = static_cast<uint32_t>(__cvta_generic_to_shared(segs));
     const acc_ref acc{ static_cast<uint32_t>(__cvta_generic_to_shared(S)), static_cast<uint32_t>(__cvta_generic_to_shared(C)) };
     uint32_t* cand_base = reinterpret_cast<uint32_t*>(segs); // the segment buffer is idle during the sweep
     uint8_t* codes = reinterpret_cast<uint8_t*>(segs + SEG_CAP + SEG_PAD);
 
-    if (member == 0)
+    if (member == 0 && !GLOBAL)
     {
         for (uint32_t b = lane; b < np; b += 32)
         {
@@ -1895,7 +1990,8 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
                         if (lane < SEG_PAD) { segs[nseg + lane] = make_uint2(0, 0); }
                         __syncwarp();
                         EPK_PHASE(2)
-                        gather_segments<U, CT, GATHER_ONLY>(db.postings, acc, segs_shared, nseg, lane, p.prefetch, &sink);
+                        if (GLOBAL) { gather_segments_global<U>(db.postings, S, reinterpret_cast<uint32_t*>(C), segs_shared, nseg, lane); }
+                        else { gather_segments<U, CT, GATHER_ONLY>(db.postings, acc, segs_shared, nseg, lane, p.prefetch, &sink); }
                         EPK_PHASE(3)
                         nseg = 0;
                         __syncwarp();
@@ -1906,7 +2002,8 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
                     {
                         const uint64_t s = __shfl_sync(FULL, slot[r], done);
                         const uint32_t l = static_cast<uint32_t>(s & LEN_MASK);
-                        if (l) { apply_list<CT>(db.postings, acc, s >> LEN_BITS, l, lane); }
+                        if (l && GLOBAL) { apply_list_global(db.postings, S, reinterpret_cast<uint32_t*>(C), s >> LEN_BITS, l, lane); }
+                        else if (l) { apply_list<CT>(db.postings, acc, s >> LEN_BITS, l, lane); }
                     }
                     ++done;
                     continue;
@@ -1929,7 +2026,8 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
             if (lane < SEG_PAD) { segs[nseg + lane] = make_uint2(0, 0); }
             __syncwarp();
             EPK_PHASE(2)
-            gather_segments<U, CT, GATHER_ONLY>(db.postings, acc, segs_shared, nseg, lane, p.prefetch, &sink);
+            if (GLOBAL) { gather_segments_global<U>(db.postings, S, reinterpret_cast<uint32_t*>(C), segs_shared, nseg, lane); }
+            else { gather_segments<U, CT, GATHER_ONLY>(db.postings, acc, segs_shared, nseg, lane, p.prefetch, &sink); }
             EPK_PHASE(3)
         }
         __syncwarp();
@@ -2027,8 +2125,16 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
                                     // added to the LOG score (place.cpp:391,400-410)
                                     const float prob = static_cast<float>(pow(10.0, static_cast<double>(__uint_as_float(entry.y))));
                                     const float mean = __fdiv_rn(__fadd_rn(prob, thr_rest), kf);
-                                    S[entry.x] = __fadd_rn(S[entry.x], mean);
-                                    C[entry.x] = static_cast<CT>(C[entry.x] + 1u);
+                                    if (GLOBAL) // (through L2 like every other access of a row in HBM: no stale L1 line)
+                                    {
+                                        __stcg(S + entry.x, __fadd_rn(__ldcg(S + entry.x), mean));
+                                        __stcg(C + entry.x, static_cast<CT>(__ldcg(C + entry.x) + 1u));
+                                    }
+                                    else
+                                    {
+                                        S[entry.x] = __fadd_rn(S[entry.x], mean);
+                                        C[entry.x] = static_cast<CT>(C[entry.x] + 1u);
+                                    }
                                 }
                             }
                             __syncwarp();
@@ -2052,6 +2158,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
         // ---- correction, likelihood mass, top-k, weight ratios (place.cpp:417-422, 164-184, 134-159, 241-267) ----
         const uint32_t gathered = __reduce_add_sync(FULL, static_cast<uint32_t>(min(static_cast<unsigned long long>(ctr_entries - entries_before), 0xFFFFFFull)));
         if (TEAM) { finish_query_leader<CT>(p, S, C, np, static_cast<uint32_t>(n_windows), gathered, q, lane, team_area, warp, team); }
+        else if (GLOBAL) { finish_query(p, global_acc{ S, reinterpret_cast<uint32_t*>(C) }, np, n_windows, gathered, q, lane, cand_base); }
         else
         {
 #ifdef EPK_PHASE_CLOCKS

@@ -121,6 +121,9 @@ struct epk_placer
     device_buffer<unsigned long long> totals;          // running work counters (bumped by the launches)
     device_buffer<unsigned long long> device_counters; // per-launch counters of epk_place_device
     device_buffer<uint32_t> device_class_reads;
+    uint32_t global_mask = 0;                        // classes placed with their accumulators in HBM (place_kernel<..., GLOBAL>)
+    device_buffer<unsigned char> acc_scratch;         // N_SLOTS + 1 regions of n_sms * 8 rows (one region per stream that may launch)
+    size_t acc_region_bytes = 0;
     device_buffer<device_db> shard_views;   // epk_placer_set_shard_views: the shards of a database-sharded group, from this device
     uint32_t n_shard_views = 0;
     device_buffer<uint32_t> seen_scratch;   // bitmaps of the finalising launch's ambiguous-window replay (one per warp)
@@ -164,6 +167,13 @@ namespace
                                                  : place_kernel<TABLE_HASH, 8, uint8_t, MODE_GATHER_ONLY>;
     }
 
+    // the launch for classes whose accumulators do not fit shared memory: rows in HBM, 32-bit counts, 8 warps per CTA
+    kernel_fn pick_global_kernel(const epk_placer& pl)
+    {
+        return pl.db->table_kind == TABLE_DIRECT ? place_kernel<TABLE_DIRECT, 4, uint32_t, MODE_FULL, false, MAX_WARPS_PER_CTA, true>
+                                                 : place_kernel<TABLE_HASH, 4, uint32_t, MODE_FULL, false, MAX_WARPS_PER_CTA, true>;
+    }
+
     kernel_fn pick_kernel(const epk_placer& pl, int cls)
     {
         if (pl.wide[cls])
@@ -200,7 +210,7 @@ namespace
     // the classes the caller knows to be present (all of them when it does not know).
     void launch(epk_placer& pl, const char* d_seq, const uint64_t* d_off, uint32_t n, const epk_result& d_out,
                 unsigned long long* counters, uint32_t* class_reads, uint32_t class_mask, cudaStream_t stream,
-                uint32_t* trace = nullptr)
+                uint32_t* trace = nullptr, uint32_t acc_region = N_SLOTS)
     {
         place_params p{};
         p.db = pl.db->d;
@@ -235,9 +245,22 @@ namespace
             ++pl.n_launches;
             for (int c = 0; c < N_CLASSES; ++c)
             {
-                if (!((class_mask >> c) & 1u) || pl.warps_per_cta[c] == 0) { continue; }
+                if (!((class_mask >> c) & 1u)) { continue; }
                 p.cls = static_cast<uint32_t>(c);
                 p.counters = counters + c * CTR_COUNT;
+                if ((pl.global_mask >> c) & 1u)
+                {
+                    // accumulators in HBM: this stream's region of rows, one per warp of the grid
+                    p.acc_scratch = pl.acc_scratch.get() + static_cast<size_t>(acc_region) * pl.acc_region_bytes;
+                    p.team = 1;
+                    const unsigned grid = static_cast<unsigned>(
+                        std::min<uint64_t>(pl.n_sms, (static_cast<uint64_t>(n) + MAX_WARPS_PER_CTA - 1) / MAX_WARPS_PER_CTA));
+                    pick_global_kernel(pl)<<<grid, MAX_WARPS_PER_CTA * 32, CTA_SMEM_FIXED + MAX_WARPS_PER_CTA * GLOBAL_WARP_SMEM, stream>>>(p);
+                    EPK_CUDA(cudaGetLastError());
+                    ++pl.n_launches;
+                    continue;
+                }
+                if (pl.warps_per_cta[c] == 0) { continue; }
                 const unsigned grid = static_cast<unsigned>(
                     std::min<uint64_t>(pl.n_sms, (static_cast<uint64_t>(n) + pl.sets_fused[c] - 1) / pl.sets_fused[c]));
                 p.team = pl.team[c];
@@ -370,7 +393,7 @@ extern "C" epk_status epk_placer_create(const epk_db* db, uint64_t keep_at_most,
             const size_t per_warp = warp_smem_bytes(db->d.n_nodes, class_count_bytes(c));
             if (CTA_SMEM_FIXED + per_warp > static_cast<size_t>(max_smem))
             {
-                pl->unsupported_mask |= 1u << c;
+                pl->global_mask |= 1u << c; // too large for shared memory: this class keeps its accumulators in HBM
                 continue;
             }
             pl->warps_per_cta[c] = static_cast<uint32_t>(
@@ -410,9 +433,13 @@ extern "C" epk_status epk_placer_create(const epk_db* db, uint64_t keep_at_most,
                 EPK_CUDA(cudaFuncSetAttribute(pick_partial_kernel(*pl, c), cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
             }
         }
-        if (pl->warps_per_cta[0] == 0)
+        if (pl->global_mask)
         {
-            throw error(EPK_E_UNSUPPORTED, "tree too large for the shared-memory accumulators of this build");
+            pl->acc_region_bytes = static_cast<size_t>(pl->n_sms) * MAX_WARPS_PER_CTA * global_acc_bytes(db->d.n_nodes);
+            pl->acc_scratch.resize((N_SLOTS + 1) * pl->acc_region_bytes);
+            EPK_CUDA(cudaMemset(pl->acc_scratch.get(), 0, pl->acc_scratch.bytes()));
+            EPK_CUDA(cudaFuncSetAttribute(pick_global_kernel(*pl), cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          static_cast<int>(CTA_SMEM_FIXED + MAX_WARPS_PER_CTA * GLOBAL_WARP_SMEM)));
         }
 
         // zero-hit queries: keep_at_most placements on branches 0..K-1, all tied, pushed through
@@ -599,7 +626,7 @@ extern "C" epk_status epk_place(epk_placer* pl, const char* seq, const uint64_t*
             d.count = s.out.count.get();
             // offsets stay absolute: bias the base pointer instead of rewriting them
             launch(*pl, s.seq.get() - seq_off[first], s.off.get(), m, d, s.counters.get(), s.class_reads.get(),
-                   classes_of(seq_off, first, last, k), s.stream);
+                   classes_of(seq_off, first, last, k), s.stream, nullptr, static_cast<uint32_t>((turn - 1) % N_SLOTS));
 
             if (out_pinned)
             {
@@ -735,6 +762,7 @@ extern "C" epk_status epk_gather_ceiling_device(epk_placer* pl, const char* d_se
 {
     return guarded([&] {
         if (!pl || (n && (!d_seq_off || !d_checksum))) { throw error(EPK_E_INVALID, "null argument"); }
+        if (pl->warps_per_cta[0] == 0) { throw error(EPK_E_UNSUPPORTED, "the ceiling launch exists for trees whose accumulators fit shared memory"); }
         EPK_CUDA(cudaSetDevice(pl->db->device));
         const cudaStream_t s = static_cast<cudaStream_t>(stream);
         place_params p{};

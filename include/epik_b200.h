@@ -203,8 +203,11 @@ typedef struct epk_counters
 {
     uint64_t n_reads, n_windows, n_hits, n_entries, n_launches;
     uint64_t n_short;       /* sequences shorter than k - 1 letters (left with n_place = 0)            */
-    uint64_t n_unsupported; /* sequences with more windows than the shared-memory accumulators of this */
-                            /* tree size can count (left with n_place = 0)                             */
+    uint64_t n_unsupported; /* sequences left with n_place = 0 because a launch form does not exist for */
+                            /* them: only in database-sharded mode (more than 65535 windows, a tree too */
+                            /* large for shared memory, ambiguous windows without shard views). The      */
+                            /* fused path places everything: accumulators that do not fit shared memory  */
+                            /* live in HBM (slower, same results)                                        */
 } epk_counters;
 epk_status epk_placer_counters(epk_placer* placer, epk_counters* out);
 

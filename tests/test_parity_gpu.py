@@ -236,45 +236,34 @@ def test_database_validation_errors():
         Database(flat, mu=1.5)  # check_mu, main.cpp:196-202
 
 
-def test_reads_too_long_for_the_accumulators_are_counted_not_placed():
-    """The uint32-count class needs 8 bytes of shared memory per node: past ~28 k nodes it has no launch. Its reads
-    come back with n_place = 0 and are counted (epk_place: EPK_E_UNSUPPORTED once everything else is placed;
-    epk_place_device: the counter only); the other reads of the batch are placed as if the long one were not there."""
-    flat = synth.make_db(0, 8, 15001, 0.3, 4.0, seed=77)  # N = 30001
+@pytest.mark.parametrize("n_leaves", [15001, 25001], ids=["long-read-on-30k-nodes", "50k-nodes"])
+def test_accumulators_that_do_not_fit_shared_memory_live_in_hbm(n_leaves):
+    """The shared-memory accumulators bound the tree (8 bytes per node with 32-bit counts: ~28 k nodes; 5 bytes with
+    8-bit counts: ~44 k); the reference has no such bound (place.cpp:92-96). Beyond it the same kernel keeps a warp's
+    accumulators in a row of global memory: a 70 000-letter read on a 30 001-node tree, and every read on a 50 001-node
+    tree, are placed with the reference's results - scores bit for bit."""
+    flat = synth.make_db(0, 8, n_leaves, 0.3, 4.0, seed=77)
     rng = np.random.default_rng(12)
     seqs = ["".join(rng.choice(list("ACGT"), size=150)) for _ in range(24)]
     seqs.insert(5, "".join(rng.choice(list("ACGT"), size=70000)))
+    seqs.insert(9, "".join(rng.choice(list("ACGTN"), size=400)))   # ambiguous windows too
+    seqs.append("ACGTACG")                                         # k - 1 letters: the fake placements
     data, off = pack_sequences(seqs)
     p = Placer(Database(flat))
-    with pytest.raises(capi.EpkError) as e:
-        p.place_packed(data, off)
-    assert e.value.status == capi.EPK_E_UNSUPPORTED
-    assert p.counters()["n_unsupported"] == 1
-    import torch
-    dev = torch.device("cuda:0")
-    n, K = len(seqs), 7
-    d_seq = torch.from_numpy(data).to(dev)
-    d_off = torch.from_numpy(off.view(np.int64)).to(dev)
-    d_out = {"n_place": torch.full((n,), 99, dtype=torch.int32, device=dev),
-             "branch": torch.zeros(n * K, dtype=torch.int32, device=dev),
-             "score": torch.zeros(n * K, dtype=torch.float32, device=dev),
-             "lwr": torch.zeros(n * K, dtype=torch.float64, device=dev),
-             "count": torch.zeros(n * K, dtype=torch.int32, device=dev)}
-    p.place_device(d_seq, d_off, n, d_out)
-    torch.cuda.synchronize()
+    got = p.place_packed(data, off)
     c = p.counters()
-    assert c["n_unsupported"] == 1 and c["n_short"] == 0
-    n_place = d_out["n_place"].cpu().numpy().view(np.uint32)
-    assert n_place[5] == 0
-    keep = np.arange(n) != 5
-    got = {"n_place": n_place[keep],
-           "branch": d_out["branch"].cpu().numpy().view(np.uint32).reshape(n, K)[keep],
-           "score": d_out["score"].cpu().numpy().reshape(n, K)[keep],
-           "lwr": d_out["lwr"].cpu().numpy().reshape(n, K)[keep],
-           "count": d_out["count"].cpu().numpy().view(np.uint32).reshape(n, K)[keep]}
+    assert c["n_unsupported"] == 0 and c["n_short"] == 0 and c["n_reads"] == len(seqs)
     oracle, kind = best_oracle(flat, threads=2)
-    want = oracle.place([s for i, s in enumerate(seqs) if i != 5], threads=2)
-    helpers.assert_same_placements(got, want, lengths=False, what="batch with an unsupported read " + kind)
+    want = oracle.place_packed(data, off, threads=2)
+    helpers.assert_same_placements(got, want, what="accumulators in HBM " + kind)
+    valid = np.arange(7)[None, :] < want["n_place"][:, None]
+    assert np.array_equal(got["score"][valid], want["score"][valid])
+    # several passes, chunks on the placer's three streams (each with its own rows): nothing is left behind in them
+    many, moff = pack_sequences(seqs[:5] * 40)
+    small = Placer(Database(flat), chunk_reads=16)
+    again = small.place_packed(many, moff)
+    for name in ("n_place", "branch", "score", "lwr", "count"):
+        assert np.array_equal(again[name][:5], got[name][:5]) and np.array_equal(again[name][-5:], got[name][:5]), name
 
 
 def test_hit_count_widths_and_mixed_lengths():
