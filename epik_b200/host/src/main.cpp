@@ -257,7 +257,7 @@ int main(int argc, char** argv)
         size_t num_seq_placed = 0, num_iterations = 0;
         double average_speed = 0.0;
 
-        epik::io::batch_fasta reader(query_file, batch_size * device_batches);
+        epik::io::batch_fasta reader(query_file, batch_size * device_batches, num_threads);
         // Two passes are in flight: while the jplace text of one device pass is produced (on the -j threads) and
         // appended, the next pass is read and placed. A pass owns its records: the results hold views into them.
         using records_t = decltype(reader.next_batch());

@@ -6,7 +6,10 @@
 int main(int argc, char** argv)
 {
     if (argc < 3) { return 2; }
-    epik::io::batch_fasta reader(argv[1], static_cast<size_t>(std::stoul(argv[2])));
+    // optional: host threads, bytes per read block (tiny blocks put every kind of boundary inside a record)
+    const size_t threads = argc > 3 ? std::stoul(argv[3]) : 1, block = argc > 4 ? std::stoul(argv[4]) : (32u << 20);
+    epik::io::batch_fasta reader(argv[1], static_cast<size_t>(std::stoul(argv[2])), threads, block);
+    if (threads > 1) { reader.set_records_per_thread(1); }
     size_t b = 0;
     while (true)
     {

@@ -58,13 +58,22 @@ def test_fasta_reader(tmp_path):
     path = tmp_path / "q.fasta"
     path.write_bytes(text)
     want = [("r1 first read", "ACGTACGT"), ("r2", "ACGTNN--"), ("empty", ""), ("r4\tx", "acgt" + "A" * 5000), ("last", "TTTT")]
-    for batch_size in (1, 2, 3, 100):
-        out = subprocess.run([exe, str(path), str(batch_size)], check=True, capture_output=True).stdout.decode().split("\n")
+    for batch_size, threads, block in ((1, 1, 1 << 25), (2, 1, 7), (3, 4, 1), (100, 3, 64), (2, 2, 5000), (4, 8, 1 << 25)):
+        out = subprocess.run([exe, str(path), str(batch_size), str(threads), str(block)], check=True, capture_output=True).stdout.decode().split("\n")
         recs = [l.split("\t") for l in out if l and not l.startswith("bytes")]
         got = [("\t".join(r[1:-1]), r[-1]) for r in recs]
-        assert got == want, batch_size
+        assert got == want, (batch_size, threads, block)
         assert [int(r[0]) for r in recs] == [i // batch_size for i in range(len(want))]
         assert out[-2] == "bytes\t%d" % len(text)
+    # many records over several blocks and threads: the same records as one thread reads
+    big = tmp_path / "big.fasta"
+    rng = np.random.default_rng(4)
+    with open(big, "wb") as f:
+        for i in range(20000):
+            f.write(b">read%d some text\n" % i + bytes(rng.choice(np.frombuffer(b"ACGTN", np.uint8), size=int(rng.integers(0, 300)))) + (b"\r\n" if i % 7 == 0 else b"\n"))
+    one = subprocess.run([exe, str(big), "3000", "1"], check=True, capture_output=True).stdout
+    for threads, block in ((4, 100000), (16, 1 << 25), (5, 333)):
+        assert subprocess.run([exe, str(big), "3000", str(threads), str(block)], check=True, capture_output=True).stdout == one
 
 
 def test_epkdb_round_trip(tmp_path):

@@ -30,6 +30,8 @@ def main():
     ap.add_argument("--reads", type=int, default=2_000_000)
     ap.add_argument("--out", default="")
     ap.add_argument("--device-batches", type=int, default=128)
+    ap.add_argument("--devices", default="1", help="--devices of the driver: GPUs behind the one process, or 'all'")
+    ap.add_argument("--keep-jplace", default="", help="copy the jplace here (to compare runs byte for byte)")
     ap.add_argument("--jobs", type=int, default=len(os.sched_getaffinity(0)), help="-j of the driver: host threads")
     args = ap.parse_args()
     from epik_b200 import flatdb, synth
@@ -57,7 +59,7 @@ def main():
             f.write(block)
     exe = os.path.join(ROOT, "bin", "epik", "epik-aa" if alphabet else "epik-dna")
     argv = [exe, "-d", db_path, "-q", q_path, "-j", str(args.jobs), "--omega", "1.5", "--mu", "1.0", "-o", tmp,
-            "--device-batches", str(args.device_batches), q_path]
+            "--device-batches", str(args.device_batches), "--devices", args.devices, q_path]
     t0 = time.perf_counter()
     run = subprocess.run(argv, capture_output=True, text=True)
     wall = time.perf_counter() - t0
@@ -68,13 +70,24 @@ def main():
     jplace = os.path.join(tmp, "placements_q.fasta.jplace")
     line = {
         "what": "bin/epik/%s: FASTA file -> placements -> jplace file" % os.path.basename(exe),
-        "workload": args.workload, "reads": args.reads, "read_len": read_len, "jobs": args.jobs,
+        "workload": args.workload, "reads": args.reads, "read_len": read_len, "jobs": args.jobs, "devices": args.devices,
         "placement_time_ms": ms, "reads_per_s_file_to_file": args.reads / (ms / 1e3),
         "driver_average_speed": speed, "process_wall_s": wall,
         "fasta_bytes": os.path.getsize(q_path), "jplace_bytes": os.path.getsize(jplace),
         "db_file_bytes": os.path.getsize(db_path),
     }
+    import hashlib
+    h = hashlib.sha256()
+    with open(jplace, "rb") as f:
+        for _ in range(4):
+            f.readline()  # (the metadata block holds the invocation, which differs between runs)
+        for block in iter(lambda: f.read(1 << 24), b""):
+            h.update(block)
+    line["jplace_sha256_without_head"] = h.hexdigest()
     print(json.dumps(line))
+    if args.keep_jplace:
+        import shutil
+        shutil.copy(jplace, args.keep_jplace)
     if args.out:
         with open(args.out, "w") as f:
             f.write(json.dumps(line) + "\n")
