@@ -111,7 +111,7 @@ constexpr int CHUNK = 32 * WPL;        // windows staged per pass
 constexpr int CODE_BYTES = CHUNK + 32; // letter codes of one pass (k - 1 <= 31 extra letters)
 constexpr int SEG_CAP = 256;           // segment descriptors buffered per warp
 constexpr int SEG_LEN = 64;            // postings per segment: one 128-bit load per lane
-constexpr int SEG_PAD = 8;             // zero descriptors after the last one (= segments in flight)
+constexpr int SEG_PAD = 16;            // zero descriptors after the last one (>= segments in flight)
 constexpr int SWEEP_STEP = 128;        // branches per warp and run of the sweep (4 consecutive ones per lane)
 
 __host__ __device__ inline uint32_t padded_nodes(uint32_t n_nodes)

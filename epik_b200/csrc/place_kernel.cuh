@@ -334,6 +334,9 @@ struct acc_ref
 // list are distinct, so the two read-modify-writes of a lane and those of different lanes are
 // independent. Lanes past the end of the segment hold 0 or an older, valid branch: they read it
 // and store nothing.
+#ifndef EPK_APPLY_SYNC
+#define EPK_APPLY_SYNC __syncwarp();
+#endif
 #define EPK_APPLY_SEGMENT(NAME, CT, LD, ST, P0, EXTRA)                                                     \
     __device__ __forceinline__ void NAME(const acc_ref& acc, uint32_t lane2, const seg_regs& r, CT)          \
     {                                                                                                      \
@@ -366,7 +369,7 @@ struct acc_ref
               "r"(lane2), "r"(lane2 + 1u), "r"(acc.s_shared), "r"(acc.c_shared),                           \
               "n"(static_cast<int>(sizeof(CT))) EXTRA                                                      \
             : "memory");                                                                                   \
-        __syncwarp(); /* the next segment may name the same branches from other lanes */                  \
+        EPK_APPLY_SYNC /* the next segment may name the same branches from other lanes */                   \
     }
 #define EPK_P0_PLAIN "setp.lt.u32 p0, %5, %4;\n\t"
 #define EPK_P0_RANGE "setp.ge.u32 p0, %5, %10;\n\tsetp.lt.and.u32 p0, %5, %4, p0;\n\t" /* lane2 in [start, cnt) */
