@@ -463,6 +463,8 @@ static void build_db(const db_shape& d, raw_source& src, const epk_load_filter* 
     }
 
     db.omega = omega;
+    db.shard_index = shard_index;
+    db.shard_count = shard_count;
     db.n_entries_total = n_total;
     db.n_entries_loaded = h_totals[0];
     db.n_keys_loaded = h_totals[1];

@@ -20,6 +20,7 @@ struct epk_db
     std::vector<double> distal, pendant; // place.cpp:98-125, by post-order id
     float omega = 0.0f;
     uint64_t n_entries_total = 0, n_entries_loaded = 0, n_keys_loaded = 0;
+    uint32_t shard_index = 0, shard_count = 1; // database-sharded mode: which part of the keys this is
 };
 
 namespace epk

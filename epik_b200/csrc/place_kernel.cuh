@@ -80,6 +80,7 @@ struct place_params
     const unsigned char* rows_in;        // finalize launch: n_shards slabs of n rows each
     uint64_t shard_stride;               // bytes from a row of shard g to the same row of shard g + 1
     uint32_t n_shards;
+    uint32_t row_format;                 // partial rows: ROW_DENSE or ROW_COMPACT (both launches of a step agree on it)
     uint32_t team;                       // warps per accumulator set (TEAM launches)
     uint32_t prefetch;                   // L2 prefetch of a descriptor buffer's postings before it is gathered (PREFETCH_*)
     uint32_t* trace;                     // [4 n] per query: keys looked up, keys found, postings, checksum of the k-mer stream (NULL: none)
@@ -88,6 +89,7 @@ struct place_params
     // ---- finalize launch: ambiguous windows of database-sharded mode, replayed by the owner ----
     const device_db* shard_views;        // [n_shards] the shards' tables and postings as seen from this device (NULL: none)
     uint32_t* seen_scratch;              // np / 32 words per warp of the finalize grid, zero between queries
+    unsigned char* amb_scratch;          // float S[np] | uint16 C[np] per warp of the finalize grid, zero between queries
 };
 
 
@@ -785,46 +787,151 @@ struct shared_acc
     }
 };
 
+// the layout of a compact partial row (what it is and why: "partial rows" below)
+constexpr uint32_t ROW_HEADER_BYTES = 16;
+__host__ __device__ inline uint64_t row_bitmap_offset() { return ROW_HEADER_BYTES; }
+__host__ __device__ inline uint64_t row_steps_offset(uint32_t np) { return ROW_HEADER_BYTES + np / 8; }
+__host__ __device__ inline uint64_t row_s_offset(uint32_t np) { return ROW_HEADER_BYTES + np / 8 + 4ull * (np / SWEEP_STEP); }
+__host__ __device__ inline uint64_t row_c_offset(uint32_t np) { return row_s_offset(np) + 4ull * np; }
+
+enum row_format_kind { ROW_DENSE = 0, ROW_COMPACT = 1 };
+
 struct rows_acc
 {
-    const unsigned char* s_rows; // S of shard 0; shard g is g * stride further
-    const unsigned char* c_rows; // C (uint16) of shard 0
+    const unsigned char* row0;   // the query's row of shard 0; shard g is g * stride further
     uint64_t stride;
     uint32_t n_shards;
-    bool modified;               // this launch has written to the rows (ambiguous windows replayed by the owner): read
-                                 // them through L2 (ld.global.cg), not through the read-only path
-    __device__ __forceinline__ float4 load_s(const unsigned char* at) const
-    {
-        return modified ? __ldcg(reinterpret_cast<const float4*>(at)) : __ldg(reinterpret_cast<const float4*>(at));
-    }
-    __device__ __forceinline__ uint2 load_c(const unsigned char* at) const
-    {
-        return modified ? __ldcg(reinterpret_cast<const uint2*>(at)) : __ldg(reinterpret_cast<const uint2*>(at));
-    }
+    uint32_t np;
+    uint32_t format;             // ROW_DENSE: float S[np] | uint16 C[np] behind the header; ROW_COMPACT: bitmap, step counts, values
+    float* amb_s;                // dense contributions of the ambiguous windows the owner replayed (NULL: none);
+    uint16_t* amb_c;             // taken - and cleared - with the rows
+
     __device__ __forceinline__ bool any(uint32_t j) const
     {
         uint32_t seen = 0;
         for (uint32_t g = 0; g < n_shards; ++g)
         {
-            const uint2 u = load_c(c_rows + g * stride + 2ull * j);
+            if (format == ROW_DENSE)
+            {
+                const uint2 u = __ldg(reinterpret_cast<const uint2*>(row0 + g * stride + ROW_HEADER_BYTES + 4ull * np + 2ull * j));
+                seen |= u.x | u.y;
+                continue;
+            }
+            const uint32_t word = __ldg(reinterpret_cast<const uint32_t*>(row0 + g * stride + ROW_HEADER_BYTES) + j / 32u);
+            seen |= (word >> (j % 32u)) & 0xFu;
+        }
+        if (amb_c)
+        {
+            const uint2 u = __ldcg(reinterpret_cast<const uint2*>(amb_c + j));
             seen |= u.x | u.y;
         }
         return seen != 0u;
     }
     __device__ __forceinline__ float4 take(uint32_t j, uint32_t (&c)[4]) const
     {
-        float4 s4 = load_s(s_rows + 4ull * j);
-        uint2 c2 = load_c(c_rows + 2ull * j);
-        for (uint32_t g = 1; g < n_shards; ++g)
+        float sv[4] = { 0.0f, 0.0f, 0.0f, 0.0f };
+        c[0] = c[1] = c[2] = c[3] = 0u;
+        const uint32_t step = j / SWEEP_STEP, in_step = j % SWEEP_STEP;
+        const uint32_t which = in_step / 32u, shift = in_step % 32u;
+        constexpr uint32_t GROUP = 4; // shards whose loads are in flight together (a row's bitmap, its step count, its values)
+        if (format == ROW_DENSE)
         {
-            const float4 t = load_s(s_rows + g * stride + 4ull * j);
-            const uint2 u = load_c(c_rows + g * stride + 2ull * j);
-            s4.x = __fadd_rn(s4.x, t.x); s4.y = __fadd_rn(s4.y, t.y);
-            s4.z = __fadd_rn(s4.z, t.z); s4.w = __fadd_rn(s4.w, t.w);
-            c2.x += u.x; c2.y += u.y; // 16-bit halves cannot carry: a branch is hit at most n_windows <= 65535 times
+            const unsigned char* s_rows = row0 + ROW_HEADER_BYTES + 4ull * j;
+            const unsigned char* c_rows = row0 + ROW_HEADER_BYTES + 4ull * np + 2ull * j;
+            float4 s4 = __ldg(reinterpret_cast<const float4*>(s_rows));
+            uint2 c2 = __ldg(reinterpret_cast<const uint2*>(c_rows));
+            for (uint32_t g = 1; g < n_shards; ++g)
+            {
+                const float4 t = __ldg(reinterpret_cast<const float4*>(s_rows + g * stride));
+                const uint2 u = __ldg(reinterpret_cast<const uint2*>(c_rows + g * stride));
+                s4.x = __fadd_rn(s4.x, t.x); s4.y = __fadd_rn(s4.y, t.y);
+                s4.z = __fadd_rn(s4.z, t.z); s4.w = __fadd_rn(s4.w, t.w);
+                c2.x += u.x; c2.y += u.y; // 16-bit halves cannot carry: a branch is hit at most n_windows <= 65535 times
+            }
+            sv[0] = s4.x; sv[1] = s4.y; sv[2] = s4.z; sv[3] = s4.w;
+            c[0] = c2.x & 0xFFFFu; c[1] = c2.x >> 16; c[2] = c2.y & 0xFFFFu; c[3] = c2.y >> 16;
         }
-        c[0] = c2.x & 0xFFFFu; c[1] = c2.x >> 16; c[2] = c2.y & 0xFFFFu; c[3] = c2.y >> 16;
-        return s4;
+        for (uint32_t g0 = 0; format == ROW_COMPACT && g0 < n_shards; g0 += GROUP)
+        {
+            uint4 w4[GROUP];
+            uint32_t base[GROUP];
+#pragma unroll
+            for (uint32_t i = 0; i < GROUP; ++i)
+            {
+                w4[i] = make_uint4(0u, 0u, 0u, 0u);
+                base[i] = 0u;
+                if (g0 + i < n_shards)
+                {
+                    const unsigned char* row = row0 + (g0 + i) * stride;
+                    w4[i] = __ldg(reinterpret_cast<const uint4*>(row + ROW_HEADER_BYTES) + step);
+                    base[i] = __ldg(reinterpret_cast<const uint32_t*>(row + row_steps_offset(np)) + step);
+                }
+            }
+            uint32_t nib[GROUP];
+            float vs[GROUP][4];
+            uint32_t vc[GROUP][4];
+#pragma unroll
+            for (uint32_t i = 0; i < GROUP; ++i)
+            {
+                const uint32_t w[4] = { w4[i].x, w4[i].y, w4[i].z, w4[i].w };
+                uint32_t before = 0, word = 0;
+#pragma unroll
+                for (uint32_t k = 0; k < 4; ++k)
+                {
+                    before += k < which ? __popc(w[k]) : 0u;
+                    word = k == which ? w[k] : word;
+                }
+                nib[i] = (word >> shift) & 0xFu;
+                uint32_t at = base[i] + before + __popc(word & ((1u << shift) - 1u));
+                const unsigned char* row = row0 + (g0 + i) * stride;
+                const float* s_in = reinterpret_cast<const float*>(row + row_s_offset(np));
+                const uint16_t* c_in = reinterpret_cast<const uint16_t*>(row + row_c_offset(np));
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                {
+                    vs[i][u] = 0.0f;
+                    vc[i][u] = 0u;
+                    if ((nib[i] >> u) & 1u)
+                    {
+                        vs[i][u] = __ldg(s_in + at);
+                        vc[i][u] = __ldg(c_in + at);
+                        ++at;
+                    }
+                }
+            }
+            // shard order: a fixed association, the same on every run
+#pragma unroll
+            for (uint32_t i = 0; i < GROUP; ++i)
+            {
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                {
+                    if ((nib[i] >> u) & 1u)
+                    {
+                        sv[u] = __fadd_rn(sv[u], vs[i][u]);
+                        c[u] += vc[i][u]; // a branch is hit at most n_windows <= 65535 times
+                    }
+                }
+            }
+        }
+        if (amb_c)
+        {
+            const float4 t = __ldcg(reinterpret_cast<const float4*>(amb_s + j));
+            const uint2 u = __ldcg(reinterpret_cast<const uint2*>(amb_c + j));
+            if ((u.x | u.y) != 0u)
+            {
+                const uint32_t ac[4] = { u.x & 0xFFFFu, u.x >> 16, u.y & 0xFFFFu, u.y >> 16 };
+                const float as[4] = { t.x, t.y, t.z, t.w };
+#pragma unroll
+                for (int v = 0; v < 4; ++v)
+                {
+                    if (ac[v]) { sv[v] = __fadd_rn(sv[v], as[v]); c[v] += ac[v]; }
+                }
+                __stcg(reinterpret_cast<float4*>(amb_s + j), make_float4(0.0f, 0.0f, 0.0f, 0.0f));
+                __stcg(reinterpret_cast<uint2*>(amb_c + j), make_uint2(0u, 0u));
+            }
+        }
+        return make_float4(sv[0], sv[1], sv[2], sv[3]);
     }
 };
 
@@ -1479,8 +1586,8 @@ constexpr uint32_t TEAM_CMD_DUMP = 0x40000000u;
 
 template<class CT>
 __device__ __forceinline__ void dump_partial_row(const place_params& p, float* S, CT* C, uint32_t np, uint32_t q,
-                                                 uint32_t flags, uint32_t gathered, uint32_t lane, uint32_t part = 0,
-                                                 uint32_t parts = 1);
+                                                 uint32_t flags, uint32_t gathered, uint32_t lane, uint32_t* stage, uint32_t part = 0,
+                                                 uint32_t parts = 1, uint32_t* step_counts = nullptr, uint32_t set = 0);
 
 template<int U, class CT, bool SINK>
 __device__ __noinline__ void range_gather(const device_db& db, acc_ref acc, const uint64_t* hits, uint32_t n_hits, uint2* my_segs,
@@ -1516,7 +1623,8 @@ __device__ __forceinline__ void team_helper_loop(const place_params& p, float* S
         }
         if (cmd & TEAM_CMD_DUMP)
         {
-            dump_partial_row<CT>(p, S, C, np, q, nw32, gathered, lane, member, team);
+            dump_partial_row<CT>(p, S, C, np, q, nw32, gathered, lane, member_base, member, team,
+                                 reinterpret_cast<uint32_t*>(const_cast<uint64_t*>(hits)), set);
             team_sync(set, team); // the row is out, the accumulators are clear
             continue;
         }
@@ -1645,19 +1753,26 @@ __device__ __noinline__ void range_gather(const device_db& db, acc_ref acc, cons
 // ---- partial rows (database-sharded mode) ---------------------------------------------------------
 //
 // When the database is split by key over the GPUs of a group (second row), every GPU
-// runs the encode / probe / gather phases of EVERY query against its shard and leaves, per query, a
-// row   { uint32 flags, uint32 postings gathered, 0, 0 | float S[np] | uint16 C[np] }
-// in the memory of the GPU that finalises that query (its own, a send buffer, or a peer's slab mapped
-// over NVLink). The owner adds the rows of all shards in shard order and runs finish_query on the sums.
-// The additions of one branch are no longer in window order: scores agree with the reference to
-// float rounding of a differently associated sum (asserted at 1e-5 relative), not bit for bit.
-constexpr uint32_t ROW_HEADER_BYTES = 16;
-constexpr uint32_t ROW_FLAG_AMBIGUOUS = 1u; // the query has windows with one ambiguous letter: the
-                                            // first-key-wins rule of place.cpp:391 needs the global key
-                                            // order, which a shard does not have -> reported unsupported
+// runs the encode / probe / gather phases of EVERY query against its shard and leaves, per query, a COMPACT row
+//   { uint32 flags, postings gathered, touched branches, 0
+//   | bitmap of the touched branches, np / 8 bytes
+//   | touched branches before each 128-branch step, np / 128 uint32
+//   | float S of the touched branches, in branch order | uint16 C of the touched branches, in branch order }
+// in the memory of the GPU that finalises that query (its own, a send buffer, or a peer's slab mapped over NVLink) - in
+// a slot of fixed size (partial_row_bytes: room for every branch), of which only the used prefix of each part is
+// written and read: a shard of G touches about 1 / G of what the query touches, so the bytes that cross NVLink and
+// that the owner reads scale with the touched branches, not with G x N (round 1 wrote dense 6-byte-per-branch rows:
+// 105 KB per query over NVLink at G = 8 on a 20 k-branch tree, 1.46 M reads/s; gpurun r3o). The owner walks the
+// branches in order, finds a branch's values through the bitmap and the step counts, adds the shards in shard order
+// and runs finish_query on the sums. The additions of one branch are no longer in window order: scores agree with the
+// reference to float rounding of a differently associated sum (asserted at 1e-5 relative), not bit for bit.
+constexpr uint32_t ROW_FLAG_AMBIGUOUS = 1u; // the query has windows with one ambiguous letter: the first-key-wins rule of
+                                            // place.cpp:391 needs the global key order, which a shard does not have ->
+                                            // replayed by the owner (replay_ambiguous), or reported unsupported
 __host__ __device__ inline uint64_t partial_row_bytes(uint32_t n_nodes)
 {
-    return ROW_HEADER_BYTES + 6ull * padded_nodes(n_nodes);
+    const uint32_t np = padded_nodes(n_nodes);
+    return (row_c_offset(np) + 2ull * np + 15ull) & ~15ull;
 }
 
 __device__ __forceinline__ void store_counts4_u16(unsigned char* at, const uint32_t (&c)[4])
@@ -1665,10 +1780,12 @@ __device__ __forceinline__ void store_counts4_u16(unsigned char* at, const uint3
     *reinterpret_cast<uint2*>(at) = make_uint2(c[0] | (c[1] << 16), c[2] | (c[3] << 16));
 }
 
+// The dense form of a row { header | float S[np] | uint16 C[np] }: what a shard writes when it touches a large part of the
+// tree anyway (two shards: half of what the query touches) - a straight copy, no counting, no compaction.
 // S, C of query q -> its row at the owner; leaves both arrays zeroed
 // (a team dumps a row together: member `part` of `parts` takes every parts-th 128-branch step)
 template<class CT>
-__device__ __forceinline__ void dump_partial_row(const place_params& p, float* S, CT* C, uint32_t np, uint32_t q,
+__device__ __forceinline__ void dump_dense_row(const place_params& p, float* S, CT* C, uint32_t np, uint32_t q,
                                                  uint32_t flags, uint32_t gathered, uint32_t lane, uint32_t part,
                                                  uint32_t parts)
 {
@@ -1688,6 +1805,109 @@ __device__ __forceinline__ void dump_partial_row(const place_params& p, float* S
         *reinterpret_cast<float4*>(s_out + 4ull * j) = s4;
         store_counts4_u16(c_out + 2ull * j, c);
     }
+    __syncwarp();
+}
+
+// S, C of query q -> its row at the owner; leaves both arrays zeroed.
+// `stage`: 192 words of shared memory of this warp (128 floats + 128 uint16).
+// A team dumps a row together: member `part` of `parts` takes every parts-th 128-branch step; the position of a step's
+// values in the row depends on all the steps before it, so the members first count (step_counts: shared memory of
+// the set, np / 128 words), the leader turns the counts into positions, then everybody writes.
+template<class CT>
+__device__ __forceinline__ void dump_partial_row(const place_params& p, float* S, CT* C, uint32_t np, uint32_t q,
+                                                 uint32_t flags, uint32_t gathered, uint32_t lane, uint32_t* stage, uint32_t part,
+                                                 uint32_t parts, uint32_t* step_counts, uint32_t set)
+{
+    if (p.row_format == ROW_DENSE)
+    {
+        dump_dense_row<CT>(p, S, C, np, q, flags, gathered, lane, part, parts);
+        return;
+    }
+    uint32_t g = 0;
+    while (g + 1 < p.n_owners && q >= p.owner_first[g + 1]) { ++g; }
+    unsigned char* row = p.rows_out[g] + static_cast<uint64_t>(q - p.owner_first[g]) * partial_row_bytes(p.db.n_nodes);
+    uint32_t* bitmap = reinterpret_cast<uint32_t*>(row + row_bitmap_offset());
+    uint32_t* steps = reinterpret_cast<uint32_t*>(row + row_steps_offset(np));
+    float* s_out = reinterpret_cast<float*>(row + row_s_offset(np));
+    uint16_t* c_out = reinterpret_cast<uint16_t*>(row + row_c_offset(np));
+    const uint32_t n_steps = np / SWEEP_STEP;
+    uint32_t n_touched = 0;
+    if (parts > 1)
+    {
+        for (uint32_t t = part; t < n_steps; t += parts)
+        {
+            uint32_t c[4];
+            load_counts4(C, t * SWEEP_STEP + 4u * lane, c);
+            const uint32_t mine = (c[0] != 0) + (c[1] != 0) + (c[2] != 0) + (c[3] != 0);
+            const uint32_t total = __reduce_add_sync(FULL, mine);
+            if (lane == 0) { step_counts[t] = total; }
+        }
+        __syncwarp();
+        team_sync(set, parts); // every step is counted
+        if (part == 0)
+        {
+            uint32_t running = 0;
+            for (uint32_t t0 = 0; t0 < n_steps; t0 += 32)
+            {
+                const uint32_t v = t0 + lane < n_steps ? step_counts[t0 + lane] : 0u;
+                const uint32_t incl = warp_inclusive_sum(v, lane);
+                if (t0 + lane < n_steps) { step_counts[t0 + lane] = running + incl - v; }
+                running += __shfl_sync(FULL, incl, 31);
+            }
+            n_touched = running;
+            __syncwarp();
+        }
+        team_sync(set, parts); // the positions are there
+    }
+    uint32_t base = 0;
+    for (uint32_t t = part; t < n_steps; t += parts)
+    {
+        const uint32_t j = t * SWEEP_STEP + 4u * lane;
+        const float4 s4 = *reinterpret_cast<const float4*>(S + j);
+        uint32_t c[4];
+        load_counts4(C, j, c);
+        *reinterpret_cast<float4*>(S + j) = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        clear_counts4(C, j);
+        const uint32_t nib = (c[0] != 0 ? 1u : 0u) | (c[1] != 0 ? 2u : 0u) | (c[2] != 0 ? 4u : 0u) | (c[3] != 0 ? 8u : 0u);
+        const uint32_t mine = __popc(nib);
+        const uint32_t incl = warp_inclusive_sum(mine, lane);
+        if (parts > 1) { base = step_counts[t]; }
+        // the step's values are compacted in shared memory first and leave as runs of consecutive words: a lane writing
+        // its own one to four values straight to the row made 8 partly filled store instructions per step - over NVLink
+        // that was slower than the dense row (gpurun r3r)
+        const uint32_t step_total = __shfl_sync(FULL, incl, 31);
+        uint32_t at = incl - mine;
+        const float sv[4] = { s4.x, s4.y, s4.z, s4.w };
+        float* stage_s = reinterpret_cast<float*>(stage);
+        uint16_t* stage_c = reinterpret_cast<uint16_t*>(stage + SWEEP_STEP);
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+        {
+            if ((nib >> u) & 1u)
+            {
+                stage_s[at] = sv[u];
+                stage_c[at] = static_cast<uint16_t>(c[u]);
+                ++at;
+            }
+        }
+        __syncwarp();
+        for (uint32_t i = lane; i < step_total; i += 32)
+        {
+            s_out[base + i] = stage_s[i];
+            c_out[base + i] = stage_c[i];
+        }
+        __syncwarp();
+        // the bitmap word of 8 lanes: their nibbles side by side
+        uint32_t word = nib << (4u * (lane & 7u));
+        word |= __shfl_xor_sync(FULL, word, 1);
+        word |= __shfl_xor_sync(FULL, word, 2);
+        word |= __shfl_xor_sync(FULL, word, 4);
+        if ((lane & 7u) == 0) { bitmap[t * 4u + (lane >> 3)] = word; }
+        if (lane == 0) { steps[t] = base; }
+        if (parts == 1) { base += step_total; }
+    }
+    if (parts == 1) { n_touched = base; }
+    if (lane == 0 && part == 0) { *reinterpret_cast<uint4*>(row) = make_uint4(flags, gathered, n_touched, 0u); }
     __syncwarp();
 }
 
@@ -2062,10 +2282,12 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
                 if (lane == 0) { *reinterpret_cast<team_mailbox*>(team_area) = team_mailbox{ q, row_flags, gathered_here, TEAM_CMD_DUMP }; }
                 __syncwarp();
                 team_sync(warp, team); // command: dump
-                dump_partial_row<CT>(p, S, C, np, q, row_flags, gathered_here, lane, 0u, team);
+                dump_partial_row<CT>(p, S, C, np, q, row_flags, gathered_here, lane,
+                                     reinterpret_cast<uint32_t*>(team_area + sizeof(team_mailbox) + team * sizeof(team_result)), 0u, team,
+                                     reinterpret_cast<uint32_t*>(segs), warp);
                 team_sync(warp, team);
             }
-            else { dump_partial_row<CT>(p, S, C, np, q, row_flags, gathered_here, lane); }
+            else { dump_partial_row<CT>(p, S, C, np, q, row_flags, gathered_here, lane, reinterpret_cast<uint32_t*>(segs)); }
             continue;
         }
         if (has_ambiguous)
@@ -2207,18 +2429,16 @@ __device__ __forceinline__ uint64_t view_search(const device_db& view, uint32_t 
 
 // place.cpp:373-415 for one query of database-sharded mode, by the warp that finalises it: every key an ambiguous window
 // resolves to lives in exactly one shard, so walking the windows in order and looking each key up in its shard keeps
-// the reference's global "first ambiguous key to name a branch" order. The contributions go to the query's row of
-// shard 0 (S float, C uint16, in this GPU's memory), which the sweep then adds to the other shards' rows.
-__device__ __noinline__ void replay_ambiguous_into_row(const place_params& p, const char* seq, uint64_t n_windows, unsigned char* row0,
-                                                       uint32_t np, uint32_t* seen, uint8_t* codes, const uint32_t* letters,
-                                                       uint32_t lane, uint64_t& hits, uint64_t& entries)
+// the reference's global "first ambiguous key to name a branch" order. The contributions go to a dense scratch row of
+// the warp (S float, C uint16, zero between queries), which the sweep adds to the shards' sums and clears.
+__device__ __noinline__ void replay_ambiguous(const place_params& p, const char* seq, uint64_t n_windows, float* S, uint16_t* C,
+                                              uint32_t np, uint32_t* seen, uint8_t* codes, const uint32_t* letters,
+                                              uint32_t lane, uint64_t& hits, uint64_t& entries)
 {
     const device_db& db = p.db;
     const uint32_t k = db.k, bits = db.bits;
     const float kf = static_cast<float>(k);
     const float thr_rest = __fmul_rn(static_cast<float>(k - 1), db.threshold);
-    float* S = reinterpret_cast<float*>(row0 + ROW_HEADER_BYTES);
-    uint16_t* C = reinterpret_cast<uint16_t*>(row0 + ROW_HEADER_BYTES + 4ull * np);
     for (uint64_t c0 = 0; c0 < n_windows; c0 += CHUNK)
     {
         const uint32_t nw = static_cast<uint32_t>(min(n_windows - c0, static_cast<uint64_t>(CHUNK)));
@@ -2263,11 +2483,13 @@ __device__ __noinline__ void replay_ambiguous_into_row(const place_params& p, co
                             // score (place.cpp:391,400-410)
                             const float prob = static_cast<float>(pow(10.0, static_cast<double>(__uint_as_float(entry.y))));
                             const float mean = __fdiv_rn(__fadd_rn(prob, thr_rest), kf);
-                            S[entry.x] = __fadd_rn(S[entry.x], mean);
-                            C[entry.x] = static_cast<uint16_t>(C[entry.x] + 1u);
+                            // (a branch gets ONE such contribution per query - the seen bit - so this is a plain store
+                            // into the warp's zeroed scratch, which the sweep adds to the shards' sums and clears)
+                            __stcg(S + entry.x, mean);
+                            __stcg(C + entry.x, static_cast<uint16_t>(1u));
                         }
                     }
-                    __syncwarp(); // (a list names a branch once; the next key may name the same branches from other lanes)
+                    __syncwarp();
                 }
             }
         }
@@ -2329,10 +2551,14 @@ __global__ void __launch_bounds__(FINALIZE_WARPS * 32, 2) finalize_kernel(const 
             continue;
         }
         uint64_t amb_hits = 0, amb_entries = 0;
+        float* amb_s = nullptr;
+        uint16_t* amb_c = nullptr;
         if (ambiguous)
         {
-            replay_ambiguous_into_row(p, p.seq + s0, n_windows, const_cast<unsigned char*>(row0), np, seen, codes, letters, lane,
-                                      amb_hits, amb_entries);
+            unsigned char* mine = p.amb_scratch + (static_cast<size_t>(blockIdx.x) * FINALIZE_WARPS + warp) * (6ull * np);
+            amb_s = reinterpret_cast<float*>(mine);
+            amb_c = reinterpret_cast<uint16_t*>(mine + 4ull * np);
+            replay_ambiguous(p, p.seq + s0, n_windows, amb_s, amb_c, np, seen, codes, letters, lane, amb_hits, amb_entries);
             gathered = static_cast<uint32_t>(min(static_cast<unsigned long long>(gathered) + amb_entries, 0xFFFFFFull));
         }
         if (lane == 0)
@@ -2341,7 +2567,7 @@ __global__ void __launch_bounds__(FINALIZE_WARPS * 32, 2) finalize_kernel(const 
             atomicAdd(p.counters + CTR_ENTRIES, static_cast<unsigned long long>(gathered));
             if (amb_hits) { atomicAdd(p.counters + CTR_HITS, static_cast<unsigned long long>(amb_hits)); }
         }
-        const rows_acc acc{ row0 + ROW_HEADER_BYTES, row0 + ROW_HEADER_BYTES + 4ull * np, p.shard_stride, p.n_shards, ambiguous };
+        const rows_acc acc{ row0, p.shard_stride, p.n_shards, np, p.row_format, amb_s, amb_c };
         finish_query(p, acc, np, n_windows, gathered, q, lane, cand_base);
     }
 }

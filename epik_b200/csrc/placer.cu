@@ -2,6 +2,7 @@
 // epik/include/epik/place.h:81-140, epik/src/epik/place.cpp:83-126,201-275) in front of the
 // sm_100a placement kernel (place_kernel.cuh).
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <future>
 #include <memory>
@@ -127,6 +128,7 @@ struct epk_placer
     device_buffer<device_db> shard_views;   // epk_placer_set_shard_views: the shards of a database-sharded group, from this device
     uint32_t n_shard_views = 0;
     device_buffer<uint32_t> seen_scratch;   // bitmaps of the finalising launch's ambiguous-window replay (one per warp)
+    device_buffer<unsigned char> amb_scratch; // and the dense rows its contributions go to (float S | uint16 C per warp)
     chunk_slot slots[N_SLOTS];
     uint64_t n_launches = 0, n_reads = 0;
     cudaStream_t last_stream = nullptr;
@@ -169,6 +171,19 @@ namespace
         }
         return pl.db->table_kind == TABLE_DIRECT ? place_kernel<TABLE_DIRECT, 8, uint8_t, MODE_GATHER_ONLY>
                                                  : place_kernel<TABLE_HASH, 8, uint8_t, MODE_GATHER_ONLY>;
+    }
+
+    // Partial rows of database-sharded mode: dense when a shard touches a large part of what the query touches (two
+    // shards: half), compact from three shards on - measured on BASELINE config 5: 2 GPUs 5.6 M reads/s dense / 4.1 M
+    // compact, 8 GPUs 1.5 M dense / 3.1 M compact (gpurun r3n, r3s, r3o, r3t). EPK_ROW_FORMAT=dense|compact overrides.
+    uint32_t row_format_of(const epk_placer& pl)
+    {
+        if (const char* text = std::getenv("EPK_ROW_FORMAT"))
+        {
+            if (std::strcmp(text, "dense") == 0) { return ROW_DENSE; }
+            if (std::strcmp(text, "compact") == 0) { return ROW_COMPACT; }
+        }
+        return pl.db->shard_count >= 3 ? ROW_COMPACT : ROW_DENSE;
     }
 
     // the launch for classes whose accumulators do not fit shared memory: rows in HBM, 32-bit counts, 8 warps per CTA
@@ -832,6 +847,7 @@ extern "C" epk_status epk_place_partial_device(epk_placer* pl, const char* d_seq
         p.letters = pl->db->letters.get();
         p.fake_order = pl->fake_order.get();
         p.n_owners = n_owners;
+        p.row_format = row_format_of(*pl);
         for (uint32_t g = 0; g < n_owners; ++g)
         {
             if (owner_first[g] > owner_first[g + 1]) { throw error(EPK_E_INVALID, "owner_first must be non-decreasing"); }
@@ -912,11 +928,13 @@ extern "C" epk_status epk_placer_set_shard_views(epk_placer* pl, uint32_t n_shar
         }
         pl->shard_views.resize(n_shards);
         EPK_CUDA(cudaMemcpy(pl->shard_views.get(), host.data(), n_shards * sizeof(device_db), cudaMemcpyHostToDevice));
-        const size_t words = static_cast<size_t>(2) * pl->n_sms * FINALIZE_WARPS * (padded_nodes(pl->db->d.n_nodes) / 32);
-        if (pl->seen_scratch.size() < words)
+        const size_t warps = static_cast<size_t>(2) * pl->n_sms * FINALIZE_WARPS, np = padded_nodes(pl->db->d.n_nodes);
+        if (pl->seen_scratch.size() < warps * (np / 32))
         {
-            pl->seen_scratch.resize(words);
-            EPK_CUDA(cudaMemset(pl->seen_scratch.get(), 0, words * 4));
+            pl->seen_scratch.resize(warps * (np / 32));
+            EPK_CUDA(cudaMemset(pl->seen_scratch.get(), 0, pl->seen_scratch.bytes()));
+            pl->amb_scratch.resize(warps * 6 * np);
+            EPK_CUDA(cudaMemset(pl->amb_scratch.get(), 0, pl->amb_scratch.bytes()));
         }
         pl->n_shard_views = n_shards;
     });
@@ -951,6 +969,7 @@ extern "C" epk_status epk_place_finalize_seq_device(epk_placer* pl, void* d_rows
         p.fake_order = pl->fake_order.get();
         p.rows_in = static_cast<const unsigned char*>(d_rows);
         p.n_shards = n_shards;
+        p.row_format = row_format_of(*pl);
         p.shard_stride = shard_stride_bytes;
         // ambiguous windows are replayed here when the owner can see every shard and has the letters
         if (d_seq && pl->n_shard_views == n_shards)
@@ -959,6 +978,7 @@ extern "C" epk_status epk_place_finalize_seq_device(epk_placer* pl, void* d_rows
             p.letters = pl->db->letters.get();
             p.shard_views = pl->shard_views.get();
             p.seen_scratch = pl->seen_scratch.get();
+            p.amb_scratch = pl->amb_scratch.get();
         }
         // the counters of this call replace those of the partial launch: they now describe whole queries
         EPK_CUDA(cudaMemsetAsync(pl->totals.get(), 0, pl->totals.bytes(), s));

@@ -216,9 +216,11 @@ epk_status epk_placer_counters(epk_placer* placer, epk_counters* out);
  * The reference has one phylo_kmer_db in one address space (main.cpp:277); when it does not fit one
  * HBM the keys are split over the G GPUs of a group by a hash range. Every GPU runs the encode /
  * probe / accumulate phases (place.cpp:278-316,349-371) of EVERY query against its shard and leaves a
- * partial row per query  { u32 flags, u32 postings, 0, 0 | f32 S[Np] | u16 C[Np] }  (Np = n_nodes
- * rounded up to 128) in the memory of the GPU that owns the query; the owner adds the G rows in shard
- * order and finishes the query (place.cpp:417-422, 164-199, 238-267). Transport between the two calls
+ * COMPACT partial row per query  { u32 flags, u32 postings, u32 touched, 0 | bitmap of the touched branches |
+ * touched branches before each 128-branch step | f32 S of the touched branches | u16 C of the touched branches }
+ * in a slot of epk_partial_row_bytes (room for every branch; only the used prefix of each part is written and
+ * read, so the bytes exchanged scale with the branches a shard touched) in the memory of the GPU that owns the
+ * query; the owner adds the G rows in shard order and finishes the query (place.cpp:417-422, 164-199, 238-267). Transport between the two calls
  * is the caller's: an NCCL all-to-all of the row buffers, or row buffers that ARE the owners' memory
  * (CUDA IPC / peer pointers over NVLink), in which case the partial launch is the exchange.
  * Scores agree with the reference within float rounding of a re-associated sum (1e-5 relative), not
@@ -233,7 +235,8 @@ epk_status epk_db_create_shard(const epk_db_desc* desc, const epk_load_filter* f
 /* The shard a k-mer code belongs to. */
 uint32_t epk_shard_of_key(uint32_t key, uint32_t shard_count);
 
-/* Bytes of one partial row for this placer's tree: 16 + 6 * Np. */
+/* Bytes of one partial-row slot for this placer's tree (Np = n_nodes rounded up to 128): 16 + Np / 8 + Np / 32 + 6 * Np,
+ * rounded up to 16. */
 uint64_t epk_partial_row_bytes(const epk_placer* placer);
 
 /* Phases 1-3 of placer::place_seq for n queries against this placer's (shard) database. Query i with

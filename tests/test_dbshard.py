@@ -213,6 +213,26 @@ def test_ambiguous_windows_are_replayed_by_the_owner(built, alphabet, k, leaves,
             assert np.array_equal(one[name], fused[name]), name
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("shards", [1, 2, 4])
+def test_both_row_formats_give_the_same_placements(built, monkeypatch, shards):
+    """Partial rows are dense (header | S | C) up to two shards and compact (bitmap | step counts | touched values) from
+    three on; either format carries the same sums, so forcing one or the other changes no bit of the result - reads with
+    ambiguous windows, a range-team tree and a one-warp tree included."""
+    for leaves, length in ((300, 150), (5000, 200)):
+        flat = synth.make_db(0, 8, leaves, 0.7, 24.0, seed=51)
+        data, off = synth.make_reads(0, 700, length, seed=52, amb_rate=0.01)
+        got = {}
+        for fmt in ("dense", "compact"):
+            monkeypatch.setenv("EPK_ROW_FORMAT", fmt)
+            sp = dbshard.LocalShardedPlacer(flat, shards)
+            got[fmt] = sp.place_packed(data, off, max_rows=256)
+            assert sp.unsupported == 0
+        monkeypatch.delenv("EPK_ROW_FORMAT")
+        for name in dbshard.RESULT_FIELDS:
+            assert np.array_equal(got["dense"][name], got["compact"][name]), (leaves, name)
+
+
 def _nccl_worker(rank, world, port, out_dir, transport):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
