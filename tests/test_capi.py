@@ -56,15 +56,18 @@ def test_header_compiles_as_plain_c(tmp_path):
 def test_struct_layouts_match_the_header(tmp_path):
     """ctypes mirrors vs the C compiler's sizeof/offsetof."""
     src = tmp_path / "s.c"
-    src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "epik_b200.h"\nint main(void) { printf("%zu %zu %zu %zu %zu %zu %zu %zu\\n", '
+    src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "epik_b200.h"\nint main(void) { printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu\\n", '
                    "sizeof(epk_db_desc), sizeof(epk_load_filter), sizeof(epk_db_info), sizeof(epk_placer_opts), "
-                   "sizeof(epk_result), sizeof(epk_counters), offsetof(epk_db_desc, n_nodes), offsetof(epk_db_info, n_keys_loaded)); return 0; }\n")
+                   "sizeof(epk_result), sizeof(epk_counters), offsetof(epk_db_desc, n_nodes), offsetof(epk_db_info, n_keys_loaded), "
+                   "sizeof(epk_db_view), sizeof(epk_synth_desc), offsetof(epk_synth_desc, seed), offsetof(epk_synth_desc, score_lo), "
+                   "sizeof(epk_microbench)); return 0; }\n")
     exe = tmp_path / "s"
     subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
     sizes = [int(x) for x in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
     assert sizes == [C.sizeof(capi.DbDesc), C.sizeof(capi.LoadFilter), C.sizeof(capi.DbInfo), C.sizeof(capi.PlacerOpts),
                      C.sizeof(capi.Result), C.sizeof(capi.Counters), capi.DbDesc.n_nodes.offset,
-                     capi.DbInfo.n_keys_loaded.offset]
+                     capi.DbInfo.n_keys_loaded.offset, C.sizeof(capi.DbView), C.sizeof(capi.SynthDesc),
+                     capi.SynthDesc.seed.offset, capi.SynthDesc.score_lo.offset, C.sizeof(capi.Microbench)]
 
 
 def test_group_batch_is_first_occurrence():
