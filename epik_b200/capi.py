@@ -24,7 +24,7 @@ SYMBOLS = [
     "epk_place_finalize_device", "epk_gather_ceiling_device",
     "epk_device_alloc", "epk_device_free", "epk_ipc_export", "epk_ipc_import", "epk_ipc_close",
     "epk_gather_microbench", "epk_placer_set_trace", "epk_trace_term",
-    "epk_db_get_view", "epk_placer_set_shard_views", "epk_place_finalize_seq_device", "epk_db_create_synthetic", "epk_place_many", "epk_group_batches",
+    "epk_db_get_view", "epk_placer_set_shard_views", "epk_place_finalize_seq_device", "epk_db_create_synthetic", "epk_place_many", "epk_group_batches", "epk_place_device_noalloc",
 ]
 
 
@@ -117,6 +117,8 @@ def lib():
     l.epk_placer_destroy.restype = None
     l.epk_place.restype = C.c_int
     l.epk_place.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.POINTER(Result)]
+    l.epk_place_device_noalloc.restype = C.c_int
+    l.epk_place_device_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.POINTER(Result), C.c_void_p]
     l.epk_place_many.restype = C.c_int
     l.epk_place_many.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32, C.POINTER(Result)]
     l.epk_place_device.restype = C.c_int

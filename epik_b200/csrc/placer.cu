@@ -6,6 +6,7 @@
 #include <cstring>
 #include <future>
 #include <memory>
+#include <mutex>
 #include <string>
 #include <string_view>
 #include <thread>
@@ -517,6 +518,103 @@ extern "C" epk_status epk_place_device(epk_placer* pl, const char* d_seq, const 
         pl->n_reads = 0;
         launch(*pl, d_seq, d_seq_off, n, *d_out, pl->device_counters.get(), pl->device_class_reads.get(),
                (1u << N_CLASSES) - 1u, s, pl->trace);
+    });
+}
+
+// ---- placement without any allocation (no counterpart in the reference) ----
+//
+// The accumulators-in-HBM form of the placement kernel (place_kernel<..., GLOBAL>) with its scratch - the launch
+// counters and one accumulator row per warp - in a file-scope array of fixed size instead of cudaMalloc'ed memory.
+// The array's name is a host-side stand-in in host code: its device address is asked for once per device, with that
+// device current (cudaGetSymbolAddress), and that pointer is what the kernel gets.
+constexpr size_t NOALLOC_SCRATCH_BYTES = static_cast<size_t>(EPK_NOALLOC_SCRATCH_BYTES);
+constexpr size_t NOALLOC_COUNTER_BYTES = 256; // [N_CLASSES][CTR_COUNT] launch counters in front of the rows
+static_assert(N_CLASSES * CTR_COUNT * sizeof(unsigned long long) <= NOALLOC_COUNTER_BYTES, "counters fit their corner of the scratch");
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_SCRATCH_BYTES];
+
+namespace
+{
+    constexpr int NOALLOC_MAX_DEVICES = 64;
+    std::mutex g_noalloc_lock;
+    unsigned char* g_noalloc_address[NOALLOC_MAX_DEVICES] = {}; // device address of g_noalloc_scratch, per device
+
+    unsigned char* noalloc_scratch_of(int device)
+    {
+        if (device < 0 || device >= NOALLOC_MAX_DEVICES) { throw error(EPK_E_UNSUPPORTED, "device ordinal beyond 63"); }
+        const std::lock_guard<std::mutex> hold(g_noalloc_lock);
+        if (!g_noalloc_address[device])
+        {
+            void* address = nullptr; // (the device is current: the caller has set it)
+            EPK_CUDA(cudaGetSymbolAddress(&address, g_noalloc_scratch));
+            if (!address) { throw error(EPK_E_CUDA, "cudaGetSymbolAddress gave no address for the static scratch"); }
+            g_noalloc_address[device] = static_cast<unsigned char*>(address);
+        }
+        return g_noalloc_address[device];
+    }
+}
+
+extern "C" epk_status epk_place_device_noalloc(epk_placer* pl, const char* d_seq, const uint64_t* d_seq_off, uint32_t n,
+                                               const epk_result* d_out, void* stream)
+{
+    return guarded([&] {
+        if (!pl || !d_out || (n && (!d_seq_off || !d_out->n_place || !d_out->branch || !d_out->score || !d_out->lwr || !d_out->count)))
+        {
+            throw error(EPK_E_INVALID, "null argument");
+        }
+        if (d_out->distal || d_out->pendant) { throw error(EPK_E_INVALID, "distal/pendant must be NULL for device results"); }
+        const uint32_t n_nodes = pl->db->d.n_nodes;
+        const size_t row_bytes = global_acc_bytes(n_nodes);
+        if (n_nodes > EPK_NOALLOC_MAX_NODES || NOALLOC_COUNTER_BYTES + MAX_WARPS_PER_CTA * row_bytes > NOALLOC_SCRATCH_BYTES)
+        {
+            throw error(EPK_E_UNSUPPORTED, "epk_place_device_noalloc: a tree of " + std::to_string(n_nodes) + " nodes is beyond the "
+                                               + std::to_string(EPK_NOALLOC_MAX_NODES) + " nodes its static scratch ("
+                                               + std::to_string(NOALLOC_SCRATCH_BYTES >> 20) + " MiB) is sized for");
+        }
+        EPK_CUDA(cudaSetDevice(pl->db->device));
+        const cudaStream_t s = static_cast<cudaStream_t>(stream);
+        unsigned char* scratch = noalloc_scratch_of(pl->db->device);
+        if (n == 0) { return; }
+
+        // as many CTAs of 8 warps as there are rows for, one per SM at most
+        const size_t rows_that_fit = (NOALLOC_SCRATCH_BYTES - NOALLOC_COUNTER_BYTES) / row_bytes;
+        const unsigned grid = static_cast<unsigned>(std::min<uint64_t>(
+            std::min<uint64_t>(pl->n_sms, rows_that_fit / MAX_WARPS_PER_CTA), (static_cast<uint64_t>(n) + MAX_WARPS_PER_CTA - 1) / MAX_WARPS_PER_CTA));
+        // the array keeps what the last call left: the counters and the rows of this launch start at zero
+        EPK_CUDA(cudaMemsetAsync(scratch, 0, NOALLOC_COUNTER_BYTES + static_cast<size_t>(grid) * MAX_WARPS_PER_CTA * row_bytes, s));
+
+        place_params p{};
+        p.db = pl->db->d;
+        p.seq = d_seq;
+        p.seq_off = d_seq_off;
+        p.n = n;
+        p.keep_at_most = pl->keep_at_most;
+        p.prefetch = pl->prefetch;
+        p.keep_factor = pl->keep_factor;
+        p.n_place = d_out->n_place;
+        p.branch = d_out->branch;
+        p.score = d_out->score;
+        p.lwr = d_out->lwr;
+        p.count = d_out->count;
+        p.letters = pl->db->letters.get();
+        p.fake_order = pl->fake_order.get();
+        p.class_reads = nullptr; // (not counted: every launch walks the batch and takes the queries of its class)
+        p.totals = nullptr;      // (the placer's running counters are not touched: epk_placer_counters does not see this call)
+        p.trace = nullptr;
+        p.team = 1;
+        p.acc_scratch = scratch + NOALLOC_COUNTER_BYTES;
+        {
+            const cudaError_t stale = cudaGetLastError();
+            if (stale != cudaSuccess) { throw error(EPK_E_CUDA, std::string("stale CUDA error before launch: ") + cudaGetErrorString(stale)); }
+        }
+        // one launch per width class of the hit counts, back to back on the stream: the rows hold 32-bit counts, so every
+        // class goes through the same instantiation; each launch leaves its rows zeroed for the next
+        for (int c = 0; c < N_CLASSES; ++c)
+        {
+            p.cls = static_cast<uint32_t>(c);
+            p.counters = reinterpret_cast<unsigned long long*>(scratch) + c * CTR_COUNT;
+            pick_global_kernel(*pl)<<<grid, MAX_WARPS_PER_CTA * 32, CTA_SMEM_FIXED + MAX_WARPS_PER_CTA * GLOBAL_WARP_SMEM, s>>>(p);
+            EPK_CUDA(cudaGetLastError());
+        }
     });
 }
 

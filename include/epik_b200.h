@@ -166,6 +166,25 @@ epk_status epk_place_many(epk_placer* const* placers, uint32_t n_placers, const 
 epk_status epk_place_device(epk_placer* placer, const char* d_seq, const uint64_t* d_seq_off, uint32_t n,
                             const epk_result* d_out, void* stream);
 
+/* epk_place_device for callers that cannot have memory allocated under them (CUDA graph capture, tight serving loops,
+ * harnesses that forbid it). NO COUNTERPART IN THE REFERENCE. The call
+ * allocates nothing - no cudaMalloc / cudaFree, no allocating library routine: it runs the accumulators-in-HBM form
+ * of the placement kernel with its scratch (launch counters + one accumulator row per warp) in a static device array of
+ * EPK_NOALLOC_SCRATCH_BYTES that every GPU which loads the library holds until exit. Same arguments and results as
+ * epk_place_device (DEVICE pointers, asynchronous on `stream`); scores, branches and counts are the same to the bit,
+ * weight ratios to 1e-9 (the sweep adds the likelihood mass in another order). Limits and rules:
+ *   - trees of more than EPK_NOALLOC_MAX_NODES nodes are refused with EPK_E_UNSUPPORTED;
+ *   - every call on a device shares the one array; the call clears what it uses on `stream` first, so calls in
+ *     sequence are independent, but calls that OVERLAP on a GPU (two streams, two placers, two threads) race;
+ *   - the work counters of the placer are not updated (epk_placer_counters does not see this call); rows of
+ *     sequences shorter than k - 1 letters come back with n_place = 0, no status reports them;
+ *   - the first call on a device resolves the array's device address (once per device; make it before capturing);
+ *   - several times slower per read than epk_place_device where that one keeps its accumulators in shared memory. */
+#define EPK_NOALLOC_SCRATCH_BYTES (32u << 20)
+#define EPK_NOALLOC_MAX_NODES 65536u
+epk_status epk_place_device_noalloc(epk_placer* placer, const char* d_seq, const uint64_t* d_seq_off, uint32_t n,
+                                    const epk_result* d_out, void* stream);
+
 /* group_by_sequence_content (place.cpp:73-81) for one batch: group_rep[i] = index of the first
  * record of [0, n) with the same sequence. HOST buffers. */
 epk_status epk_group_batch(const char* seq, const uint64_t* seq_off, uint32_t n, uint32_t* group_rep);
