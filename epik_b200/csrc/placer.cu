@@ -111,6 +111,7 @@ struct epk_placer
     uint32_t prefetch = 0;   // prefetch_mode of the gathers
     uint32_t* trace = nullptr; // epk_placer_set_trace: DEVICE array of the caller, [4 n] of the next epk_place_device calls
     uint32_t chunk_reads = 0;
+    bool auto_chunk = true;  // chunk_reads was not given: small passes are cut finer so that their copies overlap too
     int n_sms = 0;
     uint32_t warps_per_cta[N_CLASSES] = { 0, 0, 0 }; // 0: the accumulators of this class do not fit shared memory
     size_t smem_bytes[N_CLASSES] = { 0, 0, 0 };
@@ -402,6 +403,7 @@ extern "C" epk_status epk_placer_create(const epk_db* db, uint64_t keep_at_most,
         // bits 4-7 of the variant word: 0 = this build's default, otherwise prefetch_mode + 1 (kernel experiments)
         pl->prefetch = opts && (opts->variant >> 4) ? ((opts->variant >> 4) & 0xFu) - 1u : PREFETCH_LINES;
         pl->chunk_reads = opts && opts->chunk_reads ? opts->chunk_reads : (1u << 18);
+        pl->auto_chunk = !(opts && opts->chunk_reads);
 
         int max_smem = 0;
         EPK_CUDA(cudaDeviceGetAttribute(&pl->n_sms, cudaDevAttrMultiProcessorCount, db->device));
@@ -703,9 +705,18 @@ extern "C" epk_status epk_place(epk_placer* pl, const char* seq, const uint64_t*
         int turn = 0;
         while (first < n)
         {
-            // chunk = up to chunk_reads sequences and about max_chunk_bytes letters
-            uint32_t last = static_cast<uint32_t>(std::min<uint64_t>(n, static_cast<uint64_t>(first) + pl->chunk_reads));
-            while (last > first + 1 && seq_off[last] - seq_off[first] > max_chunk_bytes)
+            // chunk = up to chunk_reads sequences and about max_chunk_bytes letters; a pass of fewer than eight such chunks
+            // is cut into about eight (of 16 k reads or 32 MB at least) so that its copies overlap its launches too: one
+            // chunk of 100 k 1.5-kb reads spent as long copying as computing (C1p: 4.4 M reads/s end to end, 7.8 M resident)
+            uint32_t per_chunk = pl->chunk_reads;
+            size_t chunk_bytes = max_chunk_bytes;
+            if (pl->auto_chunk)
+            {
+                per_chunk = std::min<uint32_t>(per_chunk, std::max<uint32_t>(16384u, n / 8u));
+                chunk_bytes = std::min<size_t>(chunk_bytes, std::max<size_t>(32u << 20, (seq_off[n] - seq_off[0]) / 8));
+            }
+            uint32_t last = static_cast<uint32_t>(std::min<uint64_t>(n, static_cast<uint64_t>(first) + per_chunk));
+            while (last > first + 1 && seq_off[last] - seq_off[first] > chunk_bytes)
             {
                 last = first + (last - first) / 2;
             }
