@@ -1148,6 +1148,9 @@ __device__ __forceinline__ sweep_result sweep(const ACC acc, uint32_t np, uint32
 #ifndef EPK_SWEEP_NQ
 #define EPK_SWEEP_NQ 2
 #endif
+#ifndef EPK_WIDE_AHEAD
+#define EPK_WIDE_AHEAD 1 // kernel experiments: 0 = the 16-warp launch claims its queries one at a time
+#endif
 #ifndef EPK_SWEEP_P2
 #define EPK_SWEEP_P2 4
 #endif
@@ -2001,14 +2004,21 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
     // are asked for before this one's last gather (B): both are there when the sweep is over.
     // (Carrying more than that across the sweep - the next query's letters, its key-table slots for an L2 prefetch
     // of its lists - cost more in spilled registers than the latencies it hid: 28 instead of 38 M reads/s, gpurun r3g.)
+    // (In the 16-warp, 128-register launch of small trees too: 8.12 against 8.08 M reads/s on C1p, 75.0 against 74.4 M on C4; gpurun r4b.)
+    constexpr bool AHEAD = MAXW <= MAX_WARPS_PER_CTA || EPK_WIDE_AHEAD;
     uint32_t q_next = 0;
-    if (lane == 0) { q_next = static_cast<uint32_t>(atomicAdd(p.counters + CTR_CURSOR, 1ull)); }
+    if (AHEAD && lane == 0) { q_next = static_cast<uint32_t>(atomicAdd(p.counters + CTR_CURSOR, 1ull)); }
     q_next = __shfl_sync(FULL, q_next, 0);
     uint64_t next_s0 = 0, next_len = 0; // offsets of query q_next ...
     bool next_known = false;            // ... when they have been asked for
 
     while (true)
     {
+        if (!AHEAD)
+        {
+            if (lane == 0) { q_next = static_cast<uint32_t>(atomicAdd(p.counters + CTR_CURSOR, 1ull)); }
+            q_next = __shfl_sync(FULL, q_next, 0);
+        }
         const uint32_t q = q_next;
         if (q >= p.n)
         {
@@ -2021,9 +2031,9 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
             break;
         }
         uint32_t claim = 0; // A (read at B, or where this query is left early)
-        if (lane == 0) { claim = static_cast<uint32_t>(atomicAdd(p.counters + CTR_CURSOR, 1ull)); }
-        const uint64_t s0 = next_known ? next_s0 : p.seq_off[q];
-        const uint64_t len = next_known ? next_len : p.seq_off[q + 1] - s0;
+        if (AHEAD && lane == 0) { claim = static_cast<uint32_t>(atomicAdd(p.counters + CTR_CURSOR, 1ull)); }
+        const uint64_t s0 = AHEAD && next_known ? next_s0 : p.seq_off[q];
+        const uint64_t len = AHEAD && next_known ? next_len : p.seq_off[q + 1] - s0;
         next_known = false;
         if (len + 1 < k)
         {
@@ -2237,9 +2247,9 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
             }
         }
         // B: the next query's index is there; its offsets are asked for
-        q_next = __shfl_sync(FULL, claim, 0);
+        if (AHEAD) { q_next = __shfl_sync(FULL, claim, 0); }
         uint64_t off0 = 0, off1 = 0;
-        if (q_next < p.n)
+        if (AHEAD && q_next < p.n)
         {
             off0 = __ldg(p.seq_off + q_next);
             off1 = __ldg(p.seq_off + q_next + 1);
@@ -2254,7 +2264,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
             EPK_PHASE(3)
         }
         __syncwarp();
-        if (q_next < p.n)
+        if (AHEAD && q_next < p.n)
         {
             next_s0 = off0;
             next_len = off1 - off0;

@@ -109,6 +109,7 @@ struct epk_placer
     double keep_factor = 0.0;
     uint32_t variant = 0;
     uint32_t prefetch = 0;   // prefetch_mode of the gathers
+    bool prefetch_default = true; // not set through the variant word: lines, except in the 16-warp launch of small trees
     uint32_t* trace = nullptr; // epk_placer_set_trace: DEVICE array of the caller, [4 n] of the next epk_place_device calls
     uint32_t chunk_reads = 0;
     bool auto_chunk = true;  // chunk_reads was not given: small passes are cut finer so that their copies overlap too
@@ -285,6 +286,8 @@ namespace
                 const unsigned grid = static_cast<unsigned>(
                     std::min<uint64_t>(pl.n_sms, (static_cast<uint64_t>(n) + pl.sets_fused[c] - 1) / pl.sets_fused[c]));
                 p.team = pl.team[c];
+                // (prefetching a descriptor buffer's lines gains 2 % at 8 warps per SM and loses 1 - 4 % at 16: gpurun r4a)
+                p.prefetch = pl.prefetch_default && pl.wide[c] ? static_cast<uint32_t>(PREFETCH_NONE) : pl.prefetch;
                 pick_kernel(pl, c)<<<grid, pl.sets_fused[c] * pl.team[c] * 32, pl.smem_fused[c], stream>>>(p);
                 EPK_CUDA(cudaGetLastError());
                 ++pl.n_launches;
@@ -402,6 +405,7 @@ extern "C" epk_status epk_placer_create(const epk_db* db, uint64_t keep_at_most,
         pl->variant = opts ? opts->variant & 0xFu : 0;
         // bits 4-7 of the variant word: 0 = this build's default, otherwise prefetch_mode + 1 (kernel experiments)
         pl->prefetch = opts && (opts->variant >> 4) ? ((opts->variant >> 4) & 0xFu) - 1u : PREFETCH_LINES;
+        pl->prefetch_default = !(opts && (opts->variant >> 4));
         pl->chunk_reads = opts && opts->chunk_reads ? opts->chunk_reads : (1u << 18);
         pl->auto_chunk = !(opts && opts->chunk_reads);
 
