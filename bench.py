@@ -59,7 +59,7 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="C2", choices=["C2", "C3", "C4", "C1p", "C5r", "C5"])
-    ap.add_argument("--mode", default="replicated", choices=["replicated", "dbshard"],
+    ap.add_argument("--mode", default="replicated", choices=["replicated", "dbshard", "dbpool"],
                     help="replicated: queries sharded over the ranks, database in every HBM (default); "
                          "dbshard: database sharded by key over the ranks, every rank sees every query, partial rows "
                          "exchanged with an all-to-all (SURVEY.md 8e second row)")
@@ -537,6 +537,93 @@ def time_dbshard(args, workload, rank, world, local, dev, reads, steps, warmup, 
             "placed_last_pass": int(placed.item())}
 
 
+def time_dbpool(args, workload, devices, reads_per_gpu, steps, warmup):
+    """The database of `workload` POOLED over the HBM of `devices` (epk_db_pool: one process drives the GPUs, every GPU
+    places its own reads with the fused kernel and gathers each posting list from whichever HBM holds it, over NVLink).
+    Returns the record of the `dbpool` key: device-resident rate (one launch per device on its own stream, device
+    events, the slowest device counts) and the end-to-end rate through epk_place_many from pinned host buffers."""
+    import torch
+    from epik_b200 import dbshard, synth
+    from epik_b200.placer import PinnedArray, Placer
+    alphabet, k, n_leaves, p_occ, m, read_len = synth.CONFIGS[workload]
+    K, G, n = 7, len(devices), reads_per_gpu
+    flat = synth.make_config_gen2(workload) if workload in DEVICE_GENERATED else synth.make_config_db(workload)
+    t0 = time.perf_counter()
+    pooled = dbshard.PooledPlacer(flat, devices, keep_at_most=K)
+    build_s = time.perf_counter() - t0
+    info = pooled.dbs[0].info
+    h_seq = PinnedArray((G * n * read_len,), np.uint8)
+    h_off = PinnedArray((G * n + 1,), np.uint64)
+    make_reads_chunked(alphabet, G * n, read_len, 0, h_seq.array)
+    h_off.array[:] = np.arange(G * n + 1, dtype=np.uint64) * np.uint64(read_len)
+    local_off = torch.from_numpy((np.arange(n + 1, dtype=np.uint64) * np.uint64(read_len)).view(np.int64))
+    state = []
+    for g, dev_id in enumerate(devices):
+        dev = torch.device("cuda", dev_id)
+        d_seq = torch.from_numpy(h_seq.array[g * n * read_len:(g + 1) * n * read_len]).to(dev)
+        d_off = local_off.to(dev)
+        out = {"n_place": torch.zeros(n, dtype=torch.int32, device=dev), "branch": torch.zeros(n * K, dtype=torch.int32, device=dev),
+               "score": torch.zeros(n * K, dtype=torch.float32, device=dev), "lwr": torch.zeros(n * K, dtype=torch.float64, device=dev),
+               "count": torch.zeros(n * K, dtype=torch.int32, device=dev)}
+        state.append((dev, d_seq, d_off, out, torch.cuda.Stream(device=dev)))
+
+    def launch_all():
+        for g, (dev, d_seq, d_off, out, stream) in enumerate(state):
+            pooled.placers[g].place_device(d_seq, d_off, n, out, stream=stream)
+
+    def sync_all():
+        for dev, _, _, _, stream in state:
+            stream.synchronize()
+
+    for _ in range(warmup):
+        launch_all()
+    sync_all()
+    events = []
+    for dev, _, _, _, stream in state:
+        with torch.cuda.device(dev):
+            events.append((torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)))
+    for (e0, _), (dev, _, _, _, stream) in zip(events, state):
+        e0.record(stream)
+    for _ in range(steps):
+        launch_all()
+    for (_, e1), (dev, _, _, _, stream) in zip(events, state):
+        e1.record(stream)
+    sync_all()
+    secs = max(e0.elapsed_time(e1) for e0, e1 in events) / 1e3
+    placed = sum(int(out["n_place"].sum().item()) for _, _, _, out, _ in state)
+    entries = sum(p.counters()["n_entries"] for p in pooled.placers)
+    # end to end: one pass of G * n reads from pinned host memory through epk_place_many
+    out = pooled.placers[0].alloc_result(G * n, pinned=True, lengths=True)
+    pooled.place_packed(h_seq.array, h_off.array, out=out)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        pooled.place_packed(h_seq.array, h_off.array, out=out)
+    e2e_s = time.perf_counter() - t0
+    assert int(out["n_place"].sum()) == placed
+    rec = {"metric": METRIC, "value": G * n * steps / secs, "unit": UNIT, "n_gpus": G, "scaling": "weak",
+           "e2e": {"value": G * n * steps / e2e_s, "unit": UNIT, "api": "epk_place_many (C ABI): one process, %d placers, pinned host buffers" % G},
+           "workload": "%s: k=%d, %d branches, %.1f GB of postings pooled over %d GPUs (%.1f GB in each HBM), %d x %d-letter reads per GPU "
+                       "per step, each GPU places its own reads" % (workload, k, 2 * n_leaves - 1, info["n_entries_loaded"] * 8 / 1e9, G,
+                                                                    info["n_entries_loaded"] * 8 / 1e9 / G, n, read_len),
+           "ms_per_step": secs / steps * 1e3, "steps": steps, "build_s": build_s,
+           "nvlink_bytes_per_read": 8.0 * entries / (G * n) * (G - 1) / G,
+           "how": "epk_db_pool: shards mapped into one address range (CUDA VMM), a key table per GPU pointing into it, the fused "
+                  "kernel unchanged; results bit-identical to the unsharded database"}
+    pooled.close()
+    return rec
+
+
+def run_dbpool(args):
+    """--mode dbpool: ONE process (no torchrun), --gpus N devices."""
+    import torch
+    n_dev = min(args.gpus, torch.cuda.device_count())
+    rec = time_dbpool(args, args.workload if args.workload != "C2" or args.reads else "C5", list(range(n_dev)),
+                      args.reads or 1_000_000, args.steps, args.warmup)
+    rec.update({"mode": "dbpool", "steps": args.steps, "warmup": args.warmup, "higher_is_better": True, "vs_baseline": None,
+                "dtype": "f32", "data": "synthetic"})
+    emit(rec)
+
+
 def run_dbshard(args):
     """Database-sharded variant: rank r holds shard r of the keys, EVERY rank sees the whole read set of a step;
     value = reads of the step / time (strong scaling of the database, not of the queries)."""
@@ -644,6 +731,8 @@ def main():
         run_reference(args)
     elif args.mode == "dbshard":
         run_dbshard(args)
+    elif args.mode == "dbpool":
+        run_dbpool(args)
     else:
         run_ours(args)
 

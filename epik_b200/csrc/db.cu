@@ -630,7 +630,7 @@ extern "C" epk_status epk_db_get_info(const epk_db* db, epk_db_info* info)
         info->n_entries_loaded = db->n_entries_loaded;
         info->n_entries_total = db->n_entries_total;
         info->table_slots = db->table_slots;
-        info->device_bytes = db->direct.bytes() + db->hashed.bytes() + db->postings.bytes() + db->letters.bytes();
+        info->device_bytes = db->direct.bytes() + db->hashed.bytes() + db->postings.bytes() + db->letters.bytes() + db->pool_local_bytes;
     });
 }
 

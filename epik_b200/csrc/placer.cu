@@ -1010,7 +1010,7 @@ extern "C" epk_status epk_db_get_view(const epk_db* db, epk_db_view* out)
         if (!db || !out) { throw error(EPK_E_INVALID, "null argument"); }
         out->table = reinterpret_cast<uint64_t>(db->table_kind == TABLE_DIRECT ? static_cast<const void*>(db->direct.get())
                                                                                : static_cast<const void*>(db->hashed.get()));
-        out->postings = reinterpret_cast<uint64_t>(db->postings.get());
+        out->postings = reinterpret_cast<uint64_t>(db->pool ? static_cast<const void*>(db->d.postings) : static_cast<const void*>(db->postings.get()));
         out->hash_mask = db->d.hash_mask;
         out->hash_shift = db->d.hash_shift;
         out->table_kind = db->table_kind;

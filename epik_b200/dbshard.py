@@ -315,3 +315,33 @@ class ShardedPlacer:
         if len(pieces) == 1:
             return pieces[0], firsts[0], lasts[0]
         return {k: np.concatenate([p[k] for p in pieces]) for k in pieces[0]}, firsts, lasts
+
+
+class PooledPlacer:
+    """The database pooled over the HBM of `devices` (one process drives them; include/epik_b200.h "pooled database"):
+    shard g of len(devices) is built on devices[g], the shards are mapped into one address range every GPU reads, and a
+    pass is cut over one placer per device (epk_place_many) - each places its slice with the fused kernel, gathering
+    every posting list from whichever HBM holds it. Results are the unsharded database's to the bit."""
+
+    def __init__(self, flat, devices, keep_at_most: int = 7, keep_factor: float = 0.01, **load):
+        self.devices = list(devices)
+        G = len(self.devices)
+        shards = [_shard_database(flat, dev, (g, G), load) for g, dev in enumerate(self.devices)]
+        try:
+            self.dbs = Database.pool(shards)
+        finally:
+            for s in shards:
+                s.close()
+        self.placers = [Placer(db, keep_at_most, keep_factor) for db in self.dbs]
+        self.keep_at_most = keep_at_most
+
+    def place_packed(self, data, offsets, out=None):
+        return Placer.place_packed_many(self.placers, data, offsets, out=out)
+
+    def close(self):
+        for p in getattr(self, "placers", []):
+            p.close() if hasattr(p, "close") else None
+        self.placers = []
+        for d in getattr(self, "dbs", []):
+            d.close()
+        self.dbs = []

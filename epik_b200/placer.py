@@ -179,6 +179,31 @@ def _db_synthetic(cls, gen, mu: float | None = None, omega: float | None = None,
 Database.synthetic = classmethod(_db_synthetic)
 
 
+def _db_pool(cls, shards):
+    """epk_db_pool: shards[g] = shard g of len(shards) (Database(..., shard=(g, G)) or Database.synthetic, one per GPU of
+    this process) -> one Database per shard's device over the pooled postings, each a WHOLE database to a placer.
+    The shards are copied: close them afterwards."""
+    handles = (C.c_void_p * len(shards))(*[s.handle for s in shards])
+    out = (C.c_void_p * len(shards))()
+    capi.check(capi.lib().epk_db_pool(C.cast(handles, C.c_void_p), len(shards), C.cast(out, C.c_void_p)))
+    made = []
+    for g, s in enumerate(shards):
+        db = cls.__new__(cls)
+        db.flat = getattr(s, "flat", None)
+        db.gen = getattr(s, "gen", None)
+        db.handle = C.c_void_p(out[g])
+        db.device = s.device
+        db.shard = None
+        info = capi.DbInfo()
+        capi.check(capi.lib().epk_db_get_info(db.handle, C.byref(info)))
+        db.info = {name: getattr(info, name) for name, _ in capi.DbInfo._fields_}
+        made.append(db)
+    return made
+
+
+Database.pool = classmethod(_db_pool)
+
+
 def _db_view(self) -> "capi.DbView":
     """epk_db_get_view: the device addresses of this database's key table and postings."""
     v = capi.DbView()

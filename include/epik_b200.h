@@ -273,6 +273,20 @@ epk_status epk_place_finalize_device(epk_placer* placer, const void* d_rows, uin
                                      uint64_t shard_stride_bytes, const uint64_t* d_seq_off, uint32_t n,
                                      const epk_result* d_out, void* stream);
 
+/* ---- pooled database: the shards read in place over NVLink ---------------------------------------------
+ *
+ * The other way to hold a database that exceeds one HBM, for ONE process that drives the GPUs (as the reference is
+ * one process, main.cpp:332-366): shards[g] = shard g of n_shards (epk_db_create_shard / epk_db_create_synthetic,
+ * one per GPU; several on one GPU work too) are mapped one after the other into one range of virtual addresses that
+ * every GPU of the process reads (CUDA virtual memory management; the GPUs must be peers), and out[g] is a database
+ * on shards[g]'s device whose key table points into that range. To a placer out[g] is a WHOLE database: every entry
+ * point above takes it, the fused kernel gathers each posting list from whichever HBM holds it (1 / n_shards local,
+ * the rest over NVLink), and the results are those of the unsharded database to the bit. Place with one placer per
+ * out[g] and epk_place_many. The shards are copied: destroy them once the pool exists (until then each GPU holds its
+ * shard twice). Needs the direct-address key table (alphabet bits x k <= 26) and at most 2^33 postings in total.
+ * The reference has nothing like it (one phylo_kmer_db in one address space, main.cpp:277). */
+epk_status epk_db_pool(epk_db* const* shards, uint32_t n_shards, epk_db** out /* [n_shards] */);
+
 /* ---- windows with one ambiguous letter in database-sharded mode -----------------------------------------
  *
  * place.cpp:373-415 lets the FIRST ambiguous key (window order, then resolution order) that names a branch

@@ -233,6 +233,40 @@ def test_both_row_formats_give_the_same_placements(built, monkeypatch, shards):
             assert np.array_equal(got["dense"][name], got["compact"][name]), (leaves, name)
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape", ["dna-one-warp", "dna-range-teams", "dna-filtered", "dna-generated"])
+def test_pooled_database_gives_the_unsharded_results_bit_for_bit(built, shape):
+    """epk_db_pool: the shards mapped into one address range, every GPU's key table pointing into it, the fused kernel
+    unchanged on top - so nothing is re-associated and every bit of the unsharded database's placements is there,
+    ambiguous reads, load filter and range teams included. One GPU: three shards on it; more GPUs: one shard each."""
+    from epik_b200.placer import Database, Placer
+    n_dev = min(torch.cuda.device_count(), 4)
+    devices = list(range(n_dev)) if n_dev > 1 else [0, 0, 0]
+    load = {}
+    if shape == "dna-generated":
+        flat = synth.Gen2(0, 9, 600, 0.6, 16.0, seed=61)
+        whole = Database.synthetic(flat)
+    else:
+        leaves = 5000 if shape == "dna-range-teams" else 400
+        flat = synth.make_db(0, 8, leaves, 0.7, 24.0, seed=61)
+        if shape == "dna-filtered":
+            load = dict(mu=0.6, omega=1.2)
+        whole = Database(flat, **load)
+    data, off = synth.make_reads(0, 4000, 150, seed=62, amb_rate=0.01)
+    want = Placer(whole).place_packed(data, off)
+    pooled = dbshard.PooledPlacer(flat, devices, **load)
+    assert pooled.dbs[0].info["n_entries_loaded"] == whole.info["n_entries_loaded"]
+    assert pooled.dbs[0].info["n_keys_loaded"] == whole.info["n_keys_loaded"]
+    for turn in range(2):
+        got = pooled.place_packed(data, off)
+        for name in ("n_place", "branch", "score", "lwr", "count", "distal", "pendant"):
+            assert np.array_equal(got[name], want[name]), (shape, turn, name)
+    # every pooled database is a whole database on its own, too
+    alone = Placer(pooled.dbs[-1]).place_packed(data, off)
+    assert np.array_equal(alone["score"], want["score"]) and np.array_equal(alone["branch"], want["branch"])
+    pooled.close()
+
+
 def _nccl_worker(rank, world, port, out_dir, transport):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)

@@ -6,5 +6,5 @@ NAME=$1; shift
 cd "$(dirname "$0")/.."
 mkdir -p tools/_bin
 nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC -shared "$@" \
-  -o tools/_bin/libepik_b200_$NAME.so epik_b200/csrc/db.cu epik_b200/csrc/placer.cu epik_b200/csrc/microbench.cu
+  -o tools/_bin/libepik_b200_$NAME.so epik_b200/csrc/db.cu epik_b200/csrc/placer.cu epik_b200/csrc/microbench.cu epik_b200/csrc/pool.cu
 echo built tools/_bin/libepik_b200_$NAME.so
