@@ -71,6 +71,8 @@ def parse_args():
     ap.add_argument("--variant", type=int, default=0)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-dbshard", action="store_true", help="N > 1: skip the database-sharded leg (the `dbshard` key)")
+    ap.add_argument("--no-dbpool", action="store_true", help="N > 1: skip the pooled-database leg (the `dbpool` key)")
+    ap.add_argument("--dbpool-reads", type=int, default=1000000, help="reads per GPU per step of the pooled-database leg")
     ap.add_argument("--dbshard-reads", type=int, default=262144, help="reads per step of the database-sharded leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -465,6 +467,24 @@ def run_ours(args):
         dbshard_leg = time_dbshard(args, "C5", rank, world, local, dev, reads=args.dbshard_reads, steps=max(2, min(args.steps, 3)),
                                    warmup=1, transport=args.transport)
 
+    # ---- N > 1, second form of "the database does not fit one GPU": pooled over the N HBMs, read over NVLink. One
+    # process drives the GPUs (rank 0; the other ranks wait on the store, not in an NCCL kernel that would sit on their SMs)
+    dbpool_leg = None
+    if world > 1 and not args.no_dbpool:
+        store = dist.distributed_c10d._get_default_store()
+        torch.cuda.empty_cache()
+        barrier()
+        if rank == 0:
+            try:
+                dbpool_leg = time_dbpool(args, "C5", list(range(world)), args.dbpool_reads, steps=max(2, min(args.steps, 3)), warmup=1)
+            except Exception as exc:  # (the line is still worth printing)
+                dbpool_leg = {"error": "%s: %s" % (type(exc).__name__, exc)}
+            torch.cuda.set_device(local)
+            store.set("epk_dbpool_done", "1")
+        else:
+            store.wait(["epk_dbpool_done"])
+        barrier()
+
     total_reads = sum_over_ranks(float(n))
     if rank == 0:
         line = {
@@ -478,6 +498,8 @@ def run_ours(args):
         }
         if dbshard_leg is not None:
             line["dbshard"] = dbshard_leg
+        if dbpool_leg is not None:
+            line["dbpool"] = dbpool_leg
         emit(line)
     if world > 1:
         dist.destroy_process_group()
@@ -549,7 +571,7 @@ def time_dbpool(args, workload, devices, reads_per_gpu, steps, warmup):
     K, G, n = 7, len(devices), reads_per_gpu
     flat = synth.make_config_gen2(workload) if workload in DEVICE_GENERATED else synth.make_config_db(workload)
     t0 = time.perf_counter()
-    pooled = dbshard.PooledPlacer(flat, devices, keep_at_most=K)
+    pooled = dbshard.PooledPlacer(flat, devices, keep_at_most=K, variant=args.variant)
     build_s = time.perf_counter() - t0
     info = pooled.dbs[0].info
     h_seq = PinnedArray((G * n * read_len,), np.uint8)

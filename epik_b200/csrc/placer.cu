@@ -406,6 +406,10 @@ extern "C" epk_status epk_placer_create(const epk_db* db, uint64_t keep_at_most,
         // bits 4-7 of the variant word: 0 = this build's default, otherwise prefetch_mode + 1 (kernel experiments)
         pl->prefetch = opts && (opts->variant >> 4) ? ((opts->variant >> 4) & 0xFu) - 1u : PREFETCH_LINES;
         pl->prefetch_default = !(opts && (opts->variant >> 4));
+        // A pooled database (pool.cu) is read over NVLink for the most part, and prefetch.global.L2 of a PEER address is
+        // pathological: 87 k instead of 7.4 M reads/s on two GPUs (gpurun r4d / r4e; peer lines are not kept in the
+        // local L2 - the instruction seems to serialise on the link). Never there, whatever the variant word says.
+        if (db->pool) { pl->prefetch = PREFETCH_NONE; }
         pl->chunk_reads = opts && opts->chunk_reads ? opts->chunk_reads : (1u << 18);
         pl->auto_chunk = !(opts && opts->chunk_reads);
 

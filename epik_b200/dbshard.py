@@ -323,7 +323,7 @@ class PooledPlacer:
     pass is cut over one placer per device (epk_place_many) - each places its slice with the fused kernel, gathering
     every posting list from whichever HBM holds it. Results are the unsharded database's to the bit."""
 
-    def __init__(self, flat, devices, keep_at_most: int = 7, keep_factor: float = 0.01, **load):
+    def __init__(self, flat, devices, keep_at_most: int = 7, keep_factor: float = 0.01, variant: int = 0, **load):
         self.devices = list(devices)
         G = len(self.devices)
         shards = [_shard_database(flat, dev, (g, G), load) for g, dev in enumerate(self.devices)]
@@ -332,7 +332,7 @@ class PooledPlacer:
         finally:
             for s in shards:
                 s.close()
-        self.placers = [Placer(db, keep_at_most, keep_factor) for db in self.dbs]
+        self.placers = [Placer(db, keep_at_most, keep_factor, variant=variant) for db in self.dbs]
         self.keep_at_most = keep_at_most
 
     def place_packed(self, data, offsets, out=None):
