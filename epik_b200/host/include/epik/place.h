@@ -10,6 +10,7 @@
 #include <cstring>
 #include <exception>
 #include <limits>
+#include <memory>
 #include <mutex>
 #include <stdexcept>
 #include <string>
@@ -155,6 +156,42 @@ namespace epik
             impl::check(epk_db_create(&desc, filter ? &f : nullptr, device, &_handle));
             impl::check(epk_db_get_info(_handle, &_info));
         }
+        /// Shard `shard_index` of `shard_count` of the keys (database-sharded forms; epk_db_create_shard).
+        device_database(const flat_db& db, const load_filter* filter, int device, uint32_t shard_index, uint32_t shard_count)
+        {
+            const epk_db_desc desc = db.describe();
+            epk_load_filter f{};
+            if (filter)
+            {
+                f.mu = filter->mu;
+                f.omega = filter->omega;
+                f.max_entries = filter->max_entries;
+            }
+            impl::check(epk_db_create_shard(&desc, filter ? &f : nullptr, device, shard_index, shard_count, &_handle));
+            impl::check(epk_db_get_info(_handle, &_info));
+        }
+
+        /// The database POOLED over the memory of `devices` (epk_db_pool): shard g is built on devices[g], the shards are
+        /// mapped into one address range every GPU reads, and each returned database - a whole database to a placer -
+        /// sits on one of the devices. For databases that exceed one GPU; results are the unsharded database's.
+        static std::vector<std::unique_ptr<device_database>> pooled(const flat_db& db, const load_filter* filter,
+                                                                    const std::vector<int>& devices)
+        {
+            const uint32_t G = static_cast<uint32_t>(devices.size());
+            std::vector<std::unique_ptr<device_database>> shards(G);
+            impl::parallel_for(G, G, [&](size_t g) {
+                shards[g].reset(new device_database(db, filter, devices[g], static_cast<uint32_t>(g), G));
+            });
+            std::vector<epk_db*> in(G), out(G, nullptr);
+            for (uint32_t g = 0; g < G; ++g) { in[g] = shards[g]->_handle; }
+            impl::check(epk_db_pool(in.data(), G, out.data()));
+            std::vector<std::unique_ptr<device_database>> made(G);
+            for (uint32_t g = 0; g < G; ++g)
+            {
+                made[g].reset(new device_database(out[g]));
+            }
+            return made; // (the shards go out of scope here: the pool holds copies)
+        }
         device_database(const device_database&) = delete;
         device_database& operator=(const device_database&) = delete;
         ~device_database() noexcept { epk_db_destroy(_handle); }
@@ -169,6 +206,7 @@ namespace epik
         const epk_db_info& info() const noexcept { return _info; }
 
     private:
+        explicit device_database(epk_db* handle) : _handle(handle) { impl::check(epk_db_get_info(_handle, &_info)); }
         epk_db* _handle = nullptr;
         epk_db_info _info{};
     };

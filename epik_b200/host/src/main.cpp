@@ -131,6 +131,11 @@ namespace
                     help = true;
                     continue;
                 }
+                if (name == "pool-database" && !has_value) // (the one flag without an argument)
+                {
+                    values[name] = "1";
+                    continue;
+                }
                 if (!has_value)
                 {
                     if (i + 1 >= argc) { throw std::runtime_error("Option '" + name + "' is missing an argument"); }
@@ -140,6 +145,7 @@ namespace
             }
         }
         bool count(const std::string& name) const { return values.count(name) != 0; }
+        bool flag(const std::string& name) const { return count(name) && values.at(name) != "0"; }
         std::string get(const std::string& name, const std::string& fallback = "") const
         {
             const auto it = values.find(name);
@@ -165,6 +171,8 @@ namespace
         "      --keep-factor arg   Minimum LWR to report (default: 0.01)\n"
         "      --device arg        CUDA device (default: 0)\n"
         "      --devices arg       Number of CUDA devices to place on, or 'all' (default: 1)\n"
+        "      --pool-database     With --devices: the database is split over the devices' memory and\n"
+        "                          read in place over NVLink instead of being replicated\n"
         "      --device-batches arg  Batches placed per device pass (default: 128)\n"
         "  -h, --help              Print usage\n";
 }
@@ -229,9 +237,20 @@ int main(int argc, char** argv)
                                                       : std::max<size_t>(1, std::stoull(devices_arg));
         // the database is replicated: every GPU gets the filtered, flattened copy (uploaded concurrently)
         std::vector<std::unique_ptr<epik::device_database>> replicas(n_devices);
-        epik::impl::parallel_for(n_devices, n_devices, [&](size_t g) {
-            replicas[g] = std::make_unique<epik::device_database>(flat, &filter, n_devices == 1 ? device : static_cast<int>(g));
-        });
+        if (opts.flag("pool-database") && n_devices > 1)
+        {
+            // a database larger than one GPU: an n-th of it in each HBM, every GPU reads all of it (epk_db_pool)
+            std::vector<int> ids(n_devices);
+            const int present = std::max(1, epk_device_count());
+            for (size_t g = 0; g < n_devices; ++g) { ids[g] = static_cast<int>(g) % present; } // (more shards than GPUs: testing)
+            replicas = epik::device_database::pooled(flat, &filter, ids);
+        }
+        else
+        {
+            epik::impl::parallel_for(n_devices, n_devices, [&](size_t g) {
+                replicas[g] = std::make_unique<epik::device_database>(flat, &filter, n_devices == 1 ? device : static_cast<int>(g));
+            });
+        }
         const epik::device_database& db = *replicas[0];
 
         std::cout << "Database parameters:" << std::endl

@@ -169,6 +169,18 @@ def test_driver_end_to_end(built, tmp_path, states):
     # the duplicates: reads 3, 10, 11 share a record (same batch), read 400 has its own
     groups = [sorted(name_to_index[n] for n, _ in rec["nm"]) for rec in jp["placements"]]
     assert [3, 10, 11] in groups and [400] in groups
+    if not aa:
+        # the same run with the database POOLED over three shards (--devices 3 --pool-database; on a box with fewer GPUs
+        # the shards share them) and with it replicated on every GPU present: the jplace body must not change by a byte
+        import torch
+        body = open(str(tmp_path / "placements_q.fasta.jplace"), "rb").read().split(b'"tree"', 1)[1]
+        variants = [["--devices", "3", "--pool-database"]]
+        if torch.cuda.device_count() > 1:
+            variants.append(["--devices", "all"])
+        for extra in variants:
+            run = subprocess.run(argv[:-1] + extra + [q_path], capture_output=True, text=True)
+            assert run.returncode == 0, run.stderr
+            assert open(str(tmp_path / "placements_q.fasta.jplace"), "rb").read().split(b'"tree"', 1)[1] == body, extra
 
 
 @pytest.mark.gpu
