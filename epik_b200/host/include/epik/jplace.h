@@ -21,6 +21,7 @@
 #include <vector>
 
 #include <fcntl.h>
+#include <sys/mman.h>
 #include <unistd.h>
 
 #include <epik/place.h>
@@ -317,12 +318,29 @@ namespace epik::io
                 total_records += n_records[b];
                 offset[b + 1] = offset[b] + texts[b].size();
             }
-            const int fd = ::open(_filename.c_str(), O_WRONLY);
+            const int fd = ::open(_filename.c_str(), O_RDWR);
             if (fd < 0) { throw std::runtime_error("Could not open file " + _filename); }
             const size_t base = _file_bytes;
+            // Through a shared mapping of the file's new tail where the file system allows it: concurrent pwrites to ONE
+            // file take turns on its inode lock (3 GB/s with 16 threads on tmpfs - a third of a device pass's time went
+            // there), page faults of a mapping do not.
+            bool mapped = false;
+            if (offset.back() != 0 && ::ftruncate(fd, static_cast<off_t>(base + offset.back())) == 0)
+            {
+                const size_t page = static_cast<size_t>(::sysconf(_SC_PAGESIZE));
+                const size_t map_from = base / page * page, lead = base - map_from;
+                void* m = ::mmap(nullptr, lead + offset.back(), PROT_READ | PROT_WRITE, MAP_SHARED, fd, static_cast<off_t>(map_from));
+                if (m != MAP_FAILED)
+                {
+                    char* to = static_cast<char*>(m) + lead;
+                    impl::parallel_for(texts.size(), threads, [&](size_t b) { std::memcpy(to + offset[b], texts[b].data(), texts[b].size()); });
+                    ::munmap(m, lead + offset.back());
+                    mapped = true;
+                }
+            }
             try
             {
-                impl::parallel_for(texts.size(), threads, [&](size_t b) {
+                impl::parallel_for(mapped ? 0 : texts.size(), threads, [&](size_t b) {
                     size_t done = 0;
                     while (done < texts[b].size())
                     {

@@ -285,12 +285,15 @@ int main(int argc, char** argv)
             records_t records;
             std::vector<epik::impl::placed_collection> placed;
         };
-        std::future<void> writing;
+        double stage_ms[5] = { 0, 0, 0, 0, 0 }; // waited for the reader, placing, waited for the writer | inside the writer: text, append
+        std::future<void> writing, appending; // (appending is only touched by one writing task at a time, and by main after it)
         std::future<records_t> reading = std::async(std::launch::async, [&reader] { return reader.next_batch(); });
         while (true)
         {
             auto pass = std::make_shared<pass_t>();
+            const auto t_read0 = std::chrono::steady_clock::now();
             pass->records = reading.get();
+            stage_ms[0] += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_read0).count();
             if (pass->records.empty()) { break; }
             reading = std::async(std::launch::async, [&reader] { return reader.next_batch(); }); // parsed while this pass is placed
 
@@ -305,17 +308,31 @@ int main(int argc, char** argv)
             num_iterations += pass->placed.size();
             num_seq_placed += pass->records.size();
 
+            stage_ms[1] += std::chrono::duration<double, std::milli>(end_batch - begin_batch).count();
+            const auto t_write0 = std::chrono::steady_clock::now();
             if (writing.valid()) { writing.get(); } // passes are appended in order
-            writing = std::async(std::launch::async, [pass, &jplace, num_threads] {
-                std::vector<std::string> text(pass->placed.size());
+            stage_ms[2] += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_write0).count();
+            // the writer has two stages of its own: the text of a pass is produced while the text of the pass before it
+            // is being appended to the file (appends stay in order)
+            writing = std::async(std::launch::async, [pass, &jplace, num_threads, &stage_ms, &appending] {
+                const auto t0 = std::chrono::steady_clock::now();
+                auto text = std::make_shared<std::vector<std::string>>(pass->placed.size());
                 epik::impl::parallel_for(pass->placed.size(), num_threads,
-                                         [&](size_t b) { text[b] = epik::io::jplace_writer::format(pass->placed[b]); });
-                std::vector<size_t> n_records(pass->placed.size());
-                for (size_t b = 0; b < pass->placed.size(); ++b) { n_records[b] = pass->placed[b].placed_seqs.size(); }
-                jplace.append_many(text, n_records, num_threads);
+                                         [&](size_t b) { (*text)[b] = epik::io::jplace_writer::format(pass->placed[b]); });
+                auto n_records = std::make_shared<std::vector<size_t>>(pass->placed.size());
+                for (size_t b = 0; b < pass->placed.size(); ++b) { (*n_records)[b] = pass->placed[b].placed_seqs.size(); }
+                pass->placed.clear();
+                stage_ms[3] += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+                if (appending.valid()) { appending.get(); }
+                appending = std::async(std::launch::async, [text, n_records, &jplace, num_threads, &stage_ms] {
+                    const auto t1 = std::chrono::steady_clock::now();
+                    jplace.append_many(*text, *n_records, num_threads);
+                    stage_ms[4] += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t1).count();
+                });
             });
         }
         if (writing.valid()) { writing.get(); }
+        if (appending.valid()) { appending.get(); }
         jplace.end();
         if (num_iterations) { average_speed /= static_cast<double>(num_iterations); }
 
@@ -324,6 +341,11 @@ int main(int argc, char** argv)
         std::cout << "Output: " << jplace_filename << std::endl;
         const auto placement_time = std::chrono::duration_cast<std::chrono::milliseconds>(std::chrono::steady_clock::now() - begin).count();
         std::cout << "Placement time: " << placement_time / 1000 << "s (" << placement_time << " ms)" << std::endl;
+        if (std::getenv("EPK_DRIVER_TIMING"))
+        {
+            std::cerr << "stages (ms): waited for the reader " << stage_ms[0] << ", placing " << stage_ms[1] << ", waited for the writer "
+                      << stage_ms[2] << "; inside the writer: text " << stage_ms[3] << ", append " << stage_ms[4] << std::endl;
+        }
         std::cout << "Done." << '\n' << std::flush;
     }
     catch (const std::exception& error)

@@ -31,6 +31,7 @@ def main():
     ap.add_argument("--out", default="")
     ap.add_argument("--device-batches", type=int, default=128)
     ap.add_argument("--devices", default="1", help="--devices of the driver: GPUs behind the one process, or 'all'")
+    ap.add_argument("--tmpdir", default=None, help="where the FASTA, the database file and the jplace go (e.g. /dev/shm: no file system in the way)")
     ap.add_argument("--keep-jplace", default="", help="copy the jplace here (to compare runs byte for byte)")
     ap.add_argument("--jobs", type=int, default=len(os.sched_getaffinity(0)), help="-j of the driver: host threads")
     args = ap.parse_args()
@@ -40,7 +41,7 @@ def main():
     g.build_host()
     alphabet, k, n_leaves, p_occ, m, read_len = synth.CONFIGS[args.workload]
     flat = synth.make_config_db(args.workload)
-    tmp = tempfile.mkdtemp(prefix="epik_cli_")
+    tmp = tempfile.mkdtemp(prefix="epik_cli_", dir=args.tmpdir)
     db_path, q_path = os.path.join(tmp, "db.epkdb"), os.path.join(tmp, "q.fasta")
     flatdb.save_epkdb(flat, db_path, synth.tree_newick(flat.branch_length, flat.meta["parent"]))
     # FASTA: one header line + one sequence line per read, written in blocks
@@ -61,8 +62,9 @@ def main():
     argv = [exe, "-d", db_path, "-q", q_path, "-j", str(args.jobs), "--omega", "1.5", "--mu", "1.0", "-o", tmp,
             "--device-batches", str(args.device_batches), "--devices", args.devices, q_path]
     t0 = time.perf_counter()
-    run = subprocess.run(argv, capture_output=True, text=True)
+    run = subprocess.run(argv, capture_output=True, text=True, env=dict(os.environ, EPK_DRIVER_TIMING="1"))
     wall = time.perf_counter() - t0
+    stages = [l for l in run.stderr.split("\n") if l.startswith("stages")]
     if run.returncode != 0:
         raise SystemExit("driver failed: " + run.stderr[-2000:])
     ms = int(re.search(r"Placement time: \d+s \((\d+) ms\)", run.stdout).group(1))
@@ -70,11 +72,11 @@ def main():
     jplace = os.path.join(tmp, "placements_q.fasta.jplace")
     line = {
         "what": "bin/epik/%s: FASTA file -> placements -> jplace file" % os.path.basename(exe),
-        "workload": args.workload, "reads": args.reads, "read_len": read_len, "jobs": args.jobs, "devices": args.devices,
+        "workload": args.workload, "reads": args.reads, "read_len": read_len, "jobs": args.jobs, "devices": args.devices, "tmpdir": args.tmpdir or tempfile.gettempdir(),
         "placement_time_ms": ms, "reads_per_s_file_to_file": args.reads / (ms / 1e3),
         "driver_average_speed": speed, "process_wall_s": wall,
         "fasta_bytes": os.path.getsize(q_path), "jplace_bytes": os.path.getsize(jplace),
-        "db_file_bytes": os.path.getsize(db_path),
+        "db_file_bytes": os.path.getsize(db_path), "driver_stages": stages[0] if stages else None,
     }
     import hashlib
     h = hashlib.sha256()
