@@ -24,7 +24,8 @@ SYMBOLS = [
     "epk_place_finalize_device", "epk_gather_ceiling_device",
     "epk_device_alloc", "epk_device_free", "epk_ipc_export", "epk_ipc_import", "epk_ipc_close",
     "epk_gather_microbench", "epk_placer_set_trace", "epk_trace_term",
-    "epk_db_get_view", "epk_placer_set_shard_views", "epk_place_finalize_seq_device", "epk_db_create_synthetic", "epk_place_many", "epk_group_batches", "epk_place_device_noalloc", "epk_db_pool",
+    "epk_db_get_view", "epk_placer_set_shard_views", "epk_place_finalize_seq_device", "epk_db_create_synthetic", "epk_place_many", "epk_group_batches", "epk_place_device_noalloc", "epk_db_pool", "epk_db_pool_share", "epk_db_pool_join",
+    "epk_db_get_score_range", "epk_db_pool_set_score_range",
 ]
 
 
@@ -168,6 +169,15 @@ def lib():
                                           C.POINTER(C.c_void_p)]
     l.epk_db_pool.restype = C.c_int
     l.epk_db_pool.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p]
+    l.epk_db_pool_share.restype = C.c_int
+    l.epk_db_pool_share.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_uint64), C.c_char_p]
+    l.epk_db_pool_join.restype = C.c_int
+    l.epk_db_pool_join.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_char_p, C.POINTER(C.c_void_p)]
+    l.epk_db_get_score_range.restype = C.c_int
+    l.epk_db_get_score_range.argtypes = [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(C.c_uint32),
+                                         C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+    l.epk_db_pool_set_score_range.restype = C.c_int
+    l.epk_db_pool_set_score_range.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_uint32, C.c_uint64, C.c_uint64]
     l.epk_db_get_view.restype = C.c_int
     l.epk_db_get_view.argtypes = [C.c_void_p, C.POINTER(DbView)]
     l.epk_placer_set_shard_views.restype = C.c_int

@@ -22,6 +22,7 @@ struct epk_db
     uint64_t n_entries_total = 0, n_entries_loaded = 0, n_keys_loaded = 0;
     uint32_t shard_index = 0, shard_count = 1; // database-sharded mode: which part of the keys this is
     std::shared_ptr<void> pool;                // pooled database (pool.cu): the common address range d.postings points into
+    std::shared_ptr<void> exported;            // epk_db_pool_share: this shard's postings in exportable memory
     size_t pool_local_bytes = 0;               // ... and how much of it sits in this GPU's HBM
 };
 

@@ -22,6 +22,7 @@
 #include <string>
 #include <vector>
 #include <cuda.h>
+#include <unistd.h>
 
 #include "common.cuh"
 #include "db.h"
@@ -41,6 +42,8 @@ namespace
         CUresult (*MemRelease)(CUmemGenericAllocationHandle) = nullptr;
         CUresult (*MemAddressFree)(CUdeviceptr, size_t) = nullptr;
         CUresult (*GetErrorString)(CUresult, const char**) = nullptr;
+        CUresult (*MemExportToShareableHandle)(void*, CUmemGenericAllocationHandle, CUmemAllocationHandleType, unsigned long long) = nullptr;
+        CUresult (*MemImportFromShareableHandle)(CUmemGenericAllocationHandle*, void*, CUmemAllocationHandleType) = nullptr;
 
         template<class F>
         static void resolve(const char* name, F& fn)
@@ -62,6 +65,8 @@ namespace
             resolve("cuMemRelease", MemRelease);
             resolve("cuMemAddressFree", MemAddressFree);
             resolve("cuGetErrorString", GetErrorString);
+            resolve("cuMemExportToShareableHandle", MemExportToShareableHandle);
+            resolve("cuMemImportFromShareableHandle", MemImportFromShareableHandle);
         }
         void check(CUresult r, const char* what) const
         {
@@ -260,5 +265,209 @@ extern "C" epk_status epk_db_pool(epk_db* const* shards, uint32_t n_shards, epk_
             made[d] = std::move(db);
         }
         for (uint32_t g = 0; g < n_shards; ++g) { out[g] = made[g].release(); }
+    });
+}
+
+
+// ---- the same pool with one PROCESS per GPU --------------------------------------------------------------------
+//
+// Under torchrun / MPI every GPU has its own process and its own address space: the physical memory of a shard then
+// travels as a POSIX file descriptor (cuMemExportToShareableHandle; the caller passes it to the peers over a unix
+// socket, SCM_RIGHTS) and its key table as a CUDA IPC handle. Every process builds the same address range for itself.
+//   1. epk_db_pool_share(shard)        my postings move into exportable memory; I get {fd, bytes, table handle} to send
+//   2. (the caller exchanges those)
+//   3. epk_db_pool_join(shard, parts)  maps all the parts - mine and the imported ones - into one range, merges the key
+//                                      tables into one of mine, returns the pooled database on my device
+namespace
+{
+    struct exported_part
+    {
+        driver_api api;
+        CUmemGenericAllocationHandle handle = 0;
+        CUdeviceptr at = 0;
+        size_t bytes = 0;
+        int device = 0;
+        ~exported_part()
+        {
+            cudaSetDevice(device);
+            cudaDeviceSynchronize();
+            if (at) { api.MemUnmap(at, bytes); api.MemAddressFree(at, bytes); }
+            if (handle) { api.MemRelease(handle); }
+        }
+    };
+}
+
+extern "C" epk_status epk_db_pool_share(epk_db* shard, int* fd_out, uint64_t* bytes_out, unsigned char* table_handle_out)
+{
+    return guarded([&] {
+        if (!shard || !fd_out || !bytes_out || !table_handle_out) { throw error(EPK_E_INVALID, "null argument"); }
+        if (shard->table_kind != TABLE_DIRECT) { throw error(EPK_E_UNSUPPORTED, "pooled databases need the direct-address key table (alphabet bits x k <= 26)"); }
+        if (shard->pool || shard->exported) { throw error(EPK_E_INVALID, "this database is pooled or shared already"); }
+        EPK_CUDA(cudaSetDevice(shard->device));
+        EPK_CUDA(cudaFree(nullptr));
+        auto part = std::make_shared<exported_part>();
+        part->device = shard->device;
+        const driver_api& api = part->api;
+        CUmemAllocationProp prop{};
+        prop.type = CU_MEM_ALLOCATION_TYPE_PINNED;
+        prop.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+        prop.location.id = shard->device;
+        prop.requestedHandleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+        size_t granularity = 0;
+        api.check(api.MemGetAllocationGranularity(&granularity, &prop, CU_MEM_ALLOC_GRANULARITY_RECOMMENDED), "cuMemGetAllocationGranularity");
+        granularity = std::max<size_t>(granularity, 2u << 20);
+        part->bytes = (std::max<size_t>(shard->postings.bytes(), 16) + granularity - 1) / granularity * granularity;
+        api.check(api.MemCreate(&part->handle, part->bytes, &prop, 0), "cuMemCreate (exportable)");
+        api.check(api.MemAddressReserve(&part->at, part->bytes, 0, 0, 0), "cuMemAddressReserve");
+        api.check(api.MemMap(part->at, part->bytes, 0, part->handle, 0), "cuMemMap");
+        CUmemAccessDesc access{};
+        access.location = prop.location;
+        access.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+        api.check(api.MemSetAccess(part->at, part->bytes, &access, 1), "cuMemSetAccess");
+        EPK_CUDA(cudaMemcpy(reinterpret_cast<void*>(part->at), shard->postings.get(), shard->postings.bytes(), cudaMemcpyDeviceToDevice));
+        int fd = -1;
+        api.check(api.MemExportToShareableHandle(&fd, part->handle, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0), "cuMemExportToShareableHandle");
+        cudaIpcMemHandle_t table{};
+        EPK_CUDA(cudaIpcGetMemHandle(&table, shard->direct.get()));
+        static_assert(sizeof(table) == EPK_IPC_HANDLE_BYTES, "IPC handle size");
+        std::memcpy(table_handle_out, &table, sizeof(table));
+        // the shard keeps answering (its own postings stay until it is destroyed); the exported copy lives with it and
+        // with every process that maps it
+        shard->exported = part;
+        *fd_out = fd;
+        *bytes_out = part->bytes;
+    });
+}
+
+extern "C" epk_status epk_db_pool_join(epk_db* shard, uint32_t n_shards, const int* fds, const uint64_t* bytes,
+                                       const unsigned char* table_handles, epk_db** out)
+{
+    return guarded([&] {
+        if (!shard || !fds || !bytes || !table_handles || !out) { throw error(EPK_E_INVALID, "null argument"); }
+        *out = nullptr;
+        if (n_shards == 0 || n_shards > 64 || shard->shard_count != n_shards) { throw error(EPK_E_INVALID, "the shard is not one of n_shards"); }
+        if (!shard->exported) { throw error(EPK_E_INVALID, "epk_db_pool_share comes first"); }
+        const uint32_t me = shard->shard_index;
+        const auto mine = std::static_pointer_cast<exported_part>(shard->exported);
+        EPK_CUDA(cudaSetDevice(shard->device));
+        EPK_CUDA(cudaFree(nullptr));
+        auto pool = std::make_shared<pool_memory>();
+        pool->any_device = shard->device;
+        const driver_api& api = pool->api;
+        std::vector<size_t> offset(n_shards);
+        size_t total = 0;
+        for (uint32_t g = 0; g < n_shards; ++g)
+        {
+            if (bytes[g] == 0 || bytes[g] % (2u << 20) != 0) { throw error(EPK_E_INVALID, "part sizes are multiples of the allocation granularity"); }
+            offset[g] = total;
+            total += bytes[g];
+        }
+        if (bytes[me] != mine->bytes) { throw error(EPK_E_INVALID, "my own part has another size than I shared"); }
+        if (total / 8 >= (1ull << 33)) { throw error(EPK_E_UNSUPPORTED, "a pooled database holds at most 2^33 postings (64 GB)"); }
+        api.check(api.MemAddressReserve(&pool->base, total, 0, 0, 0), "cuMemAddressReserve");
+        pool->reserved = total;
+        for (uint32_t g = 0; g < n_shards; ++g)
+        {
+            CUmemGenericAllocationHandle handle = 0;
+            if (g == me)
+            {
+                // (a second reference of my own allocation: exported again and imported, so that the pool owns one)
+                handle = 0;
+                int fd = -1;
+                api.check(api.MemExportToShareableHandle(&fd, mine->handle, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0), "cuMemExportToShareableHandle");
+                const CUresult r = api.MemImportFromShareableHandle(&handle, reinterpret_cast<void*>(static_cast<uintptr_t>(fd)), CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR);
+                ::close(fd);
+                api.check(r, "cuMemImportFromShareableHandle (own part)");
+            }
+            else
+            {
+                api.check(api.MemImportFromShareableHandle(&handle, reinterpret_cast<void*>(static_cast<uintptr_t>(fds[g])), CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR),
+                          "cuMemImportFromShareableHandle (is the descriptor this process's own copy, received over a unix socket?)");
+            }
+            pool->handles.push_back(handle);
+            api.check(api.MemMap(pool->base + offset[g], bytes[g], 0, handle, 0), "cuMemMap");
+            pool->mapped.emplace_back(offset[g], static_cast<size_t>(bytes[g]));
+        }
+        CUmemAccessDesc access{};
+        access.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+        access.location.id = shard->device;
+        access.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+        api.check(api.MemSetAccess(pool->base, total, &access, 1), "cuMemSetAccess (are the GPUs peers of each other?)");
+
+        auto db = std::make_unique<epk_db>();
+        db->device = shard->device;
+        db->table_kind = TABLE_DIRECT;
+        db->table_slots = shard->table_slots;
+        db->direct.resize(shard->table_slots);
+        EPK_CUDA(cudaMemset(db->direct.get(), 0, db->direct.bytes()));
+        device_buffer<uint32_t> clash(1);
+        EPK_CUDA(cudaMemset(clash.get(), 0, 4));
+        for (uint32_t g = 0; g < n_shards; ++g)
+        {
+            const uint64_t* table = shard->direct.get();
+            void* opened = nullptr;
+            if (g != me)
+            {
+                cudaIpcMemHandle_t h{};
+                std::memcpy(&h, table_handles + static_cast<size_t>(g) * EPK_IPC_HANDLE_BYTES, sizeof(h));
+                EPK_CUDA(cudaIpcOpenMemHandle(&opened, h, cudaIpcMemLazyEnablePeerAccess));
+                table = static_cast<const uint64_t*>(opened);
+            }
+            merge_table_kernel<<<blocks_for(shard->table_slots, 256), 256>>>(table, shard->table_slots, offset[g] / 8,
+                                                                              reinterpret_cast<unsigned long long*>(db->direct.get()), clash.get());
+            const cudaError_t launched = cudaGetLastError();
+            const cudaError_t done = cudaDeviceSynchronize();
+            if (opened) { cudaIpcCloseMemHandle(opened); }
+            EPK_CUDA(launched);
+            EPK_CUDA(done);
+        }
+        uint32_t h_clash = 0;
+        EPK_CUDA(cudaMemcpy(&h_clash, clash.get(), 4, cudaMemcpyDeviceToHost));
+        if (h_clash) { throw error(EPK_E_INVALID, "two shards hold the same key: not the shards of one database"); }
+        db->letters.resize(256);
+        EPK_CUDA(cudaMemcpy(db->letters.get(), shard->letters.get(), 256 * 4, cudaMemcpyDeviceToDevice));
+        db->d = shard->d;
+        db->d.direct = db->direct.get();
+        db->d.hashed = nullptr;
+        db->d.postings = reinterpret_cast<const uint2*>(pool->base);
+        // (the score range of the OTHER shards is not known here: the sweep's short arithmetic forms are only used when
+        // the caller says all shards allow them - see epk_db_pool_set_score_range)
+        db->distal = shard->distal;
+        db->pendant = shard->pendant;
+        db->omega = shard->omega;
+        db->n_entries_total = shard->n_entries_total;
+        db->n_entries_loaded = shard->n_entries_loaded; // (of my shard; the caller sums)
+        db->n_keys_loaded = shard->n_keys_loaded;
+        db->shard_index = 0;
+        db->shard_count = 1;
+        db->pool = pool;
+        db->pool_local_bytes = bytes[me];
+        *out = db.release();
+    });
+}
+
+// The range of the scores over ALL the shards (each process knows its own: epk_db_get_score_range) decides which
+// arithmetic the sweep may use; the processes agree on it (min of lo, max of hi, AND of fast_ok) and set it.
+extern "C" epk_status epk_db_get_score_range(const epk_db* db, float* lo, float* hi, uint32_t* fast_ok, uint64_t* entries_loaded, uint64_t* keys_loaded)
+{
+    return guarded([&] {
+        if (!db || !lo || !hi || !fast_ok || !entries_loaded || !keys_loaded) { throw error(EPK_E_INVALID, "null argument"); }
+        *lo = db->d.score_lo;
+        *hi = db->d.score_hi;
+        *fast_ok = db->d.fast_ok;
+        *entries_loaded = db->n_entries_loaded;
+        *keys_loaded = db->n_keys_loaded;
+    });
+}
+
+extern "C" epk_status epk_db_pool_set_score_range(epk_db* pooled, float lo, float hi, uint32_t fast_ok, uint64_t entries_loaded, uint64_t keys_loaded)
+{
+    return guarded([&] {
+        if (!pooled || !pooled->pool) { throw error(EPK_E_INVALID, "not a pooled database"); }
+        pooled->d.score_lo = lo;
+        pooled->d.score_hi = hi;
+        pooled->d.fast_ok = fast_ok ? 1u : 0u;
+        pooled->n_entries_loaded = entries_loaded;
+        pooled->n_keys_loaded = keys_loaded;
     });
 }

@@ -345,3 +345,71 @@ class PooledPlacer:
         for d in getattr(self, "dbs", []):
             d.close()
         self.dbs = []
+
+
+class RankPooledPlacer:
+    """One rank of a pool with one PROCESS per GPU (torchrun): shard `rank` of `world` is built on this rank's device,
+    shared with the peers (its memory as a file descriptor over a unix socket, its key table as a CUDA IPC handle), and
+    joined with theirs into one address range of this process. The rank then places ITS OWN queries against the whole
+    database (`self.placer`, any entry point) - posting lists come from whichever HBM holds them, over NVLink.
+    torch.distributed only carries the few bytes of bookkeeping (any backend: gloo will do)."""
+
+    def __init__(self, flat, rank: int, world: int, group=None, device: int = 0, keep_at_most: int = 7,
+                 keep_factor: float = 0.01, variant: int = 0, **load):
+        import os
+        import socket
+        import tempfile
+        import threading
+        import torch.distributed as dist
+        shard = _shard_database(flat, device, (rank, world), load)
+        fd, nbytes, table = shard.pool_share()
+        path = os.path.join(tempfile.gettempdir(), "epk_pool_%d_%d.sock" % (os.getpid(), rank))
+        if os.path.exists(path):
+            os.unlink(path)
+        server = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+        server.bind(path)
+        server.listen(world)
+        everyone = [None] * world
+        dist.all_gather_object(everyone, (nbytes, table, path) + tuple(shard.score_range()), group=group)
+
+        def serve():
+            for _ in range(world - 1):
+                conn, _ = server.accept()
+                socket.send_fds(conn, [b"fd"], [fd])
+                conn.close()
+
+        serving = threading.Thread(target=serve)
+        serving.start()
+        fds = []
+        for r in range(world):
+            if r == rank:
+                fds.append(-1)
+                continue
+            client = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+            client.connect(everyone[r][2])
+            _, got, _, _ = socket.recv_fds(client, 16, 1)
+            client.close()
+            fds.append(got[0])
+        serving.join()
+        loaded = [e for e in everyone if e[6] > 0] or everyone
+        score_range = (min(e[3] for e in loaded), max(e[4] for e in loaded), int(all(e[5] for e in everyone)),
+                       sum(e[6] for e in everyone), sum(e[7] for e in everyone))
+        self.db = shard.pool_join(world, fds, [e[0] for e in everyone], [e[1] for e in everyone], score_range)
+        dist.barrier(group=group)  # every process has read the tables it opened and holds its own references
+        for f in fds:
+            if f >= 0:
+                os.close(f)
+        os.close(fd)
+        server.close()
+        os.unlink(path)
+        shard.close()
+        self.placer = Placer(self.db, keep_at_most, keep_factor, variant=variant)
+        self.rank, self.world, self.device, self.keep_at_most = rank, world, device, keep_at_most
+
+    def close(self):
+        if getattr(self, "placer", None) is not None:
+            self.placer.close()
+            self.placer = None
+        if getattr(self, "db", None) is not None:
+            self.db.close()
+            self.db = None

@@ -204,6 +204,43 @@ def _db_pool(cls, shards):
 Database.pool = classmethod(_db_pool)
 
 
+def _db_pool_share(self):
+    """epk_db_pool_share -> (fd, bytes, table_handle): what a peer PROCESS needs to map this shard."""
+    fd, nbytes = C.c_int(-1), C.c_uint64(0)
+    table = C.create_string_buffer(64)
+    capi.check(capi.lib().epk_db_pool_share(self.handle, C.byref(fd), C.byref(nbytes), table))
+    return fd.value, int(nbytes.value), table.raw
+
+
+def _db_score_range(self):
+    lo, hi, ok = C.c_float(), C.c_float(), C.c_uint32()
+    entries, keys = C.c_uint64(), C.c_uint64()
+    capi.check(capi.lib().epk_db_get_score_range(self.handle, C.byref(lo), C.byref(hi), C.byref(ok), C.byref(entries), C.byref(keys)))
+    return lo.value, hi.value, int(ok.value), int(entries.value), int(keys.value)
+
+
+def _db_pool_join(self, n_shards: int, fds, sizes, table_handles, score_range):
+    """epk_db_pool_join + epk_db_pool_set_score_range: the pooled database of this process (a whole database to a placer)."""
+    fd_arr = (C.c_int * n_shards)(*[int(f) for f in fds])
+    size_arr = (C.c_uint64 * n_shards)(*[int(b) for b in sizes])
+    out = C.c_void_p()
+    capi.check(capi.lib().epk_db_pool_join(self.handle, n_shards, C.cast(fd_arr, C.c_void_p), C.cast(size_arr, C.c_void_p),
+                                           b"".join(table_handles), C.byref(out)))
+    db = type(self).__new__(type(self))
+    db.flat, db.gen, db.handle, db.device, db.shard = getattr(self, "flat", None), getattr(self, "gen", None), out, self.device, None
+    lo, hi, ok, entries, keys = score_range
+    capi.check(capi.lib().epk_db_pool_set_score_range(db.handle, lo, hi, ok, entries, keys))
+    info = capi.DbInfo()
+    capi.check(capi.lib().epk_db_get_info(db.handle, C.byref(info)))
+    db.info = {name: getattr(info, name) for name, _ in capi.DbInfo._fields_}
+    return db
+
+
+Database.pool_share = _db_pool_share
+Database.score_range = _db_score_range
+Database.pool_join = _db_pool_join
+
+
 def _db_view(self) -> "capi.DbView":
     """epk_db_get_view: the device addresses of this database's key table and postings."""
     v = capi.DbView()

@@ -22,6 +22,7 @@ extern "C" {
 #endif
 
 #define EPK_ABI_VERSION 1
+#define EPK_IPC_HANDLE_BYTES 64 /* a CUDA IPC memory handle */
 
 typedef enum epk_status
 {
@@ -287,6 +288,26 @@ epk_status epk_place_finalize_device(epk_placer* placer, const void* d_rows, uin
  * The reference has nothing like it (one phylo_kmer_db in one address space, main.cpp:277). */
 epk_status epk_db_pool(epk_db* const* shards, uint32_t n_shards, epk_db** out /* [n_shards] */);
 
+/* The same pool with one PROCESS per GPU (torchrun, MPI): a shard's memory travels as a POSIX file descriptor, its key
+ * table as a CUDA IPC handle, and every process builds the common address range for itself.
+ *   1. epk_db_pool_share(shard, &fd, &bytes, table_handle): the shard's postings are copied into exportable memory;
+ *      send {fd (over a unix socket, SCM_RIGHTS), bytes, table_handle [EPK_IPC_HANDLE_BYTES]} to every peer;
+ *   2. epk_db_pool_join(shard, n_shards, fds, bytes, table_handles, &pooled): fds / bytes / table_handles are indexed by
+ *      shard (the entry of the caller's own shard index is ignored for fds and table_handles); `pooled` is the whole
+ *      database on the caller's device. Keep every shard alive until all the processes have joined (a barrier), then
+ *      close the descriptors and destroy the shards;
+ *   3. the processes agree on the score range of all the shards (epk_db_get_score_range of each shard: min of lo, max
+ *      of hi, AND of fast_ok, sums of the counts) and each sets it on its pooled database
+ *      (epk_db_pool_set_score_range) before placing: it decides which arithmetic the sweep may use.
+ * Works with several processes on one GPU too (tests). */
+epk_status epk_db_pool_share(epk_db* shard, int* fd_out, uint64_t* bytes_out, unsigned char* table_handle_out);
+epk_status epk_db_pool_join(epk_db* shard, uint32_t n_shards, const int* fds, const uint64_t* bytes,
+                            const unsigned char* table_handles /* [n_shards][EPK_IPC_HANDLE_BYTES] */, epk_db** out);
+epk_status epk_db_get_score_range(const epk_db* db, float* lo, float* hi, uint32_t* fast_ok, uint64_t* entries_loaded,
+                                  uint64_t* keys_loaded);
+epk_status epk_db_pool_set_score_range(epk_db* pooled, float lo, float hi, uint32_t fast_ok, uint64_t entries_loaded,
+                                       uint64_t keys_loaded);
+
 /* ---- windows with one ambiguous letter in database-sharded mode -----------------------------------------
  *
  * place.cpp:373-415 lets the FIRST ambiguous key (window order, then resolution order) that names a branch
@@ -324,7 +345,6 @@ epk_status epk_place_finalize_seq_device(epk_placer* placer, void* d_rows, uint3
  * epk_device_alloc, exports it (64-byte CUDA IPC handle, sent to the peers by any means), the peers
  * import it and pass the mapped address as d_rows[owner] of epk_place_partial_device: the partial
  * launch then stores its rows straight into the owner's HBM over NVLink. */
-#define EPK_IPC_HANDLE_BYTES 64
 epk_status epk_device_alloc(int device, uint64_t bytes, void** out);
 void epk_device_free(int device, void* p);
 epk_status epk_ipc_export(const void* d_ptr, unsigned char* handle_out /* [EPK_IPC_HANDLE_BYTES] */);

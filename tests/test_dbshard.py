@@ -267,6 +267,45 @@ def test_pooled_database_gives_the_unsharded_results_bit_for_bit(built, shape):
     pooled.close()
 
 
+def _pool_worker(rank, world, port, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    device = rank % torch.cuda.device_count()
+    torch.cuda.set_device(device)
+    dist.init_process_group("gloo", rank=rank, world_size=world)  # (bookkeeping only: the data path is loads over NVLink)
+    flat = synth.make_db(0, 8, 5000, 0.7, 24.0, seed=81) if rank >= 0 else None
+    data, off = synth.make_reads(0, 1200, 150, seed=82, amb_rate=0.01)
+    rp = dbshard.RankPooledPlacer(flat, rank, world, device=device, mu=0.7, omega=1.3)
+    first, last = len(off) - 1, 0
+    for _ in range(2):
+        first, last = int(dbshard.owner_bounds(len(off) - 1, world)[rank]), int(dbshard.owner_bounds(len(off) - 1, world)[rank + 1])
+        got = rp.placer.place_packed(data[int(off[first]):int(off[last])], off[first:last + 1] - off[first])
+    np.savez(os.path.join(out_dir, "pool%d.npz" % rank), first=first, last=last, entries=rp.db.info["n_entries_loaded"], **got)
+    dist.barrier()
+    rp.close()
+    dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+def test_pool_with_one_process_per_shard(built, tmp_path):
+    """The pool across PROCESSES (what torchrun gives: one per GPU; here three, sharing the GPUs that are there): memory
+    as file descriptors over unix sockets, key tables as IPC handles, one address range per process. Every rank places
+    its own slice against the whole database - bit for bit what one GPU with the unsharded, filtered database gives."""
+    from epik_b200.placer import Database, Placer
+    world = 3
+    mp.spawn(_pool_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    flat = synth.make_db(0, 8, 5000, 0.7, 24.0, seed=81)
+    data, off = synth.make_reads(0, 1200, 150, seed=82, amb_rate=0.01)
+    whole = Database(flat, mu=0.7, omega=1.3)
+    want = Placer(whole).place_packed(data, off)
+    for rank in range(world):
+        part = np.load(str(tmp_path / ("pool%d.npz" % rank)))
+        first, last = int(part["first"]), int(part["last"])
+        assert int(part["entries"]) == whole.info["n_entries_loaded"]
+        for name in ("n_place", "branch", "score", "lwr", "count", "distal", "pendant"):
+            assert np.array_equal(part[name], want[name][first:last]), (rank, name)
+
+
 def _nccl_worker(rank, world, port, out_dir, transport):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
