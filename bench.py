@@ -467,22 +467,13 @@ def run_ours(args):
         dbshard_leg = time_dbshard(args, "C5", rank, world, local, dev, reads=args.dbshard_reads, steps=max(2, min(args.steps, 3)),
                                    warmup=1, transport=args.transport)
 
-    # ---- N > 1, second form of "the database does not fit one GPU": pooled over the N HBMs, read over NVLink. One
-    # process drives the GPUs (rank 0; the other ranks wait on the store, not in an NCCL kernel that would sit on their SMs)
+    # ---- N > 1, second form of "the database does not fit one GPU": pooled over the N HBMs, read over NVLink; every
+    # rank holds an N-th of it and places its own reads
     dbpool_leg = None
     if world > 1 and not args.no_dbpool:
-        store = dist.distributed_c10d._get_default_store()
         torch.cuda.empty_cache()
         barrier()
-        if rank == 0:
-            try:
-                dbpool_leg = time_dbpool(args, "C5", list(range(world)), args.dbpool_reads, steps=max(2, min(args.steps, 3)), warmup=1)
-            except Exception as exc:  # (the line is still worth printing)
-                dbpool_leg = {"error": "%s: %s" % (type(exc).__name__, exc)}
-            torch.cuda.set_device(local)
-            store.set("epk_dbpool_done", "1")
-        else:
-            store.wait(["epk_dbpool_done"])
+        dbpool_leg = time_dbpool_ranks(args, "C5", rank, world, local, dev, args.dbpool_reads, steps=max(2, min(args.steps, 3)), warmup=1)
         barrier()
 
     total_reads = sum_over_ranks(float(n))
@@ -632,6 +623,72 @@ def time_dbpool(args, workload, devices, reads_per_gpu, steps, warmup):
            "how": "epk_db_pool: shards mapped into one address range (CUDA VMM), a key table per GPU pointing into it, the fused "
                   "kernel unchanged; results bit-identical to the unsharded database"}
     pooled.close()
+    return rec
+
+
+def time_dbpool_ranks(args, workload, rank, world, local, dev, reads_per_gpu, steps, warmup):
+    """The pooled database with one PROCESS per GPU (inside an initialised process group): rank r holds shard r of
+    `workload`'s keys in its HBM, maps everybody else's, and places ITS OWN reads with the fused kernel."""
+    import torch
+    import torch.distributed as dist
+    from epik_b200 import dbshard, synth
+    from epik_b200.placer import PinnedArray
+    alphabet, k, n_leaves, p_occ, m, read_len = synth.CONFIGS[workload]
+    K, n = 7, reads_per_gpu
+    flat = synth.make_config_gen2(workload) if workload in DEVICE_GENERATED else synth.make_config_db(workload)
+    t0 = time.perf_counter()
+    rp = dbshard.RankPooledPlacer(flat, rank, world, device=local, keep_at_most=K)
+    build_s = time.perf_counter() - t0
+    info = rp.db.info
+    h_seq = PinnedArray((n * read_len,), np.uint8)
+    h_off = PinnedArray((n + 1,), np.uint64)
+    make_reads_chunked(alphabet, n, read_len, rank * n, h_seq.array)
+    h_off.array[:] = np.arange(n + 1, dtype=np.uint64) * np.uint64(read_len)
+    d_seq = torch.from_numpy(h_seq.array).to(dev)
+    d_off = torch.from_numpy(h_off.array.view(np.int64)).to(dev)
+    out = {"n_place": torch.zeros(n, dtype=torch.int32, device=dev), "branch": torch.zeros(n * K, dtype=torch.int32, device=dev),
+           "score": torch.zeros(n * K, dtype=torch.float32, device=dev), "lwr": torch.zeros(n * K, dtype=torch.float64, device=dev),
+           "count": torch.zeros(n * K, dtype=torch.int32, device=dev)}
+    stream = torch.cuda.Stream(device=dev)
+    for _ in range(warmup):
+        rp.placer.place_device(d_seq, d_off, n, out, stream=stream)
+    stream.synchronize()
+    dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(steps):
+        rp.placer.place_device(d_seq, d_off, n, out, stream=stream)
+    e1.record(stream)
+    stream.synchronize()
+    entries = rp.placer.counters()["n_entries"]
+    dist.barrier()
+    t = torch.tensor([e0.elapsed_time(e1) / 1e3], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    secs = float(t.item())
+    # end to end: pinned host buffers through epk_place, every rank at once
+    host_out = rp.placer.alloc_result(n, pinned=True, lengths=True)
+    rp.placer.place_packed(h_seq.array, h_off.array, out=host_out)
+    dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        rp.placer.place_packed(h_seq.array, h_off.array, out=host_out)
+    t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_s = float(t.item())
+    assert int(host_out["n_place"].sum()) == int(out["n_place"].sum().item()) > 0
+    rec = {"metric": METRIC, "value": world * n * steps / secs, "unit": UNIT, "n_gpus": world, "scaling": "weak",
+           "e2e": {"value": world * n * steps / e2e_s, "unit": UNIT, "api": "epk_place (C ABI) on every rank, pinned host buffers"},
+           "workload": "%s: k=%d, %d branches, %.1f GB of postings pooled over %d GPUs, one process each (%.1f GB in each HBM), %d x "
+                       "%d-letter reads per GPU per step, each rank places its own reads" % (
+                           workload, k, 2 * n_leaves - 1, info["n_entries_loaded"] * 8 / 1e9, world,
+                           info["n_entries_loaded"] * 8 / 1e9 / world, n, read_len),
+           "ms_per_step": secs / steps * 1e3, "steps": steps, "build_s": build_s,
+           "nvlink_bytes_per_read": 8.0 * entries / n * (world - 1) / world,
+           "how": "epk_db_pool_share / epk_db_pool_join: every rank's shard exported as a file descriptor, mapped by all into one "
+                  "address range (CUDA VMM), a key table per rank pointing into it, the fused kernel unchanged; posting lists are "
+                  "gathered over NVLink from whichever HBM holds them; results bit-identical to the unsharded database"}
+    rp.close()
     return rec
 
 
