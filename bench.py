@@ -473,7 +473,10 @@ def run_ours(args):
     if world > 1 and not args.no_dbpool:
         torch.cuda.empty_cache()
         barrier()
-        dbpool_leg = time_dbpool_ranks(args, "C5", rank, world, local, dev, args.dbpool_reads, steps=max(2, min(args.steps, 3)), warmup=1)
+        try:
+            dbpool_leg = time_dbpool_ranks(args, "C5", rank, world, local, dev, args.dbpool_reads, steps=max(2, min(args.steps, 3)), warmup=1)
+        except RuntimeError as exc:  # (raised on every rank together: RankPooledPlacer agrees on failures)
+            dbpool_leg = {"error": str(exc)}
         barrier()
 
     total_reads = sum_over_ranks(float(n))

@@ -394,8 +394,17 @@ class RankPooledPlacer:
         loaded = [e for e in everyone if e[6] > 0] or everyone
         score_range = (min(e[3] for e in loaded), max(e[4] for e in loaded), int(all(e[5] for e in everyone)),
                        sum(e[6] for e in everyone), sum(e[7] for e in everyone))
-        self.db = shard.pool_join(world, fds, [e[0] for e in everyone], [e[1] for e in everyone], score_range)
-        dist.barrier(group=group)  # every process has read the tables it opened and holds its own references
+        # every process has read the tables it opened and holds its own references before anything is closed; and a
+        # failure on one rank (GPUs that are not peers, descriptors that did not arrive) is everybody's: nobody is left
+        # waiting in a collective
+        failure = None
+        try:
+            self.db = shard.pool_join(world, fds, [e[0] for e in everyone], [e[1] for e in everyone], score_range)
+        except Exception as exc:  # noqa: BLE001
+            self.db = None
+            failure = "rank %d: %s" % (rank, exc)
+        failures = [None] * world
+        dist.all_gather_object(failures, failure, group=group)
         for f in fds:
             if f >= 0:
                 os.close(f)
@@ -403,6 +412,11 @@ class RankPooledPlacer:
         server.close()
         os.unlink(path)
         shard.close()
+        if any(failures):
+            if self.db is not None:
+                self.db.close()
+                self.db = None
+            raise RuntimeError("the pool could not be built: " + "; ".join(f for f in failures if f))
         self.placer = Placer(self.db, keep_at_most, keep_factor, variant=variant)
         self.rank, self.world, self.device, self.keep_at_most = rank, world, device, keep_at_most
 
