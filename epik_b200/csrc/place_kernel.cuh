@@ -2269,11 +2269,6 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
             next_s0 = off0;
             next_len = off1 - off0;
             next_known = true;
-#ifndef EPK_NO_LETTER_PREFETCH
-            // C: its letters are asked of L2 (local memory, a line per lane) while this query is swept
-            const uint64_t lines = min((next_len + (off0 & 127u) + 127u) / 128u, static_cast<uint64_t>(CHUNK + 64) / 128u + 1u);
-            if (lane < lines) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p.seq + (off0 & ~127ull) + 128u * lane)); }
-#endif
         }
         if (GATHER_ONLY)
         {
