@@ -293,6 +293,76 @@ namespace epik::io
         }
 
         /// Appends what format() returned for a batch of n_records records (jplace.cpp:33-36: per batch).
+        /// The same text as format(), straight from the arrays of a device pass (placer::place_arrays) for the records
+        /// [first, last) of one --batch-size batch, without building a placed_collection: one record per group of
+        /// identical sequences, in order of first occurrence, its names in record order. The layout of a record is
+        /// fixed, so this writes through a raw cursor instead of the generic writer (2.3 GB/s of text from 16 threads
+        /// was what bounded the driver). Byte-identical to format() on the same placements (host test).
+        template<class Record>
+        static std::string format_arrays(const std::vector<Record>& records, const epk_result& rows, size_t K, const uint32_t* group_rep,
+                                         size_t first, size_t last, size_t* n_records_out = nullptr)
+        {
+            const size_t n = last - first;
+            // members of a group, in record order, as a chain through `next`
+            std::vector<uint32_t> next(n, 0xFFFFFFFFu), tail(n);
+            size_t n_groups = 0, name_bytes = 0;
+            for (size_t j = 0; j < n; ++j)
+            {
+                const uint32_t r = group_rep[first + j];
+                if (r == j) { ++n_groups; }
+                else { next[tail[r]] = static_cast<uint32_t>(j); }
+                tail[r] = static_cast<uint32_t>(j);
+                name_bytes += std::string_view(records[first + j].header()).size();
+            }
+            std::string text;
+            // (a generous bound: 48 bytes of frame + up to 26 per number; escapes can at most multiply a name by 6)
+            text.resize(n_groups * (96 + K * 160) + n * 48 + name_bytes * 6 + 64);
+            char* const begin = text.data();
+            char* at = begin;
+            auto put = [&at](const char* lit, size_t len) { std::memcpy(at, lit, len); at += len; };
+#define EPK_PUT(LIT) put(LIT, sizeof(LIT) - 1)
+            for (size_t j = 0; j < n; ++j)
+            {
+                if (group_rep[first + j] != j) { continue; }
+                const size_t i = first + j;
+                EPK_PUT(",\n        {\n            \"p\": [");
+                const size_t m = rows.n_place[i];
+                for (size_t p = 0; p < m; ++p)
+                {
+                    const size_t row = i * K + p;
+                    if (p) { *at++ = ','; }
+                    EPK_PUT("\n                [");
+                    at = std::to_chars(at, at + 24, static_cast<uint64_t>(rows.branch[row])).ptr;
+                    EPK_PUT(", ");
+                    at = raw_number(at, static_cast<double>(rows.score[row])); // float widened to double (jplace.cpp:131)
+                    EPK_PUT(", ");
+                    at = raw_number(at, rows.lwr[row]);
+                    EPK_PUT(", ");
+                    at = raw_number(at, rows.distal[row]);
+                    EPK_PUT(", ");
+                    at = raw_number(at, rows.pendant[row]);
+                    *at++ = ']';
+                }
+                if (m) { EPK_PUT("\n            ]"); }
+                else { *at++ = ']'; }
+                EPK_PUT(",\n            \"nm\": [");
+                bool first_name = true;
+                for (uint32_t member = static_cast<uint32_t>(j); member != 0xFFFFFFFFu; member = next[member])
+                {
+                    if (!first_name) { *at++ = ','; }
+                    first_name = false;
+                    EPK_PUT("\n                [");
+                    at = raw_string(at, std::string_view(records[first + member].header()));
+                    EPK_PUT(", 1]");
+                }
+                EPK_PUT("\n            ]\n        }");
+            }
+#undef EPK_PUT
+            text.resize(static_cast<size_t>(at - begin));
+            if (n_records_out) { *n_records_out = n_groups; }
+            return text;
+        }
+
         void append(const std::string& text, size_t n_records)
         {
             if (n_records)
@@ -370,6 +440,97 @@ namespace epik::io
         }
 
     private:
+        /// json_pretty_writer::string / ::number through a raw cursor (same bytes)
+        static char* raw_string(char* at, std::string_view s)
+        {
+            static const char hex[] = "0123456789ABCDEF";
+            *at++ = '"';
+            for (const char ch : s)
+            {
+                const unsigned char c = static_cast<unsigned char>(ch);
+                if (c >= 0x20 && c != '"' && c != '\\') { *at++ = ch; continue; }
+                *at++ = '\\';
+                switch (c)
+                {
+                    case '"': *at++ = '"'; break;
+                    case '\\': *at++ = '\\'; break;
+                    case '\b': *at++ = 'b'; break;
+                    case '\f': *at++ = 'f'; break;
+                    case '\n': *at++ = 'n'; break;
+                    case '\r': *at++ = 'r'; break;
+                    case '\t': *at++ = 't'; break;
+                    default: *at++ = 'u'; *at++ = '0'; *at++ = '0'; *at++ = hex[c >> 4]; *at++ = hex[c & 15];
+                }
+            }
+            *at++ = '"';
+            return at;
+        }
+        static char* raw_number(char* at, double v)
+        {
+            if (std::isnan(v) || std::isinf(v)) { return at; } // RapidJSON refuses them after the prefix
+            if (v == 0.0)
+            {
+                const char* zero = std::signbit(v) ? "-0.0" : "0.0";
+                const size_t len = std::strlen(zero);
+                std::memcpy(at, zero, len);
+                return at + len;
+            }
+            if (v < 0.0)
+            {
+                *at++ = '-';
+                v = -v;
+            }
+            char sci[40];
+            const auto r = std::to_chars(sci, sci + sizeof(sci), v, std::chars_format::scientific);
+            const char* e = static_cast<const char*>(std::memchr(sci, 'e', static_cast<size_t>(r.ptr - sci)));
+            char digits[24];
+            int length = 0;
+            for (const char* p = sci; p < e; ++p)
+            {
+                if (*p != '.') { digits[length++] = *p; }
+            }
+            int exp10 = 0;
+            std::from_chars(e[1] == '+' ? e + 2 : e + 1, r.ptr, exp10);
+            const int kk = exp10 + 1;
+            const int k = kk - length;
+            if (0 <= k && kk <= 21)
+            {
+                std::memcpy(at, digits, static_cast<size_t>(length)); at += length;
+                std::memset(at, '0', static_cast<size_t>(k)); at += k;
+                *at++ = '.'; *at++ = '0';
+            }
+            else if (0 < kk && kk <= 21)
+            {
+                std::memcpy(at, digits, static_cast<size_t>(kk)); at += kk;
+                *at++ = '.';
+                std::memcpy(at, digits + kk, static_cast<size_t>(length - kk)); at += length - kk;
+            }
+            else if (-6 < kk && kk <= 0)
+            {
+                *at++ = '0'; *at++ = '.';
+                std::memset(at, '0', static_cast<size_t>(-kk)); at += -kk;
+                std::memcpy(at, digits, static_cast<size_t>(length)); at += length;
+            }
+            else
+            {
+                *at++ = digits[0];
+                if (length > 1)
+                {
+                    *at++ = '.';
+                    std::memcpy(at, digits + 1, static_cast<size_t>(length - 1)); at += length - 1;
+                }
+                *at++ = 'e';
+                int x = kk - 1;
+                if (x < 0)
+                {
+                    *at++ = '-';
+                    x = -x;
+                }
+                at = std::to_chars(at, at + 8, x).ptr;
+            }
+            return at;
+        }
+
         void flush()
         {
             if (!_out.is_open()) { _out.open(_filename, std::ios_base::app); }

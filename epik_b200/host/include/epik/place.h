@@ -298,6 +298,30 @@ namespace epik
             return batches;
         }
 
+        /// What place_batched computes, left in arrays instead of objects: rows [n][keep_at_most] of the C ABI's epk_result
+        /// and, per record, the index within its --batch-size batch of the first record with the same sequence
+        /// (place.cpp:73-81). Valid until the placement after the next one (two result sets take turns). A pass of a
+        /// million reads costs more as 10^6 small objects than on the device; the driver formats its jplace straight
+        /// from these arrays (jplace_writer::format_arrays).
+        struct placed_arrays
+        {
+            epk_result rows;
+            const uint32_t* group_rep;
+            size_t keep_at_most, batch_size, n;
+        };
+        template<class Record>
+        placed_arrays place_arrays(const std::vector<Record>& seq_records, size_t batch_size)
+        {
+            const epk_result out = run(seq_records);
+            result_set& set = _sets[_turn % 2];
+            const size_t n = seq_records.size();
+            if (batch_size == 0) { batch_size = std::max<size_t>(1, n); }
+            set.group_rep.resize(n + 1);
+            impl::check(epk_group_batches(_letters.data(), _offsets.data(), static_cast<uint32_t>(n), static_cast<uint32_t>(batch_size),
+                                          static_cast<uint32_t>(_host_threads), set.group_rep.data()));
+            return placed_arrays{ out, set.group_rep.data(), _keep_at_most, batch_size, n };
+        }
+
         /// Work counters of the last place() (windows looked up, hits, postings gathered, launches).
         epk_counters counters()
         {
@@ -333,14 +357,15 @@ namespace epik
                 }
             });
 
+            result_set& set = _sets[++_turn % 2];
             epk_result out{};
-            out.n_place = _n_place.reserve(n + 1);
-            out.branch = _branch.reserve(n * K + 1);
-            out.score = _score.reserve(n * K + 1);
-            out.lwr = _lwr.reserve(n * K + 1);
-            out.count = _count.reserve(n * K + 1);
-            out.distal = _distal.reserve(n * K + 1);
-            out.pendant = _pendant.reserve(n * K + 1);
+            out.n_place = set.n_place.reserve(n + 1);
+            out.branch = set.branch.reserve(n * K + 1);
+            out.score = set.score.reserve(n * K + 1);
+            out.lwr = set.lwr.reserve(n * K + 1);
+            out.count = set.count.reserve(n * K + 1);
+            out.distal = set.distal.reserve(n * K + 1);
+            out.pendant = set.pendant.reserve(n * K + 1);
             if (_replicas.empty()) { impl::check(epk_place(_handle, letters, offsets, static_cast<uint32_t>(n), &out)); }
             else
             {
@@ -395,9 +420,17 @@ namespace epik
 
         impl::pinned_array<char> _letters;
         impl::pinned_array<uint64_t> _offsets;
-        impl::pinned_array<uint32_t> _n_place, _branch, _count;
-        impl::pinned_array<float> _score;
-        impl::pinned_array<double> _lwr, _distal, _pendant;
+        /// two sets of result arrays take turns: the results of a pass stay valid while the NEXT pass is placed (the
+        /// driver formats the text of one pass while the next one is on the device)
+        struct result_set
+        {
+            impl::pinned_array<uint32_t> n_place, branch, count;
+            impl::pinned_array<float> score;
+            impl::pinned_array<double> lwr, distal, pendant;
+            std::vector<uint32_t> group_rep;
+        };
+        result_set _sets[2];
+        size_t _turn = 0;
     };
 }
 

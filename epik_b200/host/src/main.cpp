@@ -283,7 +283,7 @@ int main(int argc, char** argv)
         struct pass_t
         {
             records_t records;
-            std::vector<epik::impl::placed_collection> placed;
+            epik::placer::placed_arrays placed{};
         };
         double stage_ms[5] = { 0, 0, 0, 0, 0 }; // waited for the reader, placing, waited for the writer | inside the writer: text, append
         std::future<void> writing, appending; // (appending is only touched by one writing task at a time, and by main after it)
@@ -298,30 +298,35 @@ int main(int argc, char** argv)
             reading = std::async(std::launch::async, [&reader] { return reader.next_batch(); }); // parsed while this pass is placed
 
             const auto begin_batch = std::chrono::steady_clock::now();
-            pass->placed = placer.place_batched(pass->records, batch_size, num_threads);
+            pass->placed = placer.place_arrays(pass->records, batch_size);
             const auto end_batch = std::chrono::steady_clock::now();
+            const size_t n_batches = (pass->records.size() + batch_size - 1) / batch_size;
 
             // the reference's figure, main.cpp:348-353: nominal batch size over the time spent in place()
-            double ms = std::chrono::duration<double, std::milli>(end_batch - begin_batch).count() / static_cast<double>(pass->placed.size());
+            double ms = std::chrono::duration<double, std::milli>(end_batch - begin_batch).count() / static_cast<double>(n_batches);
             if (ms <= 0.0) { ms = 1e-3; }
-            average_speed += 1000.0 * static_cast<double>(batch_size) / ms * static_cast<double>(pass->placed.size());
-            num_iterations += pass->placed.size();
+            average_speed += 1000.0 * static_cast<double>(batch_size) / ms * static_cast<double>(n_batches);
+            num_iterations += n_batches;
             num_seq_placed += pass->records.size();
-
             stage_ms[1] += std::chrono::duration<double, std::milli>(end_batch - begin_batch).count();
+
+            // The text of the pass before this one is read from the placer's OTHER set of result arrays while this pass is
+            // placed; the pass after this one overwrites that set, so that text must be out before going round again
             const auto t_write0 = std::chrono::steady_clock::now();
             if (writing.valid()) { writing.get(); } // passes are appended in order
             stage_ms[2] += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_write0).count();
-            // the writer has two stages of its own: the text of a pass is produced while the text of the pass before it
-            // is being appended to the file (appends stay in order)
-            writing = std::async(std::launch::async, [pass, &jplace, num_threads, &stage_ms, &appending] {
+
+            // the writer has two stages of its own: the text of a pass is produced (on the -j threads, straight from the
+            // arrays of the pass) while the text of the pass before it is being appended to the file, in order
+            writing = std::async(std::launch::async, [pass, n_batches, batch_size, &jplace, num_threads, &stage_ms, &appending] {
                 const auto t0 = std::chrono::steady_clock::now();
-                auto text = std::make_shared<std::vector<std::string>>(pass->placed.size());
-                epik::impl::parallel_for(pass->placed.size(), num_threads,
-                                         [&](size_t b) { (*text)[b] = epik::io::jplace_writer::format(pass->placed[b]); });
-                auto n_records = std::make_shared<std::vector<size_t>>(pass->placed.size());
-                for (size_t b = 0; b < pass->placed.size(); ++b) { (*n_records)[b] = pass->placed[b].placed_seqs.size(); }
-                pass->placed.clear();
+                auto text = std::make_shared<std::vector<std::string>>(n_batches);
+                auto n_records = std::make_shared<std::vector<size_t>>(n_batches);
+                const auto& placed = pass->placed;
+                epik::impl::parallel_for(n_batches, num_threads, [&](size_t b) {
+                    (*text)[b] = epik::io::jplace_writer::format_arrays(pass->records, placed.rows, placed.keep_at_most, placed.group_rep,
+                                                                        b * batch_size, std::min(placed.n, (b + 1) * batch_size), &(*n_records)[b]);
+                });
                 stage_ms[3] += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
                 if (appending.valid()) { appending.get(); }
                 appending = std::async(std::launch::async, [text, n_records, &jplace, num_threads, &stage_ms] {

@@ -1,0 +1,106 @@
+// TEST HARNESS: jplace_writer::format_arrays (the driver's path: text straight from the arrays of a device pass) must
+// give the bytes of jplace_writer::format on the placed_collection built from the same arrays. Random placements with
+// the doubles that exercise every branch of the number formatting, duplicate sequences, names that need escaping,
+// records without placements. Prints "ok <bytes>" or the first difference.
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <random>
+#include <string>
+#include <vector>
+#include <epik/fasta.h>
+#include <epik/place.h>
+#include <epik/jplace.h>
+
+int main()
+{
+    std::mt19937_64 rng(7);
+    const size_t n = 3000, K = 7, batch = 700;
+    const double specials[] = { 0.0, -0.0, 1.0, 100.0, 1e21, 1e22, 123456789012345678.0, 0.001, 1e-6, 1e-7, 9.999999778196308e21, 2.5e-7,
+                                0.30000000000000004, 5e-324, 1.7976931348623157e308, -3.25, 1e-5, 12345.678, std::nan(""), INFINITY };
+    std::vector<epik::io::seq_record> records;
+    for (size_t i = 0; i < n; ++i)
+    {
+        std::string seq(20, 'A');
+        const uint64_t pick = rng() % 400; // few distinct sequences: many duplicates inside a batch
+        for (size_t j = 0; j < 20; ++j) { seq[j] = "ACGT"[(pick >> (2 * (j % 10))) & 3]; }
+        std::string name = "read" + std::to_string(i);
+        if (i % 97 == 0) { name += " \"quoted\"\\back\tTab\x01"; }
+        records.emplace_back(name, seq);
+    }
+    std::vector<uint32_t> n_place(n), branch(n * K), count(n * K);
+    std::vector<float> score(n * K);
+    std::vector<double> lwr(n * K), distal(n * K), pendant(n * K);
+    std::uniform_real_distribution<double> unit(0.0, 1.0);
+    auto value = [&]() -> double {
+        const uint64_t r = rng() % 10;
+        if (r == 0) { return specials[rng() % (sizeof(specials) / sizeof(specials[0]))]; }
+        if (r < 4) { return std::pow(10.0, unit(rng) * 60.0 - 40.0); }
+        return unit(rng) * (r < 7 ? 1.0 : -300.0);
+    };
+    for (size_t i = 0; i < n; ++i)
+    {
+        n_place[i] = static_cast<uint32_t>(rng() % (K + 1));
+        for (size_t j = 0; j < K; ++j)
+        {
+            branch[i * K + j] = static_cast<uint32_t>(rng() % 100000);
+            score[i * K + j] = static_cast<float>(value());
+            lwr[i * K + j] = value();
+            distal[i * K + j] = value();
+            pendant[i * K + j] = value();
+            count[i * K + j] = static_cast<uint32_t>(rng() % 140);
+        }
+    }
+    epk_result rows{ n_place.data(), branch.data(), score.data(), lwr.data(), count.data(), distal.data(), pendant.data() };
+    // grouping per batch as epk_group_batches leaves it: first record of the batch with the same letters
+    std::vector<uint32_t> rep(n);
+    for (size_t first = 0; first < n; first += batch)
+    {
+        const size_t last = std::min(n, first + batch);
+        for (size_t i = first; i < last; ++i)
+        {
+            size_t j = first;
+            while (records[j].sequence() != records[i].sequence()) { ++j; }
+            rep[i] = static_cast<uint32_t>(j - first);
+            // identical sequences share one placement (place.cpp:207): the arrays hold the same rows for them
+            if (j != i)
+            {
+                n_place[i] = n_place[j];
+            }
+        }
+    }
+    size_t total = 0;
+    for (size_t first = 0; first < n; first += batch)
+    {
+        const size_t last = std::min(n, first + batch);
+        epik::impl::placed_collection c;
+        for (size_t i = first; i < last; ++i)
+        {
+            const std::string_view seq(records[i].sequence());
+            c.sequence_map[seq].push_back(records[i].header());
+            if (rep[i] != i - first) { continue; }
+            epik::impl::placed_sequence p;
+            p.sequence = seq;
+            for (size_t j = 0; j < n_place[i]; ++j)
+            {
+                const size_t at = i * K + j;
+                p.placements.push_back({ branch[at], score[at], lwr[at], count[at], distal[at], pendant[at] });
+            }
+            c.placed_seqs.push_back(std::move(p));
+        }
+        const std::string want = epik::io::jplace_writer::format(c);
+        size_t groups = 0;
+        const std::string got = epik::io::jplace_writer::format_arrays(records, rows, K, rep.data(), first, last, &groups);
+        if (got != want || groups != c.placed_seqs.size())
+        {
+            size_t at = 0;
+            while (at < got.size() && at < want.size() && got[at] == want[at]) { ++at; }
+            std::printf("batch at %zu differs at byte %zu: got ...%s\n want ...%s\n", first, at, got.substr(at > 40 ? at - 40 : 0, 120).c_str(),
+                        want.substr(at > 40 ? at - 40 : 0, 120).c_str());
+            return 1;
+        }
+        total += got.size();
+    }
+    std::printf("ok %zu\n", total);
+    return 0;
+}

@@ -51,6 +51,14 @@ def test_jplace_writer_is_byte_identical_to_the_reference_writer(built, tmp_path
         assert open(ref_out, "rb").read() == golden, "tests/golden/jplace_reference.jplace is stale"
 
 
+def test_jplace_text_from_arrays_is_the_text_from_objects(built, tmp_path):
+    """jplace_writer::format_arrays (the driver's path: straight from the arrays of a device pass) gives the bytes of
+    jplace_writer::format on the placed_collection built from the same arrays (tests/cpp/jplace_arrays_main.cpp)."""
+    exe = compile_cpp(tmp_path, "jp_arrays", OURS, [os.path.join(CPP, "jplace_arrays_main.cpp")], LINK)
+    out = subprocess.run([exe], capture_output=True, text=True)
+    assert out.returncode == 0 and out.stdout.startswith("ok "), out.stdout + out.stderr
+
+
 def test_fasta_reader(tmp_path):
     exe = compile_cpp(tmp_path, "fasta", OURS, [os.path.join(CPP, "fasta_main.cpp")])
     text = (b"; a comment before the first record\n>r1 first read\nACGT\nACGT\n\n>r2\r\nAC GT\r\nNN--\r\n>empty\n>r4\tx  \n"
