@@ -319,6 +319,8 @@ namespace epik::io
             text.resize(n_groups * (96 + K * 160) + n * 48 + name_bytes * 6 + 64);
             char* const begin = text.data();
             char* at = begin;
+            // the two lengths of a placement are properties of its branch: their text is kept per branch (and thread)
+            thread_local std::vector<memo_entry> distal_memo, pendant_memo;
             auto put = [&at](const char* lit, size_t len) { std::memcpy(at, lit, len); at += len; };
 #define EPK_PUT(LIT) put(LIT, sizeof(LIT) - 1)
             for (size_t j = 0; j < n; ++j)
@@ -338,9 +340,9 @@ namespace epik::io
                     EPK_PUT(", ");
                     at = raw_number(at, rows.lwr[row]);
                     EPK_PUT(", ");
-                    at = raw_number(at, rows.distal[row]);
+                    at = memo_number(distal_memo, rows.branch[row], rows.distal[row], at);
                     EPK_PUT(", ");
-                    at = raw_number(at, rows.pendant[row]);
+                    at = memo_number(pendant_memo, rows.branch[row], rows.pendant[row], at);
                     *at++ = ']';
                 }
                 if (m) { EPK_PUT("\n            ]"); }
@@ -465,6 +467,30 @@ namespace epik::io
             *at++ = '"';
             return at;
         }
+        /// The text of a number that is the same whenever `key` is: a memo checked against the bits of the value, so it
+        /// is right whatever the caller's idea of "the same" (a half of the 35 doubles of a record are the distal and
+        /// pendant lengths of its branches, and a shortest-round-trip double is the expensive part of a record).
+        struct memo_entry
+        {
+            uint64_t bits = 0;
+            uint8_t length = 0xFF; // 0xFF: empty
+            char text[47];
+        };
+        static char* memo_number(std::vector<memo_entry>& memo, size_t key, double v, char* at)
+        {
+            if (key >= (size_t(1) << 22)) { return raw_number(at, v); } // (bounded: 168 MB per thread at the very most)
+            if (key >= memo.size()) { memo.resize(std::max<size_t>(key + 1, 2 * memo.size())); }
+            memo_entry& entry = memo[key];
+            uint64_t bits;
+            std::memcpy(&bits, &v, sizeof(bits));
+            if (entry.length == 0xFF || entry.bits != bits)
+            {
+                entry.length = static_cast<uint8_t>(raw_number(entry.text, v) - entry.text);
+                entry.bits = bits;
+            }
+            std::memcpy(at, entry.text, entry.length);
+            return at + entry.length;
+        }
         static char* raw_number(char* at, double v)
         {
             if (std::isnan(v) || std::isinf(v)) { return at; } // RapidJSON refuses them after the prefix
@@ -479,6 +505,15 @@ namespace epik::io
             {
                 *at++ = '-';
                 v = -v;
+            }
+            if (v >= 1e-5 && v < 1e15)
+            {
+                // the usual scores, ratios and lengths: the same shortest digits, laid out by the library (the test
+                // compares with the generic writer over this range too)
+                char* const end = std::to_chars(at, at + 40, v, std::chars_format::fixed).ptr;
+                if (std::memchr(at, '.', static_cast<size_t>(end - at))) { return end; }
+                end[0] = '.'; end[1] = '0';
+                return end + 2;
             }
             char sci[40];
             const auto r = std::to_chars(sci, sci + sizeof(sci), v, std::chars_format::scientific);

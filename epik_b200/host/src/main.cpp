@@ -286,7 +286,9 @@ int main(int argc, char** argv)
             epik::placer::placed_arrays placed{};
         };
         double stage_ms[5] = { 0, 0, 0, 0, 0 }; // waited for the reader, placing, waited for the writer | inside the writer: text, append
-        std::future<void> writing, appending; // (appending is only touched by one writing task at a time, and by main after it)
+        // (appending is only touched by one writing task at a time, and by main after it; declared first: on the way out
+        // of an exception the writing task is waited for before the future it touches goes away)
+        std::future<void> appending, writing;
         std::future<records_t> reading = std::async(std::launch::async, [&reader] { return reader.next_batch(); });
         while (true)
         {

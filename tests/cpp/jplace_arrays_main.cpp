@@ -38,16 +38,22 @@ int main()
         if (r < 4) { return std::pow(10.0, unit(rng) * 60.0 - 40.0); }
         return unit(rng) * (r < 7 ? 1.0 : -300.0);
     };
+    // the lengths are properties of the branch (the writer keeps their text per branch), now and then they are not
+    // (the memo must check the value, not trust the key); a few branch ids beyond what the memo covers
+    const size_t n_branches = 3000;
+    std::vector<double> distal_of(n_branches), pendant_of(n_branches);
+    for (size_t b = 0; b < n_branches; ++b) { distal_of[b] = value(); pendant_of[b] = value(); }
     for (size_t i = 0; i < n; ++i)
     {
         n_place[i] = static_cast<uint32_t>(rng() % (K + 1));
         for (size_t j = 0; j < K; ++j)
         {
-            branch[i * K + j] = static_cast<uint32_t>(rng() % 100000);
+            const uint32_t b = static_cast<uint32_t>(rng() % n_branches);
+            branch[i * K + j] = rng() % 50 ? b : b + (1u << 22);
             score[i * K + j] = static_cast<float>(value());
             lwr[i * K + j] = value();
-            distal[i * K + j] = value();
-            pendant[i * K + j] = value();
+            distal[i * K + j] = rng() % 8 ? distal_of[b] : value();
+            pendant[i * K + j] = rng() % 8 ? pendant_of[b] : value();
             count[i * K + j] = static_cast<uint32_t>(rng() % 140);
         }
     }
