@@ -1148,6 +1148,9 @@ __device__ __forceinline__ sweep_result sweep(const ACC acc, uint32_t np, uint32
 #ifndef EPK_SWEEP_NQ
 #define EPK_SWEEP_NQ 2
 #endif
+#ifndef EPK_SWEEP_NQ_WIDE
+#define EPK_SWEEP_NQ_WIDE 1 // the 16-warp launch (128 registers per thread): C4 75.2 -> 77.4 M reads/s, C1p 8.19 -> 8.30 M (profiles/r4w)
+#endif
 #ifndef EPK_WIDE_AHEAD
 #define EPK_WIDE_AHEAD 1 // kernel experiments: 0 = the 16-warp launch claims its queries one at a time
 #endif
@@ -1441,14 +1444,14 @@ __device__ __forceinline__ bool fast_sweep_ok(const device_db& db, float nwf, fl
 // `gathered` = postings the query gathered (warp-uniform; only steers dense / scan-and-queue).
 
 // the dense form by kind of accumulators: two passes over shared memory, one pass over the partial rows in HBM
-template<int CAP, class CT>
+template<int CAP, int NQ, class CT>
 __device__ __forceinline__ sweep_result sweep_dense_form(const shared_acc<CT> acc, uint32_t np, uint32_t nw32, float logthr, float kf,
                                                          float rcp_k, uint32_t K, uint32_t lane, const cand_buffers<CAP>& cb,
                                                          uint32_t scan0, uint32_t stride EPK_PHASE_PARAMS)
 {
-    return sweep_dense_two_pass<CT, CAP, EPK_SWEEP_NQ>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride EPK_PHASE_ARGS);
+    return sweep_dense_two_pass<CT, CAP, NQ>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride EPK_PHASE_ARGS);
 }
-template<int CAP, class ACC>
+template<int CAP, int NQ, class ACC>
 __device__ __forceinline__ sweep_result sweep_dense_form(const ACC acc, uint32_t np, uint32_t nw32, float logthr, float kf,
                                                          float rcp_k, uint32_t K, uint32_t lane, const cand_buffers<CAP>& cb,
                                                          uint32_t scan0, uint32_t stride EPK_PHASE_PARAMS)
@@ -1457,7 +1460,7 @@ __device__ __forceinline__ sweep_result sweep_dense_form(const ACC acc, uint32_t
 }
 
 // the sweep form that fits the query
-template<class ACC, int CAP>
+template<class ACC, int CAP, int NQ = EPK_SWEEP_NQ>
 __device__ __forceinline__ sweep_result run_sweep(const device_db& db, const ACC acc, uint32_t np, uint32_t nw32,
                                                   uint32_t gathered, uint32_t K, uint32_t lane, const cand_buffers<CAP>& cb,
                                                   uint32_t scan0, uint32_t stride EPK_PHASE_PARAMS)
@@ -1468,7 +1471,7 @@ __device__ __forceinline__ sweep_result run_sweep(const device_db& db, const ACC
     const float nwf = static_cast<float>(nw32);
     const bool dense = 6ull * gathered >= np;
     return !fast_sweep_ok(db, nwf, kf) ? sweep_ieee<ACC, CAP>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride)
-           : dense                     ? sweep_dense_form<CAP>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride EPK_PHASE_ARGS)
+           : dense                     ? sweep_dense_form<CAP, NQ>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride EPK_PHASE_ARGS)
                                        : sweep_sparse<ACC, CAP>(acc, np, nw32, logthr, kf, rcp_k, K, lane, cb, scan0, stride);
 }
 
@@ -1535,14 +1538,14 @@ __device__ __forceinline__ void emit_query(const place_params& p, const sweep_re
 }
 
 // one warp does it all; cand_base: CAND_CAP * 3 + 64 words (the idle segment buffer)
-template<class ACC>
+template<class ACC, int NQ = EPK_SWEEP_NQ>
 __device__ __forceinline__ void finish_query(const place_params& p, const ACC acc, uint32_t np, uint64_t n_windows,
                                              uint32_t gathered, uint32_t q, uint32_t lane, uint32_t* cand_base)
 {
     const cand_buffers<CAND_CAP> cb(cand_base);
     const uint32_t nw32 = static_cast<uint32_t>(n_windows);
     EPK_PHASE_DUMMY
-    const sweep_result sw = run_sweep<ACC, CAND_CAP>(p.db, acc, np, nw32, gathered, p.keep_at_most, lane, cb, 0u, SWEEP_STEP EPK_PHASE_ARGS);
+    const sweep_result sw = run_sweep<ACC, CAND_CAP, NQ>(p.db, acc, np, nw32, gathered, p.keep_at_most, lane, cb, 0u, SWEEP_STEP EPK_PHASE_ARGS);
     emit_query(p, sw, nw32, q, lane);
 }
 
@@ -2403,7 +2406,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) place_kernel(const place_params 
             emit_query(p, sw, static_cast<uint32_t>(n_windows), q, lane);
             EPK_PHASE(6)
 #else
-            finish_query(p, shared_acc<CT>(S, C), np, n_windows, gathered, q, lane, cand_base);
+            finish_query<shared_acc<CT>, (MAXW > MAX_WARPS_PER_CTA ? EPK_SWEEP_NQ_WIDE : EPK_SWEEP_NQ)>(p, shared_acc<CT>(S, C), np, n_windows, gathered, q, lane, cand_base);
 #endif
         }
     }
