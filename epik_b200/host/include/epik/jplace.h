@@ -9,7 +9,9 @@
 #ifndef EPIK_B200_HOST_JPLACE_H
 #define EPIK_B200_HOST_JPLACE_H
 
+#include <atomic>
 #include <charconv>
+#include <chrono>
 #include <cmath>
 #include <cstdint>
 #include <cstdlib>
@@ -18,6 +20,7 @@
 #include <stdexcept>
 #include <string>
 #include <string_view>
+#include <thread>
 #include <vector>
 
 #include <fcntl.h>
@@ -302,6 +305,27 @@ namespace epik::io
         static std::string format_arrays(const std::vector<Record>& records, const epk_result& rows, size_t K, const uint32_t* group_rep,
                                          size_t first, size_t last, size_t* n_records_out = nullptr)
         {
+            std::string text;
+            text.resize(format_arrays_into(text, records, rows, K, group_rep, first, last, n_records_out));
+            return text;
+        }
+
+        /// An upper bound of the text of the records [first, last) with up to K placements each: 48 bytes of frame and up
+        /// to 26 per number, escapes can at most multiply a name by 6
+        template<class Record>
+        static size_t arrays_text_bound(const std::vector<Record>& records, size_t K, size_t first, size_t last)
+        {
+            size_t name_bytes = 0;
+            for (size_t i = first; i < last; ++i) { name_bytes += std::string_view(records[i].header()).size(); }
+            return (last - first) * (144 + K * 160) + name_bytes * 6 + 64;
+        }
+
+        /// format_arrays into the front of a buffer that only grows (a thread formats batch after batch into the same
+        /// one: a fresh 2 MB string per batch is 2 MB of page faults and zeroes); returns the length of the text.
+        template<class Record>
+        static size_t format_arrays_into(std::string& text, const std::vector<Record>& records, const epk_result& rows, size_t K,
+                                         const uint32_t* group_rep, size_t first, size_t last, size_t* n_records_out = nullptr)
+        {
             const size_t n = last - first;
             // members of a group, in record order, as a chain through `next`
             std::vector<uint32_t> next(n, 0xFFFFFFFFu), tail(n);
@@ -314,9 +338,8 @@ namespace epik::io
                 tail[r] = static_cast<uint32_t>(j);
                 name_bytes += std::string_view(records[first + j].header()).size();
             }
-            std::string text;
-            // (a generous bound: 48 bytes of frame + up to 26 per number; escapes can at most multiply a name by 6)
-            text.resize(n_groups * (96 + K * 160) + n * 48 + name_bytes * 6 + 64);
+            const size_t bound = n_groups * (96 + K * 160) + n * 48 + name_bytes * 6 + 64; // (<= arrays_text_bound)
+            if (text.size() < bound) { text.resize(bound); }
             char* const begin = text.data();
             char* at = begin;
             // the two lengths of a placement are properties of its branch: their text is kept per branch (and thread)
@@ -360,9 +383,8 @@ namespace epik::io
                 EPK_PUT("\n            ]\n        }");
             }
 #undef EPK_PUT
-            text.resize(static_cast<size_t>(at - begin));
             if (n_records_out) { *n_records_out = n_groups; }
-            return text;
+            return static_cast<size_t>(at - begin);
         }
 
         void append(const std::string& text, size_t n_records)
@@ -432,6 +454,95 @@ namespace epik::io
             _file_bytes += offset.back();
             _n_records += total_records;
             if (total_records) { _writer.add_elements(total_records); }
+        }
+
+        /// Text and append in one stage (the driver's writer): `format(b, buffer, &n_records)` leaves the text of batch b
+        /// at the front of `buffer` - one per thread, it only grows - and returns its length; the batch's place in the
+        /// file is known as soon as the batches before it are formatted (they are handed out in order), and the thread
+        /// copies its text there while it is still in its cache: no text of a pass is ever kept, nothing is read back
+        /// from memory to be appended. `max_bytes` bounds the text of all batches together (arrays_text_bound): the file
+        /// is extended and mapped that far, and cut back to what was written.
+        template<class Format>
+        void append_batches(size_t n_batches, size_t max_bytes, size_t threads, Format&& format)
+        {
+            flush(); // what is buffered (the file's opening) goes first
+            if (n_batches == 0) { return; }
+            const int fd = ::open(_filename.c_str(), O_RDWR);
+            if (fd < 0) { throw std::runtime_error("Could not open file " + _filename); }
+            const size_t base = _file_bytes;
+            void* m = MAP_FAILED;
+            size_t lead = 0;
+            if (max_bytes != 0 && ::ftruncate(fd, static_cast<off_t>(base + max_bytes)) == 0)
+            {
+                const size_t page = static_cast<size_t>(::sysconf(_SC_PAGESIZE));
+                const size_t map_from = base / page * page;
+                lead = base - map_from;
+                m = ::mmap(nullptr, lead + max_bytes, PROT_READ | PROT_WRITE, MAP_SHARED, fd, static_cast<off_t>(map_from));
+            }
+            char* const to = m == MAP_FAILED ? nullptr : static_cast<char*>(m) + lead; // (nullptr: pwrite, as append_many)
+            std::vector<size_t> start(n_batches + 1, 0);
+            std::atomic<size_t> published{ 0 }; // start[0 .. published] are final
+            std::atomic<bool> failed{ false };
+            size_t records_so_far = _n_records; // (written by the thread whose turn it is to publish)
+            auto release = [&](size_t keep_bytes) {
+                if (m != MAP_FAILED) { ::munmap(m, lead + max_bytes); }
+                const bool cut = ::ftruncate(fd, static_cast<off_t>(base + keep_bytes)) == 0;
+                ::close(fd);
+                return cut;
+            };
+            try
+            {
+                impl::parallel_for(n_batches, threads, [&](size_t b) {
+                    thread_local std::string buffer;
+                    try
+                    {
+                        size_t n_records = 0;
+                        size_t bytes = format(b, buffer, &n_records);
+                        while (published.load(std::memory_order_acquire) != b)
+                        {
+                            if (failed.load(std::memory_order_relaxed)) { return; }
+                            // (asleep, not spinning: the thread waited for may be waiting for a core, the host threads
+                            // are shared with the reader and the packing of the next pass; a batch takes milliseconds)
+                            std::this_thread::sleep_for(std::chrono::microseconds(50));
+                        }
+                        const char* from = buffer.data();
+                        if (n_records && records_so_far == 0) // no comma before the first record of the file
+                        {
+                            ++from;
+                            --bytes;
+                        }
+                        records_so_far += n_records;
+                        start[b + 1] = start[b] + bytes;
+                        if (start[b + 1] > max_bytes) { throw std::runtime_error("jplace text beyond its bound"); }
+                        published.store(b + 1, std::memory_order_release);
+                        if (to) { std::memcpy(to + start[b], from, bytes); }
+                        else
+                        {
+                            size_t done = 0;
+                            while (done < bytes)
+                            {
+                                const ssize_t w = ::pwrite(fd, from + done, bytes - done, static_cast<off_t>(base + start[b] + done));
+                                if (w <= 0) { throw std::runtime_error("Could not write to " + _filename); }
+                                done += static_cast<size_t>(w);
+                            }
+                        }
+                    }
+                    catch (...)
+                    {
+                        failed.store(true);
+                        throw;
+                    }
+                });
+            }
+            catch (...)
+            {
+                release(0);
+                throw;
+            }
+            if (!release(start[n_batches])) { throw std::runtime_error("Could not write to " + _filename); }
+            _file_bytes += start[n_batches];
+            if (records_so_far != _n_records) { _writer.add_elements(records_so_far - _n_records); }
+            _n_records = records_so_far;
         }
 
         void end()

@@ -285,10 +285,8 @@ int main(int argc, char** argv)
             records_t records;
             epik::placer::placed_arrays placed{};
         };
-        double stage_ms[5] = { 0, 0, 0, 0, 0 }; // waited for the reader, placing, waited for the writer | inside the writer: text, append
-        // (appending is only touched by one writing task at a time, and by main after it; declared first: on the way out
-        // of an exception the writing task is waited for before the future it touches goes away)
-        std::future<void> appending, writing;
+        double stage_ms[4] = { 0, 0, 0, 0 }; // waited for the reader, placing, waited for the writer | inside the writer
+        std::future<void> writing;
         std::future<records_t> reading = std::async(std::launch::async, [&reader] { return reader.next_batch(); });
         while (true)
         {
@@ -318,28 +316,20 @@ int main(int argc, char** argv)
             if (writing.valid()) { writing.get(); } // passes are appended in order
             stage_ms[2] += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_write0).count();
 
-            // the writer has two stages of its own: the text of a pass is produced (on the -j threads, straight from the
-            // arrays of the pass) while the text of the pass before it is being appended to the file, in order
-            writing = std::async(std::launch::async, [pass, n_batches, batch_size, &jplace, num_threads, &stage_ms, &appending] {
+            // the writer: every -j thread formats a batch straight from the arrays of the pass and copies the text to its
+            // place in the file, known as soon as the batches before it are formatted (jplace_writer::append_batches)
+            writing = std::async(std::launch::async, [pass, n_batches, batch_size, &jplace, num_threads, &stage_ms] {
                 const auto t0 = std::chrono::steady_clock::now();
-                auto text = std::make_shared<std::vector<std::string>>(n_batches);
-                auto n_records = std::make_shared<std::vector<size_t>>(n_batches);
                 const auto& placed = pass->placed;
-                epik::impl::parallel_for(n_batches, num_threads, [&](size_t b) {
-                    (*text)[b] = epik::io::jplace_writer::format_arrays(pass->records, placed.rows, placed.keep_at_most, placed.group_rep,
-                                                                        b * batch_size, std::min(placed.n, (b + 1) * batch_size), &(*n_records)[b]);
+                const size_t bound = epik::io::jplace_writer::arrays_text_bound(pass->records, placed.keep_at_most, 0, placed.n) + 64 * n_batches;
+                jplace.append_batches(n_batches, bound, num_threads, [&](size_t b, std::string& buffer, size_t* n_records) {
+                    return epik::io::jplace_writer::format_arrays_into(buffer, pass->records, placed.rows, placed.keep_at_most, placed.group_rep,
+                                                                       b * batch_size, std::min(placed.n, (b + 1) * batch_size), n_records);
                 });
                 stage_ms[3] += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
-                if (appending.valid()) { appending.get(); }
-                appending = std::async(std::launch::async, [text, n_records, &jplace, num_threads, &stage_ms] {
-                    const auto t1 = std::chrono::steady_clock::now();
-                    jplace.append_many(*text, *n_records, num_threads);
-                    stage_ms[4] += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t1).count();
-                });
             });
         }
         if (writing.valid()) { writing.get(); }
-        if (appending.valid()) { appending.get(); }
         jplace.end();
         if (num_iterations) { average_speed /= static_cast<double>(num_iterations); }
 
@@ -351,7 +341,7 @@ int main(int argc, char** argv)
         if (std::getenv("EPK_DRIVER_TIMING"))
         {
             std::cerr << "stages (ms): waited for the reader " << stage_ms[0] << ", placing " << stage_ms[1] << ", waited for the writer "
-                      << stage_ms[2] << "; inside the writer: text " << stage_ms[3] << ", append " << stage_ms[4] << std::endl;
+                      << stage_ms[2] << "; inside the writer (text and append) " << stage_ms[3] << std::endl;
         }
         std::cout << "Done." << '\n' << std::flush;
     }

@@ -6,13 +6,14 @@
 #include <cstdint>
 #include <cstdio>
 #include <random>
+#include <stdexcept>
 #include <string>
 #include <vector>
 #include <epik/fasta.h>
 #include <epik/place.h>
 #include <epik/jplace.h>
 
-int main()
+int main(int argc, char** argv)
 {
     std::mt19937_64 rng(7);
     const size_t n = 3000, K = 7, batch = 700;
@@ -107,6 +108,86 @@ int main()
         }
         total += got.size();
     }
-    std::printf("ok %zu\n", total);
+    // ---- the whole file: format + append_many (objects, a pass at a time) against append_batches (arrays, text and
+    // append in one stage), two passes each so that the second one starts in the middle of a page ----
+    const std::string dir = argc > 1 ? argv[1] : "/tmp";
+    auto slurp = [](const std::string& name) {
+        std::FILE* f = std::fopen(name.c_str(), "rb");
+        std::string all;
+        char buf[65536];
+        size_t got;
+        while (f && (got = std::fread(buf, 1, sizeof(buf), f)) > 0) { all.append(buf, got); }
+        if (f) { std::fclose(f); }
+        return all;
+    };
+    const size_t half = 3 * batch; // records of the first pass
+    const std::string want_name = dir + "/want.jplace";
+    {
+        epik::io::jplace_writer writer(want_name, "epik test", "(A:0.1,B:0.2);");
+        writer.start();
+        for (size_t pass_first : { size_t(0), half })
+        {
+            const size_t pass_last = pass_first == 0 ? half : n;
+            std::vector<std::string> texts;
+            std::vector<size_t> counts;
+            for (size_t first = pass_first; first < pass_last; first += batch)
+            {
+                size_t groups = 0;
+                texts.push_back(epik::io::jplace_writer::format_arrays(records, rows, K, rep.data(), first, std::min(pass_last, first + batch), &groups));
+                counts.push_back(groups);
+            }
+            writer.append_many(texts, counts, 3);
+        }
+        writer.end();
+    }
+    const std::string want_file = slurp(want_name);
+    for (size_t threads : { size_t(1), size_t(5) })
+    {
+        const std::string got_name = dir + "/got" + std::to_string(threads) + ".jplace";
+        {
+            epik::io::jplace_writer writer(got_name, "epik test", "(A:0.1,B:0.2);");
+            writer.start();
+            for (size_t pass_first : { size_t(0), half })
+            {
+                const size_t pass_last = pass_first == 0 ? half : n;
+                const size_t n_batches = (pass_last - pass_first + batch - 1) / batch;
+                const size_t bound = epik::io::jplace_writer::arrays_text_bound(records, K, pass_first, pass_last) + 64 * n_batches;
+                writer.append_batches(n_batches, bound, threads, [&](size_t b, std::string& buffer, size_t* n_records) {
+                    const size_t first = pass_first + b * batch;
+                    return epik::io::jplace_writer::format_arrays_into(buffer, records, rows, K, rep.data(), first, std::min(pass_last, first + batch), n_records);
+                });
+            }
+            writer.end();
+        }
+        const std::string got_file = slurp(got_name);
+        if (got_file != want_file || got_file.size() < total)
+        {
+            size_t at = 0;
+            while (at < got_file.size() && at < want_file.size() && got_file[at] == want_file[at]) { ++at; }
+            std::printf("file written with %zu threads differs at byte %zu of %zu / %zu\n", threads, at, got_file.size(), want_file.size());
+            return 1;
+        }
+    }
+    // a bound that is too small is an error, and the file is left as it was
+    {
+        const std::string name = dir + "/short.jplace";
+        epik::io::jplace_writer writer(name, "epik test", "(A:0.1,B:0.2);");
+        writer.start();
+        const size_t before = slurp(name).size();
+        bool refused = false;
+        try
+        {
+            writer.append_batches(2, 1000, 2, [&](size_t b, std::string& buffer, size_t* n_records) {
+                return epik::io::jplace_writer::format_arrays_into(buffer, records, rows, K, rep.data(), b * batch, (b + 1) * batch, n_records);
+            });
+        }
+        catch (const std::runtime_error&) { refused = true; }
+        if (!refused || slurp(name).size() != before)
+        {
+            std::printf("a text beyond its bound was not refused cleanly\n");
+            return 1;
+        }
+    }
+    std::printf("ok %zu %zu\n", total, want_file.size());
     return 0;
 }

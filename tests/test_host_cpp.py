@@ -53,9 +53,10 @@ def test_jplace_writer_is_byte_identical_to_the_reference_writer(built, tmp_path
 
 def test_jplace_text_from_arrays_is_the_text_from_objects(built, tmp_path):
     """jplace_writer::format_arrays (the driver's path: straight from the arrays of a device pass) gives the bytes of
-    jplace_writer::format on the placed_collection built from the same arrays (tests/cpp/jplace_arrays_main.cpp)."""
+    jplace_writer::format on the placed_collection built from the same arrays, and append_batches (text and append in one
+    stage, 1 and 5 threads, two passes) writes the file of format + append_many (tests/cpp/jplace_arrays_main.cpp)."""
     exe = compile_cpp(tmp_path, "jp_arrays", OURS, [os.path.join(CPP, "jplace_arrays_main.cpp")], LINK)
-    out = subprocess.run([exe], capture_output=True, text=True)
+    out = subprocess.run([exe, str(tmp_path)], capture_output=True, text=True)
     assert out.returncode == 0 and out.stdout.startswith("ok "), out.stdout + out.stderr
 
 
