@@ -29,7 +29,7 @@ def main():
     ap.add_argument("--workload", default="C2")
     ap.add_argument("--reads", type=int, default=2_000_000)
     ap.add_argument("--out", default="")
-    ap.add_argument("--device-batches", type=int, default=128)
+    ap.add_argument("--device-batches", default="128", help="--device-batches of the driver; a comma list runs it once per value on the same files")
     ap.add_argument("--devices", default="1", help="--devices of the driver: GPUs behind the one process, or 'all'")
     ap.add_argument("--tmpdir", default=None, help="where the FASTA, the database file and the jplace go (e.g. /dev/shm: no file system in the way)")
     ap.add_argument("--keep-jplace", default="", help="copy the jplace here (to compare runs byte for byte)")
@@ -59,40 +59,53 @@ def main():
                 block += b"\n"
             f.write(block)
     exe = os.path.join(ROOT, "bin", "epik", "epik-aa" if alphabet else "epik-dna")
-    argv = [exe, "-d", db_path, "-q", q_path, "-j", str(args.jobs), "--omega", "1.5", "--mu", "1.0", "-o", tmp,
-            "--device-batches", str(args.device_batches), "--devices", args.devices, q_path]
-    t0 = time.perf_counter()
-    run = subprocess.run(argv, capture_output=True, text=True, env=dict(os.environ, EPK_DRIVER_TIMING="1"))
-    wall = time.perf_counter() - t0
-    stages = [l for l in run.stderr.split("\n") if l.startswith("stages")]
-    if run.returncode != 0:
-        raise SystemExit("driver failed: " + run.stderr[-2000:])
-    ms = int(re.search(r"Placement time: \d+s \((\d+) ms\)", run.stdout).group(1))
-    speed = re.search(r"Average speed: ([^\n]+) seq/s", run.stdout).group(1)
-    jplace = os.path.join(tmp, "placements_q.fasta.jplace")
-    line = {
-        "what": "bin/epik/%s: FASTA file -> placements -> jplace file" % os.path.basename(exe),
-        "workload": args.workload, "reads": args.reads, "read_len": read_len, "jobs": args.jobs, "devices": args.devices, "tmpdir": args.tmpdir or tempfile.gettempdir(),
-        "placement_time_ms": ms, "reads_per_s_file_to_file": args.reads / (ms / 1e3),
-        "driver_average_speed": speed, "process_wall_s": wall,
-        "fasta_bytes": os.path.getsize(q_path), "jplace_bytes": os.path.getsize(jplace),
-        "db_file_bytes": os.path.getsize(db_path), "driver_stages": stages[0] if stages else None,
-    }
     import hashlib
-    h = hashlib.sha256()
-    with open(jplace, "rb") as f:
-        for _ in range(4):
-            f.readline()  # (the metadata block holds the invocation, which differs between runs)
-        for block in iter(lambda: f.read(1 << 24), b""):
-            h.update(block)
-    line["jplace_sha256_without_head"] = h.hexdigest()
+    import resource
+    lines = []
+    for device_batches in [int(x) for x in str(args.device_batches).split(",")]:
+        argv = [exe, "-d", db_path, "-q", q_path, "-j", str(args.jobs), "--omega", "1.5", "--mu", "1.0", "-o", tmp,
+                "--device-batches", str(device_batches), "--devices", args.devices, q_path]
+        before = resource.getrusage(resource.RUSAGE_CHILDREN)
+        t0 = time.perf_counter()
+        run = subprocess.run(argv, capture_output=True, text=True, env=dict(os.environ, EPK_DRIVER_TIMING="1"))
+        wall = time.perf_counter() - t0
+        after = resource.getrusage(resource.RUSAGE_CHILDREN)
+        stages = [l for l in run.stderr.split("\n") if l.startswith("stages")]
+        if run.returncode != 0:
+            raise SystemExit("driver failed: " + run.stderr[-2000:])
+        ms = int(re.search(r"Placement time: \d+s \((\d+) ms\)", run.stdout).group(1))
+        speed = re.search(r"Average speed: ([^\n]+) seq/s", run.stdout).group(1)
+        jplace = os.path.join(tmp, "placements_q.fasta.jplace")
+        line = {
+            "what": "bin/epik/%s: FASTA file -> placements -> jplace file" % os.path.basename(exe),
+            "workload": args.workload, "reads": args.reads, "read_len": read_len, "jobs": args.jobs, "devices": args.devices,
+            "device_batches": device_batches, "tmpdir": args.tmpdir or tempfile.gettempdir(),
+            "placement_time_ms": ms, "reads_per_s_file_to_file": args.reads / (ms / 1e3),
+            "driver_average_speed": speed, "process_wall_s": wall,
+            # (of the whole process: loading the database and creating the CUDA context included)
+            "process_cpu_s": {"user": after.ru_utime - before.ru_utime, "system": after.ru_stime - before.ru_stime},
+            "fasta_bytes": os.path.getsize(q_path), "jplace_bytes": os.path.getsize(jplace),
+            "db_file_bytes": os.path.getsize(db_path), "driver_stages": stages[0] if stages else None,
+        }
+        h = hashlib.sha256()
+        with open(jplace, "rb") as f:
+            for _ in range(4):
+                f.readline()  # (the metadata block holds the invocation, which differs between runs)
+            for block in iter(lambda: f.read(1 << 24), b""):
+                h.update(block)
+        line["jplace_sha256_without_head"] = h.hexdigest()
+        lines.append(line)
+        if len(lines) > 1:
+            print(json.dumps(lines[-2]))
+    line = lines[-1]
     print(json.dumps(line))
     if args.keep_jplace:
         import shutil
         shutil.copy(jplace, args.keep_jplace)
     if args.out:
         with open(args.out, "w") as f:
-            f.write(json.dumps(line) + "\n")
+            for one in lines:
+                f.write(json.dumps(one) + "\n")
     for p in (db_path, q_path, jplace):
         os.remove(p)
     os.rmdir(tmp)
