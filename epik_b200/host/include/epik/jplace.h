@@ -25,6 +25,7 @@
 
 #include <fcntl.h>
 #include <sys/mman.h>
+#include <sys/statvfs.h>
 #include <unistd.h>
 
 #include <epik/place.h>
@@ -399,6 +400,18 @@ namespace epik::io
             flush();
         }
 
+        /// Whether the file's new tail may be written through a shared mapping: only with room for it on the file system
+        /// (a store into a mapped page that cannot be allocated is a SIGBUS, a pwrite there is an error that can be
+        /// reported) and unless EPK_JPLACE_NO_MMAP is set (tests: the pwrite path).
+        static bool may_map(int fd, size_t bytes)
+        {
+            if (std::getenv("EPK_JPLACE_NO_MMAP")) { return false; }
+            struct statvfs fs;
+            if (::fstatvfs(fd, &fs) != 0) { return false; }
+            const unsigned long long room = static_cast<unsigned long long>(fs.f_bavail) * fs.f_frsize;
+            return room >= static_cast<unsigned long long>(bytes) + (64ull << 20);
+        }
+
         /// append() for the batches of one device pass at once: the pieces go to their places in the file with
         /// concurrent pwrite()s (one thread moves ~1.2 GB/s into the page cache; the text of a pass is ~230 MB).
         void append_many(std::vector<std::string>& texts, const std::vector<size_t>& n_records, size_t threads)
@@ -419,7 +432,7 @@ namespace epik::io
             // file take turns on its inode lock (3 GB/s with 16 threads on tmpfs - a third of a device pass's time went
             // there), page faults of a mapping do not.
             bool mapped = false;
-            if (offset.back() != 0 && ::ftruncate(fd, static_cast<off_t>(base + offset.back())) == 0)
+            if (offset.back() != 0 && may_map(fd, offset.back()) && ::ftruncate(fd, static_cast<off_t>(base + offset.back())) == 0)
             {
                 const size_t page = static_cast<size_t>(::sysconf(_SC_PAGESIZE));
                 const size_t map_from = base / page * page, lead = base - map_from;
@@ -472,7 +485,7 @@ namespace epik::io
             const size_t base = _file_bytes;
             void* m = MAP_FAILED;
             size_t lead = 0;
-            if (max_bytes != 0 && ::ftruncate(fd, static_cast<off_t>(base + max_bytes)) == 0)
+            if (max_bytes != 0 && may_map(fd, max_bytes) && ::ftruncate(fd, static_cast<off_t>(base + max_bytes)) == 0)
             {
                 const size_t page = static_cast<size_t>(::sysconf(_SC_PAGESIZE));
                 const size_t map_from = base / page * page;
