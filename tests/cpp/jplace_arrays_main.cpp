@@ -193,6 +193,39 @@ int main(int argc, char** argv)
             return 1;
         }
     }
+    // a batch whose text cannot be produced: the threads waiting for their turn behind it give up, the error comes
+    // out, the file is left as it was
+    {
+        const std::string name = dir + "/thrown.jplace";
+        epik::io::jplace_writer writer(name, "epik test", "(A:0.1,B:0.2);");
+        writer.start();
+        const size_t before = slurp(name).size();
+        bool thrown = false;
+        try
+        {
+            writer.append_batches(4, epik::io::jplace_writer::arrays_text_bound(records, K, 0, 4 * batch), 4,
+                                  [&](size_t b, std::string& buffer, size_t* n_records) -> size_t {
+                                      if (b == 1) { throw std::runtime_error("no text for this batch"); }
+                                      return epik::io::jplace_writer::format_arrays_into(buffer, records, rows, K, rep.data(), b * batch, (b + 1) * batch, n_records);
+                                  });
+        }
+        catch (const std::runtime_error&) { thrown = true; }
+        if (!thrown || slurp(name).size() != before)
+        {
+            std::printf("an error inside a batch did not come out cleanly\n");
+            return 1;
+        }
+        // and the writer is still usable
+        writer.append_batches(1, epik::io::jplace_writer::arrays_text_bound(records, K, 0, batch), 2, [&](size_t, std::string& buffer, size_t* n_records) {
+            return epik::io::jplace_writer::format_arrays_into(buffer, records, rows, K, rep.data(), 0, batch, n_records);
+        });
+        writer.end();
+        if (slurp(name).size() <= before)
+        {
+            std::printf("the writer did not go on after an error\n");
+            return 1;
+        }
+    }
     std::printf("ok %zu %zu\n", total, want_file.size());
     return 0;
 }
