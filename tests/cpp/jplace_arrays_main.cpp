@@ -109,6 +109,35 @@ int main(int argc, char** argv)
         }
         total += got.size();
     }
+    // ---- the longest text there can be: names of control characters (six bytes each once escaped), every number at its
+    // longest - the buffer is sized by a bound, it must hold ----
+    {
+        std::vector<epik::io::seq_record> worst;
+        for (size_t i = 0; i < 3; ++i) { worst.emplace_back(std::string(300 + i, '\x01'), std::string(10 + i, 'A')); }
+        const size_t wn = worst.size();
+        std::vector<uint32_t> w_n(wn, static_cast<uint32_t>(K)), w_branch(wn * K, 4294967295u), w_count(wn * K, 1), w_rep{ 0, 1, 2 };
+        std::vector<float> w_score(wn * K, -3.4028234663852886e38f);
+        std::vector<double> w_lwr(wn * K, -1.7976931348623157e308), w_distal(wn * K, -2.2250738585072014e-308), w_pendant(wn * K, -1.2345678901234567e-100);
+        epk_result w_rows{ w_n.data(), w_branch.data(), w_score.data(), w_lwr.data(), w_count.data(), w_distal.data(), w_pendant.data() };
+        epik::impl::placed_collection c;
+        for (size_t i = 0; i < wn; ++i)
+        {
+            c.sequence_map[worst[i].sequence()].push_back(worst[i].header());
+            epik::impl::placed_sequence p;
+            p.sequence = worst[i].sequence();
+            for (size_t j = 0; j < K; ++j) { p.placements.push_back({ w_branch[j], w_score[j], w_lwr[j], w_count[j], w_distal[j], w_pendant[j] }); }
+            c.placed_seqs.push_back(std::move(p));
+        }
+        const std::string want = epik::io::jplace_writer::format(c);
+        std::string buffer;
+        const size_t length = epik::io::jplace_writer::format_arrays_into(buffer, worst, w_rows, K, w_rep.data(), 0, wn);
+        const size_t bound = epik::io::jplace_writer::arrays_text_bound(worst, K, 0, wn);
+        if (length > bound || length > buffer.size() || buffer.compare(0, length, want) != 0)
+        {
+            std::printf("longest text: %zu bytes, bound %zu, buffer %zu, expected %zu\n", length, bound, buffer.size(), want.size());
+            return 1;
+        }
+    }
     // ---- the whole file: format + append_many (objects, a pass at a time) against append_batches (arrays, text and
     // append in one stage), two passes each so that the second one starts in the middle of a page ----
     const std::string dir = argc > 1 ? argv[1] : "/tmp";
