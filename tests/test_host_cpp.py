@@ -22,7 +22,9 @@ LINK = ["-pthread", "-L" + os.path.join(ROOT, "epik_b200"), "-lepik_b200", "-Wl,
 
 def compile_cpp(tmp_path, name, flags, sources, link=()):
     exe = str(tmp_path / name)
-    subprocess.run([CXX, "-std=c++17", "-O1", "-Wall", "-Wextra", "-I" + CPP] + flags + ["-o", exe] + sources + list(link), check=True)
+    # EPK_TEST_SANITIZE=address|thread|undefined: the host tests under a sanitizer (the threaded FASTA reader and jplace writer)
+    sanitize = ["-fsanitize=" + os.environ["EPK_TEST_SANITIZE"], "-g"] if os.environ.get("EPK_TEST_SANITIZE") else []
+    subprocess.run([CXX, "-std=c++17", "-O1", "-Wall", "-Wextra", "-I" + CPP] + sanitize + flags + ["-o", exe] + sources + list(link), check=True)
     return exe
 
 
